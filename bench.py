@@ -1,0 +1,212 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 parameter-server/worker synchronous SGD, samples/s over N B200s.
+
+BASELINE.json config 3: "ResNet-50 PS/worker sync SGD executed on 1/2/4/8 B200: fused push/pull
+vs NCCL baseline". Weak scaling (per-GPU batch fixed), bf16 compute with fp32 master weights on
+the PS shards, synthetic uint8 images and random-init weights (no network for datasets).
+
+  python bench.py --gpus 1 --steps 20 --warmup 5
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+      --master-port P bench.py --gpus N --steps K --warmup W
+
+Prints ONE JSON line on rank 0. ``value`` is device-timed (CUDA events, max over ranks) with the
+batch resident on the GPU; ``e2e`` goes through the public ``Trainer.step`` API including the
+pinned host->device copy of every step's inputs and the device->host read of every step's loss.
+``nccl_baseline`` is the PyTorch+NCCL PS/worker arm (same model, same buckets) measured in the
+same process right after, as BASELINE.json prescribes. ``--impl reference`` reports that the
+reference itself cannot produce this metric (it is a CPU-only scheduling simulator).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import socket
+import sys
+import time
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def parse_args() -> argparse.Namespace:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "ring"])
+    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--batch", type=int, default=64, help="per-GPU batch (weak scaling)")
+    ap.add_argument("--bucket-mb", type=float, default=8.0)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--skip-nccl", action="store_true", help="do not run the NCCL baseline arm")
+    return ap.parse_args()
+
+
+def reference_arm(args: argparse.Namespace) -> None:
+    # Install outcome: `pip install --target baseline/_ref /root/reference` fails with
+    # "Neither 'setup.py' nor 'pyproject.toml' found"; beyond packaging, the reference has no
+    # code path that executes a model, so samples/s cannot be produced by it at all.
+    print(json.dumps({
+        "impl": "reference",
+        "unavailable": "reference is a CPU-only scheduling simulator with no training/execution "
+                       "path (no samples/s metric) and no setup.py/pyproject.toml to install",
+    }))
+
+
+def init_dist(args: argparse.Namespace):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun for N>1")
+    torch.cuda.set_device(local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", str(_free_port()))
+    dist.init_process_group("nccl", rank=rank, world_size=world,
+                            device_id=torch.device("cuda", local_rank))
+    return rank, local_rank, world
+
+
+def timed_region(fn_step, steps: int, device, sampler=None):
+    """EXACTLY `steps` calls of fn_step between barrier+synchronize brackets; returns the
+    device-side elapsed milliseconds (max over ranks) and the wall time."""
+    import torch
+    import torch.distributed as dist
+    dist.barrier()
+    torch.cuda.synchronize(device)
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if sampler is not None:
+        sampler.start()
+    t0 = time.perf_counter()
+    start.record(torch.cuda.current_stream(device))
+    fn_step(steps)
+    end.record(torch.cuda.current_stream(device))
+    torch.cuda.synchronize(device)
+    dist.barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if sampler is not None else None
+    ms = torch.tensor([start.elapsed_time(end)], device=device)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()), wall, clocks
+
+
+def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, world: int):
+    import torch
+    from tiresias_b200.models import zoo
+    from tiresias_b200.ops import native
+    from tiresias_b200.parallel.trainer import Trainer
+    from tiresias_b200.utils.clocks import ClockSampler
+
+    device = torch.device("cuda", local_rank)
+    spec = zoo.resolve(args.model)
+    trainer = Trainer(spec, args.batch, mode=mode, bucket_mb=args.bucket_mb,
+                      use_graph=not args.no_graph, device=device)
+    # distinct pinned host batches so every step's H2D copy moves fresh bytes
+    host = [zoo.synthetic_batch(spec, args.batch, pinned=True, seed=1000 * rank + i) for i in range(4)]
+
+    cur = torch.cuda.current_stream(device)
+
+    def resident(k: int) -> None:
+        cur.wait_stream(trainer.stream)
+        for _ in range(k):
+            trainer.step_resident()
+        cur.wait_stream(trainer.stream)
+        cur.wait_stream(trainer.comm_stream)
+
+    losses = []
+
+    def e2e(k: int) -> None:
+        cur.wait_stream(trainer.stream)
+        for i in range(k):
+            x, y = host[i % len(host)]
+            trainer.step(x, y)
+            losses.append(trainer.loss())          # D2H read of this step's loss, every step
+        cur.wait_stream(trainer.stream)
+        cur.wait_stream(trainer.comm_stream)
+
+    # warm-up through the public API: covers allocator growth, cuDNN autotune and graph capture
+    e2e(max(args.warmup, 5 if trainer.use_graph and mode != "nccl" else args.warmup))
+    if trainer.check_status() != 0:
+        raise SystemExit("in-kernel wait timed out during warm-up")
+
+    launches0 = trainer.native_launches
+    ms, wall, clocks = timed_region(resident, args.steps, device, ClockSampler(local_rank))
+    launches = trainer.native_launches - launches0
+    ms_e2e, wall_e2e, _ = timed_region(e2e, args.steps, device)
+    status = trainer.check_status()
+    out = {
+        "ms_per_step": ms / args.steps,
+        "value": args.batch * world * args.steps / (ms / 1e3),
+        "e2e_ms_per_step": ms_e2e / args.steps,
+        "e2e_value": args.batch * world * args.steps / (ms_e2e / 1e3),
+        "wall_s": wall, "clocks": clocks, "gpu_launches": int(launches),
+        "h2d_bytes_per_step": trainer.h2d_bytes, "d2h_bytes_per_step": trainer.d2h_bytes,
+        "loss_last": losses[-1] if losses else None, "status": status,
+        "buckets": len(trainer.buckets), "graph": bool(trainer._graph is not None),
+        "params": sum(p.numel() for p in trainer.model.parameters()),
+    }
+    trainer.close()
+    del trainer
+    torch.cuda.empty_cache()
+    return out
+
+
+def main() -> None:
+    args = parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = init_dist(args)
+    mode = {"ours": "ps", "nccl": "nccl", "ring": "ring"}[args.impl]
+    res = run_arm(mode, args, rank, local_rank, world)
+    base = None
+    if args.impl == "ours" and not args.skip_nccl:
+        base = run_arm("nccl", args, rank, local_rank, world)
+    if rank == 0:
+        line = {
+            "metric": f"{args.model}_ps_sync_sgd_samples_per_s",
+            "value": round(res["value"], 2), "unit": "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(res["ms_per_step"], 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic uint8 images, random-init weights",
+            "impl": {"ps": "ours", "nccl": "nccl-baseline", "ring": "ours-ring"}[mode],
+            "config": {
+                "model": args.model, "global_batch": args.batch * world, "per_gpu_batch": args.batch,
+                "seq_len": None, "parallelism": f"ps-worker dp{world} (1 worker + 1 PS shard per GPU)",
+                "optimizer": "sgd momentum 0.9 wd 1e-4, fp32 master on PS shards",
+                "buckets": res["buckets"], "cuda_graph": res["graph"],
+                "l2": "per-step working set (activations + weights + grads, GBs) >> 126 MB L2; "
+                      "e2e copies a fresh pinned batch every step; no explicit flush",
+                "timing": "CUDA events on the launching stream, max over ranks",
+            },
+            "clocks": res["clocks"],
+            "e2e": {"value": round(res["e2e_value"], 2), "unit": "samples/s",
+                    "ms_per_step": round(res["e2e_ms_per_step"], 4),
+                    "h2d_bytes_per_step": res["h2d_bytes_per_step"],
+                    "d2h_bytes_per_step": res["d2h_bytes_per_step"]},
+            "gpu_launches": res["gpu_launches"],
+            "loss_last": res["loss_last"], "status": res["status"],
+        }
+        if base is not None:
+            line["nccl_baseline"] = {
+                "value": round(base["value"], 2), "ms_per_step": round(base["ms_per_step"], 4),
+                "e2e_value": round(base["e2e_value"], 2),
+                "speedup_device": round(res["value"] / base["value"], 4),
+                "speedup_e2e": round(res["e2e_value"] / base["e2e_value"], 4),
+            }
+        print(json.dumps(line))
+        sys.stdout.flush()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,632 @@
+// K5 / K2: hand-written tcgen05 GEMM for sm_100a.
+//
+//   D[M,N] = act(A[M,K] . B[N,K]^T + bias)      A, B bf16 (K contiguous), fp32 accumulate
+//
+// Structure (one persistent CTA per SM, 256 threads):
+//   warp 0 lane 0 : TMA producer  - cp.async.bulk.tensor tiles of A and B into a ring of
+//                   128B-swizzled shared-memory stages, completion on "full" mbarriers
+//   warp 1 lane 0 : MMA issuer    - tcgen05.mma.cta_group::1.kind::f16, accumulators in TMEM,
+//                   tcgen05.commit releases smem stages ("empty") and publishes finished
+//                   accumulators ("tmem_full")
+//   warp 2        : TMEM allocator (tcgen05.alloc / dealloc, 2 accumulator stages)
+//   warp 3        : (pull variant) TMA-stores gathered B tiles to the local weight buffer
+//   warps 4-7     : epilogue      - tcgen05.ld TMEM -> registers, bias/activation, cast, store
+//
+// The pull variant (K2) is the load side of the parameter pull that the reference only prices
+// as "model_size / bandwidth" (core/network/network_service.py:34-37): B is sharded by rows
+// over the parameter-server ranks, and the producer's TMA reads every tile straight out of the
+// owning rank's memory over NVLink, after that rank's PARAM_DONE flag says the shard is
+// updated. FC layer shapes come from core/models.py:9-20 (VGG fc6 25088x4096 etc.).
+#include "common.cuh"
+#include "../include/tiresias_b200.h"
+
+#include <cuda.h>
+#include <mutex>
+#include <unordered_map>
+
+using namespace tb200;
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 256;
+constexpr int kAccumStages = 2;
+
+template <int BLOCK_N>
+struct Cfg {
+  static constexpr int kStages = BLOCK_N == 256 ? 4 : 6;
+  static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
+  static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTmemCols = kAccumStages * BLOCK_N;  // 512 or 256 (power of two)
+  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages) * 8 + 16;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // + align slack
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t smem_src, int c0,
+                                             int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+               "r"(smem_src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 columns of fp32: thread t of the warp receives row (lane_base + t).
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
+        "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]),
+        "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor: K-major operand, 128-byte swizzle, rows of 128 bytes,
+// 8-row groups 1024 bytes apart (cute::UMMA::SmemDescriptor, version 1 = Blackwell).
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3ffff) >> 4);        // start address  [0,14)
+  d |= (uint64_t)1 << 16;                             // leading byte offset (unused for SW128 K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                   // stride byte offset [32,46)
+  d |= (uint64_t)1 << 46;                             // descriptor version
+  d |= (uint64_t)2 << 61;                             // SWIZZLE_128B
+  return d;
+}
+
+// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32, both operands K-major.
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int umma_m, int umma_n) {
+  return (1u << 4)                       // D format  = F32
+         | (1u << 7)                     // A format  = BF16
+         | (1u << 10)                    // B format  = BF16
+         | (0u << 15) | (0u << 16)       // A, B K-major
+         | ((uint32_t)(umma_n >> 3) << 17) | ((uint32_t)(umma_m >> 4) << 24);
+}
+
+__device__ __forceinline__ float load_bias(const void* bias, int dtype, size_t i) {
+  return dtype == kBF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(bias)[i])
+                        : __ldg(reinterpret_cast<const float*>(bias) + i);
+}
+
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == 1) return fmaxf(x, 0.f);
+  if (act == 2) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    float t = tanhf(k0 * (x + k1 * x * x * x));
+    return 0.5f * x * (1.f + t);
+  }
+  return x;
+}
+
+struct GemmParams {
+  int M, N, K;
+  int num_m, num_n, splits, num_kb;
+  void* D;            // final output (splits == 1)
+  float* partials;    // [splits][M][N] fp32 (splits > 1)
+  const void* bias;
+  int bias_dtype;
+  int d_dtype;
+  int act;
+  // pull variant
+  int rows_per_rank;
+  int world;
+  int rank;
+  int bucket;
+  const uint32_t* epoch;
+  const uint32_t* flags;   // local flag pad
+  int* status;
+  unsigned long long budget;
+};
+
+struct PullMaps {
+  CUtensorMap b[TB200_MAX_WORLD];  // B shard of every owner (peer-mapped addresses)
+  CUtensorMap b_local;             // this rank's full B, written by the gather-store warp
+};
+
+template <int BLOCK_N, bool kPull>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
+                    const __grid_constant__ CUtensorMap map_b,
+                    const __grid_constant__ PullMaps pull, const GemmParams p) {
+  using C = Cfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles need 1024-byte alignment.
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t b_smem = smem_base + C::kStages * C::kABytes;
+  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + kAccumStages + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * C::kStages + 2 * kAccumStages);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), kPull ? 2 : 1);
+    }
+    for (int s = 0; s < kAccumStages; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 4);  // one arrive per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                 "n"(C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int items = p.num_m * p.num_n * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    // ================= TMA producer =================
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t owner_ready = 0;  // bitmask of owners whose PARAM_DONE flag has been observed
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int ks = it % p.splits;
+      const int tile = it / p.splits;
+      const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      const int kb0 = (int)((long long)ks * p.num_kb / p.splits);
+      const int kb1 = (int)((long long)(ks + 1) * p.num_kb / p.splits);
+      const CUtensorMap* bmap = &map_b;
+      int b_row = n_blk * BLOCK_N;
+      if constexpr (kPull) {
+        const int owner = b_row / p.rows_per_rank;
+        bmap = &pull.b[owner];
+        b_row -= owner * p.rows_per_rank;
+        if (!(owner_ready & (1u << owner))) {
+          const uint32_t want = *p.epoch - 1;  // shards written during the step that just ended
+          if (!wait_epoch(p.flags + TB200_FLAG_PARAM_DONE(p.bucket, owner), want, p.budget))
+            atomicExch(p.status, 5);
+          owner_ready |= 1u << owner;
+        }
+      }
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        mbar_expect_tx(full_bar(stage), C::kStageBytes);
+        tma_load_2d(a_smem + stage * C::kABytes, &map_a, full_bar(stage), kb * BLOCK_K,
+                    m_blk * BLOCK_M);
+        tma_load_2d(b_smem + stage * C::kBBytes, bmap, full_bar(stage), kb * BLOCK_K, b_row);
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
+    int stage = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int ks = it % p.splits;
+      const int kb0 = (int)((long long)ks * p.num_kb / p.splits);
+      const int kb1 = (int)((long long)(ks + 1) * p.num_kb / p.splits);
+      mbar_wait(tempty_bar(as), aphase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + as * BLOCK_N;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint64_t adesc = make_kmajor_sw128_desc(a_smem + stage * C::kABytes);
+        const uint64_t bdesc = make_kmajor_sw128_desc(b_smem + stage * C::kBBytes);
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+          // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in 16-byte units
+          tc_mma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+        }
+        tc_commit(empty_bar(stage));  // smem stage reusable once these MMAs have read it
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(tfull_bar(as));       // accumulator complete
+      if (++as == kAccumStages) { as = 0; aphase ^= 1; }
+    }
+  } else if (kPull && warp == 3 && lane == 0) {
+    // ================= gather-store (pull variant) =================
+    // The CTAs that own m_blk == 0 write each B tile they receive into the local weight
+    // buffer, so that after this GEMM the full gathered matrix is resident locally.
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int ks = it % p.splits;
+      const int tile = it / p.splits;
+      const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      const int kb0 = (int)((long long)ks * p.num_kb / p.splits);
+      const int kb1 = (int)((long long)(ks + 1) * p.num_kb / p.splits);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        if (m_blk == 0 && (n_blk * BLOCK_N) / p.rows_per_rank != p.rank) {
+          tma_store_2d(&pull.b_local, b_smem + stage * C::kBBytes, kb * BLOCK_K, n_blk * BLOCK_N);
+          tma_store_commit();
+          tma_store_wait_read();
+        }
+        mbar_arrive(empty_bar(stage));
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+    tma_store_wait_all();
+  } else if (warp >= 4) {
+    // ================= epilogue =================
+    const int ew = warp - 4;  // == warp % 4: the TMEM lane quarter this warp may touch
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int ks = it % p.splits;
+      const int tile = it / p.splits;
+      const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const int row = m_blk * BLOCK_M + ew * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t r[32];
+        tc_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N + c * 32), r);
+        tc_ld_wait();
+        const int col0 = n_blk * BLOCK_N + c * 32;
+        if (!row_ok || col0 >= p.N) continue;
+        if (p.splits > 1) {
+          float* out = p.partials + ((size_t)ks * p.M + row) * p.N + col0;
+          if (col0 + 32 <= p.N && (p.N % 4) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(out + j) =
+                  make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                              __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) out[j] = __uint_as_float(r[j]);
+          }
+          continue;
+        }
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = __uint_as_float(r[j]);
+          if (p.bias && col0 + j < p.N) x += load_bias(p.bias, p.bias_dtype, col0 + j);
+          v[j] = apply_act(x, p.act);
+        }
+        if (p.d_dtype == kBF16) {
+          __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.N + col0;
+          if (col0 + 32 <= p.N && (p.N % 8) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 o;
+              o.x = pack_bf16(v[j], v[j + 1]); o.y = pack_bf16(v[j + 2], v[j + 3]);
+              o.z = pack_bf16(v[j + 4], v[j + 5]); o.w = pack_bf16(v[j + 6], v[j + 7]);
+              *reinterpret_cast<uint4*>(out + j) = o;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) out[j] = __float2bfloat16(v[j]);
+          }
+        } else {
+          float* out = reinterpret_cast<float*>(p.D) + (size_t)row * p.N + col0;
+          if (col0 + 32 <= p.N && (p.N % 4) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.N) out[j] = v[j];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(as));
+      if (++as == kAccumStages) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "n"(C::kTmemCols)
+                 : "memory");
+  }
+}
+
+// Split-K second pass: sum the fp32 partials in split order, then bias/activation/cast.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partials,
+                                                            int splits, size_t mn, int N,
+                                                            const void* __restrict__ bias,
+                                                            int bias_dtype, int act,
+                                                            void* __restrict__ D, int d_dtype) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < mn;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += partials[(size_t)s * mn + i];
+    if (bias) acc += load_bias(bias, bias_dtype, i % N);
+    acc = apply_act(acc, act);
+    if (d_dtype == kBF16) reinterpret_cast<__nv_bfloat16*>(D)[i] = __float2bfloat16(acc);
+    else reinterpret_cast<float*>(D)[i] = acc;
+  }
+}
+
+// ---- host side --------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle.
+int make_map(CUtensorMap* out, const void* base, int rows, int cols, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail("cuTensorMapEncodeTiled entry point not available%s");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BLOCK_K, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed (%s code %ld)", "", (long)r);
+  return 0;
+}
+
+struct Workspace {
+  float* ptr = nullptr;
+  size_t bytes = 0;
+};
+std::mutex g_ws_mutex;
+std::unordered_map<int, Workspace> g_ws;  // per device split-K scratch, grown on demand
+
+int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+int get_workspace(size_t bytes, float** out) {
+  int dev = 0;
+  TB_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_ws_mutex);
+  Workspace& w = g_ws[dev];
+  if (w.bytes < bytes) {
+    // Growing frees the old block; callers on other streams must not be using it. The
+    // Python layer sizes the workspace up-front (tb200_gemm_reserve) before graph capture.
+    if (w.ptr) TB_CUDA_OK(cudaFree(w.ptr));
+    w.ptr = nullptr;
+    w.bytes = 0;
+    TB_CUDA_OK(cudaMalloc(&w.ptr, bytes));
+    w.bytes = bytes;
+  }
+  *out = w.ptr;
+  return 0;
+}
+
+template <int BLOCK_N, bool kPull>
+int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const PullMaps& pull,
+                const GemmParams& p, int grid, cudaStream_t stream) {
+  using C = Cfg<BLOCK_N>;
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull>;
+  static bool configured = false;
+  if (!configured) {
+    TB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    configured = true;
+  }
+  kern<<<grid, kGemmThreads, C::kSmemBytes, stream>>>(ma, mb, pull, p);
+  return launched();
+}
+
+int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_per_rank,
+                const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M,
+                int N, int K, int d_dtype, int act, const uint32_t* epoch_dev, int* status_dev,
+                unsigned long long budget, cudaStream_t stream) {
+  const bool pull = world != nullptr;
+  if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
+  if (K % 8) return fail("tb200_gemm: K %s(%ld) must be a multiple of 8", "", K);
+  if (d_dtype != TB200_BF16 && d_dtype != TB200_F32) return fail("tb200_gemm: bad output dtype%s");
+
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
+  p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
+
+  // Tile width: 256 when that still yields at least one full wave, else 128.
+  const int sms = sm_count();
+  int block_n = 256;
+  if (N <= 128 || (long long)p.num_m * ((N + 255) / 256) < sms) block_n = 128;
+  if (pull && rows_per_rank % block_n) {
+    block_n = 128;
+    if (rows_per_rank % 128)
+      return fail("tb200_gemm_pull: rows_per_rank %s(%ld) must be a multiple of 128", "", rows_per_rank);
+  }
+  p.num_n = (N + block_n - 1) / block_n;
+  const int tiles = p.num_m * p.num_n;
+  // Split K when the tile grid cannot fill the machine (small-batch FC layers are weight-
+  // bandwidth bound: every SM should be streaming a slice of B).
+  int splits = 1;
+  if (tiles < sms) {
+    // Pick the split count whose work-item total packs best into whole waves of `sms` CTAs
+    // (ties go to fewer splits); keep at least 4 k-blocks per split.
+    int max_splits = p.num_kb / 4;
+    if (max_splits > 16) max_splits = 16;
+    double best = 0.0;
+    for (int s = 1; s <= max_splits; ++s) {
+      const int it = tiles * s;
+      const int waves = (it + sms - 1) / sms;
+      const double eff = (double)it / ((double)waves * sms);
+      if (eff > best + 1e-9) { best = eff; splits = s; }
+    }
+  }
+  p.splits = splits;
+  if (splits > 1) {
+    if (int rc = get_workspace((size_t)splits * M * N * sizeof(float), &p.partials)) return rc;
+  }
+
+  CUtensorMap ma, mb;
+  PullMaps pm;
+  memset(&pm, 0, sizeof(pm));
+  if (int rc = make_map(&ma, A, M, K, BLOCK_M)) return rc;
+  if (pull) {
+    p.rows_per_rank = rows_per_rank;
+    p.world = world->world;
+    p.rank = world->rank;
+    p.bucket = bucket;
+    p.epoch = epoch_dev;
+    p.flags = world->flags[world->rank];
+    p.status = status_dev;
+    p.budget = budget;
+    if ((long long)rows_per_rank * world->world < N)
+      return fail("tb200_gemm_pull: shards do not cover N%s");
+    for (int s = 0; s < world->world; ++s) {
+      const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(world->param[s]) + b_off +
+                                  (size_t)s * rows_per_rank * K;
+      int rows = rows_per_rank;
+      if ((long long)(s + 1) * rows_per_rank > N) rows = N - s * rows_per_rank;
+      if (rows <= 0) rows = 1;
+      if (int rc = make_map(&pm.b[s], base, rows, K, block_n)) return rc;
+    }
+    const __nv_bfloat16* local = reinterpret_cast<const __nv_bfloat16*>(world->param[world->rank]) + b_off;
+    if (int rc = make_map(&pm.b_local, local, N, K, block_n)) return rc;
+    mb = pm.b_local;
+  } else {
+    if (int rc = make_map(&mb, B, N, K, block_n)) return rc;
+  }
+
+  const int items = tiles * splits;
+  const int grid = items < sms ? items : sms;
+  int rc;
+  if (block_n == 256) rc = pull ? launch_gemm<256, true>(ma, mb, pm, p, grid, stream)
+                                : launch_gemm<256, false>(ma, mb, pm, p, grid, stream);
+  else rc = pull ? launch_gemm<128, true>(ma, mb, pm, p, grid, stream)
+                 : launch_gemm<128, false>(ma, mb, pm, p, grid, stream);
+  if (rc) return rc;
+  if (splits > 1) {
+    const size_t mn = (size_t)M * N;
+    int rgrid = (int)((mn + 255) / 256);
+    if (rgrid > sms * 8) rgrid = sms * 8;
+    splitk_reduce_kernel<<<rgrid, 256, 0, stream>>>(p.partials, splits, mn, N, bias, bias_dtype, act, D,
+                                                    d_dtype);
+    return launched();
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, int bias_dtype,
+                       int M, int N, int K, int d_dtype, int act, cudaStream_t stream) {
+  return gemm_common(nullptr, 0, 0, 0, A, B, D, bias, bias_dtype, M, N, K, d_dtype, act, nullptr,
+                     nullptr, 0, stream);
+}
+
+int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off,
+                            int rows_per_rank, const void* A, void* D, const void* bias,
+                            int bias_dtype, int M, int N, int K, int d_dtype, int act,
+                            const uint32_t* epoch_dev, int* status_dev,
+                            unsigned long long spin_budget, cudaStream_t stream) {
+  if (!world) return fail("tb200_gemm_bf16_nt_pull: null world%s");
+  return gemm_common(world, bucket, b_off, rows_per_rank, A, nullptr, D, bias, bias_dtype, M, N, K,
+                     d_dtype, act, epoch_dev, status_dev, spin_budget, stream);
+}
+
+// Pre-size the split-K scratch (call before CUDA-graph capture so no allocation happens
+// inside the captured region).
+int tb200_gemm_reserve(size_t bytes) {
+  float* unused = nullptr;
+  return get_workspace(bytes, &unused);
+}
+
+}  // extern "C"

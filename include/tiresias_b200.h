@@ -1,0 +1,157 @@
+/*
+ * tiresias_b200 native library — C ABI (libtiresias_b200.so, sm_100a only).
+ *
+ * Every function returns 0 on success; on failure it returns non-zero and
+ * tb200_last_error() describes why. All kernels are launched on the stream that is
+ * passed in; nothing synchronises the device unless stated.
+ *
+ * The reference simulator (matthewygf/Tiresias) has no native code.
+ * Each entry point below names the piece of the reference's *model* that it turns
+ * into an executed sm_100a kernel.
+ */
+#ifndef TIRESIAS_B200_H_
+#define TIRESIAS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB200_MAX_WORLD 8          /* one NVSwitch domain: 8 x B200                     */
+#define TB200_MAX_BUCKETS 256      /* gradient buckets per job                          */
+#define TB200_MAX_RING_CTAS 64     /* independent ring lanes (one per CTA)              */
+#define TB200_IPC_HANDLE_BYTES 64
+
+/* dtype codes */
+#define TB200_F32 0
+#define TB200_BF16 1
+
+/* Layout of one rank's flag pad (uint32 words). Every rank owns one pad in symmetric
+ * memory; peers write into it with st.release.sys, the owner polls it locally.          */
+#define TB200_FLAG_GRAD_READY(bucket, src) (((bucket) * TB200_MAX_WORLD) + (src))
+#define TB200_FLAG_PARAM_DONE(bucket, src) \
+  ((TB200_MAX_BUCKETS * TB200_MAX_WORLD) + ((bucket) * TB200_MAX_WORLD) + (src))
+#define TB200_FLAG_RING(dir, lane) \
+  ((2 * TB200_MAX_BUCKETS * TB200_MAX_WORLD) + ((dir) * TB200_MAX_RING_CTAS) + (lane))
+#define TB200_FLAG_WORDS (2 * TB200_MAX_BUCKETS * TB200_MAX_WORLD + 2 * TB200_MAX_RING_CTAS)
+
+/* ---- runtime ------------------------------------------------------------------------ */
+int tb200_version(void);
+const char* tb200_last_error(void);
+/* Number of kernels this library has launched since the last reset (bench "gpu_launches"). */
+unsigned long long tb200_launch_count(void);
+void tb200_launch_count_reset(void);
+
+/* ---- symmetric memory (replaces the reference's rack/switch network model,
+ *      infra/rack.py:10, run_sim.py:59-69) ------------------------------------------- */
+int tb200_symm_alloc(size_t bytes, void** out);               /* cudaMalloc + zero      */
+int tb200_symm_free(void* ptr);
+int tb200_ipc_export(void* ptr, unsigned char handle[TB200_IPC_HANDLE_BYTES]);
+int tb200_ipc_open(const unsigned char handle[TB200_IPC_HANDLE_BYTES], void** out);
+int tb200_ipc_close(void* ptr);
+int tb200_enable_peer_access(int device, int peer);
+int tb200_flags_fill(uint32_t* flags, size_t first, size_t count, uint32_t value,
+                     cudaStream_t stream);
+
+/* One job's view of the symmetric world. Index [rank] holds the local pointers. */
+typedef struct {
+  int world;                               /* number of workers == number of PS shards  */
+  int rank;
+  const void* grad[TB200_MAX_WORLD];       /* flat gradient buffers (grad_dtype)        */
+  void* param[TB200_MAX_WORLD];            /* flat parameter buffers (bf16)             */
+  uint32_t* flags[TB200_MAX_WORLD];        /* flag pads, TB200_FLAG_WORDS each          */
+} tb200_world_t;
+
+/* Hyper-parameters live in device memory so a captured CUDA graph picks up changes. */
+typedef struct {
+  float lr;
+  float momentum;
+  float weight_decay;
+  float grad_scale;                        /* usually 1/world                           */
+} tb200_sgd_hyper_t;
+
+/* ---- K4: optimizer step (README.md:7 "Synchronize SGD", core/jobs/job.py:72) --------- */
+/* master/momentum fp32, grad in grad_dtype, writes bf16 (or fp32) parameters.           */
+int tb200_sgd_momentum(float* master, float* momentum, const void* grad, int grad_dtype,
+                       void* param_out, int param_dtype, size_t n,
+                       const tb200_sgd_hyper_t* hyper_dev, cudaStream_t stream);
+
+/* ---- K1 + K2 (store side): worker->PS push fused with the SGD update and the PS->worker
+ *      broadcast (core/network/network_service.py:30-37 "round trip"; infra/switch.py:97-107
+ *      per-node traffic; one PS shard per GPU as in infra/switch.py:100-106).
+ *
+ * For bucket `bucket`, this rank is the parameter server of elements
+ * [shard_off, shard_off + shard_len) of the flat buffers. The kernel
+ *   1. posts "my gradients for this bucket are final" to every peer,
+ *   2. waits until every worker has posted the same,
+ *   3. reads the W gradient slices over NVLink (fixed rank order => bitwise reproducible),
+ *      scales, applies SGD+momentum+weight decay to the fp32 master shard,
+ *   4. stores the new bf16 parameters into every worker's parameter buffer (broadcast=1),
+ *      or only into its own (broadcast=0: the workers pull the shard later, inside
+ *      tb200_gemm_bf16_nt_pull),
+ *   5. posts "shard done" to every peer.
+ * *epoch_dev is the step number (device memory; see tb200_step_end).
+ * counter_dev: one zero-initialised uint32 per bucket (scratch owned by the caller).
+ * status_dev: set non-zero when a wait ran out of `spin_budget` polls (0 = wait forever).  */
+int tb200_ps_push_pull(const tb200_world_t* world, int bucket, size_t shard_off,
+                       size_t shard_len, int grad_dtype, float* master, float* momentum,
+                       const tb200_sgd_hyper_t* hyper_dev, const uint32_t* epoch_dev,
+                       uint32_t* counter_dev, int* status_dev,
+                       unsigned long long spin_budget, int max_ctas, int broadcast,
+                       cudaStream_t stream);
+
+/* Waits until all PS shards of buckets [0, num_buckets) are done for *epoch_dev, then
+ * increments *epoch_dev. Launch once per step after the last push.                       */
+int tb200_step_end(const tb200_world_t* world, int num_buckets, uint32_t* epoch_dev,
+                   int* status_dev, unsigned long long spin_budget, cudaStream_t stream);
+
+/* ---- K3: all-reduce mode (README.md:6 "All-reduce not yet implemented") ---------------- */
+/* In-place sum over `n` elements of the symmetric buffers buf[0..W-1] (same offset on every
+ * rank). algo 0 = ring (reduce-scatter + all-gather, 2(W-1) flag-synchronised steps),
+ * algo 1 = direct two-shot through NVSwitch. seq_dev: device counter bumped per call.     */
+int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD], size_t n,
+                    int dtype, float scale, int algo, uint32_t* seq_dev, int* status_dev,
+                    unsigned long long spin_budget, int num_ctas, cudaStream_t stream);
+
+/* ---- K5: tcgen05 GEMM (model_factory.py:4-55 / core/models.py:9-20 FC layers) ---------- */
+/* D[M,N] = act(A[M,K] . B[N,K]^T + bias[N]); A, B bf16 row-major (K contiguous), fp32
+ * accumulation in TMEM, D bf16 or fp32; bias fp32 or bf16 (bias_dtype), may be NULL.
+ * act: 0 none, 1 relu, 2 gelu(tanh).
+ * K must be a multiple of 8 (TMA 16-byte stride rule).                                     */
+int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, int bias_dtype,
+                       int M, int N, int K, int d_dtype, int act, cudaStream_t stream);
+
+/* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
+int tb200_gemm_reserve(size_t bytes);
+
+/* ---- K2 (load side): PS->worker pull fused into the first GEMM that consumes the weights.
+ * B is sharded by rows across the world: rank s owns rows [s*rows_per_rank, ...) inside its
+ * own parameter buffer at element offset b_off. TMA reads each B tile straight from the
+ * owner's memory (after its PARAM_DONE flag for `bucket` reaches *epoch_dev - 1, the step that just ended),
+ * and the tiles are also written to this rank's parameter buffer so later consumers
+ * (backward, the other layers) find the gathered weights locally.                           */
+int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off,
+                            int rows_per_rank, const void* A, void* D, const void* bias,
+                            int bias_dtype, int M, int N, int K, int d_dtype, int act,
+                            const uint32_t* epoch_dev, int* status_dev,
+                            unsigned long long spin_budget, cudaStream_t stream);
+
+/* ---- small fused helpers ----------------------------------------------------------------- */
+/* uint8 NHWC image batch -> normalised bf16 NHWC (mean/std per channel, C == 3).            */
+int tb200_u8_to_bf16_norm(const uint8_t* src, void* dst, size_t pixels, const float mean[3],
+                          const float inv_std[3], cudaStream_t stream);
+/* bf16 [R,C] -> bf16 [C,R] tiled transpose (feeds the NT GEMM in backward).                 */
+int tb200_transpose_bf16(const void* src, void* dst, int rows, int cols, cudaStream_t stream);
+/* out[0] = sum(x^2) over n elements; `partials` is caller-provided scratch of
+ * tb200_sumsq_scratch_floats() floats. Deterministic two-pass reduction.                    */
+size_t tb200_sumsq_scratch_floats(void);
+int tb200_sumsq(const void* x, int dtype, size_t n, float* partials, float* out,
+                cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TIRESIAS_B200_H_ */

@@ -1,0 +1,63 @@
+"""Transformer-base job model ("transformer" in model/model_factory.py:21-23; QKV/FFN shapes
+512x{512,2048} per SURVEY.md §2.6 K5). Pre-LN stack, d_model 512, 8 heads, FFN 2048 with ReLU
+(as in the original base model), tied token embedding, next-token loss on synthetic tokens.
+All projections run on the tcgen05 GEMM; attention uses torch SDPA.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+from torch.nn import functional as F
+
+from ..ops import native
+from ..ops.linear import TcLinear
+
+
+class Block(nn.Module):
+    def __init__(self, d_model: int, n_heads: int, d_ff: int):
+        super().__init__()
+        self.n_heads = n_heads
+        self.ln1 = nn.LayerNorm(d_model)
+        self.qkv = TcLinear(d_model, 3 * d_model)
+        self.proj = TcLinear(d_model, d_model)
+        self.ln2 = nn.LayerNorm(d_model)
+        self.ff1 = TcLinear(d_model, d_ff, act=native.ACT_RELU)
+        self.ff2 = TcLinear(d_ff, d_model)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        b, s, d = x.shape
+        qkv = self.qkv(self.ln1(x)).view(b, s, 3, self.n_heads, d // self.n_heads)
+        q, k, v = (t.transpose(1, 2) for t in qkv.unbind(dim=2))
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        x = x + self.proj(a.transpose(1, 2).reshape(b, s, d))
+        return x + self.ff2(self.ff1(self.ln2(x)))
+
+
+class TransformerLM(nn.Module):
+    def __init__(self, vocab: int = 32000, d_model: int = 512, n_layers: int = 12, n_heads: int = 8,
+                 d_ff: int = 2048, max_len: int = 512):
+        super().__init__()
+        self.vocab = vocab
+        self.tok = nn.Embedding(vocab, d_model)
+        self.pos = nn.Embedding(max_len, d_model)
+        self.blocks = nn.ModuleList(Block(d_model, n_heads, d_ff) for _ in range(n_layers))
+        self.ln_f = nn.LayerNorm(d_model)
+        self.head = TcLinear(d_model, vocab, bias=False)
+        nn.init.normal_(self.tok.weight, std=0.02)
+        nn.init.normal_(self.pos.weight, std=0.02)
+
+    def forward(self, tokens: torch.Tensor) -> torch.Tensor:
+        b, s = tokens.shape
+        x = self.tok(tokens) + self.pos(torch.arange(s, device=tokens.device))
+        for blk in self.blocks:
+            x = blk(x)
+        return self.head(self.ln_f(x))
+
+
+def transformer_base(vocab: int = 32000) -> TransformerLM:
+    return TransformerLM(vocab=vocab)
+
+
+def transformer_big(vocab: int = 32000) -> TransformerLM:
+    """Sized towards the 1100 MB checkpoint of model_factory.py:23 (~275 M fp32 parameters)."""
+    return TransformerLM(vocab=vocab, d_model=1024, n_layers=20, n_heads=16, d_ff=4096)

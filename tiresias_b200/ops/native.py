@@ -1,0 +1,207 @@
+"""ctypes bindings for ``libtiresias_b200.so`` (C ABI in ``include/tiresias_b200.h``).
+
+The library is built in-tree by :mod:`tiresias_b200.build`. On a machine with a GPU a missing
+or unloadable library is an error (no silent PyTorch fallback); on the CPU-only build box the
+module imports fine and :func:`lib` raises only when a kernel is actually requested.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+from typing import Optional, Sequence
+
+import torch
+
+MAX_WORLD = 8
+MAX_BUCKETS = 256
+MAX_RING_CTAS = 64
+IPC_HANDLE_BYTES = 64
+FLAG_WORDS = 2 * MAX_BUCKETS * MAX_WORLD + 2 * MAX_RING_CTAS
+
+F32, BF16 = 0, 1
+ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
+
+LIB_PATH = Path(__file__).resolve().parent.parent / "lib" / "libtiresias_b200.so"
+
+
+def flag_grad_ready(bucket: int, src: int) -> int:
+    return bucket * MAX_WORLD + src
+
+
+def flag_param_done(bucket: int, src: int) -> int:
+    return MAX_BUCKETS * MAX_WORLD + bucket * MAX_WORLD + src
+
+
+class World(C.Structure):
+    """Mirror of ``tb200_world_t``."""
+
+    _fields_ = [
+        ("world", C.c_int),
+        ("rank", C.c_int),
+        ("grad", C.c_void_p * MAX_WORLD),
+        ("param", C.c_void_p * MAX_WORLD),
+        ("flags", C.c_void_p * MAX_WORLD),
+    ]
+
+
+class SgdHyper(C.Structure):
+    _fields_ = [("lr", C.c_float), ("momentum", C.c_float), ("weight_decay", C.c_float),
+                ("grad_scale", C.c_float)]
+
+
+_lib: Optional[C.CDLL] = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, sz, u32p, ip, st = C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p
+    lib.tb200_version.restype = C.c_int
+    lib.tb200_last_error.restype = C.c_char_p
+    lib.tb200_launch_count.restype = C.c_ulonglong
+    lib.tb200_launch_count_reset.restype = None
+    lib.tb200_symm_alloc.argtypes = [sz, C.POINTER(vp)]
+    lib.tb200_symm_free.argtypes = [vp]
+    lib.tb200_ipc_export.argtypes = [vp, C.c_char_p]
+    lib.tb200_ipc_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    lib.tb200_ipc_close.argtypes = [vp]
+    lib.tb200_enable_peer_access.argtypes = [C.c_int, C.c_int]
+    lib.tb200_flags_fill.argtypes = [u32p, sz, sz, C.c_uint32, st]
+    lib.tb200_sgd_momentum.argtypes = [vp, vp, vp, C.c_int, vp, C.c_int, sz, vp, st]
+    lib.tb200_ps_push_pull.argtypes = [C.POINTER(World), C.c_int, sz, sz, C.c_int, vp, vp, vp, u32p,
+                                       u32p, ip, C.c_ulonglong, C.c_int, C.c_int, st]
+    lib.tb200_step_end.argtypes = [C.POINTER(World), C.c_int, u32p, ip, C.c_ulonglong, st]
+    lib.tb200_allreduce.argtypes = [C.POINTER(World), C.POINTER(vp), sz, C.c_int, C.c_float, C.c_int,
+                                    u32p, ip, C.c_ulonglong, C.c_int, st]
+    lib.tb200_gemm_bf16_nt.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, st]
+    lib.tb200_gemm_reserve.argtypes = [sz]
+    lib.tb200_gemm_bf16_nt_pull.argtypes = [C.POINTER(World), C.c_int, sz, C.c_int, vp, vp, vp,
+                                            C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            u32p, ip,
+                                            C.c_ulonglong, st]
+    lib.tb200_u8_to_bf16_norm.argtypes = [vp, vp, sz, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
+    lib.tb200_transpose_bf16.argtypes = [vp, vp, C.c_int, C.c_int, st]
+    lib.tb200_sumsq_scratch_floats.restype = C.c_size_t
+    lib.tb200_sumsq.argtypes = [vp, C.c_int, sz, vp, vp, st]
+    for name in ("tb200_symm_alloc", "tb200_symm_free", "tb200_ipc_export", "tb200_ipc_open",
+                 "tb200_ipc_close", "tb200_enable_peer_access", "tb200_flags_fill",
+                 "tb200_sgd_momentum", "tb200_ps_push_pull", "tb200_step_end", "tb200_allreduce",
+                 "tb200_gemm_bf16_nt", "tb200_gemm_reserve", "tb200_gemm_bf16_nt_pull",
+                 "tb200_u8_to_bf16_norm", "tb200_transpose_bf16", "tb200_sumsq"):
+        getattr(lib, name).restype = C.c_int
+
+
+def available() -> bool:
+    return LIB_PATH.exists()
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the native library; raises :class:`NativeError` if absent."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise NativeError(
+                f"{LIB_PATH} is missing: run `python -m tiresias_b200.build` (nvcc, sm_100a). "
+                "There is no PyTorch fallback for the native kernels.")
+        # torch has already loaded libcudart; make sure ours resolves to the same runtime.
+        _lib = C.CDLL(str(LIB_PATH), mode=os.RTLD_GLOBAL if hasattr(os, "RTLD_GLOBAL") else 0)
+        _declare(_lib)
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise NativeError(lib().tb200_last_error().decode(errors="replace"))
+
+
+def stream_ptr(stream: Optional[torch.cuda.Stream] = None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.float32:
+        return F32
+    if dt == torch.bfloat16:
+        return BF16
+    raise TypeError(f"unsupported dtype {dt}")
+
+
+def launch_count() -> int:
+    return int(lib().tb200_launch_count())
+
+
+def launch_count_reset() -> None:
+    lib().tb200_launch_count_reset()
+
+
+# ---- thin tensor-level wrappers ----------------------------------------------------------------
+
+def sgd_momentum(master: torch.Tensor, momentum: torch.Tensor, grad: torch.Tensor,
+                 param_out: torch.Tensor, hyper_dev: torch.Tensor) -> None:
+    """K4: fused SGD+momentum+weight-decay step. ``hyper_dev``: 4 fp32 on device
+    (lr, momentum, weight_decay, grad_scale)."""
+    n = master.numel()
+    assert momentum.numel() == n and grad.numel() == n and param_out.numel() == n
+    check(lib().tb200_sgd_momentum(master.data_ptr(), momentum.data_ptr(), grad.data_ptr(),
+                                   dtype_code(grad.dtype), param_out.data_ptr(),
+                                   dtype_code(param_out.dtype), n, hyper_dev.data_ptr(), stream_ptr()))
+
+
+def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None,
+            act: int = ACT_NONE, out_dtype: torch.dtype = torch.bfloat16,
+            out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K5: ``act(a @ b.T + bias)`` on the tcgen05 tensor cores. a [M,K], b [N,K], bf16."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.is_contiguous() and b.is_contiguous() and a.shape[1] == b.shape[1]
+    m, k = a.shape
+    n = b.shape[0]
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    bias_ptr, bias_dt = 0, F32
+    if bias is not None:
+        assert bias.numel() == n and bias.is_contiguous()
+        bias_ptr, bias_dt = bias.data_ptr(), dtype_code(bias.dtype)
+    check(lib().tb200_gemm_bf16_nt(a.data_ptr(), b.data_ptr(), out.data_ptr(), bias_ptr, bias_dt,
+                                   m, n, k, dtype_code(out.dtype), act, stream_ptr()))
+    return out
+
+
+def transpose(x: torch.Tensor) -> torch.Tensor:
+    """bf16 [R,C] -> [C,R] through the tiled transpose kernel."""
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and x.dim() == 2
+    r, c = x.shape
+    out = torch.empty((c, r), dtype=x.dtype, device=x.device)
+    check(lib().tb200_transpose_bf16(x.data_ptr(), out.data_ptr(), r, c, stream_ptr()))
+    return out
+
+
+def u8_to_bf16_norm(src: torch.Tensor, mean: Sequence[float], std: Sequence[float],
+                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 NHWC batch -> normalised bf16 NHWC."""
+    assert src.dtype == torch.uint8 and src.is_contiguous() and src.shape[-1] == 3
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*[1.0 / v for v in std])
+    check(lib().tb200_u8_to_bf16_norm(src.data_ptr(), out.data_ptr(), src.numel() // 3, m, s,
+                                      stream_ptr()))
+    return out
+
+
+def sumsq(x: torch.Tensor, scratch: Optional[torch.Tensor] = None,
+          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Deterministic sum of squares (gradient-norm watchdog)."""
+    nfl = int(lib().tb200_sumsq_scratch_floats())
+    if scratch is None:
+        scratch = torch.empty(nfl, dtype=torch.float32, device=x.device)
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=x.device)
+    assert scratch.numel() >= nfl
+    check(lib().tb200_sumsq(x.data_ptr(), dtype_code(x.dtype), x.numel(), scratch.data_ptr(),
+                            out.data_ptr(), stream_ptr()))
+    return out

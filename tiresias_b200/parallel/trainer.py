@@ -1,0 +1,435 @@
+"""Synchronous-SGD job trainer for one NVSwitch domain: parameter-server/worker (fused kernels),
+ring all-reduce (fused kernels) and the PyTorch+NCCL PS/worker baseline.
+
+This is the execution backend behind every trace job. The reference only *prices* a job's
+communication (core/network/network_service.py:3-39: ``(model_size/bandwidth + cross*latency) *
+iterations * 2``) under the assumptions "Parameter Server / Worker", "Synchronize SGD"
+(README.md:3-7) with one worker and one PS shard per GPU (infra/switch.py:97-107). Here the same
+job runs for real:
+
+``mode="ps"``    every bucket's push (reduce-scatter onto the PS shard), the SGD+momentum update
+                of the fp32 master shard and the broadcast of the new bf16 parameters are one
+                kernel (``tb200_ps_push_pull``), launched from a gradient hook on a side stream so
+                it overlaps the rest of backward. Layers marked for *pull* skip the broadcast and
+                gather their weights inside their first forward GEMM (``tb200_gemm_bf16_nt_pull``).
+``mode="ring"``  the README's unimplemented all-reduce mode: in-kernel ring all-reduce per bucket
+                followed by the stand-alone fused optimizer kernel on replicated state.
+``mode="nccl"``  the baseline named by BASELINE.json: bucketed ``reduce_scatter`` + torch SGD on the
+                shard + ``all_gather`` through NCCL, same model code, same buckets.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from ..models.zoo import ModelSpec
+from ..ops import native
+from ..ops.linear import TcLinear
+from .symm import SymmetricWorld
+
+IMAGENET_MEAN = (0.485, 0.456, 0.406)
+IMAGENET_STD = (0.229, 0.224, 0.225)
+_ALIGN = 64  # elements; keeps every parameter view 128-byte aligned inside the flat buffers
+
+
+@dataclass
+class Bucket:
+    index: int
+    offset: int                       # element offset in the flat buffers
+    length: int                       # padded to a multiple of 8 * world
+    params: List[Tuple[nn.Parameter, int]] = field(default_factory=list)   # (param, flat offset)
+    pull_layer: Optional[TcLinear] = None
+    pending: int = 0
+
+    def shard(self, rank: int, world: int) -> Tuple[int, int]:
+        n = self.length // world
+        return self.offset + rank * n, n
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def plan_buckets(model: nn.Module, world: int, bucket_elems: int, pull_min_elems: int,
+                 allow_pull: bool) -> Tuple[List[Bucket], int]:
+    """Greedy bucketing in reverse registration order (~ the order gradients become ready).
+
+    Large TcLinear weights whose rows split evenly into 128-row tiles per rank get a bucket of
+    their own so they can be row-sharded over the PS ranks and pulled inside the GEMM.
+    """
+    pull_weights: Dict[int, TcLinear] = {}
+    if allow_pull and world > 1:
+        for m in model.modules():
+            if (isinstance(m, TcLinear) and m.weight.numel() >= pull_min_elems
+                    and m.out_features % (128 * world) == 0):
+                pull_weights[id(m.weight)] = m
+    buckets: List[Bucket] = []
+    cur: Optional[Bucket] = None
+    off = 0
+    quantum = 8 * world
+
+    def close() -> None:
+        nonlocal cur, off
+        if cur is not None:
+            cur.length = _round_up(off - cur.offset, quantum)
+            off = cur.offset + cur.length
+            buckets.append(cur)
+            cur = None
+
+    for p in reversed([q for q in model.parameters() if q.requires_grad]):
+        if id(p) in pull_weights:
+            close()
+            off = _round_up(off, max(_ALIGN, quantum))
+            b = Bucket(len(buckets), off, p.numel(), [(p, off)], pull_weights[id(p)])
+            off += p.numel()
+            buckets.append(b)
+            continue
+        if cur is None:
+            off = _round_up(off, max(_ALIGN, quantum))
+            cur = Bucket(len(buckets), off, 0)
+        off = _round_up(off, _ALIGN)
+        cur.params.append((p, off))
+        off += p.numel()
+        if off - cur.offset >= bucket_elems:
+            close()
+    close()
+    if len(buckets) >= native.MAX_BUCKETS - 1:
+        raise ValueError(f"{len(buckets)} buckets exceed the flag pad; raise bucket_mb")
+    return buckets, _round_up(off, max(_ALIGN, quantum))
+
+
+class Trainer:
+    """One worker (= one rank = one GPU) of a synchronous-SGD job."""
+
+    def __init__(self, spec: ModelSpec, batch_size: int, mode: str = "ps",
+                 world: Optional[SymmetricWorld] = None, lr: float = 0.1, momentum: float = 0.9,
+                 weight_decay: float = 1e-4, bucket_mb: float = 8.0, use_graph: bool = True,
+                 pull_gemm: bool = True, pull_min_mb: float = 4.0, comm_ctas: int = 32,
+                 spin_budget: int = 50_000_000, seed: int = 0, device: Optional[torch.device] = None,
+                 model: Optional[nn.Module] = None, allreduce_algo: int = 0):
+        if mode not in ("ps", "ring", "nccl"):
+            raise ValueError(f"unknown mode {mode!r}")
+        self.spec, self.mode, self.batch_size = spec, mode, batch_size
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.symm = world if world is not None else SymmetricWorld.from_env(self.device)
+        self.world, self.rank = self.symm.world, self.symm.rank
+        self.use_graph = use_graph
+        self.comm_ctas, self.spin_budget = comm_ctas, spin_budget
+        self.allreduce_algo = allreduce_algo
+        self._lib = native.lib()
+
+        torch.manual_seed(seed)           # identical initial weights on every rank
+        with torch.device(self.device):
+            self.model = (model if model is not None else spec.build()).to(self.device)
+        self.model.train()
+        self.buckets, self.total = plan_buckets(
+            self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
+            allow_pull=(pull_gemm and mode == "ps"))
+
+        self._alloc_state()
+        self._flatten_model()
+        self.set_hyper(lr, momentum, weight_decay)
+        self._install_hooks()
+
+        self.stream = torch.cuda.Stream(self.device)
+        self.comm_stream = torch.cuda.Stream(self.device)
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._steps = 0
+        self.native_per_step = 0
+        self.native_launches = 0
+        self._pending_nccl: List[Tuple[Bucket, object]] = []
+        self._alloc_io()
+
+    # ------------------------------------------------------------------------------------------
+    # state
+    # ------------------------------------------------------------------------------------------
+    def _alloc_state(self) -> None:
+        dev, n = self.device, self.total
+        if self.mode == "nccl":
+            self.param_flat = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+            self.grad_flat = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+        else:
+            self.symm.alloc("param", n * 2)
+            self.symm.alloc("grad", n * 2)
+            self.symm.alloc("flags", native.FLAG_WORDS * 4)
+            self.param_flat = self.symm.buffers["param"].view(torch.bfloat16)
+            self.grad_flat = self.symm.buffers["grad"].view(torch.bfloat16)
+            self._world_struct = self.symm.native_world("grad", "param", "flags")
+            self._grad_ptrs = (C.c_void_p * native.MAX_WORLD)(
+                *[self.symm.buffers["grad"].ptrs[r] for r in range(self.world)])
+        replicated = self.mode == "ring"
+        shard_total = n if replicated else n // self.world
+        self.master = torch.zeros(shard_total, dtype=torch.float32, device=dev)
+        self.mom = torch.zeros(shard_total, dtype=torch.float32, device=dev)
+        # per-bucket offset of this rank's shard inside master/mom
+        self._shard_base: List[int] = []
+        acc = 0
+        for b in self.buckets:
+            self._shard_base.append(acc)
+            acc += b.length if replicated else b.length // self.world
+        self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        self.epoch = torch.ones(1, dtype=torch.int32, device=dev)         # step number, starts at 1
+        self.counters = torch.zeros(max(2, len(self.buckets)) + 2, dtype=torch.int32, device=dev)
+        self.ar_seq = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def set_hyper(self, lr: float, momentum: float, weight_decay: float) -> None:
+        self.lr, self.momentum_v, self.weight_decay = lr, momentum, weight_decay
+        self.hyper.copy_(torch.tensor([lr, momentum, weight_decay, 1.0 / self.world],
+                                      dtype=torch.float32))
+
+    @staticmethod
+    def _physical(p: torch.Tensor) -> torch.Tensor:
+        """1-D copy of ``p`` in the element order it has in memory (NHWC for conv weights)."""
+        if p.dim() == 4:
+            return p.detach().permute(0, 2, 3, 1).reshape(-1)
+        return p.detach().reshape(-1)
+
+    def _repoint(self, p: nn.Parameter, off: int) -> None:
+        n = p.numel()
+        pv, gv = self.param_flat[off: off + n], self.grad_flat[off: off + n]
+        if p.dim() == 4:
+            o, i, h, w = p.shape
+            p.data = pv.view(o, h, w, i).permute(0, 3, 1, 2)       # channels_last strides
+            p.grad = gv.view(o, h, w, i).permute(0, 3, 1, 2)
+        else:
+            p.data = pv.view(p.shape)
+            p.grad = gv.view(p.shape)
+
+    def _flatten_model(self) -> None:
+        """Move every parameter into the flat bf16 buffer (views); fp32 masters stay on the PS."""
+        replicated = self.mode == "ring"
+        if self.spec.kind == "image":
+            self.model.to(memory_format=torch.channels_last)
+        with torch.no_grad():
+            for bi, b in enumerate(self.buckets):
+                full32 = torch.zeros(b.length, dtype=torch.float32, device=self.device)
+                for p, off in b.params:
+                    full32[off - b.offset: off - b.offset + p.numel()] = self._physical(p).float()
+                self.param_flat[b.offset: b.offset + b.length] = full32.to(torch.bfloat16)
+                n = b.length if replicated else b.length // self.world
+                lo = 0 if replicated else self.rank * n
+                base = self._shard_base[bi]
+                self.master[base: base + n] = full32[lo: lo + n]
+                for p, off in b.params:
+                    self._repoint(p, off)
+            # everything that is not a trainable parameter (BN statistics...) follows to bf16
+            for mod in self.model.modules():
+                for name, buf in list(mod._buffers.items()):
+                    if buf is not None and buf.is_floating_point():
+                        mod._buffers[name] = buf.to(torch.bfloat16)
+        self.set_hyper(0.1, 0.9, 1e-4)
+        for b in self.buckets:
+            if b.pull_layer is not None:
+                b.pull_layer._pull_ctx = (self, b)
+
+    def _alloc_io(self) -> None:
+        dev, bs = self.device, self.batch_size
+        if self.spec.kind == "image":
+            self.x_dev = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.uint8, device=dev)
+            self.x_in = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.bfloat16, device=dev)
+        else:
+            self.x_dev = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.int64, device=dev)
+            self.x_in = self.x_dev
+        ydim = (bs,) if self.spec.kind == "image" else (bs, *self.spec.sample_shape)
+        self.y_dev = torch.zeros(ydim, dtype=torch.int64, device=dev)
+        self.loss_dev = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.h2d_bytes = self.x_dev.numel() * self.x_dev.element_size() + self.y_dev.numel() * 8
+        self.d2h_bytes = 4
+
+    # ------------------------------------------------------------------------------------------
+    # gradient hooks -> communication
+    # ------------------------------------------------------------------------------------------
+    def _install_hooks(self) -> None:
+        for b in self.buckets:
+            b.pending = len(b.params)
+            for p, _ in b.params:
+                p.register_post_accumulate_grad_hook(self._make_hook(b))
+
+    def _make_hook(self, bucket: Bucket):
+        def hook(_param: torch.Tensor) -> None:
+            bucket.pending -= 1
+            if bucket.pending == 0:
+                bucket.pending = len(bucket.params)
+                self._bucket_ready(bucket)
+        return hook
+
+    def _bucket_ready(self, b: Bucket) -> None:
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.comm_stream.wait_event(ev)
+        with torch.cuda.stream(self.comm_stream):
+            if self.mode == "ps":
+                self._launch_push(b)
+            elif self.mode == "ring":
+                self._launch_ring(b)
+            else:
+                self._launch_nccl(b)
+
+    def _launch_push(self, b: Bucket) -> None:
+        off, n = b.shard(self.rank, self.world)
+        base = self._shard_base[b.index]
+        native.check(self._lib.tb200_ps_push_pull(
+            C.byref(self._world_struct), b.index, off, n, native.BF16,
+            self.master.data_ptr() + 4 * base, self.mom.data_ptr() + 4 * base, self.hyper.data_ptr(),
+            self.epoch.data_ptr(), self.counters.data_ptr() + 4 * b.index, self.status.data_ptr(),
+            self.spin_budget, self.comm_ctas, 0 if b.pull_layer is not None else 1,
+            native.stream_ptr(self.comm_stream)))
+
+    def _launch_ring(self, b: Bucket) -> None:
+        st = native.stream_ptr(self.comm_stream)
+        if self.world > 1:
+            ptrs = (C.c_void_p * native.MAX_WORLD)(
+                *[self.symm.buffers["grad"].ptrs[r] + 2 * b.offset for r in range(self.world)])
+            native.check(self._lib.tb200_allreduce(
+                C.byref(self._world_struct), ptrs, b.length, native.BF16, 1.0, self.allreduce_algo,
+                self.ar_seq.data_ptr(), self.status.data_ptr(), self.spin_budget, self.comm_ctas, st))
+        base = self._shard_base[b.index]
+        native.check(self._lib.tb200_sgd_momentum(
+            self.master.data_ptr() + 4 * base, self.mom.data_ptr() + 4 * base,
+            self.grad_flat.data_ptr() + 2 * b.offset, native.BF16,
+            self.param_flat.data_ptr() + 2 * b.offset, native.BF16, b.length, self.hyper.data_ptr(), st))
+
+    def _launch_nccl(self, b: Bucket) -> None:
+        import torch.distributed as dist
+        n = b.length // self.world
+        g = self.grad_flat[b.offset: b.offset + b.length]
+        if not hasattr(b, "_shard_grad"):
+            b._shard_grad = torch.empty(n, dtype=torch.bfloat16, device=self.device)
+            b._shard_param = torch.empty(n, dtype=torch.bfloat16, device=self.device)
+        if dist.is_initialized():
+            dist.reduce_scatter_tensor(b._shard_grad, g, op=dist.ReduceOp.SUM)
+        else:
+            b._shard_grad.copy_(g[:n])
+        base = self._shard_base[b.index]
+        m, v = self.master[base: base + n], self.mom[base: base + n]
+        # plain torch SGD(momentum, weight decay) on the fp32 master shard
+        grad = b._shard_grad.float().mul_(1.0 / self.world).add_(m, alpha=self.weight_decay)
+        v.mul_(self.momentum_v).add_(grad)
+        m.add_(v, alpha=-self.lr)
+        b._shard_param.copy_(m)
+        p = self.param_flat[b.offset: b.offset + b.length]
+        if dist.is_initialized():
+            dist.all_gather_into_tensor(p, b._shard_param)
+        else:
+            p[:n].copy_(b._shard_param)
+
+    # ------------------------------------------------------------------------------------------
+    # one step
+    # ------------------------------------------------------------------------------------------
+    def _preprocess(self) -> torch.Tensor:
+        if self.spec.kind == "image":
+            native.u8_to_bf16_norm(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
+            return self.x_in.permute(0, 3, 1, 2)       # logical NCHW, physical NHWC
+        return self.x_in
+
+    def _device_step(self) -> None:
+        x = self._preprocess()
+        logits = self.model(x)
+        loss = torch.nn.functional.cross_entropy(
+            logits.float().reshape(-1, logits.shape[-1]), self.y_dev.reshape(-1))
+        self.loss_dev.copy_(loss.detach().reshape(1))
+        loss.backward()
+        with torch.cuda.stream(self.comm_stream):
+            if self.mode == "ps":
+                native.check(self._lib.tb200_step_end(
+                    C.byref(self._world_struct), len(self.buckets), self.epoch.data_ptr(),
+                    self.status.data_ptr(), self.spin_budget, native.stream_ptr(self.comm_stream)))
+        torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+        self.grad_flat.zero_()
+
+    def _capture(self) -> None:
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph, stream=self.stream):
+            self._device_step()
+
+    def _advance(self) -> None:
+        """Run one device-side step on ``self.stream`` (eager, or capture-then-replay)."""
+        graphable = self.use_graph and self.mode != "nccl"
+        if graphable and self._graph is None and self._steps >= 3:
+            torch.cuda.synchronize(self.device)
+            self.symm.barrier()
+            before = native.launch_count()
+            self._capture()
+            self.native_per_step = native.launch_count() - before
+        if graphable and self._graph is not None:
+            self._graph.replay()
+            self.native_launches += self.native_per_step      # kernel nodes replayed from the graph
+        else:
+            before = native.launch_count()
+            self._device_step()
+            self.native_per_step = native.launch_count() - before
+            self.native_launches += self.native_per_step
+        self._steps += 1
+
+    def step(self, x_host: torch.Tensor, y_host: torch.Tensor) -> None:
+        """Enqueue one training step on host tensors (pinned for asynchronous copies). The loss
+        of this step is read back with :meth:`loss` (device->host copy enqueued here)."""
+        with torch.cuda.stream(self.stream):
+            self.x_dev.copy_(x_host, non_blocking=True)
+            self.y_dev.copy_(y_host, non_blocking=True)
+            self._advance()
+            self.loss_host.copy_(self.loss_dev, non_blocking=True)
+
+    def step_resident(self) -> None:
+        """One step on the batch already resident on the device (device-only timing)."""
+        with torch.cuda.stream(self.stream):
+            self._advance()
+
+    def loss(self) -> float:
+        """Blocks until the most recent step's loss has landed in pinned host memory."""
+        self.stream.synchronize()
+        return float(self.loss_host[0])
+
+    def synchronize(self) -> None:
+        self.stream.synchronize()
+        self.comm_stream.synchronize()
+
+    def check_status(self) -> int:
+        """Watchdog hook: non-zero means an in-kernel wait ran out of spin budget (peer lost)."""
+        self.synchronize()
+        return int(self.status.item())
+
+    # ------------------------------------------------------------------------------------------
+    # checkpoint / resume (preemption support for the executor)
+    # ------------------------------------------------------------------------------------------
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        self.synchronize()
+        out = {"master": self.master.detach().to("cpu", copy=True),
+               "momentum": self.mom.detach().to("cpu", copy=True),
+               "epoch": self.epoch.detach().to("cpu", copy=True),
+               "steps": torch.tensor(self._steps)}
+        for name, buf in self.model.named_buffers():
+            out["buffer." + name] = buf.detach().to("cpu", copy=True)
+        return out
+
+    def load_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
+        """Restore the optimizer shard; parameters are rebuilt from the fp32 masters."""
+        self.synchronize()
+        self.master.copy_(state["master"])
+        self.mom.copy_(state["momentum"])
+        self._steps = int(state["steps"])
+        bufs = dict(self.model.named_buffers())
+        for k, v in state.items():
+            if k.startswith("buffer."):
+                bufs[k[len("buffer."):]].copy_(v)
+        replicated = self.mode == "ring"
+        with torch.no_grad():
+            for bi, b in enumerate(self.buckets):
+                n = b.length if replicated else b.length // self.world
+                lo = 0 if replicated else self.rank * n
+                base = self._shard_base[bi]
+                self.param_flat[b.offset + lo: b.offset + lo + n] = self.master[base: base + n].to(torch.bfloat16)
+        # other ranks' shards are restored by their own load_state_dict; peers then re-gather
+        # on the next step (ps mode broadcasts every shard at the end of each step).
+
+    def close(self) -> None:
+        self.synchronize()
+        self._graph = None
+        if self.mode != "nccl":
+            self.symm.close()
