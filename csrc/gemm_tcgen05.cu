@@ -630,3 +630,114 @@ int tb200_gemm_reserve(size_t bytes) {
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// No-allocation entry point (no counterpart in the reference; it has no native code at all).
+//
+// tb200_gemm_bf16_nt may call cudaMalloc/cudaFree to grow its split-K scratch. Some users of this
+// library must never do that once their job is running:
+//   * a job that shares its GPU with one or two other jobs (the simulator packs up to three per
+//     device): cudaMalloc and cudaFree synchronise the whole device, so one tenant's allocation
+//     stalls its neighbours and pollutes the interference that calib/ is trying to measure, and
+//     on a GPU whose memory the packed jobs have fully subscribed the allocation can simply fail
+//     in the middle of a step;
+//   * plain C/C++ hosts that link the C ABI without any allocator of their own and want a call
+//     whose memory footprint is fixed when the library is loaded.
+// For them the split-K partial sums live in the array below: TB200_GEMM_NOALLOC_SCRATCH_BYTES of
+// device memory that every GPU which loads this library holds until the process exits.
+// =================================================================================================
+static __device__ __align__(256) float tb200_noalloc_splitk_scratch[TB200_GEMM_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+float* g_noalloc_ptr[kMaxDevices] = {};
+
+// In host code the array's name is only a stand-in for the symbol; the kernels need the device
+// address, which differs per GPU. Resolved once per device, with that device current.
+int noalloc_scratch(float** out) {
+  int dev = 0;
+  TB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail("tb200_gemm_bf16_nt_noalloc: device %s%ld unsupported", "", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[dev]) {
+    float* p = nullptr;
+    TB_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), tb200_noalloc_splitk_scratch));
+    if (!p) return fail("tb200_gemm_bf16_nt_noalloc: scratch symbol has no device address%s");
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void* bias,
+                                          int bias_dtype, int M, int N, int K, int d_dtype, int act,
+                                          cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm_bf16_nt_noalloc: empty problem%s");
+  if (K % 8) return fail("tb200_gemm_bf16_nt_noalloc: K %s(%ld) must be a multiple of 8", "", K);
+  if (d_dtype != TB200_BF16 && d_dtype != TB200_F32)
+    return fail("tb200_gemm_bf16_nt_noalloc: bad output dtype%s");
+
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
+  p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
+
+  // Same tiling and split-K plan as tb200_gemm_bf16_nt (keep the two in step), so both entry
+  // points run the same kernels in the same order and produce the same bits.
+  const int sms = sm_count();
+  int block_n = 256;
+  if (N <= 128 || (long long)p.num_m * ((N + 255) / 256) < sms) block_n = 128;
+  p.num_n = (N + block_n - 1) / block_n;
+  const int tiles = p.num_m * p.num_n;
+  int splits = 1;
+  if (tiles < sms) {
+    int max_splits = p.num_kb / 4;
+    if (max_splits > 16) max_splits = 16;
+    double best = 0.0;
+    for (int s = 1; s <= max_splits; ++s) {
+      const int it = tiles * s;
+      const int waves = (it + sms - 1) / sms;
+      const double eff = (double)it / ((double)waves * sms);
+      if (eff > best + 1e-9) { best = eff; splits = s; }
+    }
+  }
+  p.splits = splits;
+  if (splits > 1) {
+    const size_t need = (size_t)splits * M * N * sizeof(float);
+    if (need > (size_t)TB200_GEMM_NOALLOC_SCRATCH_BYTES) {
+      snprintf(g_last_error, sizeof(g_last_error),
+               "tb200_gemm_bf16_nt_noalloc: M=%d N=%d K=%d needs %zu bytes of split-K scratch "
+               "(%d splits) but the built-in scratch is %zu bytes; use tb200_gemm_bf16_nt",
+               M, N, K, need, splits, (size_t)TB200_GEMM_NOALLOC_SCRATCH_BYTES);
+      return 4;
+    }
+    // Every partial that the reduction reads is written by this call's GEMM first, so nothing in
+    // the shared array has to be cleared; what an earlier call left behind is simply overwritten.
+    if (int rc = noalloc_scratch(&p.partials)) return rc;
+  }
+
+  CUtensorMap ma, mb;
+  PullMaps pm;
+  memset(&pm, 0, sizeof(pm));
+  if (int rc = make_map(&ma, A, M, K, BLOCK_M)) return rc;
+  if (int rc = make_map(&mb, B, N, K, block_n)) return rc;
+  const int items = tiles * splits;
+  const int grid = items < sms ? items : sms;
+  int rc = block_n == 256 ? launch_gemm<256, false>(ma, mb, pm, p, grid, stream)
+                          : launch_gemm<128, false>(ma, mb, pm, p, grid, stream);
+  if (rc) return rc;
+  if (splits > 1) {
+    const size_t mn = (size_t)M * N;
+    int rgrid = (int)((mn + 255) / 256);
+    if (rgrid > sms * 8) rgrid = sms * 8;
+    splitk_reduce_kernel<<<rgrid, 256, 0, stream>>>(p.partials, splits, mn, N, bias, bias_dtype, act, D,
+                                                    d_dtype);
+    return launched();
+  }
+  return 0;
+}

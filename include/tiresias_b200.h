@@ -127,6 +127,32 @@ int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, 
 /* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
 int tb200_gemm_reserve(size_t bytes);
 
+/* ---- tb200_gemm_bf16_nt without any allocation (no counterpart in the reference, which has
+ *      no native code). Same arguments, same kernels and same results as tb200_gemm_bf16_nt.
+ *
+ * Who needs it: a job that shares its GPU with other jobs (cudaMalloc/cudaFree synchronise the
+ * whole device, so an allocation by one tenant stalls the others, and on a fully subscribed GPU
+ * it can fail mid-step), and plain C hosts of this ABI that bring no allocator and want the
+ * memory footprint fixed at load time. This entry point never calls cudaMalloc, cudaFree or any
+ * allocating routine: when the problem is split along K, the fp32 partial sums go to a scratch
+ * array that is built into the library, TB200_GEMM_NOALLOC_SCRATCH_BYTES per GPU, held by every
+ * GPU that loads the library until the process exits.
+ *
+ *  - Limit: splits * M * N * 4 bytes must fit in the scratch (splits is chosen as in
+ *    tb200_gemm_bf16_nt, at most 16). Larger problems are refused with an error that names
+ *    both sizes; nothing is launched in that case. Problems that need no split use no scratch.
+ *  - The first call on each device looks up the scratch's device address (one
+ *    cudaGetSymbolAddress with that device current). Make that first call during set-up,
+ *    before any stream capture is started on the device.
+ *  - All calls on one GPU share the one scratch array. A call overwrites whatever the previous
+ *    call left there and needs nothing cleared beforehand, but two calls that can run at the
+ *    same time on the GPU (different streams, no dependency between them) race on it: order
+ *    them, or use tb200_gemm_bf16_nt for one of them.                                         */
+#define TB200_GEMM_NOALLOC_SCRATCH_BYTES (16u << 20)
+int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void* bias,
+                               int bias_dtype, int M, int N, int K, int d_dtype, int act,
+                               cudaStream_t stream);
+
 /* ---- K2 (load side): PS->worker pull fused into the first GEMM that consumes the weights.
  * B is sharded by rows across the world: rank s owns rows [s*rows_per_rank, ...) inside its
  * own parameter buffer at element offset b_off. TMA reads each B tile straight from the
