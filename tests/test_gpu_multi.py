@@ -1,0 +1,36 @@
+"""Multi-GPU checks of the in-kernel communication paths over real NVLink peer memory.
+
+Launches tests/multi_worker.py with one process per GPU (torchrun, NCCL bootstrap on 127.0.0.1)
+for every world size in {2, 4, 8} that the box has GPUs for. Skipped on single-GPU boxes; the
+single-GPU suite covers the same kernels with emulated ranks (test_gpu_kernels.py).
+"""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_in_kernel_collectives(native_lib, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs, box has {torch.cuda.device_count()}")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(ROOT, "tests", "multi_worker.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=420, cwd=ROOT)
+    tail = (res.stdout + "\n" + res.stderr)[-4000:]
+    assert res.returncode == 0, tail
+    assert "MULTI OK" in res.stdout, tail
