@@ -1,0 +1,59 @@
+"""Golden-log parity of the tick simulator against the UNMODIFIED reference.
+
+tests/golden/*.cluster.csv were produced by tests/make_golden.py: the reference's run_sim.py under
+a wrapper that seeds numpy/python RNGs with 1. The new simulator, given the same trace, flags and
+seed, must write a byte-identical cluster.csv — scheduler decisions, placement, the RNG call order
+behind avg_gpu_utilization, and the csv formatting all have to agree.
+"""
+import glob
+import os
+import shlex
+
+import pytest
+
+from tiresias_b200.cli.run_sim import run
+from tiresias_b200.sim.flags import define_simulator_flags
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = sorted(os.path.basename(p)[:-len(".args")] for p in glob.glob(os.path.join(GOLD, "*.args")))
+
+
+def _run_case(name, tmp_path, extra=()):
+    argv = shlex.split(open(os.path.join(GOLD, name + ".args")).read())
+    argv += ["--trace_file", os.path.join(GOLD, name + ".trace.csv"), "--seed", "1", "--quiet", *extra]
+    flags = define_simulator_flags()
+    flags.parse(argv)
+    out = str(tmp_path / name)
+    summary = run(flags, output_dir=out)
+    return out, summary
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_cluster_csv_is_byte_identical(name, tmp_path):
+    out, summary = _run_case(name, tmp_path)
+    got = open(os.path.join(out, "cluster.csv"), "rb").read()
+    want = open(os.path.join(GOLD, name + ".cluster.csv"), "rb").read()
+    if got != want:
+        g, w = got.split(b"\r\n"), want.split(b"\r\n")
+        for i, (a, b) in enumerate(zip(g, w)):
+            assert a == b, f"{name}: first difference at row {i}:\n ours {a!r}\n ref  {b!r}"
+        assert len(g) == len(w), f"{name}: {len(g)} rows vs {len(w)}"
+    assert summary["finished_jobs"] > 0
+
+
+def test_job_csv_header_only_and_jobs_csv_rows(tmp_path):
+    out, summary = _run_case("t64_yarn_fifo", tmp_path)
+    job = open(os.path.join(out, "job.csv"), "rb").read()
+    assert job == (b"time,job_id,num_gpu,submit_time,start_time,end_time,executed_time,JCT,duration,"
+                   b"pending_time,preempt,promote\r\n")
+    rows = open(os.path.join(out, "jobs.csv")).read().strip().split("\n")
+    assert len(rows) == 1 + summary["finished_jobs"] == 65
+    for name in ("cpu.csv", "gpu.csv", "memory.csv", "network.csv", "output.log", "summary.json"):
+        assert os.path.exists(os.path.join(out, name)), name
+
+
+def test_oversized_job_is_abandoned(tmp_path):
+    # t12 carries one 64-GPU job on a 2x4x4 = 32-GPU cluster: the run ends with it still queued (Q3)
+    out, summary = _run_case("t12_yarn_fifo", tmp_path)
+    assert summary["queued_at_end"] >= 1
+    assert summary["finished_jobs"] < 13
