@@ -66,7 +66,7 @@ def run(flags: FlagSet, output_dir: Optional[str] = None) -> Dict:
             np.random.seed(flags.seed)
             random.seed(flags.seed)
         calibration = load_calibration(flags.calibration)
-        if flags.schedule in TICK_SCHEDULES and flags.scheme != "count":
+        if _use_tick_engine(flags):
             summary = _run_tick(flags, output_dir, rng, calibration)
         else:
             from ..sim.legacy.engine import run_event_simulation
@@ -81,6 +81,18 @@ def run(flags: FlagSet, output_dir: Optional[str] = None) -> Dict:
         for h in handlers:
             util.logger.removeHandler(h)
             h.close()
+
+
+def _use_tick_engine(flags) -> bool:
+    """horus / horus+ / gandiva always tick; fifo ticks on a live-schema trace (the reference's live
+    path) and runs on the event engine (Tiresias ``sim_job_events``) for a README-schema trace or
+    ``--scheme count``."""
+    from ..sim.trace import detect_schema
+    if flags.schedule not in TICK_SCHEDULES or flags.scheme == "count":
+        return False
+    if flags.schedule == "fifo" and flags.trace_file and os.path.exists(flags.trace_file):
+        return detect_schema(flags.trace_file) == "live"
+    return True
 
 
 def _run_tick(flags: FlagSet, output_dir: str, rng, calibration) -> Dict:

@@ -128,6 +128,8 @@ def define_simulator_flags(fs: Optional[FlagSet] = None) -> FlagSet:
     fs.define_string("job_dist", None, "duration samples for the Gittins index (csv with a "
                                        "'duration' column); default: the trace itself")
     fs.define_integer("gittins_delta", 3250, "Gittins service quantum")
+    fs.define_boolean("gittins_desc", False, "gittins: highest index first (the reference's loop sorts "
+                                             "ascending, its dlas-gpu-gittins variant descending)")
     fs.define_float("solve_starvation", 0, "DLAS starvation knob: promote when pending >= x * executed")
     fs.define_string("calibration", None, "calibration json produced by tiresias_b200.calib")
     fs.define_string("comm", "ps", "communication mode priced/executed for distributed jobs: ps | ring")
