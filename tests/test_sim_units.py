@@ -1,0 +1,297 @@
+"""Unit tests of the simulator's components."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tiresias_b200.sim import infra, kmeans, models, network, scoring, util
+from tiresias_b200.sim.flags import FlagSet, define_simulator_flags
+from tiresias_b200.sim.job import Job, ORDER_PENDING, ORDER_UTILIZATION
+from tiresias_b200.sim.legacy import gittins as gi
+from tiresias_b200.sim.queues import JobQueueManager
+from tiresias_b200.sim.trace import JobGenerator, JobTraceReader, detect_schema, read_tiresias_trace
+
+
+def _flags(*argv):
+    f = define_simulator_flags()
+    f.parse(list(argv))
+    return f
+
+
+# ---- flags (C1, Q20) ---------------------------------------------------------------------------------
+def test_flag_defaults_match_reference():
+    f = _flags()
+    assert (f.trace_file, f.scheme, f.schedule) == ("tf_job.csv", "yarn", "fifo")
+    assert (f.num_switch, f.num_node_p_switch, f.num_gpu_p_node, f.num_cpu_p_node, f.mem_p_node) == \
+        (1, 32, 8, 128, 512)
+    assert (f.bandwidth, f.internode_latency, f.gpu_memory_capacity, f.num_queue) == (1250, 0.015, 32, 1)
+    assert (f.pack, f.enable_network_costs, f.enable_migration, f.print, f.flush_stdout) == \
+        (False, False, False, False, True)
+    assert f.cluster_spec is None and f.log_path.startswith("result-")
+
+
+@pytest.mark.parametrize("argv,want", [(["--pack"], True), (["--pack=True"], True), (["--pack", "True"], True),
+                                       (["--pack", "false"], False), (["--nopack"], False),
+                                       (["--noflush_stdout"], False)])
+def test_boolean_flag_forms(argv, want):
+    f = _flags(*argv)
+    assert (f.flush_stdout if "flush" in argv[0] else f.pack) is want
+
+
+def test_unknown_flags_are_ignored_and_values_assignable():
+    f = _flags("--no_such_flag", "7", "--num_switch", "3")
+    assert f.num_switch == 3 and "--no_such_flag" in f.unparsed
+    f.num_switch = 5
+    assert f.num_switch == 5
+    with pytest.raises(AttributeError):
+        f.not_a_flag
+
+
+def test_lazy_parse_on_first_read():
+    fs = FlagSet()
+    fs.define_integer("n", 1)
+    fs.set_argv(["--n", "4"])
+    assert fs.n == 4
+
+
+# ---- infrastructure (C11) ------------------------------------------------------------------------------
+def test_cluster_from_flags_ids_and_racks():
+    inf = infra.Infrastructure(_flags("--num_switch", "2", "--num_node_p_switch", "3", "--num_gpu_p_node", "4"))
+    assert list(inf.nodes) == ["1", "2", "3", "4", "5", "6"] and list(inf.racks) == ["0", "1"]
+    assert inf.nodes["4"].rack_id == "1" and inf.get_total_gpus() == 24
+    assert inf.gpu_memory_capacity == 32 * 1024
+    assert inf.get_racks_by_dist("1") == [("1", 0), ("0", 1)]
+
+
+def test_cluster_spec_file_overrides_flags_and_missing_column_gives_empty_cluster(tmp_path):
+    spec = tmp_path / "spec.csv"
+    spec.write_text("num_switch,num_node_p_switch,num_gpu_p_node,num_cpu_p_node,mem_p_node\n1,16,4,128,254")
+    inf = infra.Infrastructure(_flags("--cluster_spec", str(spec)))
+    assert (len(inf.racks), len(inf.nodes), inf.num_gpu_p_node, inf.mem_p_node) == (1, 16, 4, 254)
+    bad = tmp_path / "bad.csv"
+    bad.write_text("num_switch,num_node_p_switch,num_gpu_p_node\n1,16,4")
+    assert len(infra.Infrastructure(_flags("--cluster_spec", str(bad))).nodes) == 0       # reference quirk
+
+
+def _job(gpus=2, per=1, mem=2048.0, avg=30.0, mx=50.0, order=ORDER_PENDING, jid="j"):
+    return Job(jid, 10, 0, per, avg, mx, mem, mem / 2, gpus, order=order)
+
+
+def test_can_fit_num_task_arithmetic():
+    node = infra.Node("0", "1", 32768, cpus=30, gpus=4, memory=512)
+    job = _job(gpus=4)
+    # 4 idle devices fit 4 tasks, but 30 CPUs only fit 30 // 12 = 2 -> min is 2
+    assert node.can_fit_num_task(job.tasks) == 2
+    node.cpu_used = 30
+    assert node.can_fit_num_task(job.tasks) == 0
+    assert node.is_free()                               # memory left counts as free (Q9)
+
+
+def test_device_three_task_limit_and_memory_margin():
+    dev = infra.Device(0, "1", 32768, False)
+    small = [_job(jid=f"s{i}", gpus=1, mem=1024.0).tasks[f"s{i}_worker0"] for i in range(4)]
+    for t in small[:3]:
+        assert dev.add_task(t, pack=True)
+    assert not dev.can_fit(small[3])                    # at most 3 tasks per device
+    dev2 = infra.Device(1, "1", 32768, False)
+    big = _job(jid="b", gpus=1, mem=32768.0 - 500).tasks["b_worker0"]
+    assert not dev2.can_fit(big)                        # needs a margin strictly above 500 MiB
+    ok = _job(jid="o", gpus=1, mem=32768.0 - 501).tasks["o_worker0"]
+    assert dev2.can_fit(ok)
+    assert dev2.add_task(ok) and not dev2.add_task(small[0], pack=False)     # no sharing without pack
+
+
+def test_utilization_draw_uses_global_generator_like_reference():
+    dev = infra.Device(0, "1", 32768, False)
+    t = _job(gpus=1, avg=40.0, mx=60.0).tasks["j_worker0"]
+    dev.add_task(t)
+    np.random.seed(5)
+    got, drawn = dev.sample_utilization()
+    np.random.seed(5)
+    want = min(100, np.random.normal(loc=40.0, scale=10.0, size=1))
+    assert drawn and got == float(want[0])
+
+
+# ---- scoring (C7) ---------------------------------------------------------------------------------------
+def test_horus_and_gandiva_score_numerics():
+    node = infra.Node("0", "1", 32768, cpus=128, gpus=2, memory=512)
+    t = _job(gpus=1, mem=4096.0, avg=30.0, mx=50.0).tasks["j_worker0"]
+    scores, total, best = scoring.horus_score(node, t)
+    want = (0 + 4096.0 / 32768) * 1.3 + abs(0 + 50.0 - 100.0) / 100 + 0
+    assert scores == {0: want, 1: want} and best == want and total == want * 2
+    _, _, g_best = scoring.gandiva_score(node, t)
+    assert g_best == (4096.0 / 32768) * 1.3
+    hot = _job(jid="h", gpus=1, mem=1024.0, avg=90.0, mx=160.0).tasks["h_worker0"]
+    _, _, over = scoring.horus_score(node, hot)          # util above 100 is charged 1.6x
+    assert over == pytest.approx((1024.0 / 32768) * 1.3 + 60.0 * 1.6 / 100)
+
+
+# ---- queues / credits (C10a, Q12) -------------------------------------------------------------------------
+def test_credits_and_argmax_tie_break():
+    jq = JobQueueManager(_flags("--schedule", "horus+", "--num_queue", "3"))
+    a, b, c = (_job(jid=n, order=ORDER_UTILIZATION, avg=u) for n, u in (("a", 10.0), ("b", 20.0), ("c", 5.0)))
+    jq.insert(a, 0); jq.insert(b, 1); jq.insert(c, 1)
+    assert jq.queue_credits == [1, 2, 0]
+    jq.update_credits()
+    assert jq.queue_credits == [1, 2, 0]                  # median pending < 1 -> len(queue)
+    for j in (a, b, c):
+        j.pending_time = 4.0
+    jq.update_credits()
+    assert jq.queue_credits == [4.0, 8.0, 0] and jq.queue_idx_by_credit() == 1
+    b.pending_time = c.pending_time = 2.0
+    jq.update_credits()
+    assert jq.queue_credits == [4.0, 4.0, 0] and jq.queue_idx_by_credit() == 0     # lowest index wins ties
+    assert jq.pop(1) is c                                 # heap: lowest average utilisation first
+
+
+def test_falsy_utilisation_never_sorts_first():
+    zero, some = _job(jid="z", avg=0.0, order=ORDER_UTILIZATION), _job(jid="s", avg=9.0, order=ORDER_UTILIZATION)
+    assert not (zero < some) and not (some < zero)        # Q10
+    p1, p2 = _job(jid="p1"), _job(jid="p2")
+    p1.pending_time = 5.0
+    assert p1 < p2                                        # longer pending first
+
+
+# ---- k-means (C8, Q11) --------------------------------------------------------------------------------------
+def _random_jobs(n, seed):
+    rng = np.random.default_rng(seed)
+    return [Job(i, 10, 0, 1, float(rng.uniform(5, 70)), float(rng.uniform(70, 100)),
+                float(rng.uniform(1000, 12000)), float(rng.uniform(500, 1000)), int(rng.choice([1, 2, 4, 8])),
+                order=ORDER_UTILIZATION) for i in range(n)]
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_kmeans_shortcut_equals_full_iteration(seed):
+    jobs = _random_jobs(25, seed)
+    a = kmeans.clusterize(jobs, 3, rng=np.random.RandomState(seed))
+    b = kmeans.clusterize(jobs, 3, dist_fn=kmeans.job_dist, rng=np.random.RandomState(seed))   # scalar, <=1000 rounds
+    assert a[1] == [int(x) for x in b[1]] and [j.job_id for j in a[0]] == [j.job_id for j in b[0]]
+    assert a[2] == pytest.approx(b[2])
+
+
+def test_kmeans_deterministic_under_seed():
+    jobs = _random_jobs(30, 9)
+    np.random.seed(3)
+    first = kmeans.clusterize(jobs, 4)[1]
+    np.random.seed(3)
+    assert kmeans.clusterize(jobs, 4)[1] == first
+
+
+# ---- Gittins (D6) ------------------------------------------------------------------------------------------------
+def test_gittins_table_matches_scalar_formula():
+    rng = np.random.default_rng(4)
+    durations = [int(x) for x in np.clip(rng.lognormal(7, 1.4, size=400), 30, 1e6)]
+    table = gi.gittins_table(durations, 3250)
+    data = {"num": table["num"], "data": table["data"][:-1]}
+    for i, v in enumerate(data["data"]):
+        assert table["gittins"][i] == gi.cal_r_gittins_index(data, int(v - 1), 3250)
+    assert table["data"][-1] == gi.MAXSIZE and table["gittins"][-1] == 0.0
+    att = torch.tensor([0, 500, 10 ** 9])
+    assert gi.gittins_ranks(table, att).tolist() == [gi.get_gittins_index(table, int(a)) for a in att]
+    assert gi.get_gittins_index(table, 10 ** 9) == 0
+
+
+def test_gittins_hand_example():
+    # samples 10, 20, 30, 40; delta 15; attained 0: idx 0; first sample > 15 is index 1
+    # p = (1-0)/4 = 0.25 ; e = (10 + 15*3)/4 = 13.75 ; r = 0.25e6/13.75 = 18181.8182
+    data = {"num": 4, "data": [10, 20, 30, 40]}
+    assert gi.cal_r_gittins_index(data, 0, 15) == 18181.8182
+
+
+def test_las_queue_after():
+    att = torch.tensor([10, 3600, 7300, 99999])
+    q = torch.tensor([0, 0, 1, 3])
+    assert gi.las_queue_after(att, q, [3600, 7200, 18000]).tolist() == [0, 1, 2, 3]
+
+
+# ---- model tables (O1-O3) -------------------------------------------------------------------------------------------
+def test_model_tables():
+    assert models.model_sizes["resnet50"] == 97 and models.model_sizes["vgg16"] == 528 and len(models.model_sizes) == 17
+    lens = {n: (len(t), round(sum(t), 1)) for n, t in zip(models.m_names, models.m_tensors)}
+    assert lens == {"vgg19": (15, 547.1), "vgg16": (12, 526.8), "vgg11": (9, 506.5), "alexnet": (7, 235.8),
+                    "resnet152": (48, 149.6), "resnet101": (35, 119.7), "resnet50": (18, 80.6),
+                    "inception4": (81, 132.8), "inception3": (21, 56.6)}
+    assert models.get_model("nope")["name"] == "inception3"
+    assert models.get_model_with_scale("vgg11", 2)["total_size"] == 1013.0
+    cnn = models.estimate_gpu_utilization(97, True, 32, add_noise=False)
+    assert cnn == round((525 + 97 * 3 + 3.5 * 0.012 * 64 * 3) / ((32 - 0.07) * 1024), 2)
+    assert models.estimate_gpu_utilization(1100, False, 32, add_noise=False) == 0.52
+
+
+# ---- network cost (C12, D12) -------------------------------------------------------------------------------------------
+def test_analytic_network_cost_worked_example():
+    f = _flags("--enable_network_costs")
+    inf = infra.Infrastructure(f)
+    job = Job("n", 100, 0, 1, 30, 50, 2048.0, 1024.0, 2, model_name="resnet50", iterations=1000)
+    job.tasks_running_on = {"n_worker0": "1", "n_worker1": "2"}
+    # BASELINE.md worked example: (97/1250 + 2*0.015) * 1000 * 2 = 215.2 s
+    assert network.calculate_network_costs(inf, job) == pytest.approx(215.2)
+    job.tasks_running_on = {"n_worker0": "1", "n_worker1": "1"}
+    assert network.calculate_network_costs(inf, job) == 0
+    cal = {"comm_s_per_iter": {"resnet50": {"2": 0.001, "8": 0.004}}}
+    assert network.calculate_network_costs(inf, job, cal) == pytest.approx(1.0)
+    assert network.node_traffic_mb(80.6, [10.0, 10.1], 2, 8) == round(80.6 * 2 + 10.0 * 6 - 10.0 * 2 + 10.1 * 6 - 10.1 * 2, 1)
+
+
+# ---- traces (C10c, D15) ---------------------------------------------------------------------------------------------------
+def test_trace_reader_filters_sorts_and_shifts(tmp_path):
+    p = tmp_path / "t.csv"
+    p.write_text("type,normalized_time,minutes,gpu_per_container,used_gpus,gpu_utilization_avg,gpu_utilization_max,"
+                 "memory_max,memory_avg\n"
+                 "noninteractive,30000,10,1,2,10,20,1048576,524288\n"
+                 "interactive,5,10,1,2,10,20,1048576,524288\n"
+                 "noninteractive,10000,20,1,1,10,20,,524288\n"
+                 "noninteractive,20000,30,1,4,10,20,2097152,524288\n")
+    r = JobTraceReader(str(p))
+    r.prepare_jobs()
+    assert len(r) == 2 and r.remaining_jobs() == 2
+    first = r.generate_jobs(0)
+    assert [x.index for x in first] == [3] and first[0].normalized_time == 0.0        # label = csv row number
+    assert r.generate_jobs(0.5) == [] and [x.index for x in r.generate_jobs(1)] == [0]
+    assert r.remaining_jobs() == 0 and detect_schema(str(p)) == "live"
+
+
+def test_readme_schema_csv_and_txt(tmp_path):
+    c = tmp_path / "a.csv"
+    c.write_text("job_id,num_gpu,submit_time,iterations,model_name,duration,interval\n1,4,10,500,vgg16,3000,33\n")
+    t = tmp_path / "a.txt"
+    t.write_text("job_id num_gpu submit_time iterations model_name duration interval\n2 8 20 100 resnet50 60 20\n")
+    assert read_tiresias_trace(str(c)) == [{"job_id": 1, "num_gpu": 4, "submit_time": 10, "iterations": 500,
+                                            "model_name": "vgg16", "duration": 3000, "interval": 33}]
+    assert read_tiresias_trace(str(t))[0]["num_gpu"] == 8 and detect_schema(str(t)) == "tiresias"
+
+
+def test_job_generator_tables_and_seeded_trace():
+    import random
+    jg = JobGenerator()
+    assert (len(jg.MODEL_SAMPLE_DEF), len(jg.ITTER_SAMPLE_DEF), len(jg.DURATION_SAMPLE_DEF),
+            len(jg.ARRIVAL_SAMPLE_DEF)) == (16, 66, 60, 7)
+    assert jg.cdf([5, 1, 3]).tolist() == [0.0, 0.5, 1.0]
+    random.seed(1)
+    a = jg.generate_trace(50)
+    random.seed(1)
+    assert jg.generate_trace(50) == a and set(a) == {"model", "duration", "itter", "arrival", "num_gpu",
+                                                      "interval", "job_id"}
+    assert all(1 <= g < 128 for g in a["num_gpu"]) and all(20 <= i < 44 for i in a["interval"])
+
+
+# ---- misc ------------------------------------------------------------------------------------------------------------------
+def test_util_helpers(tmp_path):
+    assert util.convert_bytes(3 * 2 ** 30) == 3 and util.convert_bytes(2 ** 21, "MiB") == 2
+    assert util.search_dict_list([{"a": 1}, {"a": 2, "b": 3}], "a", 2) == {"a": 2, "b": 3}
+    assert util.search_dict_list([{"a": 1}], "z", 1) is None
+    d = tmp_path / "x" / "y"
+    util.make_dir_if_not_exist(str(d))
+    assert d.is_dir()
+
+
+def test_execute_builds_reference_argv():
+    from tiresias_b200.cli.execute import DEFAULT_CONFIGS, build_argv
+    argv = build_argv("horus+", "horus+", 3)
+    assert argv[:8] == ["--num_node_p_switch", "32", "--num_switch", "4", "--scheme", "horus+", "--trace_file",
+                        os.path.join("data", "month.csv")]
+    assert argv[-2:] == ["--log_path", os.path.join("nodes_p_s32_job_month", "horus+_horus+")]
+    assert "--enable_migration" in argv and DEFAULT_CONFIGS == [("horus+", "horus+", 3), ("horus+", "horus+", 4),
+                                                                 ("horus+", "horus+", 5)]
