@@ -1,0 +1,190 @@
+#!/usr/bin/env python
+"""Kernel microbenchmarks on one B200: every hand-written kernel against its roofline (measured
+peaks from MEASURED_PEAKS.json) and against the library op it replaces (cuBLAS via torch.matmul,
+torch elementwise SGD). CUDA-event timing, >= 5 warm-ups, L2 flushed (256 MiB write) between timed
+iterations. Prints one JSON object per kernel and writes them to gpurun_out/kernels.json.
+
+    python bench/kernels.py [--only gemm|sgd|push|allreduce|misc] [--iters 20]
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tiresias_b200.ops import native  # noqa: E402
+from tiresias_b200.parallel.symm import SymmetricWorld  # noqa: E402
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            d = json.load(fh)
+        return d["hbm_gbs"], d["bf16_tflops"], "measured"
+    except Exception:
+        return 6650.0, 1590.0, "fallback"
+
+
+HBM, TF, SRC = peaks()
+_flush = None
+
+
+def flush_l2():
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    _flush.fill_(1)
+
+
+def timeit(fn, iters=20, warmup=5):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        flush_l2()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def gemm_cases(iters):
+    out = []
+    shapes = [  # (M, N, K, note)
+        (64, 4096, 25088, "vgg fc6 fwd, batch 64"), (64, 4096, 4096, "vgg fc7 fwd"), (64, 1000, 4096, "vgg fc8 fwd"),
+        (256, 4096, 25088, "vgg fc6 fwd, batch 256"), (4096, 25088, 64, "vgg fc6 dW (K = batch)"),
+        (64, 1000, 2048, "resnet50 fc fwd"), (8192, 2048, 512, "transformer ffn1"), (8192, 512, 2048, "transformer ffn2"),
+        (8192, 1536, 512, "transformer qkv"), (8192, 32000, 512, "transformer lm head"),
+        (4096, 4096, 4096, "square 4k"), (8192, 8192, 8192, "square 8k"),
+    ]
+    for m, n, k, note in shapes:
+        a = torch.randn(m, k, device="cuda").to(torch.bfloat16)
+        b = (torch.randn(n, k, device="cuda") / k ** 0.5).to(torch.bfloat16)
+        bias = torch.randn(n, device="cuda")
+        o = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        ours, ours_min = timeit(lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o), iters)
+        ref = torch.relu(a.float() @ b.float().t() + bias)
+        err = (o.float() - ref).abs().max().item()
+        bt = b.t()
+        lib, lib_min = timeit(lambda: torch.relu_(torch.addmm(bias.to(torch.bfloat16), a, bt)), iters)
+        flops = 2.0 * m * n * k
+        byts = 2.0 * (m * k + n * k + m * n)
+        roof_ms = max(flops / (TF * 1e12), byts / (HBM * 1e9)) * 1e3
+        out.append({"kernel": "gemm_bf16_nt+bias+relu", "shape": [m, n, k], "note": note, "ms": round(ours, 4),
+                    "ms_min": round(ours_min, 4), "tflops": round(flops / ours / 1e9, 1),
+                    "gbs": round(byts / ours / 1e6, 1), "roofline_ms": round(roof_ms, 4),
+                    "frac_of_roofline": round(roof_ms / ours, 3), "cublas_ms": round(lib, 4),
+                    "speedup_vs_cublas": round(lib / ours, 3), "max_abs_err": round(err, 4), "peaks": SRC})
+        print(json.dumps(out[-1]), flush=True)
+    return out
+
+
+def sgd_cases(iters):
+    out = []
+    for n in (1 << 20, 25 << 20, 138 << 20):
+        master = torch.randn(n, device="cuda")
+        mom = torch.zeros(n, device="cuda")
+        grad = torch.randn(n, device="cuda").to(torch.bfloat16)
+        param = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+        hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0], device="cuda")
+        ours, _ = timeit(lambda: native.sgd_momentum(master, mom, grad, param, hyper), iters)
+
+        def torch_sgd():
+            g = grad.float().add_(master, alpha=1e-4)
+            mom.mul_(0.9).add_(g)
+            master.add_(mom, alpha=-0.1)
+            param.copy_(master)
+        lib, _ = timeit(torch_sgd, iters)
+        byts = n * (4 + 4 + 2 + 4 + 4 + 2)      # read master, mom, grad; write master, mom, param
+        out.append({"kernel": "sgd_momentum", "n": n, "ms": round(ours, 4), "gbs": round(byts / ours / 1e6, 1),
+                    "frac_of_hbm": round(byts / ours / 1e6 / HBM, 3), "torch_ms": round(lib, 4),
+                    "speedup_vs_torch": round(lib / ours, 3), "peaks": SRC})
+        print(json.dumps(out[-1]), flush=True)
+    return out
+
+
+def push_cases(iters):
+    """tb200_ps_push_pull on one GPU with W emulated ranks sharing the device: flags are pre-posted so
+    no kernel waits on another; measures the reduce + SGD + broadcast data path of one PS shard."""
+    out = []
+    lib = native.lib()
+    dev = torch.device("cuda", 0)
+    for world, n in ((1, 25 << 20), (8, 25 << 20), (8, 2 << 20)):
+        ranks = SymmetricWorld.emulated(world, dev)
+        for r in ranks:
+            r.alloc("grad", n * 2); r.alloc("param", n * 2); r.alloc("flags", native.FLAG_WORDS * 4)
+        for r in ranks:
+            r.buffers["grad"].view(torch.bfloat16).normal_()
+        shard = n // world
+        master = torch.randn(shard, device=dev); mom = torch.zeros(shard, device=dev)
+        hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0 / world], device=dev)
+        epoch = torch.ones(1, dtype=torch.int32, device=dev)
+        counter = torch.zeros(4, dtype=torch.int32, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        me = ranks[0]
+        ws = me.native_world("grad", "param", "flags")
+        me.post_flags("flags", native.flag_grad_ready(0, 0), native.MAX_WORLD, 1 << 30)
+
+        def run():
+            native.check(lib.tb200_ps_push_pull(C.byref(ws), 0, 0, shard, native.BF16, master.data_ptr(),
+                                                mom.data_ptr(), hyper.data_ptr(), epoch.data_ptr(),
+                                                counter.data_ptr(), status.data_ptr(), 1000, 64, 1,
+                                                native.stream_ptr()))
+        ms, _ = timeit(run, iters)
+        byts = shard * (2 * world + 4 + 4 + 4 + 4 + 2 * world)   # W grad reads, master/mom rw, W param writes
+        out.append({"kernel": "ps_push_pull (one shard, emulated ranks on one GPU)", "world": world,
+                    "bucket_elems": n, "shard_elems": shard, "ms": round(ms, 4), "gbs": round(byts / ms / 1e6, 1),
+                    "frac_of_hbm": round(byts / ms / 1e6 / HBM, 3), "status": int(status.item()), "peaks": SRC})
+        print(json.dumps(out[-1]), flush=True)
+        for r in ranks:
+            r._emulated_peers = None
+            r.close()
+    return out
+
+
+def misc_cases(iters):
+    out = []
+    x = torch.randint(0, 256, (256, 224, 224, 3), dtype=torch.uint8, device="cuda")
+    o = torch.empty(x.shape, dtype=torch.bfloat16, device="cuda")
+    ms, _ = timeit(lambda: native.u8_to_bf16_norm(x, (0.485, 0.456, 0.406), (0.229, 0.224, 0.225), out=o), iters)
+    byts = x.numel() * 3
+    out.append({"kernel": "u8_to_bf16_norm", "elems": x.numel(), "ms": round(ms, 4),
+                "gbs": round(byts / ms / 1e6, 1), "frac_of_hbm": round(byts / ms / 1e6 / HBM, 3)})
+    print(json.dumps(out[-1]), flush=True)
+    w = torch.randn(4096, 25088, device="cuda").to(torch.bfloat16)
+    ms, _ = timeit(lambda: native.transpose(w), iters)
+    byts = w.numel() * 4
+    out.append({"kernel": "transpose_bf16", "shape": list(w.shape), "ms": round(ms, 4),
+                "gbs": round(byts / ms / 1e6, 1), "frac_of_hbm": round(byts / ms / 1e6 / HBM, 3)})
+    print(json.dumps(out[-1]), flush=True)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="")
+    ap.add_argument("--iters", type=int, default=20)
+    args = ap.parse_args()
+    torch.cuda.set_device(0)
+    native.lib()
+    res = []
+    for name, fn in (("gemm", gemm_cases), ("sgd", sgd_cases), ("push", push_cases), ("misc", misc_cases)):
+        if args.only and args.only != name:
+            continue
+        res += fn(args.iters)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "kernels.json"), "w") as fh:
+        json.dump(res, fh, indent=1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,78 @@
+#!/usr/bin/env python
+"""Runs ONE hand-written kernel a few times inside a cudaProfilerStart/Stop range, for
+``ncu --profile-from-start off`` (see scripts/gpu_profile.sh). ``--kernel step`` brackets one eager
+ResNet-50 PS training step instead (for the per-launch time list)."""
+import argparse
+import ctypes as C
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tiresias_b200.ops import native  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "sgd", "push", "step"])
+    args = ap.parse_args()
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    prof = torch.cuda.cudart()
+    if args.kernel in ("gemm", "gemm_splitk"):
+        m, n, k = (8192, 8192, 8192) if args.kernel == "gemm" else (64, 4096, 25088)
+        a = torch.randn(m, k, device=dev).to(torch.bfloat16)
+        b = (torch.randn(n, k, device=dev) / k ** 0.5).to(torch.bfloat16)
+        bias = torch.randn(n, device=dev)
+        o = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
+        run = lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o)  # noqa: E731
+    elif args.kernel == "sgd":
+        n = 25 << 20
+        master, mom = torch.randn(n, device=dev), torch.zeros(n, device=dev)
+        grad = torch.randn(n, device=dev).to(torch.bfloat16)
+        param = torch.empty(n, device=dev, dtype=torch.bfloat16)
+        hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0], device=dev)
+        run = lambda: native.sgd_momentum(master, mom, grad, param, hyper)  # noqa: E731
+    elif args.kernel == "push":
+        from tiresias_b200.parallel.symm import SymmetricWorld
+        world, n = 8, 25 << 20
+        ranks = SymmetricWorld.emulated(world, dev)
+        for r in ranks:
+            r.alloc("grad", n * 2); r.alloc("param", n * 2); r.alloc("flags", native.FLAG_WORDS * 4)
+        shard = n // world
+        master, mom = torch.randn(shard, device=dev), torch.zeros(shard, device=dev)
+        hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0 / world], device=dev)
+        epoch = torch.ones(1, dtype=torch.int32, device=dev)
+        counter = torch.zeros(4, dtype=torch.int32, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        ws = ranks[0].native_world("grad", "param", "flags")
+        ranks[0].post_flags("flags", native.flag_grad_ready(0, 0), native.MAX_WORLD, 1 << 30)
+        lib = native.lib()
+        run = lambda: native.check(lib.tb200_ps_push_pull(  # noqa: E731
+            C.byref(ws), 0, 0, shard, native.BF16, master.data_ptr(), mom.data_ptr(), hyper.data_ptr(),
+            epoch.data_ptr(), counter.data_ptr(), status.data_ptr(), 1000, 64, 1, native.stream_ptr()))
+    else:
+        from tiresias_b200.models import zoo
+        from tiresias_b200.parallel.trainer import Trainer
+        spec = zoo.resolve("resnet50")
+        tr = Trainer(spec, batch_size=64, mode="ps", use_graph=False, device=dev)
+        x, y = zoo.synthetic_batch(spec, 64)
+
+        def run():
+            tr.step(x, y)
+            tr.loss()
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    prof.cudaProfilerStart()
+    for _ in range(1 if args.kernel == "step" else 3):
+        run()
+    torch.cuda.synchronize()
+    prof.cudaProfilerStop()
+    print("profiled", args.kernel)
+
+
+if __name__ == "__main__":
+    main()
