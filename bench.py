@@ -39,7 +39,7 @@ def parse_args() -> argparse.Namespace:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "ring"])
     ap.add_argument("--model", default="resnet50")
-    ap.add_argument("--batch", type=int, default=64, help="per-GPU batch (weak scaling)")
+    ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (weak scaling)")
     ap.add_argument("--bucket-mb", type=float, default=8.0)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--skip-nccl", action="store_true", help="do not run the NCCL baseline arm")

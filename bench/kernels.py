@@ -146,8 +146,61 @@ def push_cases(iters):
                     "frac_of_hbm": round(byts / ms / 1e6 / HBM, 3), "status": int(status.item()), "peaks": SRC})
         print(json.dumps(out[-1]), flush=True)
         for r in ranks:
-            r._emulated_peers = None
             r.close()
+    return out
+
+
+def bn_cases(iters):
+    """Fused BN(+residual+ReLU) forward and backward on ResNet-50 layer shapes (batch 64) against the
+    PyTorch ops they replace (batch_norm + add + relu, autograd backward). Bytes = one pass per tensor the
+    op must touch: fwd x (twice: statistics + apply), residual, y; bwd dy, x, y (twice) + dx + dres."""
+    from tiresias_b200.ops.batchnorm import fused_bn_act
+    out = []
+    for n, c, hw, res in ((64, 64, 112, False), (64, 256, 56, True), (64, 128, 28, False), (64, 1024, 14, True),
+                          (64, 2048, 7, True), (256, 256, 56, True)):
+        shape = (n, c, hw, hw)
+        x = torch.randn(shape, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        r = torch.randn_like(x) if res else None
+        dy = torch.randn_like(x)
+        gamma = torch.ones(c, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+        beta = torch.zeros(c, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+        rm, rv = torch.zeros(c, device="cuda"), torch.ones(c, device="cuda")
+        xg = x.clone().requires_grad_(True)
+        rg = r.clone().requires_grad_(True) if res else None
+        state = {}
+
+        def fwd():
+            state["y"] = fused_bn_act(xg, gamma, beta, rm, rv, rg, True)
+
+        def bwd():
+            state["y"].backward(dy, retain_graph=True)
+        f_ms, _ = timeit(fwd, iters)
+        fwd()
+        b_ms, _ = timeit(bwd, iters)
+        bn = torch.nn.BatchNorm2d(c).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+
+        def tfwd():
+            y = bn(xg)
+            if res:
+                y = y + rg
+            state["ty"] = torch.relu(y)
+
+        def tbwd():
+            state["ty"].backward(dy, retain_graph=True)
+        tf_ms, _ = timeit(tfwd, iters)
+        tfwd()
+        tb_ms, _ = timeit(tbwd, iters)
+        nbytes = x.numel() * 2
+        fbytes = nbytes * (3 + (1 if res else 0))
+        bbytes = nbytes * (6 + 1 + (1 if res else 0))
+        out.append({"kernel": "fused_bn_relu" + ("_add" if res else ""), "shape": list(shape),
+                    "fwd_ms": round(f_ms, 4), "fwd_gbs": round(fbytes / f_ms / 1e6, 1),
+                    "fwd_frac_of_hbm": round(fbytes / f_ms / 1e6 / HBM, 3), "bwd_ms": round(b_ms, 4),
+                    "bwd_gbs": round(bbytes / b_ms / 1e6, 1), "bwd_frac_of_hbm": round(bbytes / b_ms / 1e6 / HBM, 3),
+                    "torch_fwd_ms": round(tf_ms, 4), "torch_bwd_ms": round(tb_ms, 4),
+                    "speedup_fwd": round(tf_ms / f_ms, 2), "speedup_bwd": round(tb_ms / b_ms, 2), "peaks": SRC,
+                    "note": "L2 flushed between iterations; autograd dispatch overhead included on both sides"})
+        print(json.dumps(out[-1]), flush=True)
     return out
 
 
@@ -177,7 +230,7 @@ def main():
     torch.cuda.set_device(0)
     native.lib()
     res = []
-    for name, fn in (("gemm", gemm_cases), ("sgd", sgd_cases), ("push", push_cases), ("misc", misc_cases)):
+    for name, fn in (("gemm", gemm_cases), ("bn", bn_cases), ("sgd", sgd_cases), ("push", push_cases), ("misc", misc_cases)):
         if args.only and args.only != name:
             continue
         res += fn(args.iters)

@@ -177,6 +177,32 @@ size_t tb200_sumsq_scratch_floats(void);
 int tb200_sumsq(const void* x, int dtype, size_t n, float* partials, float* out,
                 cudaStream_t stream);
 
+/* ---- fused batch normalisation, NHWC bf16 (the ResNet jobs of model/model_factory.py:47-55).
+ * x, residual, y, dy, dx, dres: bf16 [rows, C] with C contiguous (rows = N*H*W), C % 8 == 0,
+ * C <= 4096. gamma/beta/dgamma/dbeta in param_dtype (TB200_F32 or TB200_BF16); statistics fp32.
+ * `scratch`: TB200_BN_SCRATCH_FLOATS floats, zero-filled ONCE by the caller and then left alone
+ * (the kernels keep self-resetting counters in it); one scratch serves every layer as long as
+ * the calls are ordered on one stream. Reductions run in a fixed order: results are bitwise
+ * reproducible.
+ *   fwd_train: batch statistics (biased variance for normalisation, unbiased for running_var,
+ *              momentum as in torch), y = relu?(bn(x) + residual?); saves mean / invstd for
+ *              the backward. running_mean / running_var may be NULL.
+ *   apply:     y = relu?(x*scale[c] + shift[c] + residual?) with scale_shift = [scale | shift]
+ *              (inference, or any per-channel affine).
+ *   bwd:       g = dy * (y > 0 if relu); dx, dres = g (may be NULL), dgamma, dbeta.              */
+#define TB200_BN_SCRATCH_FLOATS (1024 + 2 * 64 * 1024 + 4 * 4096)
+size_t tb200_bn_scratch_floats(void);
+int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void* gamma,
+                       const void* beta, int param_dtype, float* running_mean, float* running_var,
+                       float momentum, float eps, float* save_mean, float* save_invstd,
+                       float* scratch, size_t rows, int C, int relu, cudaStream_t stream);
+int tb200_bn_apply(const void* x, const void* residual, void* y, const float* scale_shift,
+                   size_t rows, int C, int relu, cudaStream_t stream);
+int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, int param_dtype,
+                 const float* save_mean, const float* save_invstd, void* dx, void* dres,
+                 void* dgamma, void* dbeta, float* scratch, size_t rows, int C, int relu,
+                 cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

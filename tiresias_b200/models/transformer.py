@@ -13,16 +13,34 @@ from ..ops import native
 from ..ops.linear import TcLinear
 
 
+class _TorchLinear(nn.Linear):
+    """Stock nn.Linear (+ ReLU as a separate kernel): the PyTorch+NCCL baseline arm."""
+
+    def __init__(self, cin: int, cout: int, bias: bool = True, relu: bool = False):
+        super().__init__(cin, cout, bias=bias)
+        self.relu = relu
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        y = super().forward(x)
+        return torch.relu_(y) if self.relu else y
+
+
+def _lin(cin: int, cout: int, fused: bool, relu: bool = False, bias: bool = True) -> nn.Module:
+    if fused:
+        return TcLinear(cin, cout, bias=bias, act=native.ACT_RELU if relu else native.ACT_NONE)
+    return _TorchLinear(cin, cout, bias=bias, relu=relu)
+
+
 class Block(nn.Module):
-    def __init__(self, d_model: int, n_heads: int, d_ff: int):
+    def __init__(self, d_model: int, n_heads: int, d_ff: int, fused: bool = True):
         super().__init__()
         self.n_heads = n_heads
         self.ln1 = nn.LayerNorm(d_model)
-        self.qkv = TcLinear(d_model, 3 * d_model)
-        self.proj = TcLinear(d_model, d_model)
+        self.qkv = _lin(d_model, 3 * d_model, fused)
+        self.proj = _lin(d_model, d_model, fused)
         self.ln2 = nn.LayerNorm(d_model)
-        self.ff1 = TcLinear(d_model, d_ff, act=native.ACT_RELU)
-        self.ff2 = TcLinear(d_ff, d_model)
+        self.ff1 = _lin(d_model, d_ff, fused, relu=True)
+        self.ff2 = _lin(d_ff, d_model, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         b, s, d = x.shape
@@ -35,14 +53,14 @@ class Block(nn.Module):
 
 class TransformerLM(nn.Module):
     def __init__(self, vocab: int = 32000, d_model: int = 512, n_layers: int = 12, n_heads: int = 8,
-                 d_ff: int = 2048, max_len: int = 512):
+                 d_ff: int = 2048, max_len: int = 512, fused: bool = True):
         super().__init__()
         self.vocab = vocab
         self.tok = nn.Embedding(vocab, d_model)
         self.pos = nn.Embedding(max_len, d_model)
-        self.blocks = nn.ModuleList(Block(d_model, n_heads, d_ff) for _ in range(n_layers))
+        self.blocks = nn.ModuleList(Block(d_model, n_heads, d_ff, fused) for _ in range(n_layers))
         self.ln_f = nn.LayerNorm(d_model)
-        self.head = TcLinear(d_model, vocab, bias=False)
+        self.head = _lin(d_model, vocab, fused, bias=False)
         nn.init.normal_(self.tok.weight, std=0.02)
         nn.init.normal_(self.pos.weight, std=0.02)
 
@@ -54,10 +72,10 @@ class TransformerLM(nn.Module):
         return self.head(self.ln_f(x))
 
 
-def transformer_base(vocab: int = 32000) -> TransformerLM:
-    return TransformerLM(vocab=vocab)
+def transformer_base(vocab: int = 32000, fused: bool = True) -> TransformerLM:
+    return TransformerLM(vocab=vocab, fused=fused)
 
 
-def transformer_big(vocab: int = 32000) -> TransformerLM:
+def transformer_big(vocab: int = 32000, fused: bool = True) -> TransformerLM:
     """Sized towards the 1100 MB checkpoint of model_factory.py:23 (~275 M fp32 parameters)."""
-    return TransformerLM(vocab=vocab, d_model=1024, n_layers=20, n_heads=16, d_ff=4096)
+    return TransformerLM(vocab=vocab, d_model=1024, n_layers=20, n_heads=16, d_ff=4096, fused=fused)

@@ -1,7 +1,9 @@
 """CNN job models named by the reference's model table (model/model_factory.py:4-55,
 core/models.py:20): ResNet-50/101/152, VGG-11/16/19, AlexNet. Random-init, NHWC (channels_last),
 bf16. Convolutions go through cuDNN; every fully connected layer runs on the tcgen05 GEMM
-(:class:`tiresias_b200.ops.linear.TcLinear`).
+(:class:`tiresias_b200.ops.linear.TcLinear`) and every BatchNorm (+ residual add + ReLU) on the fused
+kernels of :class:`tiresias_b200.ops.batchnorm.FusedBatchNormAct`. ``fused=False`` builds the same
+network from stock PyTorch layers only (nn.BatchNorm2d, nn.Linear): the PyTorch+NCCL baseline arm.
 """
 from __future__ import annotations
 
@@ -11,69 +13,118 @@ import torch
 from torch import nn
 
 from ..ops import native
+from ..ops.batchnorm import FusedBatchNormAct
 from ..ops.linear import TcLinear
 
 
-def _conv_bn(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0) -> List[nn.Module]:
-    return [nn.Conv2d(cin, cout, k, stride, pad, bias=False), nn.BatchNorm2d(cout)]
+class TorchBNAct(nn.Module):
+    """Stock-PyTorch counterpart of :class:`FusedBatchNormAct` (BatchNorm2d, then add, then ReLU as
+    separate library kernels) — what the PyTorch+NCCL baseline arm runs."""
+
+    def __init__(self, num_features: int, relu: bool = False):
+        super().__init__()
+        self.bn = nn.BatchNorm2d(num_features)
+        self.relu = relu
+
+    @property
+    def weight(self) -> torch.Tensor:
+        return self.bn.weight
+
+    def forward(self, x: torch.Tensor, residual: torch.Tensor = None) -> torch.Tensor:
+        y = self.bn(x)
+        if residual is not None:
+            y = y + residual
+        return torch.relu_(y) if self.relu else y
+
+
+def _bn(channels: int, relu: bool, fused: bool) -> nn.Module:
+    return FusedBatchNormAct(channels, relu=relu) if fused else TorchBNAct(channels, relu=relu)
+
+
+def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0) -> nn.Conv2d:
+    return nn.Conv2d(cin, cout, k, stride, pad, bias=False)
 
 
 class Bottleneck(nn.Module):
+    """ResNet v1.5 bottleneck (stride on the 3x3). Every BatchNorm carries its ReLU, and the last one
+    also the residual add, so a block is 3-4 convolutions + 3-4 fused normalisation passes."""
+
     expansion = 4
 
-    def __init__(self, cin: int, width: int, stride: int):
+    def __init__(self, cin: int, width: int, stride: int, fused: bool = True):
         super().__init__()
         cout = width * self.expansion
-        self.body = nn.Sequential(
-            *_conv_bn(cin, width, 1), nn.ReLU(inplace=True),
-            *_conv_bn(width, width, 3, stride, 1), nn.ReLU(inplace=True),     # v1.5: stride on 3x3
-            *_conv_bn(width, cout, 1))
-        self.down = None
+        self.conv1, self.bn1 = _conv(cin, width, 1), _bn(width, True, fused)
+        self.conv2, self.bn2 = _conv(width, width, 3, stride, 1), _bn(width, True, fused)
+        self.conv3, self.bn3 = _conv(width, cout, 1), _bn(cout, True, fused)
+        self.down_conv = self.down_bn = None
         if stride != 1 or cin != cout:
-            self.down = nn.Sequential(*_conv_bn(cin, cout, 1, stride))
-        self.relu = nn.ReLU(inplace=True)
+            self.down_conv, self.down_bn = _conv(cin, cout, 1, stride), _bn(cout, False, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        idt = x if self.down is None else self.down(x)
-        return self.relu(self.body(x) + idt)
+        idt = x if self.down_conv is None else self.down_bn(self.down_conv(x))
+        out = self.bn1(self.conv1(x))
+        out = self.bn2(self.conv2(out))
+        return self.bn3(self.conv3(out), idt)
 
 
 class ResNet(nn.Module):
-    def __init__(self, depths: Sequence[int], num_classes: int = 1000):
+    def __init__(self, depths: Sequence[int], num_classes: int = 1000, fused: bool = True):
         super().__init__()
-        self.stem = nn.Sequential(*_conv_bn(3, 64, 7, 2, 3), nn.ReLU(inplace=True),
-                                  nn.MaxPool2d(3, 2, 1))
+        self.stem_conv, self.stem_bn = _conv(3, 64, 7, 2, 3), _bn(64, True, fused)
+        self.stem_pool = nn.MaxPool2d(3, 2, 1)
         blocks: List[nn.Module] = []
         cin = 64
         for i, (n, width) in enumerate(zip(depths, (64, 128, 256, 512))):
             for j in range(n):
-                blocks.append(Bottleneck(cin, width, 2 if (j == 0 and i > 0) else 1))
+                blocks.append(Bottleneck(cin, width, 2 if (j == 0 and i > 0) else 1, fused))
                 cin = width * Bottleneck.expansion
         self.blocks = nn.Sequential(*blocks)
         self.pool = nn.AdaptiveAvgPool2d(1)
-        self.fc = TcLinear(cin, num_classes)
+        self.fc = TcLinear(cin, num_classes) if fused else nn.Linear(cin, num_classes)
         for m in self.modules():
             if isinstance(m, nn.Conv2d):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
         for m in self.modules():
             if isinstance(m, Bottleneck):
-                nn.init.zeros_(m.body[-1].weight)       # zero-init last BN of each block
+                nn.init.zeros_(m.bn3.weight)            # zero-init last BN of each block
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.blocks(self.stem(x))
+        x = self.stem_pool(self.stem_bn(self.stem_conv(x)))
+        x = self.blocks(x)
         return self.fc(torch.flatten(self.pool(x), 1))
 
 
-def resnet50(num_classes: int = 1000) -> ResNet:
-    return ResNet((3, 4, 6, 3), num_classes)
+def resnet50(num_classes: int = 1000, fused: bool = True) -> ResNet:
+    return ResNet((3, 4, 6, 3), num_classes, fused)
 
 
-def resnet101(num_classes: int = 1000) -> ResNet:
-    return ResNet((3, 4, 23, 3), num_classes)
+def resnet101(num_classes: int = 1000, fused: bool = True) -> ResNet:
+    return ResNet((3, 4, 23, 3), num_classes, fused)
 
 
-def resnet152(num_classes: int = 1000) -> ResNet:
-    return ResNet((3, 8, 36, 3), num_classes)
+def resnet152(num_classes: int = 1000, fused: bool = True) -> ResNet:
+    return ResNet((3, 8, 36, 3), num_classes, fused)
+
+
+class _TorchLinearAct(nn.Module):
+    def __init__(self, cin: int, cout: int, relu: bool):
+        super().__init__()
+        self.fc, self.relu = nn.Linear(cin, cout), relu
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        y = self.fc(x)
+        return torch.relu_(y) if self.relu else y
+
+
+def _classifier(cin: int, num_classes: int, fused: bool):
+    """fc6 / fc7 / fc8 of VGG and AlexNet: tcgen05 GEMMs with the bias+ReLU epilogue, or stock
+    nn.Linear + ReLU for the baseline arm."""
+    if fused:
+        return (TcLinear(cin, 4096, act=native.ACT_RELU), TcLinear(4096, 4096, act=native.ACT_RELU),
+                TcLinear(4096, num_classes))
+    return (_TorchLinearAct(cin, 4096, True), _TorchLinearAct(4096, 4096, True),
+            _TorchLinearAct(4096, num_classes, False))
 
 
 _VGG_CFG = {
@@ -87,7 +138,7 @@ _VGG_CFG = {
 class VGG(nn.Module):
     """fc6 (25088x4096) is the 392 MB tensor of core/models.py:9 - the bandwidth-bound bucket."""
 
-    def __init__(self, depth: int, num_classes: int = 1000):
+    def __init__(self, depth: int, num_classes: int = 1000, fused: bool = True):
         super().__init__()
         layers: List[nn.Module] = []
         cin = 3
@@ -98,9 +149,7 @@ class VGG(nn.Module):
                 layers += [nn.Conv2d(cin, v, 3, 1, 1), nn.ReLU(inplace=True)]
                 cin = v
         self.features = nn.Sequential(*layers)
-        self.fc6 = TcLinear(512 * 7 * 7, 4096, act=native.ACT_RELU)
-        self.fc7 = TcLinear(4096, 4096, act=native.ACT_RELU)
-        self.fc8 = TcLinear(4096, num_classes)
+        self.fc6, self.fc7, self.fc8 = _classifier(512 * 7 * 7, num_classes, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         x = self.features(x)
@@ -109,22 +158,22 @@ class VGG(nn.Module):
         return self.fc8(self.fc7(self.fc6(x)))
 
 
-def vgg11(num_classes: int = 1000) -> VGG:
-    return VGG(11, num_classes)
+def vgg11(num_classes: int = 1000, fused: bool = True) -> VGG:
+    return VGG(11, num_classes, fused)
 
 
-def vgg16(num_classes: int = 1000) -> VGG:
-    return VGG(16, num_classes)
+def vgg16(num_classes: int = 1000, fused: bool = True) -> VGG:
+    return VGG(16, num_classes, fused)
 
 
-def vgg19(num_classes: int = 1000) -> VGG:
-    return VGG(19, num_classes)
+def vgg19(num_classes: int = 1000, fused: bool = True) -> VGG:
+    return VGG(19, num_classes, fused)
 
 
 class AlexNet(nn.Module):
     """fc layers 144/64/15.6 MB per core/models.py:11 (9216x4096, 4096x4096, 4096x1000)."""
 
-    def __init__(self, num_classes: int = 1000):
+    def __init__(self, num_classes: int = 1000, fused: bool = True):
         super().__init__()
         self.features = nn.Sequential(
             nn.Conv2d(3, 64, 11, 4, 2), nn.ReLU(inplace=True), nn.MaxPool2d(3, 2),
@@ -132,9 +181,7 @@ class AlexNet(nn.Module):
             nn.Conv2d(192, 384, 3, 1, 1), nn.ReLU(inplace=True),
             nn.Conv2d(384, 256, 3, 1, 1), nn.ReLU(inplace=True),
             nn.Conv2d(256, 256, 3, 1, 1), nn.ReLU(inplace=True), nn.MaxPool2d(3, 2))
-        self.fc6 = TcLinear(256 * 6 * 6, 4096, act=native.ACT_RELU)
-        self.fc7 = TcLinear(4096, 4096, act=native.ACT_RELU)
-        self.fc8 = TcLinear(4096, num_classes)
+        self.fc6, self.fc7, self.fc8 = _classifier(256 * 6 * 6, num_classes, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         x = self.features(x)
@@ -142,5 +189,5 @@ class AlexNet(nn.Module):
         return self.fc8(self.fc7(self.fc6(x)))
 
 
-def alexnet(num_classes: int = 1000) -> AlexNet:
-    return AlexNet(num_classes)
+def alexnet(num_classes: int = 1000, fused: bool = True) -> AlexNet:
+    return AlexNet(num_classes, fused)

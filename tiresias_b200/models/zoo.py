@@ -68,6 +68,15 @@ STAND_IN: Dict[str, str] = {
 }
 
 
+def build(spec: ModelSpec, fused: bool = True) -> nn.Module:
+    """Instantiate ``spec``; ``fused=False`` asks for the stock-PyTorch variant (baseline arm) when the
+    builder has one."""
+    import inspect
+    if "fused" in inspect.signature(spec.build).parameters:
+        return spec.build(fused=fused)
+    return spec.build()
+
+
 def resolve(name: str) -> ModelSpec:
     """Model spec for a trace ``model_name``; unknown names fall back to inception3's stand-in,
     mirroring ``get_model``'s default pick (core/models.py:49-52)."""

@@ -18,6 +18,7 @@ MAX_BUCKETS = 256
 MAX_RING_CTAS = 64
 IPC_HANDLE_BYTES = 64
 FLAG_WORDS = 2 * MAX_BUCKETS * MAX_WORLD + 2 * MAX_RING_CTAS
+BN_SCRATCH_FLOATS = 1024 + 2 * 64 * 1024 + 4 * 4096
 
 F32, BF16 = 0, 1
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
@@ -87,11 +88,17 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_transpose_bf16.argtypes = [vp, vp, C.c_int, C.c_int, st]
     lib.tb200_sumsq_scratch_floats.restype = C.c_size_t
     lib.tb200_sumsq.argtypes = [vp, C.c_int, sz, vp, vp, st]
+    lib.tb200_bn_scratch_floats.restype = C.c_size_t
+    lib.tb200_bn_fwd_train.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_float, C.c_float, vp, vp, vp,
+                                       sz, C.c_int, C.c_int, st]
+    lib.tb200_bn_apply.argtypes = [vp, vp, vp, vp, sz, C.c_int, C.c_int, st]
+    lib.tb200_bn_bwd.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, sz, C.c_int, C.c_int, st]
     for name in ("tb200_symm_alloc", "tb200_symm_free", "tb200_ipc_export", "tb200_ipc_open",
                  "tb200_ipc_close", "tb200_enable_peer_access", "tb200_flags_fill",
                  "tb200_sgd_momentum", "tb200_ps_push_pull", "tb200_step_end", "tb200_allreduce",
                  "tb200_gemm_bf16_nt", "tb200_gemm_reserve", "tb200_gemm_bf16_nt_pull",
-                 "tb200_u8_to_bf16_norm", "tb200_transpose_bf16", "tb200_sumsq"):
+                 "tb200_u8_to_bf16_norm", "tb200_transpose_bf16", "tb200_sumsq", "tb200_bn_fwd_train",
+                 "tb200_bn_apply", "tb200_bn_bwd"):
         getattr(lib, name).restype = C.c_int
 
 

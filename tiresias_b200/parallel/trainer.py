@@ -26,7 +26,7 @@ from typing import Dict, List, Optional, Tuple
 import torch
 from torch import nn
 
-from ..models.zoo import ModelSpec
+from ..models.zoo import ModelSpec, build as zoo_build
 from ..ops import native
 from ..ops.linear import TcLinear
 from .symm import SymmetricWorld
@@ -124,7 +124,8 @@ class Trainer:
 
         torch.manual_seed(seed)           # identical initial weights on every rank
         with torch.device(self.device):
-            self.model = (model if model is not None else spec.build()).to(self.device)
+            # the NCCL arm is the stock-PyTorch network (nn.BatchNorm2d / nn.Linear, cuDNN + cuBLAS)
+            self.model = (model if model is not None else zoo_build(spec, fused=(mode != "nccl"))).to(self.device)
         self.model.train()
         self.buckets, self.total = plan_buckets(
             self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
@@ -219,6 +220,8 @@ class Trainer:
                     self._repoint(p, off)
             # everything that is not a trainable parameter (BN statistics...) follows to bf16
             for mod in self.model.modules():
+                if getattr(mod, "keep_fp32_buffers", False):
+                    continue
                 for name, buf in list(mod._buffers.items()):
                     if buf is not None and buf.is_floating_point():
                         mod._buffers[name] = buf.to(torch.bfloat16)
