@@ -1,0 +1,83 @@
+"""Execution backend without GPUs: buddy placement, the PS/worker protocol on CPU tensors over gloo
+(world_size > 1), the worker pool + real-time controller, preemption and resume, and the simulated-vs-
+executed JCT comparison."""
+import json
+import os
+
+import pytest
+import torch
+
+from tiresias_b200.exec.buddy import BuddyAllocator, all_blocks, normalize_gpus
+
+
+def test_buddy_blocks_and_best_fit():
+    assert normalize_gpus(12, 8) == 8 and normalize_gpus(3, 8) == 2 and normalize_gpus(1, 8) == 1
+    assert len(all_blocks(8)) == 15
+    b = BuddyAllocator(8)
+    one = b.alloc(1, "a")
+    assert one == (0, 1)
+    assert b.alloc(1, "b") == (1, 1)            # packs next to the first single, keeping quads whole
+    assert b.alloc(4, "c") == (4, 4)
+    assert b.alloc(2, "d") == (2, 2)
+    assert b.alloc(4, "e") is None and b.free_gpus() == 0 + 0
+    b.free((4, 4))
+    assert b.can_alloc(4) and not b.can_alloc(8)
+    b.free((0, 1)); b.free((1, 1)); b.free((2, 2))
+    assert b.alloc(8, "f") == (0, 8)
+
+
+def _write_trace(path, jobs):
+    with open(path, "w") as fh:
+        fh.write("job_id,num_gpu,submit_time,iterations,model_name,duration,interval\n")
+        for i, (g, s, it, m) in enumerate(jobs):
+            fh.write(f"{i},{g},{s},{it},{m},10,0\n")
+    return str(path)
+
+
+@pytest.mark.timeout(300)
+def test_replay_fifo_loopback_world2(tmp_path):
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(2, 0, 30, "resnet50"), (1, 0, 20, "vgg16"), (1, 0, 20, "transformer"),
+                                              (4, 1, 10, "resnet50")])
+    res = replay(trace, gpus=2, schedule="fifo", comm="ps", out=str(tmp_path / "o"), loopback=True, step_sleep=0.01)
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert all(r["status"] == "DONE" for r in recs.values())
+    assert recs["3"]["num_gpu"] == 2                         # 4-GPU request clamps to the 2-GPU box
+    assert recs["1"]["start"] >= recs["0"]["end"] - 0.05     # fifo: job 1 waits for the 2-GPU job ahead of it
+    assert res["comparison"]["n"] == 4
+    assert os.path.exists(tmp_path / "o" / "replay.json") and os.path.exists(tmp_path / "o" / "sim" / "jobs.csv")
+
+
+@pytest.mark.timeout(300)
+def test_replay_preempt_and_resume_loopback(tmp_path):
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(2, 0, 200, "resnet50"), (1, 1, 20, "vgg16")])
+    res = replay(trace, gpus=2, schedule="sjf", comm="ps", out=str(tmp_path / "o"), loopback=True, step_sleep=0.01,
+                 check_every=5)
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert recs["0"]["status"] == "DONE" and recs["1"]["status"] == "DONE"
+    assert recs["0"]["preempt"] >= 1 and recs["0"]["attempts"] >= 2      # snapshot, requeue, resume
+    assert recs["1"]["end"] < recs["0"]["end"]
+    log = open(tmp_path / "o" / "controller.log").read()
+    assert "(resume)" in log and "preempt job 0" in log
+
+
+def test_loopback_trainer_matches_single_process_sgd():
+    """world = 1: the PS protocol degenerates to plain SGD with momentum on the flat parameters."""
+    from tiresias_b200.exec.loopback import LoopbackTrainer
+    tr = LoopbackTrainer("resnet50", 0, 1, None, lr=0.05, momentum=0.9)
+    ref = torch.nn.Sequential(torch.nn.Linear(32, 48), torch.nn.ReLU(), torch.nn.Linear(48, 8))
+    ref.load_state_dict(tr.model.state_dict())
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    for _ in range(5):
+        tr.step_resident()
+        opt.zero_grad()
+        torch.nn.functional.cross_entropy(ref(tr.x), tr.y).backward()
+        opt.step()
+    for a, b in zip(tr.model.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=1e-6)
+    state = tr.state_dict()
+    tr2 = LoopbackTrainer("resnet50", 0, 1, None, seed=5)
+    tr2.load_state_dict(state)
+    for a, b in zip(tr2.model.parameters(), tr.model.parameters()):
+        assert torch.equal(a, b)

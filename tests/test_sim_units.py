@@ -295,3 +295,20 @@ def test_execute_builds_reference_argv():
     assert argv[-2:] == ["--log_path", os.path.join("nodes_p_s32_job_month", "horus+_horus+")]
     assert "--enable_migration" in argv and DEFAULT_CONFIGS == [("horus+", "horus+", 3), ("horus+", "horus+", 4),
                                                                  ("horus+", "horus+", 5)]
+
+
+def test_calibrated_mode_makes_interference_real(tmp_path):
+    """Parity mode keeps the reference's inert interference; calibrated mode stretches co-located tasks by
+    the measured factor, so a packed trace finishes later."""
+    import json as _json
+    from tiresias_b200.cli.run_sim import run
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    cal = tmp_path / "cal.json"
+    cal.write_text(_json.dumps({"interference_factor": 0.5}))
+    base = ["--trace_file", os.path.join(gold, "t64_horus_horus.trace.csv"), "--num_switch", "2", "--num_node_p_switch", "2",
+            "--num_gpu_p_node", "4", "--scheme", "horus", "--schedule", "horus", "--seed", "1", "--quiet"]
+    f1 = define_simulator_flags(); f1.parse(base)
+    s1 = run(f1, output_dir=str(tmp_path / "parity"))
+    f2 = define_simulator_flags(); f2.parse(base + ["--mode", "calibrated", "--calibration", str(cal)])
+    s2 = run(f2, output_dir=str(tmp_path / "cal"))
+    assert s2["avg_jct"] > s1["avg_jct"]

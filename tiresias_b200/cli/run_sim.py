@@ -112,6 +112,8 @@ def _run_tick(flags: FlagSet, output_dir: str, rng, calibration) -> Dict:
         reader = tiresias_trace_as_live(flags.trace_file)
     jq = JobQueueManager(flags, flags.trace_file)
     jm = JobsManager(flags, jq, rng=rng, trace_reader=reader)
+    if calibration and calibration.get("interference_factor") is not None and flags.mode == "calibrated":
+        jm.set_interference_factor(float(calibration["interference_factor"]), infrastructure)
     sched = Scheduler(infrastructure, jm, log_manager, enable_migration=flags.enable_migration,
                       calibration=calibration)
     try:

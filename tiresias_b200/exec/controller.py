@@ -1,0 +1,205 @@
+"""Real-time scheduler of the execution backend.
+
+Replays a README-schema trace (``job_id, num_gpu, submit_time, iterations, model_name, duration``) against
+the worker pool: jobs arrive at ``submit_time * time_scale`` seconds of wall clock, a policy decides what
+runs on which GPU block, finished / preempted jobs report back through the store. Policies mirror the
+simulator's (tiresias_b200.sim.legacy.schedulers):
+
+``fifo``      non-preemptive; waiting jobs are tried in arrival order until the first that does not fit
+``sjf``       preemptive, fewest GPUs first
+``shortest``  preemptive, least remaining iterations first
+``dlas-gpu``  preemptive two-level (or more) MLFQ on attained GPU-seconds with ``queue_limit`` thresholds
+
+Preemption is executable here (the reference only flips a flag, core/jobs/jobs_manager.py:150-173): the
+job's ranks snapshot their PS shards and the job later resumes from the iteration it reached, possibly on
+other GPUs.
+"""
+from __future__ import annotations
+
+import json
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+from .buddy import Block, BuddyAllocator, normalize_gpus
+
+
+@dataclass
+class ExecJob:
+    job_id: str
+    model: str
+    gpus: int
+    iters: int
+    submit: float                      # seconds after replay start
+    batch: int
+    status: str = "WAITING"            # WAITING | RUNNING | PREEMPTING | DONE | FAILED
+    done: int = 0
+    attempt: int = 0
+    block: Optional[Block] = None
+    first_start: Optional[float] = None
+    last_start: Optional[float] = None
+    end: Optional[float] = None
+    attained: float = 0.0              # seconds of service received (all attempts)
+    preempt: int = 0
+    q_id: int = 0
+    results: List[Dict] = field(default_factory=list)
+
+    def jct(self) -> Optional[float]:
+        return None if self.end is None else self.end - self.submit
+
+
+class Controller:
+    def __init__(self, store, num_gpus: int, rows: Sequence[Dict], policy: str = "fifo", comm: str = "ps",
+                 batch: int = 32, time_scale: float = 1.0, ckpt_dir: str = "/dev/shm/tb200_ckpt",
+                 queue_limit: Sequence[float] = (20.0,), check_every: int = 10, poll_s: float = 0.02,
+                 job_timeout_s: float = 600.0, step_sleep: float = 0.0, graph: bool = True, log=print):
+        self.store, self.num_gpus, self.policy, self.comm = store, num_gpus, policy, comm
+        self.time_scale, self.ckpt_dir, self.check_every, self.poll_s = time_scale, ckpt_dir, check_every, poll_s
+        self.queue_limit = list(queue_limit)
+        self.job_timeout_s, self.step_sleep, self.graph = job_timeout_s, step_sleep, graph
+        self.log = log
+        self.alloc = BuddyAllocator(num_gpus)
+        self.seq = [0] * num_gpus
+        self.jobs: List[ExecJob] = []
+        for r in sorted(rows, key=lambda x: (x["submit_time"], x["job_id"])):
+            self.jobs.append(ExecJob(str(r["job_id"]), r.get("model_name") or "resnet50",
+                                     normalize_gpus(r["num_gpu"], num_gpus), max(1, int(r["iterations"])),
+                                     float(r["submit_time"]) * time_scale, int(r.get("batch") or batch)))
+        self.t0 = 0.0
+
+    # -- pool plumbing -------------------------------------------------------------------------------
+    def wait_ready(self, timeout_s: float = 600.0) -> None:
+        self.store.wait([f"ready/{r}" for r in range(self.num_gpus)], __import__("datetime").timedelta(seconds=timeout_s))
+
+    def _send(self, rank: int, cmd: Dict) -> None:
+        self.store.set(f"cmd/{rank}/{self.seq[rank]}", json.dumps(cmd))
+        self.seq[rank] += 1
+
+    def shutdown(self) -> None:
+        for r in range(self.num_gpus):
+            self._send(r, {"op": "exit"})
+
+    def _start(self, job: ExecJob, now: float) -> bool:
+        blk = self.alloc.alloc(job.gpus, job.job_id)
+        if blk is None:
+            return False
+        job.block, job.status, job.last_start = blk, "RUNNING", now
+        if job.first_start is None:
+            job.first_start = now
+        cmd = {"op": "run", "job": job.job_id, "attempt": job.attempt, "model": job.model, "batch": job.batch,
+               "iters": job.iters, "done": job.done, "mode": self.comm, "block": list(blk),
+               "resume": job.attempt > 0, "ckpt_dir": self.ckpt_dir, "check_every": self.check_every,
+               "step_sleep": self.step_sleep, "graph": self.graph}
+        for r in range(blk[0], blk[0] + blk[1]):
+            self._send(r, cmd)
+        self.log(f"[{now:8.2f}s] start job {job.job_id} ({job.model}, {job.gpus} GPU, it {job.done}/{job.iters}) "
+                 f"on GPUs {blk[0]}..{blk[0] + blk[1] - 1}" + (" (resume)" if job.attempt else ""))
+        return True
+
+    def _request_preempt(self, job: ExecJob, now: float) -> None:
+        if job.status == "RUNNING":
+            self.store.set(f"preempt/{job.job_id}/{job.attempt}", "1")
+            job.status = "PREEMPTING"
+            self.log(f"[{now:8.2f}s] preempt job {job.job_id}")
+
+    def _collect(self, now: float) -> bool:
+        """Fold in results of attempts whose ranks have all reported. Returns True if anything changed."""
+        changed = False
+        for job in self.jobs:
+            if job.status not in ("RUNNING", "PREEMPTING"):
+                continue
+            keys = [f"res/{job.job_id}/{job.attempt}/{r}" for r in range(job.gpus)]
+            if not self.store.check(keys):
+                if now - job.last_start > self.job_timeout_s:           # watchdog
+                    job.status, job.end = "FAILED", now
+                    self.alloc.free(job.block)
+                    changed = True
+                    self.log(f"[{now:8.2f}s] job {job.job_id} timed out")
+                continue
+            res = [json.loads(self.store.get(k)) for k in keys]
+            job.results.append({"attempt": job.attempt, "block": list(job.block), "ranks": res,
+                                "t_start": job.last_start, "t_end": now})
+            self.alloc.free(job.block)
+            job.attained += now - job.last_start
+            job.block = None
+            changed = True
+            if any(r["status"] == "failed" for r in res):
+                job.status, job.end = "FAILED", now
+                self.log(f"[{now:8.2f}s] job {job.job_id} FAILED: {[r.get('error') for r in res if r['status'] == 'failed'][:1]}")
+            elif all(r["status"] == "done" for r in res):
+                job.status, job.end, job.done = "DONE", now, job.iters
+                self.log(f"[{now:8.2f}s] job {job.job_id} done (JCT {job.jct():.2f}s, {res[0]['iter_ms']:.2f} ms/iter)")
+            else:
+                job.done = min(r["done"] for r in res)
+                job.status = "WAITING"
+                job.attempt += 1
+                job.preempt += 1
+        return changed
+
+    # -- policies -------------------------------------------------------------------------------------------
+    def _schedule(self, now: float) -> None:
+        arrived = [j for j in self.jobs if j.submit <= now]
+        waiting = [j for j in arrived if j.status == "WAITING"]
+        running = [j for j in arrived if j.status in ("RUNNING", "PREEMPTING")]
+        if self.policy == "fifo":
+            for j in waiting:
+                if not self._start(j, now):
+                    break
+            return
+        # preemptive family: rank all runnable jobs, give GPUs by counting in that order
+        runnable = waiting + running
+        if self.policy == "sjf":
+            runnable.sort(key=lambda j: (j.gpus, j.submit))
+        elif self.policy == "shortest":
+            runnable.sort(key=lambda j: (j.iters - j.done, j.submit))
+        elif self.policy == "dlas-gpu":
+            for j in runnable:
+                served = (j.attained + (now - j.last_start if j.status == "RUNNING" else 0.0)) * j.gpus
+                while j.q_id < len(self.queue_limit) and served >= self.queue_limit[j.q_id]:
+                    j.q_id += 1
+            runnable.sort(key=lambda j: (j.q_id, 0 if j.status != "WAITING" else 1, j.submit))
+        else:
+            raise NotImplementedError(self.policy)
+        free = self.num_gpus
+        chosen = []
+        for j in runnable:
+            if free >= j.gpus:
+                chosen.append(j)
+                free -= j.gpus
+        chosen_ids = {j.job_id for j in chosen}
+        for j in running:
+            if j.job_id not in chosen_ids:
+                self._request_preempt(j, now)
+        if any(j.status == "PREEMPTING" for j in running):
+            return                                 # start the winners once the losers have left their GPUs
+        for j in chosen:
+            if j.status == "WAITING":
+                self._start(j, now)
+
+    # -- main loop --------------------------------------------------------------------------------------------
+    def run(self) -> List[ExecJob]:
+        self.t0 = time.time()
+        last_decision = -1.0
+        while any(j.status not in ("DONE", "FAILED") for j in self.jobs):
+            now = time.time() - self.t0
+            changed = self._collect(now)
+            due = any(j.status == "WAITING" and j.submit <= now for j in self.jobs)
+            if changed or (due and now - last_decision >= self.poll_s) or self.policy == "dlas-gpu":
+                self._schedule(now)
+                last_decision = now
+            time.sleep(self.poll_s)
+        return self.jobs
+
+    def records(self) -> List[Dict]:
+        out = []
+        for j in self.jobs:
+            iter_ms = [r["ranks"][0].get("iter_ms") for r in j.results if r["ranks"][0].get("iter_ms")]
+            startup = [max(x.get("startup_s", 0.0) for x in r["ranks"]) for r in j.results]
+            out.append({"job_id": j.job_id, "model": j.model, "num_gpu": j.gpus, "iterations": j.iters,
+                        "submit": j.submit, "start": j.first_start, "end": j.end, "jct": j.jct(),
+                        "status": j.status, "preempt": j.preempt, "attempts": len(j.results),
+                        "iter_ms": sum(iter_ms) / len(iter_ms) if iter_ms else None,
+                        "startup_s": sum(startup) / len(startup) if startup else None,
+                        "snapshot_s": max([x.get("snapshot_s", 0.0) for r in j.results for x in r["ranks"]] or [0.0]),
+                        "peak_mem_bytes": max([x.get("peak_mem_bytes", 0) for r in j.results for x in r["ranks"]] or [0])})
+        return out

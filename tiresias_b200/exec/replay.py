@@ -1,0 +1,212 @@
+"""Replay a trace on the real box and compare with the simulator (BASELINE.json config 5).
+
+    python -m tiresias_b200.exec.replay --trace trace.csv --gpus 8 --schedule fifo --comm ring \
+        --calibration calibration.json --out replay_out
+
+1. starts the worker pool (one process per GPU, :mod:`tiresias_b200.exec.worker`) and a TCPStore,
+2. lets :class:`tiresias_b200.exec.controller.Controller` run the trace in real time,
+3. simulates the same trace with the event engine on a 1 x 1 x G cluster (``--scheme count``), job
+   durations = ``startup + iterations * iteration time`` taken from the calibration file (or, with
+   ``--self-calibrate``, from this replay's own per-(model, GPUs) averages),
+4. writes ``replay.json`` with per-job executed vs simulated JCT and the error summary.
+
+``--loopback`` runs the whole thing on CPU tensors over gloo (tests / machines without GPUs).
+"""
+from __future__ import annotations
+
+import argparse
+import datetime
+import json
+import os
+import socket
+import subprocess
+import sys
+import tempfile
+import time
+from typing import Dict, List, Optional, Sequence
+
+import torch.distributed as dist
+
+from ..sim.trace import read_tiresias_trace
+from .controller import Controller
+
+MS = 1000.0
+SIM_SCHEDULE = {"fifo": "fjf", "sjf": "sjf", "shortest": "shortest", "dlas-gpu": "dlas-gpu"}
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def start_pool(gpus: int, ctl_port: int, loopback: bool, with_nccl: bool, log_path: str) -> subprocess.Popen:
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={gpus}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), "-m", "tiresias_b200.exec.worker",
+           "--ctl-port", str(ctl_port)]
+    if loopback:
+        cmd.append("--loopback")
+    if with_nccl:
+        cmd.append("--with-nccl")
+    root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    return subprocess.Popen(cmd, cwd=root, env=env, stdout=open(log_path, "w"), stderr=subprocess.STDOUT)
+
+
+def calibration_from_records(records: Sequence[Dict]) -> Dict:
+    acc: Dict[str, Dict[str, List[float]]] = {}
+    start: Dict[str, Dict[str, List[float]]] = {}
+    for r in records:
+        if r["status"] != "DONE" or not r["iter_ms"]:
+            continue
+        acc.setdefault(r["model"], {}).setdefault(str(r["num_gpu"]), []).append(r["iter_ms"] / MS)
+        start.setdefault(r["model"], {}).setdefault(str(r["num_gpu"]), []).append(r["startup_s"] or 0.0)
+    mean = lambda d: {m: {g: sum(v) / len(v) for g, v in per.items()} for m, per in d.items()}  # noqa: E731
+    return {"iter_s": mean(acc), "startup_s": mean(start), "source": "self"}
+
+
+def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:
+    per = (table or {}).get(model)
+    if not per:
+        return default
+    keys = sorted(int(k) for k in per)
+    pick = max([k for k in keys if k <= gpus], default=keys[0])
+    return float(per[str(pick)])
+
+
+def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, gpus: int, schedule: str,
+             queue_limit_s: Sequence[float], out_dir: str) -> Dict[str, Dict]:
+    """Event simulation in milliseconds on a 1 x 1 x ``gpus`` counting cluster."""
+    from ..sim.flags import define_simulator_flags
+    from ..sim.legacy.engine import run_event_simulation
+    by_id = {r["job_id"]: r for r in records}
+    sim_rows = []
+    for row in rows:
+        rec = by_id[str(row["job_id"])]
+        g = rec["num_gpu"]
+        it = _lookup(calibration.get("iter_s"), rec["model"], g, 0.05)
+        st = _lookup(calibration.get("startup_s"), rec["model"], g, 0.0)
+        sim_rows.append({"job_id": row["job_id"], "num_gpu": g, "submit_time": int(round(rec["submit"] * MS)),
+                         "iterations": row["iterations"], "model_name": rec["model"],
+                         "duration": max(1, int(round((st + it * row["iterations"]) * MS))), "interval": 0})
+    flags = define_simulator_flags()
+    argv = ["--schedule", SIM_SCHEDULE[schedule], "--scheme", "count", "--num_switch", "1", "--num_node_p_switch", "1",
+            "--num_gpu_p_node", str(gpus), "--quiet"]
+    if schedule == "dlas-gpu":
+        argv += ["--queue_limit", ",".join(str(int(q * MS)) for q in queue_limit_s)]
+    flags.parse(argv)
+    os.makedirs(out_dir, exist_ok=True)
+    from ..cli.run_sim import _attach_logging
+    from ..sim import util
+    handlers = _attach_logging(out_dir, True)
+    try:
+        run_event_simulation(flags, out_dir, None, rows=sim_rows)
+    finally:
+        for h in handlers:
+            util.logger.removeHandler(h)
+            h.close()
+    import csv
+    with open(os.path.join(out_dir, "jobs.csv")) as fh:
+        return {r["job_id"]: r for r in csv.DictReader(fh)}
+
+
+def compare(records: Sequence[Dict], sim: Dict[str, Dict]) -> Dict:
+    rows, errs = [], []
+    for r in records:
+        s = sim.get(str(r["job_id"]))
+        if r["status"] != "DONE" or s is None:
+            continue
+        sim_jct = float(s["JCT"]) / MS
+        err = (sim_jct - r["jct"]) / r["jct"] * 100.0
+        errs.append(err)
+        rows.append({"job_id": r["job_id"], "model": r["model"], "num_gpu": r["num_gpu"], "exec_jct_s": round(r["jct"], 3),
+                     "sim_jct_s": round(sim_jct, 3), "error_pct": round(err, 2)})
+    n = len(rows)
+    if not n:
+        return {"jobs": [], "n": 0}
+    avg_exec = sum(x["exec_jct_s"] for x in rows) / n
+    avg_sim = sum(x["sim_jct_s"] for x in rows) / n
+    mk_exec = max(r["end"] for r in records if r["end"] is not None)
+    mk_sim = max(float(s["end_time"]) for s in sim.values()) / MS
+    return {"n": n, "avg_jct_exec_s": round(avg_exec, 3), "avg_jct_sim_s": round(avg_sim, 3),
+            "avg_jct_error_pct": round((avg_sim - avg_exec) / avg_exec * 100.0, 2),
+            "mean_abs_job_error_pct": round(sum(abs(e) for e in errs) / n, 2),
+            "makespan_exec_s": round(mk_exec, 3), "makespan_sim_s": round(mk_sim, 3),
+            "makespan_error_pct": round((mk_sim - mk_exec) / mk_exec * 100.0, 2), "jobs": rows}
+
+
+def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out: str = "replay_out",
+           calibration_path: Optional[str] = None, loopback: bool = False, batch: int = 32, time_scale: float = 1.0,
+           queue_limit_s: Sequence[float] = (20.0,), check_every: int = 10, step_sleep: float = 0.0,
+           iters_scale: float = 1.0, graph: bool = True) -> Dict:
+    os.makedirs(out, exist_ok=True)
+    rows = read_tiresias_trace(trace)
+    for r in rows:
+        r["iterations"] = max(1, int(round(r["iterations"] * iters_scale)))
+    port = _free_port()
+    store = dist.TCPStore("127.0.0.1", port, is_master=True, timeout=datetime.timedelta(days=1),
+                          wait_for_workers=False)
+    pool = start_pool(gpus, port, loopback, comm == "nccl", os.path.join(out, "pool.log"))
+    ckpt_dir = tempfile.mkdtemp(prefix="tb200_ckpt_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    log_lines: List[str] = []
+
+    def log(msg: str) -> None:
+        log_lines.append(msg)
+        print(msg, flush=True)
+    ctl = Controller(store, gpus, rows, policy=schedule, comm=comm, batch=batch, time_scale=time_scale,
+                     ckpt_dir=ckpt_dir, queue_limit=queue_limit_s, check_every=check_every, step_sleep=step_sleep,
+                     graph=graph, log=log)
+    try:
+        ctl.wait_ready()
+        t_pool = time.time()
+        ctl.run()
+        wall = time.time() - t_pool
+    finally:
+        ctl.shutdown()
+        try:
+            pool.wait(timeout=120)
+        except subprocess.TimeoutExpired:
+            pool.kill()
+    records = ctl.records()
+    if calibration_path:
+        with open(calibration_path) as fh:
+            calibration = json.load(fh)
+    else:
+        calibration = calibration_from_records(records)
+    sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"))
+    result = {"trace": trace, "gpus": gpus, "schedule": schedule, "comm": comm, "loopback": loopback,
+              "wall_s": round(wall, 2), "calibration_source": calibration.get("source", calibration_path),
+              "records": records, "comparison": compare(records, sim)}
+    with open(os.path.join(out, "replay.json"), "w") as fh:
+        json.dump(result, fh, indent=1)
+    with open(os.path.join(out, "controller.log"), "w") as fh:
+        fh.write("\n".join(log_lines) + "\n")
+    return result
+
+
+def main(argv: Optional[Sequence[str]] = None) -> None:
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("--trace", required=True)
+    ap.add_argument("--gpus", type=int, default=8)
+    ap.add_argument("--schedule", default="fifo", choices=sorted(SIM_SCHEDULE))
+    ap.add_argument("--comm", default="ps", choices=["ps", "ring", "nccl"])
+    ap.add_argument("--out", default="replay_out")
+    ap.add_argument("--calibration", default=None)
+    ap.add_argument("--loopback", action="store_true")
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--time-scale", type=float, default=1.0)
+    ap.add_argument("--iters-scale", type=float, default=1.0)
+    ap.add_argument("--queue-limit", default="20", help="dlas-gpu thresholds in GPU-seconds, comma separated")
+    ap.add_argument("--check-every", type=int, default=10)
+    ap.add_argument("--step-sleep", type=float, default=0.0, help="loopback only: seconds per iteration")
+    ap.add_argument("--no-graph", action="store_true")
+    a = ap.parse_args(list(argv) if argv is not None else None)
+    res = replay(a.trace, a.gpus, a.schedule, a.comm, a.out, a.calibration, a.loopback, a.batch, a.time_scale,
+                 [float(x) for x in a.queue_limit.split(",")], a.check_every, a.step_sleep, a.iters_scale,
+                 not a.no_graph)
+    c = res["comparison"]
+    print(json.dumps({k: v for k, v in c.items() if k != "jobs"}))
+
+
+if __name__ == "__main__":
+    main()

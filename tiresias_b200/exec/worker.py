@@ -1,0 +1,155 @@
+"""Worker pool: one long-lived process per GPU that trains whatever job the controller assigns to it.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node G --master-addr 127.0.0.1 \
+        -m tiresias_b200.exec.worker --ctl-port P [--loopback]
+
+Start-up: NCCL (or gloo with ``--loopback``) world of G ranks, then one *gloo* group per aligned
+power-of-two GPU block (:func:`tiresias_b200.exec.buddy.all_blocks`) — the bootstrap channel over which a
+job's ranks exchange their CUDA-IPC handles (``SymmetricWorld``) and agree on preemption. With
+``--with-nccl`` the same blocks also get NCCL groups for the ``nccl`` baseline mode.
+
+Protocol (a ``TCPStore`` served by the controller):
+  controller -> rank r : key ``cmd/<r>/<seq>`` = JSON {op: run|exit, job, attempt, model, batch, iters,
+                         done, mode, block: [start, size], resume: bool, ckpt_dir, check_every}
+  controller -> job    : key ``preempt/<job>/<attempt>`` (existence = please stop)
+  rank -> controller   : key ``res/<job>/<attempt>/<rank_in_block>`` = JSON result
+
+A run trains ``iters - done`` iterations of the job's model on the block's GPUs with the requested
+communication mode (``ps`` fused push/pull kernels, ``ring`` in-kernel all-reduce, ``nccl`` baseline).
+Every ``check_every`` iterations the ranks agree (max over a gloo all-reduce) whether a preemption was
+requested; if so each rank snapshots its PS shard (fp32 master + momentum) to ``ckpt_dir`` — host memory
+when that is /dev/shm — and reports how far it got. A resumed run loads those shards, on whatever block
+it is given next.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+import traceback
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .buddy import all_blocks
+
+
+def _make_trainer(cmd: Dict, rank_in_block: int, size: int, group, nccl_group, loopback: bool, device):
+    if loopback:
+        from .loopback import LoopbackTrainer
+        return LoopbackTrainer(cmd["model"], rank_in_block, size, group, step_sleep=cmd.get("step_sleep", 0.0))
+    from ..models import zoo
+    from ..parallel.symm import SymmetricWorld
+    from ..parallel.trainer import Trainer
+    spec = zoo.resolve(cmd["model"])
+    world = SymmetricWorld(rank_in_block, size, device, group=group)
+    return Trainer(spec, cmd["batch"], mode=cmd.get("mode", "ps"), world=world, device=device,
+                   use_graph=bool(cmd.get("graph", True)), comm_group=nccl_group,
+                   bucket_mb=float(cmd.get("bucket_mb", 8.0)))
+
+
+def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, device) -> Dict:
+    start, size = cmd["block"]
+    r = rank - start
+    grp = groups[(start, size)]
+    t_begin = time.time()
+    trainer = _make_trainer(cmd, r, size, grp, nccl_groups.get((start, size)), loopback, device)
+    ckpt = os.path.join(cmd["ckpt_dir"], f"{cmd['job']}_{r}.pt")
+    if cmd.get("resume"):
+        trainer.load_state_dict(torch.load(ckpt))
+    if not loopback:
+        from ..models import zoo
+        x, y = zoo.synthetic_batch(zoo.resolve(cmd["model"]), cmd["batch"], seed=rank)
+        trainer.step(x, y)                     # loads the batch; the remaining steps reuse it on the device
+        trainer.loss()
+        done0 = 1
+    else:
+        done0 = 0
+    startup_s = time.time() - t_begin
+    done, iters = int(cmd.get("done", 0)) + done0, int(cmd["iters"])
+    check_every = max(1, int(cmd.get("check_every", 10)))
+    preempt_key = f"preempt/{cmd['job']}/{cmd['attempt']}"
+    t_run = time.time()
+    first = done
+    preempted = False
+    flag = torch.zeros(1, dtype=torch.int32)
+    while done < iters:
+        upto = min(iters, done + check_every)
+        for _ in range(upto - done):
+            trainer.step_resident()
+        done = upto
+        if done < iters:
+            flag[0] = 1 if (r == 0 and store.check([preempt_key])) else 0
+            if size > 1:
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=grp)
+            if int(flag[0]):
+                preempted = True
+                break
+    trainer.synchronize()
+    run_s = time.time() - t_run
+    status = trainer.check_status()
+    snapshot_s = 0.0
+    if preempted:
+        t0 = time.time()
+        os.makedirs(cmd["ckpt_dir"], exist_ok=True)
+        torch.save(trainer.state_dict(), ckpt)
+        snapshot_s = time.time() - t0
+    peak = torch.cuda.max_memory_allocated(device) if (not loopback and torch.cuda.is_available()) else 0
+    loss = trainer.loss()
+    trainer.close()
+    return {"job": cmd["job"], "attempt": cmd["attempt"], "rank": r, "status": "preempted" if preempted else "done",
+            "done": done, "iters_run": done - first, "run_s": run_s, "startup_s": startup_s,
+            "iter_ms": (run_s / max(1, done - first)) * 1e3, "snapshot_s": snapshot_s, "kernel_status": status,
+            "peak_mem_bytes": int(peak), "loss": loss, "t_end": time.time()}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--ctl-port", type=int, required=True)
+    ap.add_argument("--ctl-host", default="127.0.0.1")
+    ap.add_argument("--loopback", action="store_true", help="CPU tensors over gloo (no GPU needed)")
+    ap.add_argument("--with-nccl", action="store_true", help="also build NCCL groups per block (mode nccl)")
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    device = None
+    if args.loopback:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    else:
+        torch.cuda.set_device(local)
+        device = torch.device("cuda", local)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+        from ..ops import native
+        native.lib()
+    groups: Dict[Tuple[int, int], object] = {}
+    nccl_groups: Dict[Tuple[int, int], object] = {}
+    for blk in all_blocks(world):
+        ranks = list(range(blk[0], blk[0] + blk[1]))
+        groups[blk] = dist.new_group(ranks, backend="gloo")
+        if args.with_nccl and not args.loopback and blk[1] > 1:
+            nccl_groups[blk] = dist.new_group(ranks, backend="nccl")
+    store = dist.TCPStore(args.ctl_host, args.ctl_port, is_master=False, timeout=__import__("datetime").timedelta(days=1))
+    store.set(f"ready/{rank}", "1")
+    seq = 0
+    while True:
+        raw = store.get(f"cmd/{rank}/{seq}")              # blocks until the controller posts it
+        seq += 1
+        cmd = json.loads(raw)
+        if cmd["op"] == "exit":
+            break
+        try:
+            res = run_job(cmd, rank, store, groups, nccl_groups, args.loopback, device)
+        except Exception as exc:                             # report instead of dying: the pool survives
+            res = {"job": cmd.get("job"), "attempt": cmd.get("attempt"), "rank": rank - cmd["block"][0],
+                   "status": "failed", "error": f"{type(exc).__name__}: {exc}", "trace": traceback.format_exc()[-1500:],
+                   "t_end": time.time()}
+        store.set(f"res/{cmd['job']}/{cmd['attempt']}/{res['rank']}", json.dumps(res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

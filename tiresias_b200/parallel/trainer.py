@@ -110,7 +110,7 @@ class Trainer:
                  weight_decay: float = 1e-4, bucket_mb: float = 8.0, use_graph: bool = True,
                  pull_gemm: bool = True, pull_min_mb: float = 4.0, comm_ctas: int = 32,
                  spin_budget: int = 50_000_000, seed: int = 0, device: Optional[torch.device] = None,
-                 model: Optional[nn.Module] = None, allreduce_algo: int = 0):
+                 model: Optional[nn.Module] = None, allreduce_algo: int = 0, comm_group=None):
         if mode not in ("ps", "ring", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
         self.spec, self.mode, self.batch_size = spec, mode, batch_size
@@ -120,6 +120,7 @@ class Trainer:
         self.use_graph = use_graph
         self.comm_ctas, self.spin_budget = comm_ctas, spin_budget
         self.allreduce_algo = allreduce_algo
+        self.comm_group = comm_group          # NCCL group of this job's ranks (mode "nccl" only)
         self._lib = native.lib()
 
         torch.manual_seed(seed)           # identical initial weights on every rank
@@ -305,8 +306,8 @@ class Trainer:
         if not hasattr(b, "_shard_grad"):
             b._shard_grad = torch.empty(n, dtype=torch.bfloat16, device=self.device)
             b._shard_param = torch.empty(n, dtype=torch.bfloat16, device=self.device)
-        if dist.is_initialized():
-            dist.reduce_scatter_tensor(b._shard_grad, g, op=dist.ReduceOp.SUM)
+        if dist.is_initialized() and self.world > 1:
+            dist.reduce_scatter_tensor(b._shard_grad, g, op=dist.ReduceOp.SUM, group=self.comm_group)
         else:
             b._shard_grad.copy_(g[:n])
         base = self._shard_base[b.index]
@@ -317,8 +318,8 @@ class Trainer:
         m.add_(v, alpha=-self.lr)
         b._shard_param.copy_(m)
         p = self.param_flat[b.offset: b.offset + b.length]
-        if dist.is_initialized():
-            dist.all_gather_into_tensor(p, b._shard_param)
+        if dist.is_initialized() and self.world > 1:
+            dist.all_gather_into_tensor(p, b._shard_param, group=self.comm_group)
         else:
             p[:n].copy_(b._shard_param)
 

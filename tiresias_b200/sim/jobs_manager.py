@@ -201,4 +201,21 @@ class JobsManager:
         return len(rows)
 
     def prepare_finish_tasks(self, current_time) -> List[Job]:
-        return [j for j in self.running_jobs.values() if not j.time_processed() < j.duration]
+        """Jobs whose furthest task has processed ``duration`` ticks. Parity mode compares against
+        ``Job.duration`` only (as the reference does, which is one reason its interference stretch is
+        inert); calibrated mode honours the per-task durations that co-location has stretched."""
+        if not self.apply_interference:
+            return [j for j in self.running_jobs.values() if not j.time_processed() < j.duration]
+        out = []
+        for j in self.running_jobs.values():
+            need = max([j.duration] + [t.duration for t in j.tasks.values()])
+            if not j.time_processed() < need:
+                out.append(j)
+        return out
+
+    def set_interference_factor(self, factor: float, infrastructure=None) -> None:
+        """Replace the reference's constant 0.2 (infra/interference.py:1) by a measured slowdown."""
+        self.interference_factor = factor
+        if infrastructure is not None:
+            for node in infrastructure.nodes.values():
+                node.interference_factor = factor
