@@ -66,6 +66,8 @@ class Controller:
                                      normalize_gpus(r["num_gpu"], num_gpus), max(1, int(r["iterations"])),
                                      float(r["submit_time"]) * time_scale, int(r.get("batch") or batch)))
         self.t0 = 0.0
+        self.pending: List[ExecJob] = []           # fifo: arrived, could not start yet
+        self.seen: set = set()
 
     # -- pool plumbing -------------------------------------------------------------------------------
     def wait_ready(self, timeout_s: float = 600.0) -> None:
@@ -142,9 +144,22 @@ class Controller:
         waiting = [j for j in arrived if j.status == "WAITING"]
         running = [j for j in arrived if j.status in ("RUNNING", "PREEMPTING")]
         if self.policy == "fifo":
-            for j in waiting:
-                if not self._start(j, now):
+            # the simulator's sim_job_events (reference run_sim.py:1533-1599), statement for statement:
+            # pending jobs first, in list order, until one does not fit (removing the started job from the
+            # list being iterated skips its successor for this event, as there); then the new arrivals,
+            # which start at once if they fit and pend otherwise; finally pending is sorted by num_gpu.
+            for j in self.pending:
+                if self._start(j, now):
+                    self.pending.remove(j)
+                else:
                     break
+            for j in waiting:
+                if j.job_id in self.seen:
+                    continue
+                self.seen.add(j.job_id)
+                if j.status == "WAITING" and not self._start(j, now):
+                    self.pending.append(j)
+            self.pending.sort(key=lambda j: j.gpus)
             return
         # preemptive family: rank all runnable jobs, give GPUs by counting in that order
         runnable = waiting + running
@@ -178,15 +193,17 @@ class Controller:
 
     # -- main loop --------------------------------------------------------------------------------------------
     def run(self) -> List[ExecJob]:
+        """Decisions are taken at the simulator's event instants only — a job arrives, or an attempt
+        ends — plus, for dlas-gpu, on every poll (queue demotions happen between events)."""
         self.t0 = time.time()
-        last_decision = -1.0
+        announced: set = set()
         while any(j.status not in ("DONE", "FAILED") for j in self.jobs):
             now = time.time() - self.t0
             changed = self._collect(now)
-            due = any(j.status == "WAITING" and j.submit <= now for j in self.jobs)
-            if changed or (due and now - last_decision >= self.poll_s) or self.policy == "dlas-gpu":
+            arrivals = [j for j in self.jobs if j.submit <= now and j.job_id not in announced]
+            announced.update(j.job_id for j in arrivals)
+            if changed or arrivals or self.policy == "dlas-gpu":
                 self._schedule(now)
-                last_decision = now
             time.sleep(self.poll_s)
         return self.jobs
 

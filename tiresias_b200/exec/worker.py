@@ -106,6 +106,19 @@ def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, de
             "peak_mem_bytes": int(peak), "loss": loss, "t_end": time.time()}
 
 
+def _warm_up(device) -> None:
+    """Pay the one-off costs (CUDA context, cuDNN / cuBLAS handles, allocator pools) before the first job,
+    so that every job's start-up time is the same few tens of milliseconds."""
+    x = torch.randn(8, 16, 32, 32, device=device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    conv = torch.nn.Conv2d(16, 16, 3, padding=1).to(device).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    y = conv(x)
+    y.float().sum().backward()
+    a = torch.randn(256, 256, device=device, dtype=torch.bfloat16)
+    (a @ a).sum().item()
+    torch.nn.functional.scaled_dot_product_attention(a.view(1, 4, 256, 64), a.view(1, 4, 256, 64), a.view(1, 4, 256, 64))
+    torch.cuda.synchronize(device)
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--ctl-port", type=int, required=True)
@@ -124,6 +137,7 @@ def main() -> None:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
         from ..ops import native
         native.lib()
+        _warm_up(device)
     groups: Dict[Tuple[int, int], object] = {}
     nccl_groups: Dict[Tuple[int, int], object] = {}
     for blk in all_blocks(world):

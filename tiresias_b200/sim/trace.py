@@ -204,6 +204,11 @@ class JobGenerator:
 
 # ---- README schema ---------------------------------------------------------------------------------
 
+def _int_or_float(text: str):
+    v = float(text)
+    return int(v) if v == int(v) else v
+
+
 def read_tiresias_trace(path: str) -> List[dict]:
     """Rows of a README-schema trace as dicts with typed values. ``*.csv`` is comma-delimited,
     ``*.txt`` space-delimited (README.md:17-25)."""
@@ -220,7 +225,7 @@ def read_tiresias_trace(path: str) -> List[dict]:
             rows.append({
                 "job_id": int(float(row["job_id"])),
                 "num_gpu": int(float(row["num_gpu"])),
-                "submit_time": int(float(row["submit_time"])),
+                "submit_time": _int_or_float(row["submit_time"]),
                 "iterations": int(float(row.get("iterations") or 0)),
                 "model_name": row.get("model_name") or "",
                 "duration": int(float(row["duration"])),
