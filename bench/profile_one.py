@@ -16,18 +16,27 @@ from tiresias_b200.ops import native  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "sgd", "push", "step"])
+    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn"])
     args = ap.parse_args()
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
     prof = torch.cuda.cudart()
-    if args.kernel in ("gemm", "gemm_splitk"):
-        m, n, k = (8192, 8192, 8192) if args.kernel == "gemm" else (64, 4096, 25088)
+    if args.kernel in ("gemm", "gemm_splitk", "gemm_smallk"):
+        m, n, k = {"gemm": (8192, 8192, 8192), "gemm_splitk": (64, 4096, 25088), "gemm_smallk": (8192, 2048, 512)}[args.kernel]
         a = torch.randn(m, k, device=dev).to(torch.bfloat16)
         b = (torch.randn(n, k, device=dev) / k ** 0.5).to(torch.bfloat16)
         bias = torch.randn(n, device=dev)
         o = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
         run = lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o)  # noqa: E731
+    elif args.kernel == "bn":
+        from tiresias_b200.ops.batchnorm import fused_bn_act
+        x = torch.randn(64, 256, 56, 56, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+        res = torch.randn_like(x).requires_grad_(True)
+        gamma = torch.ones(256, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        beta = torch.zeros(256, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        rm, rv = torch.zeros(256, device=dev), torch.ones(256, device=dev)
+        dy = torch.randn_like(x)
+        run = lambda: fused_bn_act(x, gamma, beta, rm, rv, res, True).backward(dy)  # noqa: E731
     elif args.kernel == "sgd":
         n = 25 << 20
         master, mom = torch.randn(n, device=dev), torch.zeros(n, device=dev)

@@ -42,7 +42,13 @@ struct Cfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = kAccumStages * BLOCK_N;  // 512 or 256 (power of two)
   static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages) * 8 + 16;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // + align slack
+  // Epilogue staging: per epilogue warp two 32-row x 128-byte tiles (swizzle-128B), TMA-stored.
+  static constexpr int kEpiTileBytes = 32 * 128;
+  static constexpr int kEpiBytes = 4 * 2 * kEpiTileBytes;
+  static constexpr int kEpiBiasBytes = kAccumStages * 256 * 4;   // the tile's bias row, per accumulator stage
+  static constexpr int kSmemBytes =
+      kStages * kStageBytes + kEpiBytes + kEpiBiasBytes + kBarrierBytes;
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
@@ -80,6 +86,23 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sm
                                              int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
                "r"(smem_src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t smem_src, int c0,
+                                             int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+               "r"(smem_src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+// Make generic-proxy shared-memory writes visible to the async proxy (TMA) before a bulk store.
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read_1() {
+  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
+__device__ __forceinline__ void st_shared_16(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -164,6 +187,7 @@ struct GemmParams {
   int bias_dtype;
   int d_dtype;
   int act;
+  int direct_store;   // 1: per-thread global stores (row stride not 16-byte aligned); 0: TMA store
   // pull variant
   int rows_per_rank;
   int world;
@@ -180,18 +204,83 @@ struct PullMaps {
   CUtensorMap b_local;             // this rank's full B, written by the gather-store warp
 };
 
+// Epilogue of one 32-row slice of an accumulator tile (one epilogue warp): per 128 output bytes per row
+// (64 bf16 or 32 fp32 columns) TMEM -> registers, + bias (the tile's bias row sits in shared memory, loaded
+// by the epilogue warps while the tile's MMAs were still running; every lane reads it with broadcast
+// 16-byte loads), activation, pack, swizzled st.shared, TMA store.
+template <int BLOCK_N, int ACT, bool BIAS, bool F32>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* map_d, uint32_t tcol,
+                                              uint32_t bufs, uint32_t tile_bytes, int& epi_buf, float* bias_s,
+                                              int row0, int col_base, int ks, int lane) {
+  constexpr int kCols = F32 ? 32 : 64;
+  if (row0 >= p.M) return;
+  const uint32_t swz = (uint32_t)(lane & 7);
+#pragma unroll 1
+  for (int c = 0; c < BLOCK_N / kCols; ++c) {
+    const int col0 = col_base + c * kCols;
+    if (col0 >= p.N) break;
+    uint32_t r[kCols];
+    tc_ld_32x32(tcol + c * kCols, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+    if constexpr (!F32) tc_ld_32x32(tcol + c * kCols + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+    tc_ld_wait();
+#pragma unroll
+    for (int q = 0; q < kCols / 4; ++q) {
+      float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+      if constexpr (BIAS) b = *reinterpret_cast<const float4*>(bias_s + c * kCols + 4 * q);
+      float x0 = __uint_as_float(r[4 * q]) + b.x, x1 = __uint_as_float(r[4 * q + 1]) + b.y;
+      float x2 = __uint_as_float(r[4 * q + 2]) + b.z, x3 = __uint_as_float(r[4 * q + 3]) + b.w;
+      if constexpr (ACT == 1) {
+        x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f);
+      } else if constexpr (ACT == 2) {
+        x0 = apply_act(x0, 2); x1 = apply_act(x1, 2); x2 = apply_act(x2, 2); x3 = apply_act(x3, 2);
+      }
+      r[4 * q] = __float_as_uint(x0); r[4 * q + 1] = __float_as_uint(x1);
+      r[4 * q + 2] = __float_as_uint(x2); r[4 * q + 3] = __float_as_uint(x3);
+    }
+    const uint32_t buf = bufs + (uint32_t)epi_buf * tile_bytes;
+    if (lane == 0) tma_store_wait_read_1();            // the store that last used this buffer is done
+    __syncwarp();
+    const uint32_t row_addr = buf + (uint32_t)lane * 128u;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {                      // eight 16-byte units per 128-byte row
+      uint4 o;
+      if constexpr (F32) {
+        o = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+      } else {
+        o.x = pack_bf16(__uint_as_float(r[8 * q]), __uint_as_float(r[8 * q + 1]));
+        o.y = pack_bf16(__uint_as_float(r[8 * q + 2]), __uint_as_float(r[8 * q + 3]));
+        o.z = pack_bf16(__uint_as_float(r[8 * q + 4]), __uint_as_float(r[8 * q + 5]));
+        o.w = pack_bf16(__uint_as_float(r[8 * q + 6]), __uint_as_float(r[8 * q + 7]));
+      }
+      st_shared_16(row_addr + (((uint32_t)q ^ swz) << 4), o);
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      if (p.splits > 1) tma_store_3d(map_d, buf, col0, row0, ks);
+      else tma_store_2d(map_d, buf, col0, row0);
+      tma_store_commit();
+    }
+    epi_buf ^= 1;
+  }
+}
+
 template <int BLOCK_N, bool kPull>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                     const __grid_constant__ CUtensorMap map_b,
+                    const __grid_constant__ CUtensorMap map_d,
                     const __grid_constant__ PullMaps pull, const GemmParams p) {
   using C = Cfg<BLOCK_N>;
-  extern __shared__ uint8_t smem_raw[];
-  // SWIZZLE_128B tiles need 1024-byte alignment.
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // SWIZZLE_128B tiles need 1024-byte alignment (the kernel has no static shared memory, so the
+  // dynamic segment starts at the CTA's 1024-byte aligned shared-memory base).
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = smem_u32(smem_raw);
   const uint32_t a_smem = smem_base;
   const uint32_t b_smem = smem_base + C::kStages * C::kABytes;
-  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  const uint32_t epi_smem = smem_base + C::kStages * C::kStageBytes;   // 1024-byte aligned
+  const uint32_t epi_bias_smem = epi_smem + C::kEpiBytes;
+  const uint32_t bar_base = epi_bias_smem + C::kEpiBiasBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + s); };
@@ -206,6 +295,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_d) : "memory");
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < C::kStages; ++s) {
@@ -323,14 +413,54 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     const int ew = warp - 4;  // == warp % 4: the TMEM lane quarter this warp may touch
     int as = 0;
     uint32_t aphase = 0;
+    int epi_buf = 0;
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       const int ks = it % p.splits;
       const int tile = it / p.splits;
       const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      if (p.bias && p.splits == 1 && !p.direct_store) {
+        // Stage this tile's bias row (fp32) before waiting for the accumulator: the loads overlap the
+        // MMAs. Buffer `as` was last read two tiles ago; the barrier of the tile in between orders it.
+        float* bt = reinterpret_cast<float*>(smem_raw + (epi_bias_smem - smem_u32(smem_raw))) + as * 256;
+        for (int j = threadIdx.x - 128; j < BLOCK_N; j += 128) {
+          const int col = n_blk * BLOCK_N + j;
+          bt[j] = col < p.N ? load_bias(p.bias, p.bias_dtype, col) : 0.f;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");     // the four epilogue warps only
+      }
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const int row = m_blk * BLOCK_M + ew * 32 + lane;
       const bool row_ok = row < p.M;
+      if (!p.direct_store) {
+        // ---- TMEM -> registers -> swizzled smem tile -> TMA store (coalesced, clipped at M / N) ----
+        const int row0 = m_blk * BLOCK_M + ew * 32;
+        const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
+        const uint32_t bufs = epi_smem + (uint32_t)(ew * 2) * C::kEpiTileBytes;
+        float* bias_s = reinterpret_cast<float*>(smem_raw + (epi_bias_smem - smem_u32(smem_raw))) + as * 256;
+        const int col_base = n_blk * BLOCK_N;
+        // One compact instruction stream per (activation, bias, output type): the element loop must not
+        // carry per-element branches (a first version did and was instruction-fetch bound).
+        const int variant = (p.splits > 1) ? 12 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0));
+        switch (variant) {
+#define TB_EPI(ID, ACT, BIAS, F32)                                                                        \
+  case ID:                                                                                                \
+    epilogue_tile<BLOCK_N, ACT, BIAS, F32>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf, bias_s, row0, \
+                                           col_base, ks, lane);                                           \
+    break;
+          TB_EPI(0, 0, false, false) TB_EPI(1, 0, false, true) TB_EPI(2, 0, true, false) TB_EPI(3, 0, true, true)
+          TB_EPI(4, 1, false, false) TB_EPI(5, 1, false, true) TB_EPI(6, 1, true, false) TB_EPI(7, 1, true, true)
+          TB_EPI(8, 2, false, false) TB_EPI(9, 2, false, true) TB_EPI(10, 2, true, false) TB_EPI(11, 2, true, true)
+          TB_EPI(12, 0, false, true)
+#undef TB_EPI
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(as));
+        if (++as == kAccumStages) { as = 0; aphase ^= 1; }
+        continue;
+      }
+
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t r[32];
@@ -393,6 +523,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       if (lane == 0) mbar_arrive(tempty_bar(as));
       if (++as == kAccumStages) { as = 0; aphase ^= 1; }
     }
+    if (lane == 0) tma_store_wait_all();     // smem must outlive the last bulk stores
   }
 
   tc_fence_before();
@@ -456,6 +587,25 @@ int make_map(CUtensorMap* out, const void* base, int rows, int cols, int box_row
   return 0;
 }
 
+// Output tensor map for the epilogue's TMA stores: rows of `cols` elements, box = 32 rows x 128 bytes,
+// 128-byte swizzle. `planes` > 1 adds a third dimension (split-K partial planes of M x N fp32).
+int make_out_map(CUtensorMap* out, const void* base, int rows, int cols, bool f32, int planes) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail("cuTensorMapEncodeTiled entry point not available%s");
+  const cuuint64_t esz = f32 ? 4 : 2;
+  cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)planes};
+  cuuint64_t strides[2] = {(cuuint64_t)cols * esz, (cuuint64_t)cols * esz * (cuuint64_t)rows};
+  cuuint32_t box[3] = {(cuuint32_t)(128 / esz), 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  const int rank = planes > 1 ? 3 : 2;
+  CUresult r = enc(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled (output) failed (%s code %ld)", "", (long)r);
+  return 0;
+}
+
 struct Workspace {
   float* ptr = nullptr;
   size_t bytes = 0;
@@ -493,7 +643,7 @@ int get_workspace(size_t bytes, float** out) {
 }
 
 template <int BLOCK_N, bool kPull>
-int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const PullMaps& pull,
+int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const PullMaps& pull,
                 const GemmParams& p, int grid, cudaStream_t stream) {
   using C = Cfg<BLOCK_N>;
   auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull>;
@@ -502,14 +652,15 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const PullMaps& pu
     TB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     configured = true;
   }
-  kern<<<grid, kGemmThreads, C::kSmemBytes, stream>>>(ma, mb, pull, p);
+  kern<<<grid, kGemmThreads, C::kSmemBytes, stream>>>(ma, mb, md, pull, p);
   return launched();
 }
 
 int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_per_rank,
                 const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M,
                 int N, int K, int d_dtype, int act, const uint32_t* epoch_dev, int* status_dev,
-                unsigned long long budget, cudaStream_t stream) {
+                unsigned long long budget, cudaStream_t stream, float* fixed_scratch = nullptr,
+                size_t fixed_scratch_bytes = 0) {
   const bool pull = world != nullptr;
   if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
   if (K % 8) return fail("tb200_gemm: K %s(%ld) must be a multiple of 8", "", K);
@@ -550,10 +701,35 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   }
   p.splits = splits;
   if (splits > 1) {
-    if (int rc = get_workspace((size_t)splits * M * N * sizeof(float), &p.partials)) return rc;
+    const size_t need = (size_t)splits * M * N * sizeof(float);
+    if (fixed_scratch) {
+      // allocation-free entry point: the partial sums must fit the caller's fixed scratch. Every partial
+      // the reduction reads is written by this call's GEMM first, so nothing has to be cleared.
+      if (need > fixed_scratch_bytes) {
+        snprintf(g_last_error, sizeof(g_last_error),
+                 "tb200_gemm_bf16_nt_noalloc: M=%d N=%d K=%d needs %zu bytes of split-K scratch "
+                 "(%d splits) but the built-in scratch is %zu bytes; use tb200_gemm_bf16_nt",
+                 M, N, K, need, splits, fixed_scratch_bytes);
+        return 4;
+      }
+      p.partials = fixed_scratch;
+    } else if (int rc = get_workspace(need, &p.partials)) {
+      return rc;
+    }
   }
+  // TMA-store epilogue needs a 16-byte aligned row stride; odd widths fall back to direct stores.
+  const bool f32_out = splits > 1 || d_dtype == TB200_F32;
+  p.direct_store = (N % (f32_out ? 4 : 8)) != 0;
 
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, md;
+  memset(&md, 0, sizeof(md));
+  if (!p.direct_store) {
+    if (splits > 1) {
+      if (int rc = make_out_map(&md, p.partials, M, N, true, splits)) return rc;
+    } else if (int rc = make_out_map(&md, D, M, N, d_dtype == TB200_F32, 1)) {
+      return rc;
+    }
+  }
   PullMaps pm;
   memset(&pm, 0, sizeof(pm));
   if (int rc = make_map(&ma, A, M, K, BLOCK_M)) return rc;
@@ -586,10 +762,10 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   const int items = tiles * splits;
   const int grid = items < sms ? items : sms;
   int rc;
-  if (block_n == 256) rc = pull ? launch_gemm<256, true>(ma, mb, pm, p, grid, stream)
-                                : launch_gemm<256, false>(ma, mb, pm, p, grid, stream);
-  else rc = pull ? launch_gemm<128, true>(ma, mb, pm, p, grid, stream)
-                 : launch_gemm<128, false>(ma, mb, pm, p, grid, stream);
+  if (block_n == 256) rc = pull ? launch_gemm<256, true>(ma, mb, md, pm, p, grid, stream)
+                                : launch_gemm<256, false>(ma, mb, md, pm, p, grid, stream);
+  else rc = pull ? launch_gemm<128, true>(ma, mb, md, pm, p, grid, stream)
+                 : launch_gemm<128, false>(ma, mb, md, pm, p, grid, stream);
   if (rc) return rc;
   if (splits > 1) {
     const size_t mn = (size_t)M * N;
@@ -676,68 +852,10 @@ int noalloc_scratch(float** out) {
 extern "C" int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void* bias,
                                           int bias_dtype, int M, int N, int K, int d_dtype, int act,
                                           cudaStream_t stream) {
-  if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm_bf16_nt_noalloc: empty problem%s");
-  if (K % 8) return fail("tb200_gemm_bf16_nt_noalloc: K %s(%ld) must be a multiple of 8", "", K);
-  if (d_dtype != TB200_BF16 && d_dtype != TB200_F32)
-    return fail("tb200_gemm_bf16_nt_noalloc: bad output dtype%s");
-
-  GemmParams p{};
-  p.M = M; p.N = N; p.K = K;
-  p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
-  p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
-  p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
-
-  // Same tiling and split-K plan as tb200_gemm_bf16_nt (keep the two in step), so both entry
-  // points run the same kernels in the same order and produce the same bits.
-  const int sms = sm_count();
-  int block_n = 256;
-  if (N <= 128 || (long long)p.num_m * ((N + 255) / 256) < sms) block_n = 128;
-  p.num_n = (N + block_n - 1) / block_n;
-  const int tiles = p.num_m * p.num_n;
-  int splits = 1;
-  if (tiles < sms) {
-    int max_splits = p.num_kb / 4;
-    if (max_splits > 16) max_splits = 16;
-    double best = 0.0;
-    for (int s = 1; s <= max_splits; ++s) {
-      const int it = tiles * s;
-      const int waves = (it + sms - 1) / sms;
-      const double eff = (double)it / ((double)waves * sms);
-      if (eff > best + 1e-9) { best = eff; splits = s; }
-    }
-  }
-  p.splits = splits;
-  if (splits > 1) {
-    const size_t need = (size_t)splits * M * N * sizeof(float);
-    if (need > (size_t)TB200_GEMM_NOALLOC_SCRATCH_BYTES) {
-      snprintf(g_last_error, sizeof(g_last_error),
-               "tb200_gemm_bf16_nt_noalloc: M=%d N=%d K=%d needs %zu bytes of split-K scratch "
-               "(%d splits) but the built-in scratch is %zu bytes; use tb200_gemm_bf16_nt",
-               M, N, K, need, splits, (size_t)TB200_GEMM_NOALLOC_SCRATCH_BYTES);
-      return 4;
-    }
-    // Every partial that the reduction reads is written by this call's GEMM first, so nothing in
-    // the shared array has to be cleared; what an earlier call left behind is simply overwritten.
-    if (int rc = noalloc_scratch(&p.partials)) return rc;
-  }
-
-  CUtensorMap ma, mb;
-  PullMaps pm;
-  memset(&pm, 0, sizeof(pm));
-  if (int rc = make_map(&ma, A, M, K, BLOCK_M)) return rc;
-  if (int rc = make_map(&mb, B, N, K, block_n)) return rc;
-  const int items = tiles * splits;
-  const int grid = items < sms ? items : sms;
-  int rc = block_n == 256 ? launch_gemm<256, false>(ma, mb, pm, p, grid, stream)
-                          : launch_gemm<128, false>(ma, mb, pm, p, grid, stream);
-  if (rc) return rc;
-  if (splits > 1) {
-    const size_t mn = (size_t)M * N;
-    int rgrid = (int)((mn + 255) / 256);
-    if (rgrid > sms * 8) rgrid = sms * 8;
-    splitk_reduce_kernel<<<rgrid, 256, 0, stream>>>(p.partials, splits, mn, N, bias, bias_dtype, act, D,
-                                                    d_dtype);
-    return launched();
-  }
-  return 0;
+  // Same planning, kernels and results as tb200_gemm_bf16_nt; only the home of the split-K partial
+  // sums differs (the built-in array instead of a cudaMalloc'ed workspace).
+  float* scratch = nullptr;
+  if (int rc = noalloc_scratch(&scratch)) return rc;
+  return gemm_common(nullptr, 0, 0, 0, A, B, D, bias, bias_dtype, M, N, K, d_dtype, act, nullptr, nullptr,
+                     0, stream, scratch, (size_t)TB200_GEMM_NOALLOC_SCRATCH_BYTES);
 }
