@@ -1,0 +1,65 @@
+"""Model registry and trainer planning logic that need no GPU."""
+import torch
+from torch import nn
+
+from tiresias_b200.models import zoo
+from tiresias_b200.ops.batchnorm import FusedBatchNormAct
+from tiresias_b200.parallel.trainer import plan_buckets
+from tiresias_b200.sim import models as sim_models
+
+
+def test_every_reference_model_name_resolves_to_an_executable_model():
+    assert set(zoo.MODEL_SIZES_MB) == set(sim_models.model_sizes)          # 17 names, same table
+    for name in zoo.MODEL_SIZES_MB:
+        spec = zoo.resolve(name)
+        assert spec.kind in ("image", "tokens") and callable(spec.build)
+    assert zoo.resolve("no_such_model").name == zoo.resolve("inception3").name   # get_model's default pick
+
+
+def test_parameter_counts_match_the_architectures():
+    counts = {n: sum(p.numel() for p in zoo.build(zoo.resolve(n)).parameters())
+              for n in ("resnet50", "vgg16", "alexnet")}
+    assert counts == {"resnet50": 25557032, "vgg16": 138357544, "alexnet": 61100840}
+    # checkpoint MB of the reference table ~ 4 bytes per parameter
+    assert abs(counts["resnet50"] * 4 / 2 ** 20 - zoo.MODEL_SIZES_MB["resnet50"]) < 2
+    assert abs(counts["vgg16"] * 4 / 2 ** 20 - zoo.MODEL_SIZES_MB["vgg16"]) < 2
+
+
+def test_fused_and_stock_variants_agree_on_cpu():
+    torch.manual_seed(0)
+    fused, stock = zoo.build(zoo.resolve("resnet50"), True), zoo.build(zoo.resolve("resnet50"), False)
+    remap = {}
+    for k, v in fused.state_dict().items():
+        parts = k.split(".")
+        if parts[-2].startswith("bn") or parts[-2].endswith("_bn"):
+            parts.insert(-1, "bn")
+        remap[".".join(parts)] = v
+    stock.load_state_dict(remap, strict=False)
+    x = torch.randn(2, 3, 64, 64)
+    assert torch.allclose(fused(x), stock(x), atol=1e-4)
+
+
+def test_fused_bn_module_cpu_fallback_matches_batchnorm2d():
+    torch.manual_seed(1)
+    mod, ref = FusedBatchNormAct(16, relu=True), nn.BatchNorm2d(16)
+    x, res = torch.randn(4, 16, 5, 5), torch.randn(4, 16, 5, 5)
+    assert torch.allclose(mod(x, res), torch.relu(ref(x) + res), atol=1e-5)
+    assert torch.allclose(mod.running_var, ref.running_var, atol=1e-6)
+    mod.to(torch.bfloat16)
+    assert mod.running_mean.dtype == torch.float32 and mod.weight.dtype == torch.bfloat16
+
+
+def test_bucket_plan_covers_every_parameter_once_and_shards_evenly():
+    model = zoo.build(zoo.resolve("resnet50"))
+    for world in (1, 2, 8):
+        buckets, total = plan_buckets(model, world, bucket_elems=4 << 20, pull_min_elems=1 << 21, allow_pull=True)
+        seen = set()
+        for b in buckets:
+            assert b.length % (8 * world) == 0 and b.offset % 64 == 0
+            for p, off in b.params:
+                assert id(p) not in seen and b.offset <= off and off + p.numel() <= b.offset + b.length
+                seen.add(id(p))
+            lo, n = b.shard(world - 1, world)
+            assert lo + n == b.offset + b.length
+        assert len(seen) == len(list(model.parameters())) and total >= sum(p.numel() for p in model.parameters())
+        assert buckets[-1].offset + buckets[-1].length <= total
