@@ -25,20 +25,21 @@ from ..exec.replay import calibration_from_records, replay
 
 
 def measure(gpus: int, models: Sequence[str], comm: str, iters: int, batch: int, out_dir: str,
-            loopback: bool = False, step_sleep: float = 0.0) -> Dict:
+            loopback: bool = False, step_sleep: float = 0.0, repeats: int = 2) -> Dict:
     os.makedirs(out_dir, exist_ok=True)
     trace = os.path.join(out_dir, "calibration_trace.csv")
     sizes = [g for g in (1, 2, 4, 8) if g <= gpus]
     with open(trace, "w") as fh:
         fh.write("job_id,num_gpu,submit_time,iterations,model_name,duration,interval\n")
         jid = 0
-        for g in reversed(sizes):                       # big jobs first: the small ones then fill the box
-            for m in models:
-                fh.write(f"{jid},{g},0,{iters},{m},1,0\n")
-                jid += 1
+        for rep in range(repeats):                      # every configuration `repeats` times; the fastest counts
+            for g in reversed(sizes):                   # big jobs first: the small ones then fill the box
+                for m in models:
+                    fh.write(f"{jid},{g},0,{iters},{m},1,0\n")
+                    jid += 1
     res = replay(trace, gpus, "fifo", comm, os.path.join(out_dir, "calib_run"), None, loopback, batch,
                  step_sleep=step_sleep)
-    cal = calibration_from_records(res["records"])
+    cal = calibration_from_records(res["records"], reduce="min")
     comm_tab: Dict[str, Dict[str, float]] = {}
     for m, per in cal["iter_s"].items():
         base = per.get("1")
@@ -62,9 +63,10 @@ def main(argv: Optional[Sequence[str]] = None) -> None:
     ap.add_argument("--work", default=None)
     ap.add_argument("--loopback", action="store_true")
     ap.add_argument("--step-sleep", type=float, default=0.0)
+    ap.add_argument("--repeats", type=int, default=2)
     a = ap.parse_args(list(argv) if argv is not None else None)
     work = a.work or tempfile.mkdtemp(prefix="tb200_calib_")
-    cal = measure(a.gpus, a.models.split(","), a.comm, a.iters, a.batch, work, a.loopback, a.step_sleep)
+    cal = measure(a.gpus, a.models.split(","), a.comm, a.iters, a.batch, work, a.loopback, a.step_sleep, a.repeats)
     if a.interference and os.path.exists(a.interference):
         inter = json.load(open(a.interference))
         cal["interference_factor"] = inter.get("interference_factor")

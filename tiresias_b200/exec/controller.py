@@ -130,7 +130,8 @@ class Controller:
                 self.log(f"[{now:8.2f}s] job {job.job_id} FAILED: {[r.get('error') for r in res if r['status'] == 'failed'][:1]}")
             elif all(r["status"] == "done" for r in res):
                 job.status, job.end, job.done = "DONE", now, job.iters
-                self.log(f"[{now:8.2f}s] job {job.job_id} done (JCT {job.jct():.2f}s, {res[0]['iter_ms']:.2f} ms/iter)")
+                self.log(f"[{now:8.2f}s] job {job.job_id} done (JCT {job.jct():.2f}s, "
+                         f"{(res[0].get('iter_ms') or 0.0):.2f} ms/iter)")
             else:
                 job.done = min(r["done"] for r in res)
                 job.status = "WAITING"

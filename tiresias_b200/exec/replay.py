@@ -53,7 +53,9 @@ def start_pool(gpus: int, ctl_port: int, loopback: bool, with_nccl: bool, log_pa
     return subprocess.Popen(cmd, cwd=root, env=env, stdout=open(log_path, "w"), stderr=subprocess.STDOUT)
 
 
-def calibration_from_records(records: Sequence[Dict]) -> Dict:
+def calibration_from_records(records: Sequence[Dict], reduce: str = "mean") -> Dict:
+    """``iter_s`` / ``startup_s`` per (model, GPUs) from finished jobs. ``reduce="min"`` (calibration runs,
+    which repeat every configuration) discards first-use effects such as library autotuning."""
     acc: Dict[str, Dict[str, List[float]]] = {}
     start: Dict[str, Dict[str, List[float]]] = {}
     for r in records:
@@ -61,8 +63,9 @@ def calibration_from_records(records: Sequence[Dict]) -> Dict:
             continue
         acc.setdefault(r["model"], {}).setdefault(str(r["num_gpu"]), []).append(r["iter_ms"] / MS)
         start.setdefault(r["model"], {}).setdefault(str(r["num_gpu"]), []).append(r["startup_s"] or 0.0)
-    mean = lambda d: {m: {g: sum(v) / len(v) for g, v in per.items()} for m, per in d.items()}  # noqa: E731
-    return {"iter_s": mean(acc), "startup_s": mean(start), "source": "self"}
+    fold = (lambda v: min(v)) if reduce == "min" else (lambda v: sum(v) / len(v))
+    table = lambda d: {m: {g: fold(v) for g, v in per.items()} for m, per in d.items()}  # noqa: E731
+    return {"iter_s": table(acc), "startup_s": table(start), "source": "self"}
 
 
 def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:

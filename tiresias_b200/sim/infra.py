@@ -35,7 +35,7 @@ def global_rng() -> np.random.RandomState:
 class Device:
     """One GPU. ``running_tasks`` holds every task *placed* on it (reserved or running)."""
 
-    __slots__ = ("device_id", "node_id", "memory", "enable_pack", "running_tasks", "rng")
+    __slots__ = ("device_id", "node_id", "memory", "enable_pack", "running_tasks", "rng", "_normal", "_mem")
 
     def __init__(self, device_id, node_id, memory_cap, enable_pack, rng=None):
         self.device_id = device_id
@@ -44,6 +44,8 @@ class Device:
         self.enable_pack = enable_pack
         self.running_tasks: "OrderedDict[str, object]" = OrderedDict()
         self.rng = rng if rng is not None else global_rng()
+        self._normal = self.rng.normal
+        self._mem = 0                   # cached get_current_memory(); None = recompute
 
     def is_idle(self) -> bool:
         return not self.running_tasks
@@ -53,8 +55,10 @@ class Device:
         at 100, running sum capped at 100. The flag records whether the reference's value would be
         a 1-element ndarray (any uncapped draw contributed) or a plain int — that decides how
         ``cluster.csv`` prints it (``[4.51]`` vs ``100``)."""
+        if not self.running_tasks:
+            return 0.0, False
         total, drawn = 0.0, False
-        normal = self.rng.normal
+        normal = self._normal
         for t in self.running_tasks.values():
             x = normal(t.gpu_utilization_avg, (t.gpu_utilization_max - t.gpu_utilization_avg) / 2)
             if x < 100:
@@ -70,13 +74,19 @@ class Device:
         return self.sample_utilization()[0]
 
     def get_current_memory(self):
-        mem = 0
-        cap = self.memory
-        for t in self.running_tasks.values():
-            m = t.gpu_memory_max
-            mem += cap if cap < m else m
-            if cap < mem:
-                mem = cap
+        """Sum of the resident tasks' peak memory, each and the total capped at the capacity. Cached
+        between changes of the resident set (recomputed in resident order, so the float sum is the
+        reference's)."""
+        mem = self._mem
+        if mem is None:
+            mem = 0
+            cap = self.memory
+            for t in self.running_tasks.values():
+                m = t.gpu_memory_max
+                mem += cap if cap < m else m
+                if cap < mem:
+                    mem = cap
+            self._mem = mem
         return mem
 
     def can_fit(self, task) -> bool:
@@ -90,13 +100,16 @@ class Device:
         if not pack and self.running_tasks:
             return False
         self.running_tasks[task.task_id] = task
+        self._mem = None
         return True
 
     def pop_task(self, task_id):
+        self._mem = None
         return self.running_tasks.pop(task_id, None)
 
     def reset(self) -> None:
         self.running_tasks = OrderedDict()
+        self._mem = 0
 
 
 class Node:
@@ -272,7 +285,8 @@ class Node:
         self.mem_used -= task.mem
         relieved: Dict[str, str] = {}
         for d in self.device_cache.values():
-            d.running_tasks.pop(task.task_id, None)
+            if task.task_id in d.running_tasks:
+                d.pop_task(task.task_id)
             if len(d.running_tasks) <= 1:
                 for t in d.running_tasks.values():
                     if t.interfered:
