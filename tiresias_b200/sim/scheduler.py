@@ -19,6 +19,7 @@ import time
 from typing import Dict, Optional
 
 from . import util
+from .infra import sample_utilizations
 from .logs import ArrayLike, LogInfo
 from .network import calculate_network_costs
 from .placement import placement_algorithms
@@ -169,6 +170,7 @@ class Scheduler:
         util_sum, util_is_array = 0.0, False
         mem_sum = 0
         mem_cap = 0
+        busy = []
         for n in self.infrastructure.nodes.values():
             if n.is_idle():
                 idle_nodes += 1
@@ -176,14 +178,16 @@ class Scheduler:
                 busy_nodes += 1
             for d in n.device_cache.values():
                 if d.running_tasks:
-                    busy_gpus += 1
-                    u, drawn = d.sample_utilization()
-                    util_sum += u
-                    util_is_array = util_is_array or drawn
-                    mem_sum += d.get_current_memory()
+                    busy.append(d)
                 else:
                     idle_gpus += 1
                 mem_cap += d.memory
+        busy_gpus = len(busy)
+        # one generator call for the whole cluster (same stream order as device-by-device draws)
+        for d, (u, drawn) in zip(busy, sample_utilizations(busy, self.infrastructure.rng)):
+            util_sum += u
+            util_is_array = util_is_array or drawn
+            mem_sum += d.get_current_memory()
         avg_util = util_sum / (idle_gpus + busy_gpus)
         avg_util = ArrayLike(avg_util) if util_is_array else avg_util
         avg_mem = mem_sum / mem_cap

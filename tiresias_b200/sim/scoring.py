@@ -11,6 +11,8 @@ from __future__ import annotations
 
 from typing import Dict, Tuple
 
+from .infra import MEMORY_MARGIN_MIB, sample_utilizations
+
 UTILCOST = 1.6
 MEMCOST = 1.3
 
@@ -19,11 +21,29 @@ def _score(node, task, overflow_term: bool) -> Tuple[Dict[int, float], float, fl
     device_scores: Dict[int, float] = {}
     total = 0
     best = 999
-    for d in node.device_cache.values():
-        if not d.can_fit(task):
-            continue
+    devices = node.device_cache.values()
+    if not any(d.running_tasks for d in devices):
+        # Fast path for a node with nothing resident: every device scores the same and no utilisation
+        # draw is consumed (the reference draws once per *resident* task), so one evaluation serves
+        # all devices; the sum is accumulated device by device to stay bit-identical.
+        for d in devices:
+            if not d.memory - (0 + task.gpu_memory_max) > MEMORY_MARGIN_MIB:
+                return device_scores, total, best
+            mem_cost = 0 + task.gpu_memory_max / d.memory
+            util_cost = 0.0
+            if overflow_term:
+                util_cost = (util_cost + task.gpu_utilization_max) - 100.0
+                util_cost = abs(util_cost) * UTILCOST if util_cost > 0 else abs(util_cost)
+            cost = (mem_cost * MEMCOST) + (util_cost / 100) + 0
+            break
+        for d in devices:
+            device_scores[d.device_id] = cost
+            total += cost
+        return device_scores, total, cost
+    fitting = [d for d in devices if d.can_fit(task)]
+    utils = sample_utilizations(fitting, fitting[0].rng) if fitting else []
+    for d, (util_cost, _) in zip(fitting, utils):
         mem_cost = d.get_current_memory() + task.gpu_memory_max / d.memory
-        util_cost = d.get_current_utilization()
         if overflow_term:
             util_cost = (util_cost + task.gpu_utilization_max) - 100.0
             util_cost = abs(util_cost) * UTILCOST if util_cost > 0 else abs(util_cost)
