@@ -78,8 +78,10 @@ def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:
 
 
 def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, gpus: int, schedule: str,
-             queue_limit_s: Sequence[float], out_dir: str) -> Dict[str, Dict]:
-    """Event simulation in milliseconds on a 1 x 1 x ``gpus`` counting cluster."""
+             queue_limit_s: Sequence[float], out_dir: str, scheme: str = "buddy") -> Dict[str, Dict]:
+    """Event simulation in milliseconds on a 1 x 1 x ``gpus`` cluster. ``scheme="buddy"`` places jobs on
+    aligned power-of-two GPU blocks like the worker pool does (non-preemptive schedules); the preemptive
+    ones hand out GPUs by counting, as their reference loops do."""
     from ..sim.flags import define_simulator_flags
     from ..sim.legacy.engine import run_event_simulation
     by_id = {r["job_id"]: r for r in records}
@@ -93,7 +95,7 @@ def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, g
                          "iterations": row["iterations"], "model_name": rec["model"],
                          "duration": max(1, int(round((st + it * row["iterations"]) * MS))), "interval": 0})
     flags = define_simulator_flags()
-    argv = ["--schedule", SIM_SCHEDULE[schedule], "--scheme", "count", "--num_switch", "1", "--num_node_p_switch", "1",
+    argv = ["--schedule", SIM_SCHEDULE[schedule], "--scheme", scheme, "--num_switch", "1", "--num_node_p_switch", "1",
             "--num_gpu_p_node", str(gpus), "--quiet"]
     if schedule == "dlas-gpu":
         argv += ["--queue_limit", ",".join(str(int(q * MS)) for q in queue_limit_s)]
@@ -134,6 +136,9 @@ def compare(records: Sequence[Dict], sim: Dict[str, Dict]) -> Dict:
     return {"n": n, "avg_jct_exec_s": round(avg_exec, 3), "avg_jct_sim_s": round(avg_sim, 3),
             "avg_jct_error_pct": round((avg_sim - avg_exec) / avg_exec * 100.0, 2),
             "mean_abs_job_error_pct": round(sum(abs(e) for e in errs) / n, 2),
+            "median_abs_job_error_pct": round(sorted(abs(e) for e in errs)[n // 2], 2),
+            "jct_weighted_abs_error_pct": round(sum(abs(x["sim_jct_s"] - x["exec_jct_s"]) for x in rows)
+                                                / sum(x["exec_jct_s"] for x in rows) * 100.0, 2),
             "makespan_exec_s": round(mk_exec, 3), "makespan_sim_s": round(mk_sim, 3),
             "makespan_error_pct": round((mk_sim - mk_exec) / mk_exec * 100.0, 2), "jobs": rows}
 
@@ -176,7 +181,8 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
             calibration = json.load(fh)
     else:
         calibration = calibration_from_records(records)
-    sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"))
+    sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"),
+                   "buddy" if schedule == "fifo" else "count")
     result = {"trace": trace, "gpus": gpus, "schedule": schedule, "comm": comm, "loopback": loopback,
               "wall_s": round(wall, 2), "calibration_source": calibration.get("source", calibration_path),
               "records": records, "comparison": compare(records, sim)}
@@ -187,9 +193,30 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
     return result
 
 
+def resimulate(out: str, calibration_path: Optional[str] = None, scheme: str = "buddy") -> Dict:
+    """Recompute the simulated side of an existing ``replay.json`` (no GPU needed)."""
+    with open(os.path.join(out, "replay.json")) as fh:
+        res = json.load(fh)
+    rows = [{"job_id": r["job_id"], "iterations": r["iterations"]} for r in res["records"]]
+    if calibration_path:
+        with open(calibration_path) as fh:
+            calibration = json.load(fh)
+    else:
+        calibration = calibration_from_records(res["records"])
+    sim = simulate(rows, res["records"], calibration, res["gpus"], res["schedule"], (20.0,),
+                   os.path.join(out, "sim_" + scheme), scheme)
+    res["comparison"] = compare(res["records"], sim)
+    res["sim_scheme"] = scheme
+    with open(os.path.join(out, "replay.json"), "w") as fh:
+        json.dump(res, fh, indent=1)
+    return res
+
+
 def main(argv: Optional[Sequence[str]] = None) -> None:
     ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
-    ap.add_argument("--trace", required=True)
+    ap.add_argument("--resimulate", default=None, metavar="DIR", help="recompute the comparison of an existing run")
+    ap.add_argument("--sim-scheme", default="buddy", choices=["buddy", "count"])
+    ap.add_argument("--trace", required=False)
     ap.add_argument("--gpus", type=int, default=8)
     ap.add_argument("--schedule", default="fifo", choices=sorted(SIM_SCHEDULE))
     ap.add_argument("--comm", default="ps", choices=["ps", "ring", "nccl"])
@@ -204,6 +231,10 @@ def main(argv: Optional[Sequence[str]] = None) -> None:
     ap.add_argument("--step-sleep", type=float, default=0.0, help="loopback only: seconds per iteration")
     ap.add_argument("--no-graph", action="store_true")
     a = ap.parse_args(list(argv) if argv is not None else None)
+    if a.resimulate:
+        res = resimulate(a.resimulate, a.calibration, a.sim_scheme)
+        print(json.dumps({k: v for k, v in res["comparison"].items() if k != "jobs"}))
+        return
     res = replay(a.trace, a.gpus, a.schedule, a.comm, a.out, a.calibration, a.loopback, a.batch, a.time_scale,
                  [float(x) for x in a.queue_limit.split(",")], a.check_every, a.step_sleep, a.iters_scale,
                  not a.no_graph)

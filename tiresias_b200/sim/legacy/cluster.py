@@ -194,6 +194,7 @@ class TCluster:
         self.gpu_list: List[float] = []
         self.free_nodes: List[TNode] = []
         self.node_g: Dict[int, List[dict]] = {k: [] for k in self.GANDIVA_CLASSES}
+        self._buddy = None
         self.set_spec(flags.num_switch, flags.num_node_p_switch, flags.num_gpu_p_node,
                       flags.num_cpu_p_node, flags.mem_p_node)
 
@@ -222,6 +223,7 @@ class TCluster:
 
     def empty_infra(self) -> None:
         self.free_gpu = self.num_gpu
+        self._buddy = None
         for node in self.nodes():
             node.init_node(self.num_gpu_p_node, self.num_cpu_p_node, self.mem_p_node)
         if self.flags.schedule == "dlas-gpu-pack":
@@ -265,7 +267,23 @@ class TCluster:
             return lp_placement(self, job, consolidate=(scheme == "cbalance"))
         if scheme == "gandiva":
             return self.gandiva_placement(job)
+        if scheme == "buddy":
+            return self.buddy_placement(job)
         raise KeyError(f"unknown placement scheme {scheme!r}")
+
+    def buddy_placement(self, job: TJob) -> bool:
+        """One NVSwitch domain as the execution backend sees it (tiresias_b200.exec.buddy): a job runs on
+        an aligned power-of-two block of GPUs, so a free GPU count is not enough — the block must exist.
+        Lets the simulator reproduce the fragmentation the real 8xB200 replay experiences."""
+        from ...exec.buddy import BuddyAllocator, normalize_gpus
+        if self._buddy is None:
+            self._buddy = BuddyAllocator(self.num_gpu)
+        blk = self._buddy.alloc(normalize_gpus(job.num_gpu, self.num_gpu), str(job.job_id))
+        if blk is None:
+            return False
+        job.placements.append({"buddy": blk})
+        self.free_gpu -= blk[1]
+        return True
 
     def none_placement(self, job: TJob) -> bool:
         if self.free_gpu >= job.num_gpu:
@@ -455,6 +473,14 @@ class TCluster:
             return True
         if self.flags.scheme == "count":
             self.free_gpu = min(self.num_gpu, self.free_gpu + job.num_gpu)
+            job.status = "END"
+            return True
+        if self.flags.scheme == "buddy":
+            for placement in job.placements:
+                if self._buddy is not None and "buddy" in placement:
+                    self._buddy.free(tuple(placement["buddy"]))
+                    self.free_gpu = min(self.num_gpu, self.free_gpu + placement["buddy"][1])
+            del job.placements[:]
             job.status = "END"
             return True
         for placement in job.placements:

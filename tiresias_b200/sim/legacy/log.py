@@ -31,7 +31,7 @@ class TLog:
         self.log_path = path
         self.flags = flags
         self.cluster = cluster
-        self.is_count = flags.scheme == "count"
+        self.is_count = flags.scheme in ("count", "buddy")
         self.finished_rows: List[list] = []
         self._files = {}
 
