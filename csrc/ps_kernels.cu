@@ -473,6 +473,71 @@ int grid_for(size_t nvec, int per_thread, int max_ctas) {
 
 }  // namespace
 
+// Same normalisation, but every pixel is written as 8 bf16 channels (r, g, b, 0, 0, 0, 0, 0 = one
+// 16-byte store): a first convolution with 8 input channels takes cuDNN's sm_100 implicit-GEMM path,
+// which needs channel counts that are multiples of 8; with 3 channels it falls back to a legacy kernel
+// that is ~4x slower (profiles/step_launches: cutlass__5x_cudnn fprop_optimized 1.47 ms at batch 256).
+__global__ void __launch_bounds__(kThreads) u8_to_bf16_norm_pad8_kernel(
+    const uint8_t* __restrict__ src, uint4* __restrict__ dst, size_t pixels, float m0, float m1,
+    float m2, float s0, float s1, float s2) {
+  const size_t groups = pixels / 4;
+  const float k = 1.0f / 255.0f;
+  for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < groups;
+       g += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(src + g * 12);
+    const uint32_t w[3] = {p[0], p[1], p[2]};
+#pragma unroll
+    for (int px = 0; px < 4; ++px) {
+      float c[3];
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) {
+        const int e = px * 3 + ch;
+        c[ch] = (float)((w[e / 4] >> (8 * (e % 4))) & 0xffu) * k;
+      }
+      dst[g * 4 + px] = make_uint4(pack_bf16((c[0] - m0) * s0, (c[1] - m1) * s1),
+                                   pack_bf16((c[2] - m2) * s2, 0.f), 0u, 0u);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < pixels % 4) {
+    const size_t px = groups * 4 + threadIdx.x;
+    const uint8_t* q = src + px * 3;
+    dst[px] = make_uint4(pack_bf16((q[0] * k - m0) * s0, (q[1] * k - m1) * s1),
+                         pack_bf16((q[2] * k - m2) * s2, 0.f), 0u, 0u);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Gradient packing: up to TB200_PACK_MAX tensors are copied into their slots of the flat, symmetric
+// gradient buffer by ONE launch (autograd hands every parameter's gradient over as a separate
+// tensor; accumulating each into a flat view costs one add kernel per parameter — 161 launches per
+// ResNet-50 step — where one launch per bucket suffices).
+// ---------------------------------------------------------------------------------------------
+constexpr unsigned kPackElemsPerBlock = 8192;
+
+struct PackArgs {
+  int count;
+  tb200_pack_item_t items[TB200_PACK_MAX];
+  unsigned block_start[TB200_PACK_MAX + 1];
+};
+
+__global__ void __launch_bounds__(kThreads) pack_bf16_kernel(const PackArgs a) {
+  int it = 0;
+  while (it + 1 < a.count && blockIdx.x >= a.block_start[it + 1]) ++it;     // <= 64 items: linear scan
+  const tb200_pack_item_t item = a.items[it];
+  const size_t begin = (size_t)(blockIdx.x - a.block_start[it]) * kPackElemsPerBlock;
+  const size_t end = begin + kPackElemsPerBlock < item.n ? begin + kPackElemsPerBlock : (size_t)item.n;
+  const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(item.src);
+  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(item.dst);
+  if ((((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
+    const size_t v0 = begin / 8, v1 = end / 8;                  // begin is a multiple of 8
+    for (size_t v = v0 + threadIdx.x; v < v1; v += kThreads)
+      st_stream_16(reinterpret_cast<uint4*>(dst) + v, ld_stream_16(reinterpret_cast<const uint4*>(src) + v));
+    for (size_t i = v1 * 8 + threadIdx.x; i < end; i += kThreads) dst[i] = src[i];
+  } else {
+    for (size_t i = begin + threadIdx.x; i < end; i += kThreads) dst[i] = src[i];
+  }
+}
+
 extern "C" {
 
 int tb200_sgd_momentum(float* master, float* momentum, const void* grad, int grad_dtype,
@@ -614,6 +679,36 @@ int tb200_u8_to_bf16_norm(const uint8_t* src, void* dst, size_t pixels, const fl
       src, reinterpret_cast<__nv_bfloat16*>(dst), pixels, mean[0], mean[1], mean[2], inv_std[0],
       inv_std[1], inv_std[2]);
   return launched();
+}
+
+int tb200_u8_to_bf16_norm_pad8(const uint8_t* src, void* dst, size_t pixels, const float mean[3],
+                               const float inv_std[3], cudaStream_t stream) {
+  if (pixels == 0) return 0;
+  const int grid = grid_for(pixels / 4 + 1, 2, 148 * 8);
+  u8_to_bf16_norm_pad8_kernel<<<grid, kThreads, 0, stream>>>(
+      src, reinterpret_cast<uint4*>(dst), pixels, mean[0], mean[1], mean[2], inv_std[0], inv_std[1],
+      inv_std[2]);
+  return launched();
+}
+
+int tb200_pack_bf16(const tb200_pack_item_t* items, int count, cudaStream_t stream) {
+  if (count <= 0) return 0;
+  if (!items) return fail("tb200_pack_bf16: null items%s");
+  for (int base = 0; base < count; base += TB200_PACK_MAX) {
+    PackArgs a{};
+    a.count = count - base < TB200_PACK_MAX ? count - base : TB200_PACK_MAX;
+    unsigned blocks = 0;
+    for (int i = 0; i < a.count; ++i) {
+      a.items[i] = items[base + i];
+      a.block_start[i] = blocks;
+      blocks += (unsigned)((a.items[i].n + kPackElemsPerBlock - 1) / kPackElemsPerBlock);
+    }
+    a.block_start[a.count] = blocks;
+    if (blocks == 0) continue;
+    pack_bf16_kernel<<<blocks, kThreads, 0, stream>>>(a);
+    if (int rc = launched()) return rc;
+  }
+  return 0;
 }
 
 int tb200_transpose_bf16(const void* src, void* dst, int rows, int cols, cudaStream_t stream) {

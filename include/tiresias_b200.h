@@ -169,6 +169,19 @@ int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off
 /* uint8 NHWC image batch -> normalised bf16 NHWC (mean/std per channel, C == 3).            */
 int tb200_u8_to_bf16_norm(const uint8_t* src, void* dst, size_t pixels, const float mean[3],
                           const float inv_std[3], cudaStream_t stream);
+/* Same, writing 8 channels per pixel (r, g, b, 0, 0, 0, 0, 0) so the first convolution can use the
+ * 8-channel-aligned tensor-core path; dst holds pixels * 8 bf16.                                   */
+int tb200_u8_to_bf16_norm_pad8(const uint8_t* src, void* dst, size_t pixels, const float mean[3],
+                               const float inv_std[3], cudaStream_t stream);
+/* Copy up to any number of bf16 tensors into their destinations with one launch per TB200_PACK_MAX
+ * items (gathers per-parameter gradients into the flat symmetric gradient buffer of a bucket).      */
+#define TB200_PACK_MAX 64
+typedef struct {
+  const void* src;
+  void* dst;
+  unsigned long long n;                    /* elements (bf16) */
+} tb200_pack_item_t;
+int tb200_pack_bf16(const tb200_pack_item_t* items, int count, cudaStream_t stream);
 /* bf16 [R,C] -> bf16 [C,R] tiled transpose (feeds the NT GEMM in backward).                 */
 int tb200_transpose_bf16(const void* src, void* dst, int rows, int cols, cudaStream_t stream);
 /* out[0] = sum(x^2) over n elements; `partials` is caller-provided scratch of

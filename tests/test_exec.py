@@ -81,3 +81,17 @@ def test_loopback_trainer_matches_single_process_sgd():
     tr2.load_state_dict(state)
     for a, b in zip(tr2.model.parameters(), tr.model.parameters()):
         assert torch.equal(a, b)
+
+
+@pytest.mark.timeout(300)
+def test_failed_job_is_reported_and_the_pool_keeps_serving(tmp_path):
+    """Fault injection: a job whose model cannot be built fails on its ranks; the controller marks it FAILED,
+    frees its GPUs, and the jobs behind it still run (the reference aborts the whole simulation on any
+    error, core/util.py:17-19)."""
+    from tiresias_b200.exec import loopback
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(2, 0, 10, "__explode__"), (1, 0, 10, "vgg16")])
+    res = replay(trace, gpus=2, schedule="fifo", comm="ps", out=str(tmp_path / "o"), loopback=True, step_sleep=0.005)
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert recs["0"]["status"] == "FAILED" and recs["1"]["status"] == "DONE"
+    assert hasattr(loopback, "LoopbackTrainer")

@@ -201,3 +201,38 @@ def test_direct_allreduce_emulated(cuda_device, world):
         assert torch.allclose(got, ref, rtol=1e-5, atol=1e-5)
     for r in ranks:
         r.close()
+
+
+def test_u8_norm_pad8(cuda_device):
+    x = torch.randint(0, 256, (3, 9, 7, 3), dtype=torch.uint8, device=cuda_device)      # 189 pixels: tail of 1
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    got = native.u8_to_bf16_norm_pad8(x, mean, std)
+    assert got.shape == (3, 9, 7, 8) and float(got[..., 3:].abs().sum()) == 0.0
+    want = (x.float() / 255.0 - torch.tensor(mean, device=cuda_device)) / torch.tensor(std, device=cuda_device)
+    assert torch.allclose(got[..., :3].float(), want, rtol=1e-2, atol=2e-2)
+
+
+def test_pack_bf16_gathers_many_tensors(cuda_device):
+    import ctypes as C
+    torch.manual_seed(3)
+    sizes = [5, 8, 64, 1000, 8192, 8193, 70000] + [17] * 80            # > TB200_PACK_MAX items, odd sizes
+    srcs = [torch.randn(n, device=cuda_device).to(torch.bfloat16) for n in sizes]
+    offs, total = [], 0
+    for n in sizes:
+        total = (total + 63) // 64 * 64
+        offs.append(total)
+        total += n
+    flat = torch.zeros(total + 64, dtype=torch.bfloat16, device=cuda_device)
+    items = (native.PackItem * len(sizes))(*[native.PackItem(s.data_ptr(), flat.data_ptr() + 2 * o, n)
+                                             for s, o, n in zip(srcs, offs, sizes)])
+    native.check(native.lib().tb200_pack_bf16(items, len(sizes), native.stream_ptr()))
+    torch.cuda.synchronize()
+    for s, o, n in zip(srcs, offs, sizes):
+        assert torch.equal(flat[o:o + n], s)
+    assert float(flat[offs[0] + sizes[0]:offs[1]].abs().sum()) == 0.0             # gaps untouched
+    # an unaligned destination takes the scalar path
+    dst = torch.zeros(100, dtype=torch.bfloat16, device=cuda_device)
+    one = (native.PackItem * 1)(native.PackItem(srcs[3].data_ptr(), dst.data_ptr() + 2, 50))
+    native.check(native.lib().tb200_pack_bf16(one, 1, native.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(dst[1:51], srcs[3][:50]) and float(dst[0]) == 0.0

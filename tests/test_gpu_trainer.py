@@ -117,3 +117,15 @@ def test_resnet50_step(cuda_device):
     assert l0 == l0 and 0 < l0 < 20
     assert tr.check_status() == 0
     tr.close()
+
+
+def test_profile_phases_reports_every_phase(cuda_device):
+    from tiresias_b200.parallel.trainer import Trainer
+    tr = Trainer(TINY, batch_size=32, mode="ps", use_graph=False, device=cuda_device, bucket_mb=0.05)
+    x, y = synthetic_batch(TINY, 32, seed=0)
+    tr.step(x, y)
+    ph = tr.profile_phases(x, y, steps=3)
+    assert set(ph) == {"h2d", "preprocess", "forward", "backward", "comm_tail", "total"}
+    assert all(v >= 0 for v in ph.values()) and ph["total"] >= ph["forward"] + ph["backward"] - 1e-3
+    assert tr.check_status() == 0
+    tr.close()

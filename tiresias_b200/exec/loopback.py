@@ -17,6 +17,8 @@ from torch import nn
 class LoopbackTrainer:
     def __init__(self, model_name: str, rank: int, world: int, group=None, lr: float = 0.05,
                  momentum: float = 0.9, hidden: int = 64, step_sleep: float = 0.0, seed: int = 0):
+        if model_name == "__explode__":                       # fault-injection hook for the pool's tests
+            raise RuntimeError("injected failure while building the model")
         self.rank, self.world, self.group = rank, world, group
         self.lr, self.momentum = lr, momentum
         self.step_sleep = step_sleep

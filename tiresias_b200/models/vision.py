@@ -89,8 +89,20 @@ class ResNet(nn.Module):
             if isinstance(m, Bottleneck):
                 nn.init.zeros_(m.bn3.weight)            # zero-init last BN of each block
 
+    input_channels = 3          # the trainer may feed 8 (rgb + 5 zero channels): see _stem
+
+    def _stem(self, x: torch.Tensor) -> torch.Tensor:
+        """7x7/2 convolution. An 8-channel input (rgb00000, written by tb200_u8_to_bf16_norm_pad8) is
+        convolved with the 3-channel weight zero-padded to 8 input channels — same result, but cuDNN can
+        use its 8-channel-aligned sm_100 kernels instead of the legacy 3-channel one."""
+        conv = self.stem_conv
+        if x.shape[1] == 8:
+            w8 = torch.nn.functional.pad(conv.weight, (0, 0, 0, 0, 0, 5))
+            return torch.nn.functional.conv2d(x, w8, None, conv.stride, conv.padding)
+        return conv(x)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.stem_pool(self.stem_bn(self.stem_conv(x)))
+        x = self.stem_pool(self.stem_bn(self._stem(x)))
         x = self.blocks(x)
         return self.fc(torch.flatten(self.pool(x), 1))
 

@@ -46,6 +46,12 @@ class World(C.Structure):
     ]
 
 
+class PackItem(C.Structure):
+    """Mirror of ``tb200_pack_item_t``."""
+
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("n", C.c_ulonglong)]
+
+
 class SgdHyper(C.Structure):
     _fields_ = [("lr", C.c_float), ("momentum", C.c_float), ("weight_decay", C.c_float),
                 ("grad_scale", C.c_float)]
@@ -85,7 +91,11 @@ def _declare(lib: C.CDLL) -> None:
                                             u32p, ip,
                                             C.c_ulonglong, st]
     lib.tb200_u8_to_bf16_norm.argtypes = [vp, vp, sz, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
+    lib.tb200_u8_to_bf16_norm_pad8.argtypes = [vp, vp, sz, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
+    lib.tb200_u8_to_bf16_norm_pad8.restype = C.c_int
     lib.tb200_transpose_bf16.argtypes = [vp, vp, C.c_int, C.c_int, st]
+    lib.tb200_pack_bf16.argtypes = [C.POINTER(PackItem), C.c_int, st]
+    lib.tb200_pack_bf16.restype = C.c_int
     lib.tb200_sumsq_scratch_floats.restype = C.c_size_t
     lib.tb200_sumsq.argtypes = [vp, C.c_int, sz, vp, vp, st]
     lib.tb200_bn_scratch_floats.restype = C.c_size_t
@@ -197,6 +207,19 @@ def u8_to_bf16_norm(src: torch.Tensor, mean: Sequence[float], std: Sequence[floa
     s = (C.c_float * 3)(*[1.0 / v for v in std])
     check(lib().tb200_u8_to_bf16_norm(src.data_ptr(), out.data_ptr(), src.numel() // 3, m, s,
                                       stream_ptr()))
+    return out
+
+
+def u8_to_bf16_norm_pad8(src: torch.Tensor, mean: Sequence[float], std: Sequence[float],
+                         out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 NHWC batch [..., 3] -> normalised bf16 NHWC [..., 8] (channels 3..7 zero)."""
+    assert src.dtype == torch.uint8 and src.is_contiguous() and src.shape[-1] == 3
+    if out is None:
+        out = torch.empty((*src.shape[:-1], 8), dtype=torch.bfloat16, device=src.device)
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*[1.0 / v for v in std])
+    check(lib().tb200_u8_to_bf16_norm_pad8(src.data_ptr(), out.data_ptr(), src.numel() // 3, m, s,
+                                           stream_ptr()))
     return out
 
 

@@ -110,7 +110,8 @@ class Trainer:
                  weight_decay: float = 1e-4, bucket_mb: float = 8.0, use_graph: bool = True,
                  pull_gemm: bool = True, pull_min_mb: float = 4.0, comm_ctas: int = 32,
                  spin_budget: int = 50_000_000, seed: int = 0, device: Optional[torch.device] = None,
-                 model: Optional[nn.Module] = None, allreduce_algo: int = 0, comm_group=None):
+                 model: Optional[nn.Module] = None, allreduce_algo: int = 0, comm_group=None,
+                 stem_pad8: bool = False):
         if mode not in ("ps", "ring", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
         self.spec, self.mode, self.batch_size = spec, mode, batch_size
@@ -121,6 +122,7 @@ class Trainer:
         self.comm_ctas, self.spin_budget = comm_ctas, spin_budget
         self.allreduce_algo = allreduce_algo
         self.comm_group = comm_group          # NCCL group of this job's ranks (mode "nccl" only)
+        self.stem_pad8 = stem_pad8
         self._lib = native.lib()
 
         torch.manual_seed(seed)           # identical initial weights on every rank
@@ -132,6 +134,8 @@ class Trainer:
             self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
             allow_pull=(pull_gemm and mode == "ps"))
 
+        self.pack_grads = mode != "nccl"
+        self._grad_view: Dict[int, torch.Tensor] = {}
         self._alloc_state()
         self._flatten_model()
         self.set_hyper(lr, momentum, weight_decay)
@@ -144,6 +148,7 @@ class Trainer:
         self.native_per_step = 0
         self.native_launches = 0
         self._pending_nccl: List[Tuple[Bucket, object]] = []
+        self._phase_events = None
         self._alloc_io()
 
     # ------------------------------------------------------------------------------------------
@@ -197,10 +202,14 @@ class Trainer:
         if p.dim() == 4:
             o, i, h, w = p.shape
             p.data = pv.view(o, h, w, i).permute(0, 3, 1, 2)       # channels_last strides
-            p.grad = gv.view(o, h, w, i).permute(0, 3, 1, 2)
+            gview = gv.view(o, h, w, i).permute(0, 3, 1, 2)
         else:
             p.data = pv.view(p.shape)
-            p.grad = gv.view(p.shape)
+            gview = gv.view(p.shape)
+        self._grad_view[id(p)] = gview
+        # nccl arm (DDP-style): gradients accumulate in place into bucket views. ps / ring: autograd
+        # hands over a fresh tensor per parameter and one pack kernel per bucket gathers them.
+        p.grad = gview if self.pack_grads is False else None
 
     def _flatten_model(self) -> None:
         """Move every parameter into the flat bf16 buffer (views); fp32 masters stay on the PS."""
@@ -233,9 +242,15 @@ class Trainer:
 
     def _alloc_io(self) -> None:
         dev, bs = self.device, self.batch_size
+        # Optional: feed the ResNets 8 input channels (rgb + 5 zeros) so the stem convolution takes cuDNN's
+        # 8-channel-aligned sm_100 path. Measured on B200 at batch 256 that path is SLOWER for the 7x7/2
+        # stem (2.72 ms vs 1.47 ms for the 3-channel kernel), so it stays off; the kernel and the model
+        # support are kept for convolution back-ends where it pays.
+        self._pad8 = bool(self.stem_pad8) and self.spec.kind == "image" and hasattr(self.model, "_stem")
         if self.spec.kind == "image":
             self.x_dev = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.uint8, device=dev)
-            self.x_in = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.bfloat16, device=dev)
+            in_shape = (*self.spec.sample_shape[:-1], 8) if self._pad8 else self.spec.sample_shape
+            self.x_in = torch.zeros((bs, *in_shape), dtype=torch.bfloat16, device=dev)
         else:
             self.x_dev = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.int64, device=dev)
             self.x_in = self.x_dev
@@ -263,7 +278,27 @@ class Trainer:
                 self._bucket_ready(bucket)
         return hook
 
+    def _pack_bucket(self, b: Bucket) -> None:
+        """Gather the bucket's per-parameter gradients into the flat symmetric buffer: one launch per 64
+        tensors (tb200_pack_bf16). A gradient whose memory layout differs from the parameter's falls
+        back to a strided torch copy."""
+        items = []
+        for p, off in b.params:
+            g = p.grad
+            if g is None:
+                continue
+            if g.dtype == torch.bfloat16 and g.stride() == p.stride():
+                items.append((g.data_ptr(), self.grad_flat.data_ptr() + 2 * off, p.numel()))
+            else:
+                self._grad_view[id(p)].copy_(g)
+            p.grad = None
+        if items:
+            arr = (native.PackItem * len(items))(*[native.PackItem(s, d, n) for s, d, n in items])
+            native.check(self._lib.tb200_pack_bf16(arr, len(items), native.stream_ptr()))
+
     def _bucket_ready(self, b: Bucket) -> None:
+        if self.pack_grads:
+            self._pack_bucket(b)
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
         self.comm_stream.wait_event(ev)
@@ -328,24 +363,71 @@ class Trainer:
     # ------------------------------------------------------------------------------------------
     def _preprocess(self) -> torch.Tensor:
         if self.spec.kind == "image":
-            native.u8_to_bf16_norm(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
+            if self._pad8:
+                native.u8_to_bf16_norm_pad8(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
+            else:
+                native.u8_to_bf16_norm(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
             return self.x_in.permute(0, 3, 1, 2)       # logical NCHW, physical NHWC
         return self.x_in
 
+    def _mark(self, name: str) -> None:
+        """Phase boundary for :meth:`profile_phases` (a CUDA event on the compute stream)."""
+        if self._phase_events is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(self.device))
+            self._phase_events.append((name, ev))
+
     def _device_step(self) -> None:
+        self._mark("begin")
         x = self._preprocess()
+        self._mark("preprocess")
         logits = self.model(x)
         loss = torch.nn.functional.cross_entropy(
             logits.float().reshape(-1, logits.shape[-1]), self.y_dev.reshape(-1))
         self.loss_dev.copy_(loss.detach().reshape(1))
+        self._mark("forward")
         loss.backward()
+        self._mark("backward")
         with torch.cuda.stream(self.comm_stream):
             if self.mode == "ps":
                 native.check(self._lib.tb200_step_end(
                     C.byref(self._world_struct), len(self.buckets), self.epoch.data_ptr(),
                     self.status.data_ptr(), self.spin_budget, native.stream_ptr(self.comm_stream)))
         torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
-        self.grad_flat.zero_()
+        if not self.pack_grads:
+            self.grad_flat.zero_()         # in-place accumulation needs a clean slate; packing overwrites
+        self._mark("comm_tail")
+
+    def profile_phases(self, x_host: torch.Tensor, y_host: torch.Tensor, steps: int = 5) -> Dict[str, float]:
+        """Per-phase device time of an *eager* step, in ms (CUDA events on the compute stream, averaged
+        over ``steps``; with ``torch.distributed`` initialised the maximum over ranks): ``h2d`` input copy,
+        ``preprocess``, ``forward`` (incl. loss), ``backward`` (the per-bucket push / all-reduce kernels
+        overlap it on the communication stream), ``comm_tail`` (what communication is left exposed after
+        backward: the wait for the last buckets + step_end), ``total``. The reference times only its whole
+        loop with ``time.time()`` (core/scheduling/schedule.py:179,210-212)."""
+        acc: Dict[str, float] = {}
+        for _ in range(steps):
+            self._phase_events = []
+            with torch.cuda.stream(self.stream):
+                self._mark("start")
+                self.x_dev.copy_(x_host, non_blocking=True)
+                self.y_dev.copy_(y_host, non_blocking=True)
+                self._device_step()
+                self._steps += 1
+            self.synchronize()
+            evs, self._phase_events = self._phase_events, None
+            names = {"begin": "h2d"}
+            for (_, a), (name, b) in zip(evs, evs[1:]):
+                key = names.get(name, name)
+                acc[key] = acc.get(key, 0.0) + a.elapsed_time(b)
+            acc["total"] = acc.get("total", 0.0) + evs[0][1].elapsed_time(evs[-1][1])
+        out = {k: v / steps for k, v in acc.items()}
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and self.world > 1 and self.symm.group is None:
+            t = torch.tensor([out[k] for k in sorted(out)], device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            out = dict(zip(sorted(out), t.tolist()))
+        return out
 
     def _capture(self) -> None:
         self._graph = torch.cuda.CUDAGraph()
