@@ -293,7 +293,10 @@ struct BwdArgs {
   int C, vecC;
   Chunking ck;
   int relu;
+  int recompute_mask;      // relu without a saved output: mask = (x*scale + shift > 0), exact for layers
+                           // without a residual input (same fp32 fma as the forward)
   const void* gamma;
+  const void* beta;
   int param_dtype;
   const float* save_mean;
   const float* save_invstd;
@@ -304,7 +307,9 @@ struct BwdArgs {
   float* coef;             // [0,C) A = gamma*invstd, [C,2C) mean(g), [2C,3C) mean(g*xhat)
 };
 
-__global__ void __launch_bounds__(kTX * kTY) bn_bwd_reduce_kernel(const BwdArgs a) {
+// MASK: 0 = no ReLU, 1 = ReLU mask from the saved output y, 2 = ReLU mask recomputed from x.
+template <int MASK>
+__global__ void __launch_bounds__(kTX * kTY, 2) bn_bwd_reduce_kernel(const BwdArgs a) {
   __shared__ float smem[2][kTY][kGroup];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int cg = blockIdx.x, chunk = blockIdx.y;
@@ -314,20 +319,27 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_reduce_kernel(const BwdArgs 
   const size_t r1 = min(a.rows, r0 + (size_t)a.ck.rows_per_chunk);
   float acc[2][8] = {};
   if (col_ok) {
-    float mean[8], istd[8];
+    float mean[8], istd[8], sc[8], sh[8];
+    constexpr bool saved_mask = MASK == 1;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       mean[k] = a.save_mean[vcol * 8 + k];
       istd[k] = a.save_invstd[vcol * 8 + k];
+      sc[k] = sh[k] = 0.f;
+      if constexpr (MASK == 2) {
+        sc[k] = load_param(a.gamma, a.param_dtype, vcol * 8 + k) * istd[k];
+        sh[k] = load_param(a.beta, a.param_dtype, vcol * 8 + k) - mean[k] * sc[k];
+      }
     }
     auto one = [&](const uint4& gr, const uint4& xr, const uint4& yr) {
       float g[8], xv[8], yv[8];
       unpack8(gr, g);
       unpack8(xr, xv);
-      if (a.relu) unpack8(yr, yv);
+      if (saved_mask) unpack8(yr, yv);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const float gk = (a.relu && !(yv[k] > 0.f)) ? 0.f : g[k];
+        if constexpr (MASK == 2) yv[k] = fmaf(xv[k], sc[k], sh[k]);
+        const float gk = (MASK != 0 && !(yv[k] > 0.f)) ? 0.f : g[k];
         acc[0][k] += gk;
         acc[1][k] += gk * ((xv[k] - mean[k]) * istd[k]);
       }
@@ -340,7 +352,7 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_reduce_kernel(const BwdArgs 
         const size_t i = (r + u * kTY) * a.vecC + vcol;
         gr[u] = ld_stream_16(a.dy + i);
         xr[u] = ld_stream_16(a.x + i);
-        if (a.relu) yr[u] = ld_stream_16(a.y + i);
+        if (saved_mask) yr[u] = ld_stream_16(a.y + i);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) one(gr[u], xr[u], yr[u]);
@@ -348,7 +360,7 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_reduce_kernel(const BwdArgs 
     for (; r < r1; r += kTY) {
       const size_t i = r * a.vecC + vcol;
       uint4 yr = make_uint4(0, 0, 0, 0);
-      if (a.relu) yr = ld_stream_16(a.y + i);
+      if (saved_mask) yr = ld_stream_16(a.y + i);
       one(ld_stream_16(a.dy + i), ld_stream_16(a.x + i), yr);
     }
   }
@@ -396,19 +408,22 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_reduce_kernel(const BwdArgs 
   }
 }
 
-__global__ void __launch_bounds__(kTX * kTY) bn_bwd_apply_kernel(const BwdArgs a) {
+template <int MASK>
+__global__ void __launch_bounds__(kTX * kTY, 2) bn_bwd_apply_kernel(const BwdArgs a) {
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int vcol = blockIdx.x * kTX + tx;
   if (vcol >= a.vecC) return;
-  float A[8], mg[8], mgx[8], mean[8], istd[8];
+  float A[8], mg[8], mgx[8], mean[8], istd[8], sh[8];
+  constexpr bool saved_mask = MASK == 1;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const int ch = vcol * 8 + k;
-    A[k] = a.coef[ch];
+    A[k] = a.coef[ch];                       // gamma * invstd == the forward's scale
     mg[k] = a.coef[a.C + ch];
     mgx[k] = a.coef[2 * a.C + ch];
     mean[k] = a.save_mean[ch];
     istd[k] = a.save_invstd[ch];
+    sh[k] = MASK == 2 ? load_param(a.beta, a.param_dtype, ch) - mean[k] * A[k] : 0.f;
   }
   const size_t r0 = (size_t)blockIdx.y * a.ck.rows_per_chunk;
   const size_t r1 = min(a.rows, r0 + (size_t)a.ck.rows_per_chunk);
@@ -416,10 +431,11 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_apply_kernel(const BwdArgs a
     float g[8], xv[8], yv[8];
     unpack8(gr, g);
     unpack8(xr, xv);
-    if (a.relu) unpack8(yr, yv);
+    if (saved_mask) unpack8(yr, yv);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const float gk = (a.relu && !(yv[k] > 0.f)) ? 0.f : g[k];
+      if constexpr (MASK == 2) yv[k] = fmaf(xv[k], A[k], sh[k]);
+      const float gk = (MASK != 0 && !(yv[k] > 0.f)) ? 0.f : g[k];
       g[k] = gk;
       xv[k] = A[k] * (gk - mg[k] - (xv[k] - mean[k]) * istd[k] * mgx[k]);
     }
@@ -434,7 +450,7 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_apply_kernel(const BwdArgs a
       const size_t i = (r + u * kTY) * a.vecC + vcol;
       gr[u] = ld_stream_16(a.dy + i);
       xr[u] = ld_stream_16(a.x + i);
-      if (a.relu) yr[u] = ld_stream_16(a.y + i);
+      if (saved_mask) yr[u] = ld_stream_16(a.y + i);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) one(gr[u], xr[u], yr[u], (r + u * kTY) * a.vecC + vcol);
@@ -442,7 +458,7 @@ __global__ void __launch_bounds__(kTX * kTY) bn_bwd_apply_kernel(const BwdArgs a
   for (; r < r1; r += kTY) {
     const size_t i = r * a.vecC + vcol;
     uint4 yr = make_uint4(0, 0, 0, 0);
-    if (a.relu) yr = ld_stream_16(a.y + i);
+    if (saved_mask) yr = ld_stream_16(a.y + i);
     one(ld_stream_16(a.dy + i), ld_stream_16(a.x + i), yr, i);
   }
 }
@@ -530,28 +546,37 @@ int tb200_bn_apply(const void* x, const void* residual, void* y, const float* sc
   return launched();
 }
 
-int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, int param_dtype,
-                 const float* save_mean, const float* save_invstd, void* dx, void* dres,
+int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,
+                 int param_dtype, const float* save_mean, const float* save_invstd, void* dx, void* dres,
                  void* dgamma, void* dbeta, float* scratch, size_t rows, int C, int relu,
                  cudaStream_t stream) {
   if (int rc = check_shape("tb200_bn_bwd", rows, C)) return rc;
-  if (relu && !y) return fail("tb200_bn_bwd: relu needs the forward output%s");
+  if (relu && !y && !beta) return fail("tb200_bn_bwd: relu needs the forward output, or beta to recompute it%s");
+  if (relu && !y && dres) return fail("tb200_bn_bwd: a layer with a residual input must pass its forward output%s");
   const int groups = (C + kGroup - 1) / kGroup;
   BwdArgs b{};
   b.dy = reinterpret_cast<const uint4*>(dy); b.x = reinterpret_cast<const uint4*>(x);
   b.y = reinterpret_cast<const uint4*>(y); b.dx = reinterpret_cast<uint4*>(dx);
   b.dres = reinterpret_cast<uint4*>(dres);
   b.rows = rows; b.C = C; b.vecC = C / 8; b.ck = plan_chunks(rows, C, groups, 4, 296); b.relu = relu;
-  b.gamma = gamma; b.param_dtype = param_dtype; b.save_mean = save_mean; b.save_invstd = save_invstd;
+  b.gamma = gamma; b.beta = beta; b.param_dtype = param_dtype; b.save_mean = save_mean; b.save_invstd = save_invstd;
+  b.recompute_mask = (relu && !y) ? 1 : 0;
   b.dgamma = dgamma; b.dbeta = dbeta;
   b.counters = reinterpret_cast<uint32_t*>(scratch);
   b.partials = scratch + kCounterWords;
   b.coef = scratch + kCounterWords + kMaxPartialFloats;
   const dim3 block(kTX, kTY);
-  bn_bwd_reduce_kernel<<<dim3(groups, b.ck.nchunks), block, 0, stream>>>(b);
+  const int mask = !relu ? 0 : (b.recompute_mask ? 2 : 1);
+  const dim3 rgrid(groups, b.ck.nchunks);
+  if (mask == 0) bn_bwd_reduce_kernel<0><<<rgrid, block, 0, stream>>>(b);
+  else if (mask == 1) bn_bwd_reduce_kernel<1><<<rgrid, block, 0, stream>>>(b);
+  else bn_bwd_reduce_kernel<2><<<rgrid, block, 0, stream>>>(b);
   if (int rc = launched()) return rc;
   b.ck = plan_chunks(rows, C, groups, 8, 4096);
-  bn_bwd_apply_kernel<<<dim3(groups, b.ck.nchunks), block, 0, stream>>>(b);
+  const dim3 agrid(groups, b.ck.nchunks);
+  if (mask == 0) bn_bwd_apply_kernel<0><<<agrid, block, 0, stream>>>(b);
+  else if (mask == 1) bn_bwd_apply_kernel<1><<<agrid, block, 0, stream>>>(b);
+  else bn_bwd_apply_kernel<2><<<agrid, block, 0, stream>>>(b);
   return launched();
 }
 

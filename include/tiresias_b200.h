@@ -202,7 +202,9 @@ int tb200_sumsq(const void* x, int dtype, size_t n, float* partials, float* out,
  *              the backward. running_mean / running_var may be NULL.
  *   apply:     y = relu?(x*scale[c] + shift[c] + residual?) with scale_shift = [scale | shift]
  *              (inference, or any per-channel affine).
- *   bwd:       g = dy * (y > 0 if relu); dx, dres = g (may be NULL), dgamma, dbeta.              */
+ *   bwd:       g = dy * (y > 0 if relu); dx, dres = g (may be NULL), dgamma, dbeta. For a ReLU layer
+ *              WITHOUT residual input, y may be NULL: the mask is then recomputed from x with the
+ *              forward's own fp32 fma (needs beta), which saves one activation read per pass.      */
 #define TB200_BN_SCRATCH_FLOATS (1024 + 2 * 64 * 1024 + 4 * 4096)
 size_t tb200_bn_scratch_floats(void);
 int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void* gamma,
@@ -211,10 +213,19 @@ int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void*
                        float* scratch, size_t rows, int C, int relu, cudaStream_t stream);
 int tb200_bn_apply(const void* x, const void* residual, void* y, const float* scale_shift,
                    size_t rows, int C, int relu, cudaStream_t stream);
-int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, int param_dtype,
-                 const float* save_mean, const float* save_invstd, void* dx, void* dres,
+int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,
+                 int param_dtype, const float* save_mean, const float* save_invstd, void* dx, void* dres,
                  void* dgamma, void* dbeta, float* scratch, size_t rows, int C, int relu,
                  cudaStream_t stream);
+
+/* ---- 3x3 / stride 2 / pad 1 max pooling, NHWC bf16 (ResNet stem). C % 8 == 0. The forward also writes
+ * `argmax` (one byte per output element: kh*3+kw of the window's first maximum, torch's tie rule; may be
+ * NULL for inference); the backward gathers with it — deterministic, no atomics. N, H, W, C describe the
+ * INPUT of the pooling in both calls.                                                                 */
+int tb200_maxpool3x3s2_fwd(const void* x, void* out, void* argmax, int N, int H, int W, int C,
+                           cudaStream_t stream);
+int tb200_maxpool3x3s2_bwd(const void* argmax, const void* dout, void* dx, int N, int H, int W, int C,
+                           cudaStream_t stream);
 
 #ifdef __cplusplus
 }

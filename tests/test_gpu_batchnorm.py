@@ -123,3 +123,22 @@ def test_resnet50_fused_vs_stock_forward(cuda_device):
     x = torch.randn(8, 3, 96, 96, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     yf, ys = fused(x).float(), stock(x).float()
     assert torch.allclose(yf, ys, rtol=5e-2, atol=8e-2), (yf - ys).abs().max().item()
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 112, 112), (3, 16, 9, 7), (1, 8, 5, 6), (2, 24, 2, 2)])
+def test_maxpool3x3s2_matches_torch_including_ties(cuda_device, shape):
+    from tiresias_b200.ops.pooling import MaxPool3x3S2
+    g = torch.Generator(device=cuda_device).manual_seed(sum(shape))
+    # post-ReLU-like input: many exact zeros and (bf16) repeated values => plenty of ties
+    x = torch.relu(torch.randn(shape, device=cuda_device, generator=g)).mul(4).round().div(4).to(torch.bfloat16)
+    x = x.contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = MaxPool3x3S2()(x)
+    dy = torch.randn(y.shape, device=cuda_device, generator=g).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_(True)
+    yr = torch.nn.functional.max_pool2d(xr, 3, 2, 1)
+    yr.backward(dy.float())
+    assert torch.equal(y.float(), yr)
+    # torch accumulates several windows' gradients in fp32; ours in fp32 then rounds once to bf16
+    assert torch.allclose(x.grad.float(), xr.grad, rtol=1e-2, atol=2e-2), (x.grad.float() - xr.grad).abs().max().item()
+    assert abs(float(x.grad.float().sum()) - float(dy.float().sum())) < 0.05 * dy.numel() ** 0.5 + 1.0

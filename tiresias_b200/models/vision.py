@@ -15,6 +15,7 @@ from torch import nn
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
 from ..ops.linear import TcLinear
+from ..ops.pooling import MaxPool3x3S2
 
 
 class TorchBNAct(nn.Module):
@@ -72,7 +73,7 @@ class ResNet(nn.Module):
     def __init__(self, depths: Sequence[int], num_classes: int = 1000, fused: bool = True):
         super().__init__()
         self.stem_conv, self.stem_bn = _conv(3, 64, 7, 2, 3), _bn(64, True, fused)
-        self.stem_pool = nn.MaxPool2d(3, 2, 1)
+        self.stem_pool = MaxPool3x3S2() if fused else nn.MaxPool2d(3, 2, 1)
         blocks: List[nn.Module] = []
         cin = 64
         for i, (n, width) in enumerate(zip(depths, (64, 128, 256, 512))):

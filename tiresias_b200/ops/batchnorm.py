@@ -53,12 +53,13 @@ class _FusedBNFn(torch.autograd.Function):
             float(momentum), float(eps), save_mean.data_ptr(), save_invstd.data_ptr(),
             scratch.data_ptr(), rows, c, int(relu), native.stream_ptr()))
         ctx.relu, ctx.has_res, ctx.rows, ctx.c = bool(relu), residual is not None, rows, c
-        ctx.save_for_backward(x, y if relu else None, gamma, save_mean, save_invstd)
+        # the ReLU mask of a layer without residual input is recomputed from x in the backward
+        ctx.save_for_backward(x, y if (relu and residual is not None) else None, gamma, beta, save_mean, save_invstd)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, gamma, save_mean, save_invstd = ctx.saved_tensors
+        x, y, gamma, beta, save_mean, save_invstd = ctx.saved_tensors
         dy, _, _ = _rows_channels(dy)
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.has_res else None
@@ -67,7 +68,7 @@ class _FusedBNFn(torch.autograd.Function):
         scratch = _get_scratch(x.device)
         native.check(native.lib().tb200_bn_bwd(
             dy.data_ptr(), x.data_ptr(), y.data_ptr() if y is not None else 0, gamma.data_ptr(),
-            native.dtype_code(gamma.dtype), save_mean.data_ptr(), save_invstd.data_ptr(), dx.data_ptr(),
+            beta.data_ptr(), native.dtype_code(gamma.dtype), save_mean.data_ptr(), save_invstd.data_ptr(), dx.data_ptr(),
             dres.data_ptr() if dres is not None else 0, dgamma.data_ptr(), dbeta.data_ptr(),
             scratch.data_ptr(), ctx.rows, ctx.c, int(ctx.relu), native.stream_ptr()))
         return dx, dres, dgamma, dbeta, None, None, None, None, None

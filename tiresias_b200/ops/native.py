@@ -94,6 +94,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_u8_to_bf16_norm_pad8.argtypes = [vp, vp, sz, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
     lib.tb200_u8_to_bf16_norm_pad8.restype = C.c_int
     lib.tb200_transpose_bf16.argtypes = [vp, vp, C.c_int, C.c_int, st]
+    lib.tb200_maxpool3x3s2_fwd.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, st]
+    lib.tb200_maxpool3x3s2_fwd.restype = C.c_int
+    lib.tb200_maxpool3x3s2_bwd.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, st]
+    lib.tb200_maxpool3x3s2_bwd.restype = C.c_int
     lib.tb200_pack_bf16.argtypes = [C.POINTER(PackItem), C.c_int, st]
     lib.tb200_pack_bf16.restype = C.c_int
     lib.tb200_sumsq_scratch_floats.restype = C.c_size_t
@@ -102,7 +106,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_bn_fwd_train.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_float, C.c_float, vp, vp, vp,
                                        sz, C.c_int, C.c_int, st]
     lib.tb200_bn_apply.argtypes = [vp, vp, vp, vp, sz, C.c_int, C.c_int, st]
-    lib.tb200_bn_bwd.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, sz, C.c_int, C.c_int, st]
+    lib.tb200_bn_bwd.argtypes = [vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, sz, C.c_int, C.c_int, st]
     for name in ("tb200_symm_alloc", "tb200_symm_free", "tb200_ipc_export", "tb200_ipc_open",
                  "tb200_ipc_close", "tb200_enable_peer_access", "tb200_flags_fill",
                  "tb200_sgd_momentum", "tb200_ps_push_pull", "tb200_step_end", "tb200_allreduce",
