@@ -122,7 +122,7 @@ struct FwdArgs {
   float* coef;                 // [0,C) scale, [C,2C) shift
 };
 
-__global__ void __launch_bounds__(kTX * kTY) bn_stats_kernel(const FwdArgs a) {
+__global__ void __launch_bounds__(kTX * kTY, 2) bn_stats_kernel(const FwdArgs a) {
   __shared__ float smem[2][kTY][kGroup];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int cg = blockIdx.x, chunk = blockIdx.y;
@@ -134,14 +134,16 @@ __global__ void __launch_bounds__(kTX * kTY) bn_stats_kernel(const FwdArgs a) {
   if (col_ok) {
     const uint4* p = a.x + vcol;
     size_t r = r0 + ty;
-    for (; r + 3 * kTY < r1; r += 4 * kTY) {
-      uint4 v0 = ld_stream_16(p + r * a.vecC), v1 = ld_stream_16(p + (r + kTY) * a.vecC);
-      uint4 v2 = ld_stream_16(p + (r + 2 * kTY) * a.vecC), v3 = ld_stream_16(p + (r + 3 * kTY) * a.vecC);
-      float f[8];
 #define TB_ACC(V)                                                              \
   unpack8(V, f);                                                               \
   _Pragma("unroll") for (int k = 0; k < 8; ++k) { acc[0][k] += f[k]; acc[1][k] += f[k] * f[k]; }
-      TB_ACC(v0) TB_ACC(v1) TB_ACC(v2) TB_ACC(v3)
+    for (; r + 7 * kTY < r1; r += 8 * kTY) {      // eight independent 16-byte loads in flight per thread
+      uint4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = ld_stream_16(p + (r + u * kTY) * a.vecC);
+      float f[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { TB_ACC(v[u]) }
     }
     for (; r < r1; r += kTY) {
       uint4 v0 = ld_stream_16(p + r * a.vecC);
@@ -515,7 +517,7 @@ int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void*
   FwdArgs f{};
   f.x = reinterpret_cast<const uint4*>(x);
   f.rows = rows; f.C = C; f.vecC = C / 8;
-  f.ck = plan_chunks(rows, C, groups, 4, 296);
+  f.ck = plan_chunks(rows, C, groups, 6, 296);
   f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype;
   f.running_mean = running_mean; f.running_var = running_var;
   f.momentum = momentum; f.eps = eps;

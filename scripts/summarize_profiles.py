@@ -28,8 +28,11 @@ SASS = re.compile(r"\b(UTC[A-Z]*MMA|LDTM|STTM|UTMALDG|UTMASTG|UBLKCP|UTCBAR|SYNC
 
 
 def ncu_rows(rep):
-    res = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
-    rows = list(csv.reader(io.StringIO(res.stdout)))
+    if rep.endswith(".raw.csv"):
+        text = open(rep).read()
+    else:
+        text = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(text)))
     if len(rows) < 3:
         return []
     hdr, units = rows[0], rows[1]
@@ -52,11 +55,17 @@ def ncu_rows(rep):
 def write_ncu(tag):
     lines = [f"# ncu --set full captures ({tag}; --clock-control none; 3 launches per kernel after warm-up)", "",
              "| capture | kernel | " + " | ".join(s for _, s in METRICS) + " |", "|---|---|" + "---|" * len(METRICS)]
-    for rep in sorted(glob.glob(os.path.join(GP, "prof_*.ncu-rep"))):
-        name = os.path.basename(rep)[5:-8]
+    for rep in sorted(glob.glob(os.path.join(GP, "prof_*.raw.csv")) or glob.glob(os.path.join(GP, "prof_*.ncu-rep"))):
+        name = os.path.basename(rep)[5:].replace(".raw.csv", "").replace(".ncu-rep", "")
         for d in ncu_rows(rep):
             lines.append(f"| {name} | `{d['kernel'][:60]}` | " + " | ".join(d.get(s, "") for _, s in METRICS) + " |")
     open(os.path.join(OUT, f"ncu_summary_{tag}.md"), "w").write("\n".join(lines) + "\n")
+    tops = sorted(glob.glob(os.path.join(GP, "prof_*.top_sass.txt")))
+    if tops:
+        with open(os.path.join(OUT, f"ncu_hot_sass_{tag}.txt"), "w") as fh:
+            fh.write("Most-sampled SASS instructions per captured kernel (ncu --page source, warp stall sampling)\n\n")
+            for t in tops:
+                fh.write(f"#### {os.path.basename(t)[5:-13]}\n" + open(t).read() + "\n")
 
 
 def write_sass(tag):
