@@ -12,6 +12,8 @@ echo "== calib exit $?"; tail -n 4 gpurun_out/replay/calib.log | cut -c1-600
 python scripts/make_exec_trace.py gpurun_out/replay/trace.csv --jobs $JOBS --seed 0 --mean-gap ${GAP:-1.2}
 timeout 1200 python -m tiresias_b200.exec.replay --trace gpurun_out/replay/trace.csv --gpus $N --schedule $SCHED --comm $COMM \
   --batch ${BATCH:-32} --calibration gpurun_out/replay/calibration_$COMM.json --out gpurun_out/replay/run_${SCHED}_$COMM \
+  --queue-limit ${QLIMIT:-20} --check-every ${CHECK_EVERY:-10} \
   > gpurun_out/replay/replay.log 2>&1
 echo "== replay exit $?"; tail -n 6 gpurun_out/replay/replay.log | cut -c1-600
-tail -n 20 gpurun_out/replay/run_${SCHED}_$COMM/pool.log | cut -c1-300
+tail -n 6 gpurun_out/replay/run_${SCHED}_$COMM/pool.log | cut -c1-300
+rm -rf gpurun_out/replay/calib_work/calib_run/sim gpurun_out/replay/run_${SCHED}_$COMM/sim
