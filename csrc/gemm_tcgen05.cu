@@ -154,12 +154,28 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
   return d;
 }
 
-// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32, both operands K-major.
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int umma_m, int umma_n) {
+// Shared-memory matrix descriptor for an MN-major operand (the non-reduction dimension is the
+// contiguous one, e.g. W[N_red, K_out] used as the B of dx = dy . W). The tile is stored as slabs of
+// 64 MN-elements x BLOCK_K reduction rows (each slab one TMA box of 128-byte rows, 128-byte swizzle):
+// inside a slab 8 reduction rows form one 1024-byte swizzle atom (stride byte offset), slabs are
+// 64*128 = 8192 bytes apart (leading byte offset). Canonical form ((8,n),(8,k)):((1,LBO),(8,SBO)) in
+// 16-byte units, cute::UMMA::make_umma_desc<Major::MN>.
+__device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3ffff) >> 4);
+  d |= (uint64_t)(8192 >> 4) << 16;                   // leading byte offset: next 64-wide MN slab
+  d |= (uint64_t)(1024 >> 4) << 32;                   // stride byte offset: next 8 reduction rows
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32; a_mn / b_mn select MN-major operands.
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int umma_m, int umma_n, int a_mn = 0, int b_mn = 0) {
   return (1u << 4)                       // D format  = F32
          | (1u << 7)                     // A format  = BF16
          | (1u << 10)                    // B format  = BF16
-         | (0u << 15) | (0u << 16)       // A, B K-major
+         | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16)       // 0 = K-major, 1 = MN-major
          | ((uint32_t)(umma_n >> 3) << 17) | ((uint32_t)(umma_m >> 4) << 24);
 }
 
@@ -188,6 +204,7 @@ struct GemmParams {
   int d_dtype;
   int act;
   int direct_store;   // 1: per-thread global stores (row stride not 16-byte aligned); 0: TMA store
+  int a_mn, b_mn;     // operand is stored [K, M] / [K, N] (non-reduction dimension contiguous)
   // pull variant
   int rows_per_rank;
   int world;
@@ -348,15 +365,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1);
         mbar_expect_tx(full_bar(stage), C::kStageBytes);
-        tma_load_2d(a_smem + stage * C::kABytes, &map_a, full_bar(stage), kb * BLOCK_K,
-                    m_blk * BLOCK_M);
-        tma_load_2d(b_smem + stage * C::kBBytes, bmap, full_bar(stage), kb * BLOCK_K, b_row);
+        if (!p.a_mn) {
+          tma_load_2d(a_smem + stage * C::kABytes, &map_a, full_bar(stage), kb * BLOCK_K,
+                      m_blk * BLOCK_M);
+        } else {
+#pragma unroll
+          for (int sl = 0; sl < BLOCK_M / 64; ++sl)           // 64-wide slabs of the [K, M] matrix
+            tma_load_2d(a_smem + stage * C::kABytes + sl * 8192, &map_a, full_bar(stage),
+                        m_blk * BLOCK_M + sl * 64, kb * BLOCK_K);
+        }
+        if (!p.b_mn) {
+          tma_load_2d(b_smem + stage * C::kBBytes, bmap, full_bar(stage), kb * BLOCK_K, b_row);
+        } else {
+#pragma unroll
+          for (int sl = 0; sl < BLOCK_N / 64; ++sl)
+            tma_load_2d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage), b_row + sl * 64,
+                        kb * BLOCK_K);
+        }
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1 && lane == 0) {
     // ================= MMA issuer =================
-    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N);
+    const uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, p.a_mn, p.b_mn);
+    // advancing the reduction index by UMMA_K = 16: 32 bytes inside a K-major swizzle atom, two whole
+    // 1024-byte atoms for an MN-major operand (descriptor addresses are in 16-byte units)
+    const uint32_t a_step = p.a_mn ? 128u : 2u, b_step = p.b_mn ? 128u : 2u;
     int stage = 0;
     uint32_t phase = 0;
     int as = 0;
@@ -371,13 +405,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        const uint64_t adesc = make_kmajor_sw128_desc(a_smem + stage * C::kABytes);
-        const uint64_t bdesc = make_kmajor_sw128_desc(b_smem + stage * C::kBBytes);
+        const uint64_t adesc = p.a_mn ? make_mnmajor_sw128_desc(a_smem + stage * C::kABytes)
+                                      : make_kmajor_sw128_desc(a_smem + stage * C::kABytes);
+        const uint64_t bdesc = p.b_mn ? make_mnmajor_sw128_desc(b_smem + stage * C::kBBytes)
+                                      : make_kmajor_sw128_desc(b_smem + stage * C::kBBytes);
 #pragma unroll
-        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-          // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in 16-byte units
-          tc_mma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-        }
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+          tc_mma_bf16(tmem_d, adesc + a_step * k, bdesc + b_step * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         tc_commit(empty_bar(stage));  // smem stage reusable once these MMAs have read it
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
       }
@@ -587,6 +621,21 @@ int make_map(CUtensorMap* out, const void* base, int rows, int cols, int box_row
   return 0;
 }
 
+// [k_rows, mn_cols] bf16 row-major matrix of an MN-major operand: box = 64 reduction rows x 64 columns.
+int make_map_mn(CUtensorMap* out, const void* base, int k_rows, int mn_cols) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail("cuTensorMapEncodeTiled entry point not available%s");
+  cuuint64_t dims[2] = {(cuuint64_t)mn_cols, (cuuint64_t)k_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)mn_cols * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)BLOCK_K};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled (MN-major) failed (%s code %ld)", "", (long)r);
+  return 0;
+}
+
 // Output tensor map for the epilogue's TMA stores: rows of `cols` elements, box = 32 rows x 128 bytes,
 // 128-byte swizzle. `planes` > 1 adds a third dimension (split-K partial planes of M x N fp32).
 int make_out_map(CUtensorMap* out, const void* base, int rows, int cols, bool f32, int planes) {
@@ -660,15 +709,29 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
                 const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M,
                 int N, int K, int d_dtype, int act, const uint32_t* epoch_dev, int* status_dev,
                 unsigned long long budget, cudaStream_t stream, float* fixed_scratch = nullptr,
-                size_t fixed_scratch_bytes = 0) {
+                size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0) {
   const bool pull = world != nullptr;
   if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
-  if (K % 8) return fail("tb200_gemm: K %s(%ld) must be a multiple of 8", "", K);
+  // cuTensorMapEncodeTiled is a driver call and needs the primary context bound to THIS thread; a thread
+  // that has made no runtime call yet (e.g. autograd's backward thread, when the GEMM is the first thing
+  // it runs) has none. cudaFree(0) binds it; once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    TB_CUDA_OK(cudaFree(nullptr));
+    ctx_bound = true;
+  }
+  // TMA needs 16-byte row strides: the contiguous dimension of each operand must be a multiple of 8
+  if (!a_mn && K % 8) return fail("tb200_gemm: K %s(%ld) must be a multiple of 8", "", K);
+  if (!b_mn && K % 8) return fail("tb200_gemm: K %s(%ld) must be a multiple of 8", "", K);
+  if (a_mn && M % 8) return fail("tb200_gemm: M %s(%ld) must be a multiple of 8 for an MN-major A", "", M);
+  if (b_mn && N % 8) return fail("tb200_gemm: N %s(%ld) must be a multiple of 8 for an MN-major B", "", N);
+  if (pull && (a_mn || b_mn)) return fail("tb200_gemm_pull: operands must be K-major%s");
   if (d_dtype != TB200_BF16 && d_dtype != TB200_F32) return fail("tb200_gemm: bad output dtype%s");
 
   GemmParams p{};
   p.M = M; p.N = N; p.K = K;
   p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
+  p.a_mn = a_mn; p.b_mn = b_mn;
   p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
 
@@ -732,7 +795,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   }
   PullMaps pm;
   memset(&pm, 0, sizeof(pm));
-  if (int rc = make_map(&ma, A, M, K, BLOCK_M)) return rc;
+  if (int rc = a_mn ? make_map_mn(&ma, A, K, M) : make_map(&ma, A, M, K, BLOCK_M)) return rc;
   if (pull) {
     p.rows_per_rank = rows_per_rank;
     p.world = world->world;
@@ -756,7 +819,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
     if (int rc = make_map(&pm.b_local, local, N, K, block_n)) return rc;
     mb = pm.b_local;
   } else {
-    if (int rc = make_map(&mb, B, N, K, block_n)) return rc;
+    if (int rc = b_mn ? make_map_mn(&mb, B, K, N) : make_map(&mb, B, N, K, block_n)) return rc;
   }
 
   const int items = tiles * splits;
@@ -786,6 +849,12 @@ int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, 
                        int M, int N, int K, int d_dtype, int act, cudaStream_t stream) {
   return gemm_common(nullptr, 0, 0, 0, A, B, D, bias, bias_dtype, M, N, K, d_dtype, act, nullptr,
                      nullptr, 0, stream);
+}
+
+int tb200_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
+                    int K, int a_mn_major, int b_mn_major, int d_dtype, int act, cudaStream_t stream) {
+  return gemm_common(nullptr, 0, 0, 0, A, B, D, bias, bias_dtype, M, N, K, d_dtype, act, nullptr, nullptr, 0,
+                     stream, nullptr, 0, a_mn_major ? 1 : 0, b_mn_major ? 1 : 0);
 }
 
 int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off,

@@ -124,6 +124,15 @@ int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD
 int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, int bias_dtype,
                        int M, int N, int K, int d_dtype, int act, cudaStream_t stream);
 
+/* Same kernel with selectable operand layouts: D[M,N] = act(op(A) . op(B)^T + bias) where A is stored
+ * [M,K] (a_mn_major = 0, K contiguous) or [K,M] (a_mn_major = 1, M contiguous), and B is stored [N,K]
+ * (b_mn_major = 0) or [K,N] (b_mn_major = 1). The linear layer's backward needs no transposes:
+ *   dx[M,K] = dy[M,N] . W[N,K]      -> A = dy (K-major over N),  B = W with b_mn_major = 1
+ *   dW[N,K] = dy[M,N]^T . x[M,K]    -> A = dy with a_mn_major = 1, B = x with b_mn_major = 1
+ * The contiguous dimension of every operand must be a multiple of 8.                               */
+int tb200_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
+                    int K, int a_mn_major, int b_mn_major, int d_dtype, int act, cudaStream_t stream);
+
 /* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
 int tb200_gemm_reserve(size_t bytes);
 

@@ -236,3 +236,19 @@ def test_pack_bf16_gathers_many_tensors(cuda_device):
     native.check(native.lib().tb200_pack_bf16(one, 1, native.stream_ptr()))
     torch.cuda.synchronize()
     assert torch.equal(dst[1:51], srcs[3][:50]) and float(dst[0]) == 0.0
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 128, 64), (256, 384, 512), (200, 136, 72), (1024, 2048, 512), (8192, 512, 2048),
+                                   (64, 1000, 2048)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+def test_gemm_operand_layouts_match_fp32(cuda_device, m, n, k, a_mn, b_mn):
+    if (a_mn and m % 8) or (b_mn and n % 8):
+        pytest.skip("MN-major operands need a contiguous dimension that is a multiple of 8")
+    g = torch.Generator(device=cuda_device).manual_seed(m + n + k)
+    a = torch.randn(m, k, device=cuda_device, generator=g).to(torch.bfloat16)
+    b = (torch.randn(n, k, device=cuda_device, generator=g) / k ** 0.5).to(torch.bfloat16)
+    a_arg = a.t().contiguous() if a_mn else a
+    b_arg = b.t().contiguous() if b_mn else b
+    got = native.gemm(a_arg, b_arg, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32)
+    ref = a.float() @ b.float().t()
+    assert torch.allclose(got, ref, rtol=2e-2, atol=2e-2), (got - ref).abs().max().item()

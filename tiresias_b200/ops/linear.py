@@ -1,8 +1,9 @@
 """Linear layers on the hand-written tcgen05 GEMM (K5).
 
 Forward  : y  = act(x @ W^T + b)              one NT GEMM, bias/activation in the epilogue
-Backward : dx = dy @ W      = NT(dy, W^T)     W^T from the tiled transpose kernel
-           dW = dy^T @ x    = NT(dy^T, x^T)
+Backward : dx = dy @ W                        W consumed as stored (MN-major B descriptor)
+           dW = dy^T @ x                      dy and x consumed as stored (MN-major A and B)
+           (widths that are not multiples of 8 fall back to explicit transposes + the NT GEMM)
 The FC shapes that dominate the reference's model table (core/models.py:9-11: VGG fc6
 25088x4096 = 392 MB fp32, fc7 4096x4096, fc8 4096x1000) all run through here.
 """
@@ -65,15 +66,22 @@ class _TcLinearFn(torch.autograd.Function):
             raise NotImplementedError("fused GELU backward: use act=ACT_NONE + torch gelu")
         m = dy.shape[0]
         dx = dw = db = None
+        n_out, k_in = weight.shape
+        mn_ok = n_out % 8 == 0 and k_in % 8 == 0       # MN-major operands need 16-byte row strides
         if ctx.needs_input_grad[0]:
-            dx = native.gemm_nt(dy, native.transpose(weight))            # [M,N] x [K,N]^T
+            if mn_ok:
+                dx = native.gemm(dy, weight, b_mn_major=True)            # dy[M,N] . W[N,K], W read as stored
+            else:
+                dx = native.gemm_nt(dy, native.transpose(weight))
         if ctx.needs_input_grad[1]:
-            # the GEMM's reduction dim is the batch here; TMA needs it to be a multiple of 8
-            dyt = native.transpose(_pad_rows(dy, 8))                      # [N,M']
-            xt = native.transpose(_pad_rows(x2d, 8))                      # [K,M']
-            dw = native.gemm_nt(dyt, xt)                                  # [N,K]
+            if mn_ok:
+                dw = native.gemm(dy, x2d, a_mn_major=True, b_mn_major=True)   # dy^T . x, no transposes
+            else:
+                dyt = native.transpose(_pad_rows(dy, 8))                  # [N,M']
+                xt = native.transpose(_pad_rows(x2d, 8))                  # [K,M']
+                dw = native.gemm_nt(dyt, xt)                              # [N,K]
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dy.float().sum(dim=0).to(dy.dtype)
+            db = dy.sum(dim=0, dtype=torch.float32).to(dy.dtype)
         return dx, dw, db, None, None
 
 

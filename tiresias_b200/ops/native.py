@@ -85,6 +85,9 @@ def _declare(lib: C.CDLL) -> None:
                                     u32p, ip, C.c_ulonglong, C.c_int, st]
     lib.tb200_gemm_bf16_nt.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_int, st]
+    lib.tb200_gemm_bf16.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_int, st]
+    lib.tb200_gemm_bf16.restype = C.c_int
     lib.tb200_gemm_reserve.argtypes = [sz]
     lib.tb200_gemm_bf16_nt_pull.argtypes = [C.POINTER(World), C.c_int, sz, C.c_int, vp, vp, vp,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -189,6 +192,25 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
         bias_ptr, bias_dt = bias.data_ptr(), dtype_code(bias.dtype)
     check(lib().tb200_gemm_bf16_nt(a.data_ptr(), b.data_ptr(), out.data_ptr(), bias_ptr, bias_dt,
                                    m, n, k, dtype_code(out.dtype), act, stream_ptr()))
+    return out
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, a_mn_major: bool = False, b_mn_major: bool = False,
+         bias: Optional[torch.Tensor] = None, act: int = ACT_NONE, out_dtype: torch.dtype = torch.bfloat16,
+         out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K5 with selectable operand layouts. ``a`` is [M,K] (or [K,M] when ``a_mn_major``), ``b`` is [N,K]
+    (or [K,N] when ``b_mn_major``); returns ``act(A @ B^T + bias)`` as [M,N]."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
+    k, m = (a.shape if a_mn_major else a.shape[::-1])
+    kb, n = (b.shape if b_mn_major else b.shape[::-1])
+    assert k == kb, (a.shape, b.shape)
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    bias_ptr, bias_dt = 0, F32
+    if bias is not None:
+        bias_ptr, bias_dt = bias.data_ptr(), dtype_code(bias.dtype)
+    check(lib().tb200_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), bias_ptr, bias_dt, m, n, k,
+                                int(a_mn_major), int(b_mn_major), dtype_code(out.dtype), act, stream_ptr()))
     return out
 
 
