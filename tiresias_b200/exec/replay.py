@@ -99,6 +99,12 @@ def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, g
             "--num_gpu_p_node", str(gpus), "--quiet"]
     if schedule == "dlas-gpu":
         argv += ["--queue_limit", ",".join(str(int(q * MS)) for q in queue_limit_s)]
+    if schedule != "fifo":
+        # restart cost of a resumed job, measured in this very replay: start-up + shard snapshot
+        pre = [r for r in records if r.get("preempt")]
+        if pre:
+            over = sum((r.get("startup_s") or 0.0) + (r.get("snapshot_s") or 0.0) for r in pre) / len(pre)
+            argv += ["--resume_overhead", str(int(round(over * MS)))]
     flags.parse(argv)
     os.makedirs(out_dir, exist_ok=True)
     from ..cli.run_sim import _attach_logging
@@ -184,6 +190,7 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
     sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"),
                    "buddy" if schedule == "fifo" else "count")
     result = {"trace": trace, "gpus": gpus, "schedule": schedule, "comm": comm, "loopback": loopback,
+              "queue_limit_s": list(queue_limit_s),
               "wall_s": round(wall, 2), "calibration_source": calibration.get("source", calibration_path),
               "records": records, "comparison": compare(records, sim)}
     with open(os.path.join(out, "replay.json"), "w") as fh:
@@ -203,8 +210,8 @@ def resimulate(out: str, calibration_path: Optional[str] = None, scheme: str = "
             calibration = json.load(fh)
     else:
         calibration = calibration_from_records(res["records"])
-    sim = simulate(rows, res["records"], calibration, res["gpus"], res["schedule"], (20.0,),
-                   os.path.join(out, "sim_" + scheme), scheme)
+    sim = simulate(rows, res["records"], calibration, res["gpus"], res["schedule"],
+                   res.get("queue_limit_s") or (20.0,), os.path.join(out, "sim_" + scheme), scheme)
     res["comparison"] = compare(res["records"], sim)
     res["sim_scheme"] = scheme
     with open(os.path.join(out, "replay.json"), "w") as fh:

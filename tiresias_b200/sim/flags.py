@@ -131,6 +131,8 @@ def define_simulator_flags(fs: Optional[FlagSet] = None) -> FlagSet:
     fs.define_boolean("gittins_desc", False, "gittins: highest index first (the reference's loop sorts "
                                              "ascending, its dlas-gpu-gittins variant descending)")
     fs.define_float("solve_starvation", 0, "DLAS starvation knob: promote when pending >= x * executed")
+    fs.define_integer("resume_overhead", 0, "time units charged to a job each time it resumes after a "
+                                            "preemption (measured restart cost; 0 = free, as in the reference)")
     fs.define_string("calibration", None, "calibration json produced by tiresias_b200.calib")
     fs.define_string("comm", "ps", "communication mode priced/executed for distributed jobs: ps | ring")
     fs.define_boolean("quiet", False, "do not mirror the log to stderr")

@@ -81,6 +81,9 @@ def _earliest_completion(runnable: List[TJob], event_time: int) -> Optional[dict
     return event
 
 
+RESUME_OVERHEAD = 0      # time units added to a job each time it resumes after a preemption (0 = reference)
+
+
 def _apply_switches(preempt_jobs: List[TJob], run_jobs: List[TJob], event_time: Optional[int]) -> None:
     for j in preempt_jobs:
         j.status = "PENDING"
@@ -88,6 +91,12 @@ def _apply_switches(preempt_jobs: List[TJob], run_jobs: List[TJob], event_time: 
     for j in run_jobs:
         j.status = "RUNNING"
         j.resume = int(j.resume + 1)
+        if RESUME_OVERHEAD and j.preempt > 0 and j.total_executed_time > 0:
+            # The reference prices preemption at zero (progress simply continues). On real
+            # GPUs a resumed job rebuilds its model, re-exchanges IPC handles and reloads its PS shards:
+            # the measured restart cost (calibration "resume_overhead") is charged as extra work.
+            j.duration = int(j.duration + RESUME_OVERHEAD)
+            j.remaining_time = int(j.duration - j.total_executed_time)
         if event_time is not None and j.start_time == MAXSIZE:
             j.start_time = event_time
 
@@ -553,6 +562,8 @@ def gpu_demands(sim: Sim) -> None:
 
 def dispatch(sim: Sim) -> None:
     """``--schedule`` -> loop (run_sim.py's README-documented names)."""
+    global RESUME_OVERHEAD
+    RESUME_OVERHEAD = int(getattr(sim.flags, "resume_overhead", 0) or 0)
     s = sim.flags.schedule
     starve = float(getattr(sim.flags, "solve_starvation", 0) or 0)
     if s in ("fifo", "fjf"):
