@@ -1,0 +1,152 @@
+#!/usr/bin/env python
+"""Communication microbenchmark over real NVLink: the fused PS push/pull kernel and the in-kernel
+all-reduce against their NCCL equivalents, with the achieved fraction of the NVLink roofline.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 bench/comm.py
+
+Per bucket size (bf16 elements, the same on every rank):
+  ours/ps     tb200_ps_push_pull  : every rank reduces its shard of all W gradient buffers over NVLink,
+                                    applies SGD+momentum on its fp32 master shard and stores the new bf16
+                                    parameters into all W parameter buffers (+ tb200_step_end)
+  nccl/ps     reduce_scatter_tensor + torch SGD on the shard + all_gather_into_tensor
+  ours/ring   tb200_allreduce algo 0 (ring) and algo 1 (direct two-shot)
+  nccl/ar     all_reduce
+Roofline: per GPU the push moves (W-1)/W * n * 2 bytes in and the pull the same amount out, each direction
+at the measured 770 GB/s peer-copy bandwidth (B200_PROFILING.md); the HBM side (fp32 master + momentum,
+16 bytes per shard element, plus the local bf16 traffic) runs at the measured copy bandwidth. Roofline
+time = max(NVLink time, HBM time). CUDA-event timing, max over ranks, 5 warm-ups, 20 timed iterations.
+"""
+import ctypes as C
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tiresias_b200.ops import native  # noqa: E402
+from tiresias_b200.parallel.symm import SymmetricWorld  # noqa: E402
+
+NVLINK_GBS = 770.0
+
+
+def hbm_gbs():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        return 6650.0
+
+
+def timed(fn, dev, iters=20, warmup=5):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize(dev)
+    t = torch.tensor([s.elapsed_time(e) / iters], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    lib = native.lib()
+    sizes = [1 << 20, 12 << 20, 48 << 20, 264 << 20]           # 2 MB .. 528 MB (VGG-16) of bf16 gradients
+    nmax = max(sizes)
+    symm = SymmetricWorld.from_env(dev)
+    symm.alloc("grad", nmax * 2)
+    symm.alloc("param", nmax * 2)
+    symm.alloc("flags", native.FLAG_WORDS * 4)
+    ws = symm.native_world("grad", "param", "flags")
+    grad = symm.buffers["grad"].view(torch.bfloat16)
+    param = symm.buffers["param"].view(torch.bfloat16)
+    grad.normal_()
+    master = torch.zeros(nmax // world, device=dev)
+    mom = torch.zeros(nmax // world, device=dev)
+    hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0 / world], device=dev)
+    epoch = torch.ones(1, dtype=torch.int32, device=dev)
+    counters = torch.zeros(8, dtype=torch.int32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    seq = torch.zeros(2, dtype=torch.int32, device=dev)
+    ptrs = (C.c_void_p * native.MAX_WORLD)(*[symm.buffers["grad"].ptrs[r] for r in range(world)])
+    st = native.stream_ptr()
+    hbm = hbm_gbs()
+    rows = []
+    for n in sizes:
+        shard = n // world
+        for ctas in (32, 148):
+            def ours_ps():
+                native.check(lib.tb200_ps_push_pull(C.byref(ws), 0, rank * shard, shard, native.BF16,
+                                                    master.data_ptr(), mom.data_ptr(), hyper.data_ptr(),
+                                                    epoch.data_ptr(), counters.data_ptr(), status.data_ptr(),
+                                                    400_000_000, ctas, 1, st))
+                native.check(lib.tb200_step_end(C.byref(ws), 1, epoch.data_ptr(), status.data_ptr(), 400_000_000, st))
+            ms = timed(ours_ps, dev)
+            link_bytes = (world - 1) / world * n * 2                      # in (push) == out (pull), per direction
+            hbm_bytes = shard * 16 + shard * 2 + shard * 2 + link_bytes  # master+mom r/w, local grad, local param, remote-served reads
+            roof_ms = max(link_bytes / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6)) if world > 1 else hbm_bytes / (hbm * 1e6)
+            rows.append({"op": "ps_push_pull+sgd (fused)", "impl": "ours", "ctas": ctas, "elems": n, "world": world,
+                         "ms": round(ms, 4), "nvlink_gbs_per_dir": round(link_bytes / ms / 1e6, 1),
+                         "roofline_ms": round(roof_ms, 4), "frac_of_roofline": round(roof_ms / ms, 3)})
+        g, p = grad[:n], param[:n]
+        sg = torch.empty(shard, dtype=torch.bfloat16, device=dev)
+        sp = torch.empty(shard, dtype=torch.bfloat16, device=dev)
+        m, v = master[:shard], mom[:shard]
+
+        def nccl_ps():
+            if world > 1:
+                dist.reduce_scatter_tensor(sg, g, op=dist.ReduceOp.SUM)
+            else:
+                sg.copy_(g[:shard])
+            gr = sg.float().mul_(1.0 / world).add_(m, alpha=1e-4)
+            v.mul_(0.9).add_(gr)
+            m.add_(v, alpha=-0.1)
+            sp.copy_(m)
+            if world > 1:
+                dist.all_gather_into_tensor(p, sp)
+            else:
+                p[:shard].copy_(sp)
+        ms_n = timed(nccl_ps, dev)
+        rows.append({"op": "reduce_scatter + torch SGD + all_gather", "impl": "nccl", "elems": n, "world": world,
+                     "ms": round(ms_n, 4), "nvlink_gbs_per_dir": round((world - 1) / world * n * 2 / ms_n / 1e6, 1)})
+        if world > 1:
+            for algo, name in ((0, "ring"), (1, "direct")):
+                def ours_ar():
+                    native.check(lib.tb200_allreduce(C.byref(ws), ptrs, n, native.BF16, 1.0 / world, algo,
+                                                     seq.data_ptr(), status.data_ptr(), 400_000_000, 64, st))
+                ms_a = timed(ours_ar, dev)
+                link = 2 * (world - 1) / world * n * 2
+                rows.append({"op": f"allreduce ({name})", "impl": "ours", "elems": n, "world": world, "ms": round(ms_a, 4),
+                             "busbw_gbs": round(link / ms_a / 1e6, 1),
+                             "frac_of_roofline": round((link / 2 / (NVLINK_GBS * 1e6)) / ms_a, 3)})
+            gg = g.clone()
+            ms_b = timed(lambda: dist.all_reduce(gg), dev)
+            rows.append({"op": "all_reduce", "impl": "nccl", "elems": n, "world": world, "ms": round(ms_b, 4),
+                         "busbw_gbs": round(2 * (world - 1) / world * n * 2 / ms_b / 1e6, 1)})
+        grad.normal_()
+    torch.cuda.synchronize(dev)
+    bad = int(status.item())
+    if rank == 0:
+        for r in rows:
+            print(json.dumps(r), flush=True)
+        print(json.dumps({"status_word": bad}))
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        json.dump(rows, open(os.path.join(ROOT, "gpurun_out", f"comm_n{world}.json"), "w"), indent=1)
+    dist.barrier()
+    symm.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

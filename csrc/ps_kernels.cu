@@ -68,6 +68,42 @@ struct VecIO<float> {
   }
 };
 
+// Raw (unconverted) 8-element vector: lets a thread put many peer loads in flight before it touches any.
+// NVLink needs ~2 MB in flight per GPU to run at link rate (770 GB/s x ~2.5 us); with the 32 CTAs a job
+// may use next to its own backward pass that means 8-16 outstanding 16-byte loads per thread.
+template <typename T>
+struct RawVec {
+  static constexpr int kQ = sizeof(T) * 8 / 16;
+  uint4 q[kQ];
+};
+template <typename T>
+__device__ __forceinline__ RawVec<T> load_raw(const void* base, size_t vec) {
+  RawVec<T> r;
+  const uint4* p = reinterpret_cast<const uint4*>(base) + vec * RawVec<T>::kQ;
+#pragma unroll
+  for (int i = 0; i < RawVec<T>::kQ; ++i) r.q[i] = ld_stream_16(p + i);
+  return r;
+}
+__device__ __forceinline__ void add_raw(const RawVec<__nv_bfloat16>& r, F8& acc) {
+  acc.v[0] += bf16_lo(r.q[0].x); acc.v[1] += bf16_hi(r.q[0].x);
+  acc.v[2] += bf16_lo(r.q[0].y); acc.v[3] += bf16_hi(r.q[0].y);
+  acc.v[4] += bf16_lo(r.q[0].z); acc.v[5] += bf16_hi(r.q[0].z);
+  acc.v[6] += bf16_lo(r.q[0].w); acc.v[7] += bf16_hi(r.q[0].w);
+}
+__device__ __forceinline__ void add_raw(const RawVec<float>& r, F8& acc) {
+  acc.v[0] += __uint_as_float(r.q[0].x); acc.v[1] += __uint_as_float(r.q[0].y);
+  acc.v[2] += __uint_as_float(r.q[0].z); acc.v[3] += __uint_as_float(r.q[0].w);
+  acc.v[4] += __uint_as_float(r.q[1].x); acc.v[5] += __uint_as_float(r.q[1].y);
+  acc.v[6] += __uint_as_float(r.q[1].z); acc.v[7] += __uint_as_float(r.q[1].w);
+}
+// vectors per thread per round, chosen so that (peers x vectors x 16-byte units) stays near 16 loads
+template <typename T, int W>
+struct CommUnroll {
+  static constexpr int kLoads = W * RawVec<T>::kQ;
+  static constexpr int value = kLoads >= 16 ? 1 : (kLoads >= 8 ? 2 : (kLoads >= 4 ? 4 : 8));
+};
+constexpr int kCommThreads = 512;
+
 __device__ __forceinline__ void sgd_update8(F8& g, float* master, float* mom, size_t elem,
                                             const tb200_sgd_hyper_t& h, F8& out) {
   float4* mp = reinterpret_cast<float4*>(master + elem);
@@ -125,7 +161,7 @@ struct PushArgs {
 };
 
 template <typename GT, int W>
-__global__ void __launch_bounds__(kThreads) ps_push_pull_kernel(const PushArgs a) {
+__global__ void __launch_bounds__(kCommThreads) ps_push_pull_kernel(const PushArgs a) {
   const int rank = a.w.rank;
   const uint32_t epoch = *a.epoch;
   __shared__ int s_ok;
@@ -154,15 +190,31 @@ __global__ void __launch_bounds__(kThreads) ps_push_pull_kernel(const PushArgs a
   const tb200_sgd_hyper_t h = *a.hyper;
   const size_t voff = a.shard_off / 8;  // shard_off is a multiple of 8 elements
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < a.nvec; i += stride) {
-    F8 g = {};
+  constexpr int U = CommUnroll<GT, W>::value;
+  for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < a.nvec; i0 += stride * U) {
+    RawVec<GT> raw[U][W];
 #pragma unroll
-    for (int w = 0; w < W; ++w) VecIO<GT>::load_add(a.w.grad[w], voff + i, g);
-    F8 p;
-    sgd_update8(g, a.master, a.mom, i * 8, h, p);
+    for (int u = 0; u < U; ++u) {                      // all peer loads of this round go out first
+      const size_t i = i0 + (size_t)u * stride;
+      if (i < a.nvec) {
 #pragma unroll
-    for (int w = 0; w < W; ++w)
-      if (a.broadcast || w == rank) VecIO<__nv_bfloat16>::store(a.w.param[w], voff + i, p);
+        for (int w = 0; w < W; ++w) raw[u][w] = load_raw<GT>(a.w.grad[w], voff + i);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i < a.nvec) {
+        F8 g = {};
+#pragma unroll
+        for (int w = 0; w < W; ++w) add_raw(raw[u][w], g);          // fixed rank order: reproducible
+        F8 p;
+        sgd_update8(g, a.master, a.mom, i * 8, h, p);
+#pragma unroll
+        for (int w = 0; w < W; ++w)
+          if (a.broadcast || w == rank) VecIO<__nv_bfloat16>::store(a.w.param[w], voff + i, p);
+      }
+    }
   }
 
   // 5. Publish: all CTAs' stores must be visible system-wide before the flag.
@@ -222,7 +274,7 @@ struct RingArgs {
 };
 
 template <typename T>
-__global__ void __launch_bounds__(kThreads) ring_allreduce_kernel(const RingArgs a) {
+__global__ void __launch_bounds__(kCommThreads) ring_allreduce_kernel(const RingArgs a) {
   const int W = a.w.world, rank = a.w.rank;
   const int prev = (rank + W - 1) % W, next = (rank + 1) % W;
   const int lane = blockIdx.x;
@@ -260,17 +312,33 @@ __global__ void __launch_bounds__(kThreads) ring_allreduce_kernel(const RingArgs
                          : (rank - (int)(s - (W - 1)) + 2 * W) % W;
     const size_t cbase = (size_t)c * chunk_vec;
     const bool last_reduce = (s == (uint32_t)(W - 2));
-    for (size_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-      F8 acc = {};
-      VecIO<T>::load_add(theirs, cbase + i, acc);
-      if (reduce) {
-        VecIO<T>::load_add(mine, cbase + i, acc);
-        if (last_reduce) {
+    constexpr int U = 4;
+    for (size_t i0 = lo + threadIdx.x; i0 < hi; i0 += (size_t)blockDim.x * U) {
+      RawVec<T> rt[U], rm[U];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) acc.v[k] *= a.scale;
+      for (int u = 0; u < U; ++u) {                    // peer (and local) loads first, then the math
+        const size_t i = i0 + (size_t)u * blockDim.x;
+        if (i < hi) {
+          rt[u] = load_raw<T>(theirs, cbase + i);
+          if (reduce) rm[u] = load_raw<T>(mine, cbase + i);
         }
       }
-      VecIO<T>::store(mine, cbase + i, acc);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const size_t i = i0 + (size_t)u * blockDim.x;
+        if (i < hi) {
+          F8 acc = {};
+          add_raw(rt[u], acc);
+          if (reduce) {
+            add_raw(rm[u], acc);
+            if (last_reduce) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) acc.v[k] *= a.scale;
+            }
+          }
+          VecIO<T>::store(mine, cbase + i, acc);
+        }
+      }
     }
     __threadfence_system();
     __syncthreads();
@@ -304,7 +372,7 @@ struct DirectArgs {
 };
 
 template <typename T, int W>
-__global__ void __launch_bounds__(kThreads) direct_allreduce_kernel(const DirectArgs a) {
+__global__ void __launch_bounds__(kCommThreads) direct_allreduce_kernel(const DirectArgs a) {
   const int rank = a.w.rank;
   const int slot = TB200_MAX_BUCKETS - 1;
   const uint32_t epoch = *a.seq + 1;
@@ -324,14 +392,30 @@ __global__ void __launch_bounds__(kThreads) direct_allreduce_kernel(const Direct
   const size_t slice_vec = a.n / 8 / W;
   const size_t vbase = (size_t)rank * slice_vec;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < slice_vec; i += stride) {
-    F8 acc = {};
+  constexpr int U = CommUnroll<T, W>::value;
+  for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < slice_vec; i0 += stride * U) {
+    RawVec<T> raw[U][W];
 #pragma unroll
-    for (int w = 0; w < W; ++w) VecIO<T>::load_add(a.bufs[w], vbase + i, acc);
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i < slice_vec) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc.v[k] *= a.scale;
+        for (int w = 0; w < W; ++w) raw[u][w] = load_raw<T>(a.bufs[w], vbase + i);
+      }
+    }
 #pragma unroll
-    for (int w = 0; w < W; ++w) VecIO<T>::store(a.bufs[w], vbase + i, acc);
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i < slice_vec) {
+        F8 acc = {};
+#pragma unroll
+        for (int w = 0; w < W; ++w) add_raw(raw[u][w], acc);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc.v[k] *= a.scale;
+#pragma unroll
+        for (int w = 0; w < W; ++w) VecIO<T>::store(a.bufs[w], vbase + i, acc);
+      }
+    }
   }
   __threadfence_system();
   __syncthreads();
@@ -586,10 +670,10 @@ int tb200_ps_push_pull(const tb200_world_t* world, int bucket, size_t shard_off,
   a.budget = spin_budget;
   a.broadcast = broadcast;
   if (max_ctas <= 0) max_ctas = 32;
-  const int grid = grid_for(a.nvec, 2, max_ctas);
+  const int grid = grid_for(a.nvec * kThreads / kCommThreads, 2, max_ctas);
 #define TB_CASE(GT, WW)                                                       \
   case WW:                                                                    \
-    ps_push_pull_kernel<GT, WW><<<grid, kThreads, 0, stream>>>(a);            \
+    ps_push_pull_kernel<GT, WW><<<grid, kCommThreads, 0, stream>>>(a);        \
     break
 #define TB_SWITCH(GT)                                                         \
   switch (world->world) {                                                     \
@@ -635,8 +719,8 @@ int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD
       // nothing to exchange; only the scale applies (kept on the GPU for stream ordering)
       num_ctas = 1;
     }
-    if (dtype == TB200_BF16) ring_allreduce_kernel<__nv_bfloat16><<<num_ctas, kThreads, 0, stream>>>(a);
-    else if (dtype == TB200_F32) ring_allreduce_kernel<float><<<num_ctas, kThreads, 0, stream>>>(a);
+    if (dtype == TB200_BF16) ring_allreduce_kernel<__nv_bfloat16><<<num_ctas, kCommThreads, 0, stream>>>(a);
+    else if (dtype == TB200_F32) ring_allreduce_kernel<float><<<num_ctas, kCommThreads, 0, stream>>>(a);
     else return fail("tb200_allreduce: bad dtype%s");
     if (int rc = launched()) return rc;
     bump_seq_kernel<<<1, 1, 0, stream>>>(seq_dev);
@@ -654,7 +738,7 @@ int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD
   const int grid = grid_for(n / 8 / W, 2, num_ctas);
 #define TB_CASE(T, WW)                                                        \
   case WW:                                                                    \
-    direct_allreduce_kernel<T, WW><<<grid, kThreads, 0, stream>>>(a);         \
+    direct_allreduce_kernel<T, WW><<<grid, kCommThreads, 0, stream>>>(a);     \
     break
 #define TB_SWITCH(T)                                                          \
   switch (W) {                                                                \
