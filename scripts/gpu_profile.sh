@@ -5,7 +5,6 @@ mkdir -p gpurun_out
 python -m tiresias_b200.build > gpurun_out/build.log 2>&1 || { echo BUILD FAILED; tail -20 gpurun_out/build.log; exit 1; }
 timeout 900 python bench/kernels.py --iters 15 > gpurun_out/kernels.log 2>&1; echo "== kernels exit $?"; tail -n 30 gpurun_out/kernels.log
 NCU="ncu --clock-control none --profile-from-start off"
-[ -n "$SKIP_KERNELS_BENCH" ] || true
 timeout 300 python bench/profile_one.py --kernel step > gpurun_out/plain_step.log 2>&1 && \
   timeout 900 $NCU --metrics gpu__time_duration.sum --csv --log-file gpurun_out/launches_step.csv \
     python bench/profile_one.py --kernel step > gpurun_out/ncu_step.log 2>&1
