@@ -129,3 +129,22 @@ def test_profile_phases_reports_every_phase(cuda_device):
     assert all(v >= 0 for v in ph.values()) and ph["total"] >= ph["forward"] + ph["backward"] - 1e-3
     assert tr.check_status() == 0
     tr.close()
+
+
+def test_conv1x1_on_tcgen05_matches_torch(cuda_device):
+    from tiresias_b200.ops.conv import TcConv1x1
+    torch.manual_seed(0)
+    conv = TcConv1x1(64, 256).to(cuda_device).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    x = torch.randn(4, 64, 14, 14, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    x.requires_grad_(True)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_(True)
+    wr = conv.weight.detach().float().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xr, wr)
+    yr.backward(dy.float())
+    assert y.shape == yr.shape and torch.allclose(y.float(), yr, rtol=3e-2, atol=3e-2)
+    assert torch.allclose(x.grad.float(), xr.grad, rtol=3e-2, atol=5e-2)
+    assert conv.weight.grad.shape == conv.weight.shape
+    assert torch.allclose(conv.weight.grad.float(), wr.grad, rtol=3e-2, atol=2e-1)

@@ -14,8 +14,17 @@ from torch import nn
 
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
+from ..ops.conv import TcConv1x1
 from ..ops.linear import TcLinear
 from ..ops.pooling import MaxPool3x3S2
+
+import os
+
+# 1x1 / stride-1 convolutions on the tcgen05 GEMM: correct (tests/test_gpu_trainer.py) but, measured on B200 at
+# batch 256, 7 % slower end to end than cuDNN's kernels for these thin, memory-bound shapes (26.4 vs 24.6 ms
+# per ResNet-50 step), so it is opt-in (TB200_TC_CONV1X1=1) until the GEMM grows a BatchNorm-statistics
+# epilogue that removes the separate statistics pass.
+TC_CONV1X1 = os.environ.get("TB200_TC_CONV1X1", "0") == "1"
 
 
 class TorchBNAct(nn.Module):
@@ -42,7 +51,11 @@ def _bn(channels: int, relu: bool, fused: bool) -> nn.Module:
     return FusedBatchNormAct(channels, relu=relu) if fused else TorchBNAct(channels, relu=relu)
 
 
-def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0) -> nn.Conv2d:
+def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0, fused: bool = False) -> nn.Module:
+    """cuDNN convolution, except 1x1 / stride 1 in the fused build: those are plain GEMMs over the NHWC
+    pixel rows and run on the tcgen05 kernel (ops/conv.py)."""
+    if fused and TC_CONV1X1 and k == 1 and stride == 1 and pad == 0:
+        return TcConv1x1(cin, cout)
     return nn.Conv2d(cin, cout, k, stride, pad, bias=False)
 
 
@@ -55,12 +68,12 @@ class Bottleneck(nn.Module):
     def __init__(self, cin: int, width: int, stride: int, fused: bool = True):
         super().__init__()
         cout = width * self.expansion
-        self.conv1, self.bn1 = _conv(cin, width, 1), _bn(width, True, fused)
+        self.conv1, self.bn1 = _conv(cin, width, 1, fused=fused), _bn(width, True, fused)
         self.conv2, self.bn2 = _conv(width, width, 3, stride, 1), _bn(width, True, fused)
-        self.conv3, self.bn3 = _conv(width, cout, 1), _bn(cout, True, fused)
+        self.conv3, self.bn3 = _conv(width, cout, 1, fused=fused), _bn(cout, True, fused)
         self.down_conv = self.down_bn = None
         if stride != 1 or cin != cout:
-            self.down_conv, self.down_bn = _conv(cin, cout, 1, stride), _bn(cout, False, fused)
+            self.down_conv, self.down_bn = _conv(cin, cout, 1, stride, fused=fused), _bn(cout, False, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         idt = x if self.down_conv is None else self.down_bn(self.down_conv(x))
@@ -84,7 +97,7 @@ class ResNet(nn.Module):
         self.pool = nn.AdaptiveAvgPool2d(1)
         self.fc = TcLinear(cin, num_classes) if fused else nn.Linear(cin, num_classes)
         for m in self.modules():
-            if isinstance(m, nn.Conv2d):
+            if isinstance(m, (nn.Conv2d, TcConv1x1)):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
         for m in self.modules():
             if isinstance(m, Bottleneck):

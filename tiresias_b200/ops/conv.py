@@ -1,0 +1,71 @@
+"""1x1 convolutions on the hand-written tcgen05 GEMM.
+
+In NHWC a 1x1 / stride-1 convolution *is* a GEMM over the N*H*W pixel rows:
+    y[R, Cout] = x[R, Cin] . W[Cout, Cin]^T          (forward, NT)
+    dx[R, Cin] = dy[R, Cout] . W[Cout, Cin]          (W consumed as stored: MN-major B)
+    dW[Cout, Cin] = dy[R, Cout]^T . x[R, Cin]        (dy and x consumed as stored: MN-major A and B)
+so no im2col, no transposes and no layout change are needed — the activations are only re-viewed. Two
+thirds of ResNet-50's convolutions (conv1 / conv3 of every bottleneck, the stride-1 projection) are of
+this kind. Strided 1x1 and k x k convolutions stay on cuDNN for now (known gaps).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+from torch import nn
+
+from . import native
+
+
+class _Conv1x1Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        n, cin, h, w = x.shape
+        cout = weight.shape[0]
+        x2d = x.permute(0, 2, 3, 1).reshape(n * h * w, cin)               # a view of the NHWC storage
+        w2d = weight.permute(0, 2, 3, 1).reshape(cout, cin)
+        if not w2d.is_contiguous():
+            w2d = w2d.contiguous()
+        y2d = native.gemm_nt(x2d, w2d)
+        ctx.save_for_backward(x2d, w2d)
+        ctx.shape = (n, cin, h, w, cout)
+        return y2d.view(n, h, w, cout).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        x2d, w2d = ctx.saved_tensors
+        n, cin, h, w, cout = ctx.shape
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dy2d = dy.permute(0, 2, 3, 1).reshape(n * h * w, cout)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = native.gemm(dy2d, w2d, b_mn_major=True).view(n, h, w, cin).permute(0, 3, 1, 2)
+        if ctx.needs_input_grad[1]:
+            dw = native.gemm(dy2d, x2d, a_mn_major=True, b_mn_major=True).view(cout, 1, 1, cin).permute(0, 3, 1, 2)
+        return dx, dw
+
+
+class TcConv1x1(nn.Module):
+    """``nn.Conv2d(cin, cout, 1, bias=False)`` whose three GEMMs run on the tcgen05 kernel for bf16
+    channels-last CUDA inputs (anything else goes to ``F.conv2d``). The weight keeps Conv2d's shape
+    ``[cout, cin, 1, 1]``, so checkpoints and the trainer's flat parameter layout are unchanged."""
+
+    def __init__(self, in_channels: int, out_channels: int):
+        super().__init__()
+        if in_channels % 8 or out_channels % 8:
+            raise ValueError("channel counts must be multiples of 8 (TMA 16-byte stride rule)")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, 1, 1))
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
+            return _Conv1x1Fn.apply(x, self.weight)
+        return torch.nn.functional.conv2d(x, self.weight)
+
+    def extra_repr(self) -> str:
+        return f"{self.in_channels}, {self.out_channels}, kernel_size=(1, 1), tcgen05"
