@@ -65,6 +65,8 @@ def gemm_cases(iters):
         (64, 1000, 2048, "resnet50 fc fwd"), (8192, 2048, 512, "transformer ffn1"), (8192, 512, 2048, "transformer ffn2"),
         (8192, 1536, 512, "transformer qkv"), (8192, 32000, 512, "transformer lm head"),
         (4096, 4096, 4096, "square 4k"), (8192, 8192, 8192, "square 8k"),
+        (802816, 256, 64, "resnet conv3 1x1, layer1 (b256)"), (802816, 64, 256, "resnet conv1 1x1, layer1 (b256)"),
+        (200704, 512, 128, "resnet conv3 1x1, layer2 (b256)"), (50176, 1024, 256, "resnet conv3 1x1, layer3 (b256)"),
     ]
     for m, n, k, note in shapes:
         a = torch.randn(m, k, device="cuda").to(torch.bfloat16)

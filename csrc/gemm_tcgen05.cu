@@ -34,9 +34,11 @@ constexpr int UMMA_K = 16;
 constexpr int kGemmThreads = 256;
 constexpr int kAccumStages = 2;
 
-template <int BLOCK_N>
+// THIN = short reduction (K <= 256): the kernel is bound by its output stores, not by the mainloop, so it
+// trades one mainloop stage for a deeper store pipeline in the epilogue.
+template <int BLOCK_N, bool THIN>
 struct Cfg {
-  static constexpr int kStages = BLOCK_N == 256 ? 4 : 6;
+  static constexpr int kStages = (BLOCK_N == 256 ? 4 : 6) - (THIN ? 1 : 0);
   static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -44,7 +46,10 @@ struct Cfg {
   static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages) * 8 + 16;
   // Epilogue staging: per epilogue warp two 32-row x 128-byte tiles (swizzle-128B), TMA-stored.
   static constexpr int kEpiTileBytes = 32 * 128;
-  static constexpr int kEpiBytes = 4 * 2 * kEpiTileBytes;
+  // kEpiBufs staging tiles per epilogue warp: a TMA store occupies its tile for ~1 us, so with two tiles a
+  // warp could not retire more than ~8 GB/s and thin-K (store-bound) shapes topped out near 2.4 TB/s.
+  static constexpr int kEpiBufs = THIN ? 4 : 2;
+  static constexpr int kEpiBytes = 4 * kEpiBufs * kEpiTileBytes;
   static constexpr int kEpiBiasBytes = kAccumStages * 256 * 4;   // the tile's bias row, per accumulator stage
   static constexpr int kSmemBytes =
       kStages * kStageBytes + kEpiBytes + kEpiBiasBytes + kBarrierBytes;
@@ -98,8 +103,10 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t sm
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
-__device__ __forceinline__ void tma_store_wait_read_1() {
-  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+// at most N bulk stores of this thread may still be reading their staging tiles
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read_n() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void st_shared_16(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
@@ -225,7 +232,7 @@ struct PullMaps {
 // (64 bf16 or 32 fp32 columns) TMEM -> registers, + bias (the tile's bias row sits in shared memory, loaded
 // by the epilogue warps while the tile's MMAs were still running; every lane reads it with broadcast
 // 16-byte loads), activation, pack, swizzled st.shared, TMA store.
-template <int BLOCK_N, int ACT, bool BIAS, bool F32>
+template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* map_d, uint32_t tcol,
                                               uint32_t bufs, uint32_t tile_bytes, int& epi_buf, float* bias_s,
                                               int row0, int col_base, int ks, int lane) {
@@ -255,7 +262,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
       r[4 * q + 2] = __float_as_uint(x2); r[4 * q + 3] = __float_as_uint(x3);
     }
     const uint32_t buf = bufs + (uint32_t)epi_buf * tile_bytes;
-    if (lane == 0) tma_store_wait_read_1();            // the store that last used this buffer is done
+    if (lane == 0) tma_store_wait_read_n<EPI_BUFS - 1>();   // the store that last used this tile is done
     __syncwarp();
     const uint32_t row_addr = buf + (uint32_t)lane * 128u;
 #pragma unroll
@@ -278,17 +285,17 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
       else tma_store_2d(map_d, buf, col0, row0);
       tma_store_commit();
     }
-    epi_buf ^= 1;
+    epi_buf = (epi_buf + 1) % EPI_BUFS;
   }
 }
 
-template <int BLOCK_N, bool kPull>
+template <int BLOCK_N, bool kPull, bool THIN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                     const __grid_constant__ CUtensorMap map_b,
                     const __grid_constant__ CUtensorMap map_d,
                     const __grid_constant__ PullMaps pull, const GemmParams p) {
-  using C = Cfg<BLOCK_N>;
+  using C = Cfg<BLOCK_N, THIN>;
   // SWIZZLE_128B tiles need 1024-byte alignment (the kernel has no static shared memory, so the
   // dynamic segment starts at the CTA's 1024-byte aligned shared-memory base).
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -470,7 +477,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         // ---- TMEM -> registers -> swizzled smem tile -> TMA store (coalesced, clipped at M / N) ----
         const int row0 = m_blk * BLOCK_M + ew * 32;
         const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-        const uint32_t bufs = epi_smem + (uint32_t)(ew * 2) * C::kEpiTileBytes;
+        const uint32_t bufs = epi_smem + (uint32_t)(ew * C::kEpiBufs) * C::kEpiTileBytes;
+
         float* bias_s = reinterpret_cast<float*>(smem_raw + (epi_bias_smem - smem_u32(smem_raw))) + as * 256;
         const int col_base = n_blk * BLOCK_N;
         // One compact instruction stream per (activation, bias, output type): the element loop must not
@@ -479,7 +487,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         switch (variant) {
 #define TB_EPI(ID, ACT, BIAS, F32)                                                                        \
   case ID:                                                                                                \
-    epilogue_tile<BLOCK_N, ACT, BIAS, F32>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf, bias_s, row0, \
+    epilogue_tile<BLOCK_N, C::kEpiBufs, ACT, BIAS, F32>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf, bias_s, row0, \
                                            col_base, ks, lane);                                           \
     break;
           TB_EPI(0, 0, false, false) TB_EPI(1, 0, false, true) TB_EPI(2, 0, true, false) TB_EPI(3, 0, true, true)
@@ -691,11 +699,11 @@ int get_workspace(size_t bytes, float** out) {
   return 0;
 }
 
-template <int BLOCK_N, bool kPull>
+template <int BLOCK_N, bool kPull, bool THIN>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const PullMaps& pull,
                 const GemmParams& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BLOCK_N>;
-  auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull>;
+  using C = Cfg<BLOCK_N, THIN>;
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull, THIN>;
   static bool configured = false;
   if (!configured) {
     TB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -752,8 +760,16 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   if (tiles < sms) {
     // Pick the split count whose work-item total packs best into whole waves of `sms` CTAs
     // (ties go to fewer splits); keep at least 4 k-blocks per split.
+    // ... and no more splits than SMs, nor so many that the fp32 partial planes add more than ~10 % to the
+    // bf16 input traffic, with a floor of 16 (a long-reduction, tiny-output GEMM such as a 1x1 convolution's
+    // dW — K = N*H*W pixels, output Cout x Cin — wants one split per SM; a square-ish problem wants few).
     int max_splits = p.num_kb / 4;
-    if (max_splits > 16) max_splits = 16;
+    if (max_splits > sms) max_splits = sms;
+    const double in_bytes = 2.0 * ((double)M * K + (double)N * K);
+    const double plane_bytes = 4.0 * (double)M * N;
+    int by_traffic = (int)(0.1 * in_bytes / plane_bytes);
+    if (by_traffic < 16) by_traffic = 16;
+    if (max_splits > by_traffic) max_splits = by_traffic;
     double best = 0.0;
     for (int s = 1; s <= max_splits; ++s) {
       const int it = tiles * s;
@@ -825,10 +841,16 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   const int items = tiles * splits;
   const int grid = items < sms ? items : sms;
   int rc;
-  if (block_n == 256) rc = pull ? launch_gemm<256, true>(ma, mb, md, pm, p, grid, stream)
-                                : launch_gemm<256, false>(ma, mb, md, pm, p, grid, stream);
-  else rc = pull ? launch_gemm<128, true>(ma, mb, md, pm, p, grid, stream)
-                 : launch_gemm<128, false>(ma, mb, md, pm, p, grid, stream);
+  const bool thin = !pull && p.num_kb <= 4 && splits == 1;      // store-bound: deeper epilogue pipeline
+  if (block_n == 256) {
+    rc = pull ? launch_gemm<256, true, false>(ma, mb, md, pm, p, grid, stream)
+              : (thin ? launch_gemm<256, false, true>(ma, mb, md, pm, p, grid, stream)
+                      : launch_gemm<256, false, false>(ma, mb, md, pm, p, grid, stream));
+  } else {
+    rc = pull ? launch_gemm<128, true, false>(ma, mb, md, pm, p, grid, stream)
+              : (thin ? launch_gemm<128, false, true>(ma, mb, md, pm, p, grid, stream)
+                      : launch_gemm<128, false, false>(ma, mb, md, pm, p, grid, stream));
+  }
   if (rc) return rc;
   if (splits > 1) {
     const size_t mn = (size_t)M * N;

@@ -54,9 +54,10 @@ def _call(lib, fn_name, a, b, bias, out):
 
 
 def test_noalloc_matches_allocating_entry_point_twice_in_a_row(cabi, cuda_device):
-    # first a split-K problem that fills most of the scratch, then a smaller split-K problem that
-    # finds the first call's partial sums still lying in the shared array
+    # first a split-K problem whose partial sums take several MiB of the scratch, then a smaller split-K
+    # problem that finds the first call's partial sums still lying in the shared array
     shapes = [(64, 4096, 25088), (64, 1000, 2048)]
+    # (64 x 4096 x 25088 plans 9 splits = 9 MiB of fp32 partials on a 148-SM B200)
     problems = [_problem(cuda_device, *s, seed=i) for i, s in enumerate(shapes)]
     wants = []
     for a, b, bias in problems:
