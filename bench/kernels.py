@@ -4,7 +4,7 @@ peaks from MEASURED_PEAKS.json) and against the library op it replaces (cuBLAS v
 torch elementwise SGD). CUDA-event timing, >= 5 warm-ups, L2 flushed (256 MiB write) between timed
 iterations. Prints one JSON object per kernel and writes them to gpurun_out/kernels.json.
 
-    python bench/kernels.py [--only gemm|sgd|push|allreduce|misc] [--iters 20]
+    python bench/kernels.py [--only gemm|conv|bn|sgd|push|misc] [--iters 20]
 """
 import argparse
 import ctypes as C
@@ -224,6 +224,49 @@ def misc_cases(iters):
     return out
 
 
+def conv_cases(iters):
+    """Implicit-GEMM convolutions (im2col TMA + tcgen05) against cuDNN through torch, ResNet-50 shapes at
+    batch 256: forward, input gradient (stride 1 only) and weight gradient."""
+    out = []
+    shapes = [  # (n, cin, cout, hw, k, stride, pad, note)
+        (256, 64, 64, 56, 3, 1, 1, "layer1 3x3"), (256, 128, 128, 56, 3, 2, 1, "layer2.0 3x3 s2"),
+        (256, 128, 128, 28, 3, 1, 1, "layer2 3x3"), (256, 256, 256, 28, 3, 2, 1, "layer3.0 3x3 s2"),
+        (256, 256, 256, 14, 3, 1, 1, "layer3 3x3"), (256, 512, 512, 14, 3, 2, 1, "layer4.0 3x3 s2"),
+        (256, 512, 512, 7, 3, 1, 1, "layer4 3x3"), (256, 256, 512, 56, 1, 2, 0, "layer2 downsample 1x1 s2"),
+        (256, 512, 1024, 28, 1, 2, 0, "layer3 downsample 1x1 s2"), (256, 1024, 2048, 14, 1, 2, 0, "layer4 downsample 1x1 s2"),
+    ]
+    aten = torch.ops.aten.convolution_backward
+    for n, cin, cout, hw, k, stride, pad, note in shapes:
+        x = torch.randn(n, cin, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(cout, cin, k, k, device="cuda") / (cin * k * k) ** 0.5).to(torch.bfloat16)
+        w = w.contiguous(memory_format=torch.channels_last)
+        y = torch.nn.functional.conv2d(x, w, stride=stride, padding=pad)
+        dy = torch.randn_like(y)
+        oh = y.shape[2]
+        flops = 2.0 * n * oh * oh * cout * cin * k * k
+        act_bytes = 2.0 * (x.numel() + y.numel() + w.numel())
+        roof_ms = max(flops / (TF * 1e12), act_bytes / (HBM * 1e9)) * 1e3
+        row = {"kernel": "conv2d implicit GEMM", "shape": [n, cin, cout, hw, k, stride, pad], "note": note,
+               "gflop": round(flops / 1e9, 1), "roofline_ms": round(roof_ms, 4), "peaks": SRC}
+        ours, _ = timeit(lambda: native.conv2d_fprop(x, w, stride, pad), iters)
+        lib, _ = timeit(lambda: torch.nn.functional.conv2d(x, w, stride=stride, padding=pad), iters)
+        err = (native.conv2d_fprop(x, w, stride, pad).float() - y.float()).abs().max().item()
+        row.update({"fprop_ms": round(ours, 4), "fprop_cudnn_ms": round(lib, 4), "fprop_frac_of_roofline": round(roof_ms / ours, 3),
+                    "fprop_tflops": round(flops / ours / 1e9, 1), "fprop_max_abs_diff_vs_cudnn": round(err, 4)})
+        if stride == 1:
+            ours, _ = timeit(lambda: native.conv2d_dgrad(dy, w, x.shape, stride, pad), iters)
+            lib, _ = timeit(lambda: aten(dy, x, w, None, [stride] * 2, [pad] * 2, [1, 1], False, [0, 0], 1,
+                                         [True, False, False]), iters)
+            row.update({"dgrad_ms": round(ours, 4), "dgrad_cudnn_ms": round(lib, 4)})
+        ours, _ = timeit(lambda: native.conv2d_wgrad(x, dy, (k, k), stride, pad), iters)
+        lib, _ = timeit(lambda: aten(dy, x, w, None, [stride] * 2, [pad] * 2, [1, 1], False, [0, 0], 1,
+                                     [False, True, False]), iters)
+        row.update({"wgrad_ms": round(ours, 4), "wgrad_cudnn_ms": round(lib, 4)})
+        out.append(row)
+        print(json.dumps(row), flush=True)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
@@ -232,7 +275,7 @@ def main():
     torch.cuda.set_device(0)
     native.lib()
     res = []
-    for name, fn in (("gemm", gemm_cases), ("bn", bn_cases), ("sgd", sgd_cases), ("push", push_cases), ("misc", misc_cases)):
+    for name, fn in (("gemm", gemm_cases), ("conv", conv_cases), ("bn", bn_cases), ("sgd", sgd_cases), ("push", push_cases), ("misc", misc_cases)):
         if args.only and args.only != name:
             continue
         res += fn(args.iters)

@@ -87,6 +87,28 @@ __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap
       "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+// im2col-mode TMA over an NHWC activation tensor: loads `pixelsPerColumn` consecutive output pixels
+// (traversing W, then H, then N inside the map's bounding box, by the map's traversal stride) x
+// `channelsPerPixel` channels starting at channel c, for the filter tap (off_h, off_w). (w, h) is the
+// input-space position of the first pixel's window corner, i.e. out_pos * stride - pad. Positions that
+// fall into the padding or past the last image are zero-filled. The box lands as rows of 128 bytes
+// (64 bf16 channels), 128-byte swizzled: the same layout a tiled box {64, rows} produces.
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar,
+                                                   int c, int w, int h, int n, int off_w, int off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(smem_dst),
+      "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t smem_src, int c0,
                                              int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
@@ -201,8 +223,24 @@ __device__ __forceinline__ float apply_act(float x, int act) {
   return x;
 }
 
+// Implicit-GEMM convolution (NHWC activations, [Cout, R, S, Cin] weights): the producer warp replaces one
+// operand's tiled TMA loads by im2col-mode loads; mainloop, TMEM accumulators and epilogue are the GEMM's.
+//   mode 1 (fprop, and dgrad of a stride-1 convolution run as an fprop over dy with flipped taps):
+//          A[pixel, (tap, c)] = act[n, oh*stride - pad + r, ow*stride - pad + s, c]   (K-major, 128 pixels)
+//   mode 2 (wgrad): B[(tap, c), pixel] — the same box with 64 pixels, used as an MN-major operand whose
+//          reduction dimension is the pixel index.
+struct ConvGeom {
+  int mode;          // 0: plain GEMM
+  int OH, OW;        // extent of the pixel grid the GEMM dimension enumerates
+  int stride, lower; // traversal stride, lower corner (= -pad) of the im2col bounding box
+  int R, S;          // filter taps
+  int cblocks;       // 64-channel blocks per tap of the im2col operand
+  int flip;          // mode 1: weights are read as tap (R-1-r, S-1-s) through a 3-D map, MN-major (dgrad)
+};
+
 struct GemmParams {
   int M, N, K;
+  ConvGeom conv;
   int num_m, num_n, splits, num_kb;
   void* D;            // final output (splits == 1)
   float* partials;    // [splits][M][N] fp32 (splits > 1)
@@ -369,9 +407,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           owner_ready |= 1u << owner;
         }
       }
+      // implicit-GEMM convolution, mode 1: the tile's first output pixel -> (image, window corner)
+      int cv_n = 0, cv_h = 0, cv_w = 0;
+      if (p.conv.mode == 1) {
+        const int pix = m_blk * BLOCK_M, plane = p.conv.OH * p.conv.OW;
+        cv_n = pix / plane;
+        const int rem = pix - cv_n * plane, oh = rem / p.conv.OW;
+        cv_h = oh * p.conv.stride + p.conv.lower;
+        cv_w = (rem - oh * p.conv.OW) * p.conv.stride + p.conv.lower;
+      }
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1);
         mbar_expect_tx(full_bar(stage), C::kStageBytes);
+        if (p.conv.mode == 1) {
+          // reduction block kb = (tap, 64-channel block); taps in (r, s) order like the weight's K axis
+          const int tap = kb / p.conv.cblocks, cb = kb - tap * p.conv.cblocks;
+          const int r = tap / p.conv.S, sx = tap - r * p.conv.S;
+          tma_load_im2col_4d(a_smem + stage * C::kABytes, &map_a, full_bar(stage), cb * 64, cv_w, cv_h, cv_n,
+                             sx, r);
+          if (!p.conv.flip) {
+            tma_load_2d(b_smem + stage * C::kBBytes, bmap, full_bar(stage), kb * BLOCK_K, b_row);
+          } else {
+            // dgrad: dx[., ci] += dy[. + (pad' - r, pad' - s), co] * W[co, R-1-r, S-1-s, ci]; the weight
+            // is a 3-D tensor (ci, tap, co): 64 co rows x 64 ci columns per box, MN-major B slabs
+            const int wtap = (p.conv.R - 1 - r) * p.conv.S + (p.conv.S - 1 - sx);
+#pragma unroll
+            for (int sl = 0; sl < BLOCK_N / 64; ++sl)
+              tma_load_3d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage), b_row + sl * 64,
+                          wtap, cb * 64);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          continue;
+        }
         if (!p.a_mn) {
           tma_load_2d(a_smem + stage * C::kABytes, &map_a, full_bar(stage), kb * BLOCK_K,
                       m_blk * BLOCK_M);
@@ -381,7 +448,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             tma_load_2d(a_smem + stage * C::kABytes + sl * 8192, &map_a, full_bar(stage),
                         m_blk * BLOCK_M + sl * 64, kb * BLOCK_K);
         }
-        if (!p.b_mn) {
+        if (p.conv.mode == 2) {
+          // wgrad: reduction block kb = 64 consecutive output pixels; each 64-column slab of the tile is
+          // one (tap, 64-channel block) of the im2col matrix
+          const int pix = kb * BLOCK_K, plane = p.conv.OH * p.conv.OW;
+          const int n = pix / plane, rem = pix - n * plane, oh = rem / p.conv.OW;
+          const int h = oh * p.conv.stride + p.conv.lower;
+          const int w = (rem - oh * p.conv.OW) * p.conv.stride + p.conv.lower;
+#pragma unroll
+          for (int sl = 0; sl < BLOCK_N / 64; ++sl) {
+            const int blk = (b_row >> 6) + sl;                 // 64-column block index along (tap, c)
+            const int tap = blk / p.conv.cblocks, cb = blk - tap * p.conv.cblocks;
+            const int r = tap / p.conv.S, sx = tap - r * p.conv.S;
+            // slabs past the last tap (N tail) still have to deliver their bytes: clamp to a valid tap,
+            // the epilogue's store clips those columns
+            const bool in = tap < p.conv.R * p.conv.S;
+            tma_load_im2col_4d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage),
+                               in ? cb * 64 : 0, w, h, n, in ? sx : 0, in ? r : 0);
+          }
+        } else if (!p.b_mn) {
           tma_load_2d(b_smem + stage * C::kBBytes, bmap, full_bar(stage), kb * BLOCK_K, b_row);
         } else {
 #pragma unroll
@@ -614,6 +699,67 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeIm2colFn get_encode_im2col() {
+  static EncodeIm2colFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeIm2colFn>(p);
+  });
+  return fn;
+}
+
+// im2col-mode map over an NHWC bf16 activation tensor [n, h, w, c] for an R x S filter with the given
+// stride and padding: every load delivers `pixels` consecutive output positions x 64 channels of one tap.
+// Bounding box of window corners: lower = -pad, upper = pad - (taps - 1) (cuTensorMapEncodeIm2col's
+// convention: corners relative to the tensor's first / last element).
+int make_im2col_map(CUtensorMap* out, const void* base, int n, int h, int w, int c, int R, int S, int stride,
+                    int pad, int pixels) {
+  EncodeIm2colFn enc = get_encode_im2col();
+  if (!enc) return fail("cuTensorMapEncodeIm2col entry point not available%s");
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
+  int lower[2] = {-pad, -pad};
+  int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower,
+                   upper, 64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeIm2col failed (%s code %ld)", "", (long)r);
+  // Drivers up to 13.1 encode im2col maps of tensors smaller than 128 KiB with a flag that makes the
+  // loads fault; CUTLASS (cute/atom/copy_traits_sm90_im2col.hpp) clears the same bit.
+  int driver = 0;
+  if (cudaDriverGetVersion(&driver) == cudaSuccess && driver <= 13010 &&
+      (size_t)n * h * w * c * 2 < 131072)
+    reinterpret_cast<uint64_t*>(out)[1] &= ~(1ull << 21);
+  return 0;
+}
+
+// [cout][taps][cin] bf16 weights as a 3-D tensor for the dgrad's MN-major B slabs: box = 64 cout rows of
+// one tap x 64 cin columns.
+int make_weight_tap_map(CUtensorMap* out, const void* base, int cout, int taps, int cin) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail("cuTensorMapEncodeTiled entry point not available%s");
+  cuuint64_t dims[3] = {(cuuint64_t)cin, (cuuint64_t)taps, (cuuint64_t)cout};
+  cuuint64_t strides[2] = {(cuuint64_t)cin * 2, (cuuint64_t)taps * cin * 2};
+  cuuint32_t box[3] = {64, 1, (cuuint32_t)BLOCK_K};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled (weight taps) failed (%s code %ld)", "", (long)r);
+  return 0;
+}
+
 // 2-D bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle.
 int make_map(CUtensorMap* out, const void* base, int rows, int cols, int box_rows) {
   EncodeTiledFn enc = get_encode();
@@ -713,11 +859,20 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap&
   return launched();
 }
 
+// Host-side description of the im2col operand of an implicit-GEMM convolution (see ConvGeom).
+struct ConvHost {
+  ConvGeom g;
+  const void* act;          // NHWC tensor the im2col map walks (x for fprop / wgrad, dy for dgrad)
+  int n, h, w, c;           // its extent
+  int pad;                  // padding of the walk (dgrad: taps - 1 - pad)
+  int wcout, wtaps, wcin;   // weight extent (flip only)
+};
+
 int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_per_rank,
                 const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M,
                 int N, int K, int d_dtype, int act, const uint32_t* epoch_dev, int* status_dev,
                 unsigned long long budget, cudaStream_t stream, float* fixed_scratch = nullptr,
-                size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0) {
+                size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0, const ConvHost* conv = nullptr) {
   const bool pull = world != nullptr;
   if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
   // cuTensorMapEncodeTiled is a driver call and needs the primary context bound to THIS thread; a thread
@@ -740,6 +895,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   p.M = M; p.N = N; p.K = K;
   p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
   p.a_mn = a_mn; p.b_mn = b_mn;
+  if (conv) p.conv = conv->g;
   p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
 
@@ -811,8 +967,20 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   }
   PullMaps pm;
   memset(&pm, 0, sizeof(pm));
-  if (int rc = a_mn ? make_map_mn(&ma, A, K, M) : make_map(&ma, A, M, K, BLOCK_M)) return rc;
-  if (pull) {
+  if (conv && conv->g.mode == 1) {
+    if (int rc = make_im2col_map(&ma, conv->act, conv->n, conv->h, conv->w, conv->c, conv->g.R, conv->g.S,
+                                 conv->g.stride, conv->pad, BLOCK_M))
+      return rc;
+  } else if (int rc = a_mn ? make_map_mn(&ma, A, K, M) : make_map(&ma, A, M, K, BLOCK_M)) {
+    return rc;
+  }
+  if (conv && conv->g.mode == 2) {
+    if (int rc = make_im2col_map(&mb, conv->act, conv->n, conv->h, conv->w, conv->c, conv->g.R, conv->g.S,
+                                 conv->g.stride, conv->pad, BLOCK_K))
+      return rc;
+  } else if (conv && conv->g.flip) {
+    if (int rc = make_weight_tap_map(&mb, B, conv->wcout, conv->wtaps, conv->wcin)) return rc;
+  } else if (pull) {
     p.rows_per_rank = rows_per_rank;
     p.world = world->world;
     p.rank = world->rank;
@@ -841,7 +1009,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   const int items = tiles * splits;
   const int grid = items < sms ? items : sms;
   int rc;
-  const bool thin = !pull && p.num_kb <= 4 && splits == 1;      // store-bound: deeper epilogue pipeline
+  const bool thin = !pull && p.num_kb <= 4 && splits == 1;   // store-bound: deeper epilogue pipeline
   if (block_n == 256) {
     rc = pull ? launch_gemm<256, true, false>(ma, mb, md, pm, p, grid, stream)
               : (thin ? launch_gemm<256, false, true>(ma, mb, md, pm, p, grid, stream)
@@ -887,6 +1055,65 @@ int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off
   if (!world) return fail("tb200_gemm_bf16_nt_pull: null world%s");
   return gemm_common(world, bucket, b_off, rows_per_rank, A, nullptr, D, bias, bias_dtype, M, N, K,
                      d_dtype, act, epoch_dev, status_dev, spin_budget, stream);
+}
+
+// ---- implicit-GEMM convolutions (K5: "convs as implicit GEMM on the same mainloop") ----------------
+// x [n, h, w, cin] and y / dy [n, oh, ow, cout] are NHWC bf16 (torch channels_last), weights
+// [cout, R, S, cin] bf16 (a channels_last torch weight). Square stride / padding, no dilation, no groups.
+static int conv_out(int in, int k, int stride, int pad) { return (in + 2 * pad - k) / stride + 1; }
+
+static int conv_check(const char* who, int n, int h, int w, int cin, int cout, int R, int S, int stride,
+                      int pad, int im2col_channels) {
+  if (n <= 0 || h <= 0 || w <= 0 || cin <= 0 || cout <= 0) return fail("%s: empty problem", who);
+  if (R <= 0 || S <= 0 || R > 16 || S > 16 || stride <= 0 || stride > 8 || pad < 0 || pad >= 16)
+    return fail("%s: unsupported filter geometry", who);
+  if (conv_out(h, R, stride, pad) <= 0 || conv_out(w, S, stride, pad) <= 0) return fail("%s: empty output", who);
+  if (im2col_channels % 64)
+    return fail("%s: the gathered tensor's channel count (%ld) must be a multiple of 64", who, im2col_channels);
+  return 0;
+}
+
+int tb200_conv2d_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
+                       int S, int stride, int pad, cudaStream_t stream) {
+  if (int rc = conv_check("tb200_conv2d_fprop", n, h, wd, cin, cout, R, S, stride, pad, cin)) return rc;
+  const int oh = conv_out(h, R, stride, pad), ow = conv_out(wd, S, stride, pad);
+  ConvHost c{};
+  c.g = ConvGeom{1, oh, ow, stride, -pad, R, S, cin / 64, 0};
+  c.act = x; c.n = n; c.h = h; c.w = wd; c.c = cin; c.pad = pad;
+  return gemm_common(nullptr, 0, 0, 0, nullptr, w, y, nullptr, 0, n * oh * ow, cout, R * S * cin, TB200_BF16, 0,
+                     nullptr, nullptr, 0, stream, nullptr, 0, 0, 0, &c);
+}
+
+int tb200_conv2d_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout, int R,
+                       int S, int stride, int pad, cudaStream_t stream) {
+  if (stride != 1) return fail("tb200_conv2d_dgrad: only stride 1 is implemented%s");
+  if (pad > R - 1 || pad > S - 1) return fail("tb200_conv2d_dgrad: padding larger than the filter%s");
+  if (int rc = conv_check("tb200_conv2d_dgrad", n, h, wd, cin, cout, R, S, stride, pad, cout)) return rc;
+  if (R != S) return fail("tb200_conv2d_dgrad: square filters only%s");
+  if (cin % 8) return fail("tb200_conv2d_dgrad: cin %s(%ld) must be a multiple of 8", "", cin);
+  const int oh = conv_out(h, R, 1, pad), ow = conv_out(wd, S, 1, pad);
+  // dx = "full" correlation of dy with the flipped filter: an fprop over dy with padding taps-1-pad whose
+  // output grid is x's
+  ConvHost c{};
+  c.g = ConvGeom{1, h, wd, 1, -(R - 1 - pad), R, S, cout / 64, 1};
+  c.act = dy; c.n = n; c.h = oh; c.w = ow; c.c = cout; c.pad = R - 1 - pad;
+  c.wcout = cout; c.wtaps = R * S; c.wcin = cin;
+  return gemm_common(nullptr, 0, 0, 0, nullptr, w, dx, nullptr, 0, n * h * wd, cin, R * S * cout, TB200_BF16, 0,
+                     nullptr, nullptr, 0, stream, nullptr, 0, 0, 1, &c);
+}
+
+int tb200_conv2d_wgrad(const void* x, const void* dy, void* dw, int n, int h, int wd, int cin, int cout, int R,
+                       int S, int stride, int pad, int dw_dtype, cudaStream_t stream) {
+  if (int rc = conv_check("tb200_conv2d_wgrad", n, h, wd, cin, cout, R, S, stride, pad, cin)) return rc;
+  if (cout % 8) return fail("tb200_conv2d_wgrad: cout %s(%ld) must be a multiple of 8", "", cout);
+  const int oh = conv_out(h, R, stride, pad), ow = conv_out(wd, S, stride, pad);
+  // dW[cout, (tap, cin)] = dy[pixel, cout]^T . im2col(x)[pixel, (tap, cin)]: both operands are stored
+  // with the reduction (pixel) index outermost, i.e. MN-major
+  ConvHost c{};
+  c.g = ConvGeom{2, oh, ow, stride, -pad, R, S, cin / 64, 0};
+  c.act = x; c.n = n; c.h = h; c.w = wd; c.c = cin; c.pad = pad;
+  return gemm_common(nullptr, 0, 0, 0, dy, nullptr, dw, nullptr, 0, cout, R * S * cin, n * oh * ow, dw_dtype, 0,
+                     nullptr, nullptr, 0, stream, nullptr, 0, 1, 1, &c);
 }
 
 // Pre-size the split-K scratch (call before CUDA-graph capture so no allocation happens

@@ -133,6 +133,19 @@ int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, 
 int tb200_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
                     int K, int a_mn_major, int b_mn_major, int d_dtype, int act, cudaStream_t stream);
 
+/* Implicit-GEMM convolutions on the same tcgen05 mainloop (K5): one operand is gathered by im2col-mode
+ * TMA loads instead of tiled ones. x [n,h,w,cin], y/dy [n,oh,ow,cout] NHWC bf16 (torch channels_last),
+ * w / dw [cout,R,S,cin] (a channels_last weight); square stride and padding, no dilation, no groups.
+ *   fprop: y  = conv(x, w)                     cin  % 64 == 0
+ *   dgrad: dx = conv_transpose(dy, w)          cout % 64 == 0, cin % 8 == 0, stride 1 only
+ *   wgrad: dw = dy^T . im2col(x)               cin  % 64 == 0, cout % 8 == 0; dw bf16 or fp32 (split-K)  */
+int tb200_conv2d_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
+                       int S, int stride, int pad, cudaStream_t stream);
+int tb200_conv2d_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout, int R,
+                       int S, int stride, int pad, cudaStream_t stream);
+int tb200_conv2d_wgrad(const void* x, const void* dy, void* dw, int n, int h, int wd, int cin, int cout, int R,
+                       int S, int stride, int pad, int dw_dtype, cudaStream_t stream);
+
 /* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
 int tb200_gemm_reserve(size_t bytes);
 

@@ -1,0 +1,87 @@
+"""Implicit-GEMM convolutions (tb200_conv2d_fprop / _dgrad / _wgrad: im2col-mode TMA loads feeding the
+tcgen05 mainloop) against a plain PyTorch fp32 convolution of the same bf16-rounded operands."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(dev, n, cin, cout, hw, k, stride, pad, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    x = torch.randn(n, cin, hw, hw, generator=g).to(dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).to(dev).to(torch.bfloat16)
+    w = w.contiguous(memory_format=torch.channels_last)
+    return x, w
+
+
+# (n, cin, cout, hw, k, stride, pad): 3x3 same, 3x3 stride 2, 1x1 stride 2, a pixel count that is not a
+# multiple of the 128-row tile, an input below the 128 KiB small-tensor threshold, 5x5
+SHAPES = [
+    (8, 64, 64, 28, 3, 1, 1),
+    (8, 128, 128, 28, 3, 2, 1),
+    (8, 256, 512, 14, 1, 2, 0),
+    (3, 512, 512, 7, 3, 1, 1),
+    (2, 64, 128, 14, 3, 1, 1),
+    (4, 64, 96, 12, 5, 1, 2),
+    (4, 128, 64, 15, 3, 2, 1),
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "x".join(map(str, s)))
+def test_fprop_matches_fp32(cuda_device, shape):
+    from tiresias_b200.ops import native
+    n, cin, cout, hw, k, stride, pad = shape
+    x, w = _case(cuda_device, *shape)
+    y = native.conv2d_fprop(x, w, stride, pad)
+    ref = torch.nn.functional.conv2d(x.float(), w.float(), stride=stride, padding=pad)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-2), float((y.float() - ref).abs().max())
+
+
+@pytest.mark.parametrize("shape", [s for s in SHAPES if s[5] == 1 and s[2] % 64 == 0], ids=lambda s: "x".join(map(str, s)))
+def test_dgrad_matches_fp32(cuda_device, shape):
+    from tiresias_b200.ops import native
+    n, cin, cout, hw, k, stride, pad = shape
+    x, w = _case(cuda_device, *shape)
+    xr = x.float().requires_grad_(True)
+    ref_y = torch.nn.functional.conv2d(xr, w.float(), stride=stride, padding=pad)
+    dy = torch.randn_like(ref_y).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ref_y.backward(dy.float())
+    dx = native.conv2d_dgrad(dy, w, x.shape, stride, pad)
+    assert dx.shape == x.shape
+    assert torch.allclose(dx.float(), xr.grad, rtol=2e-2, atol=3e-2), float((dx.float() - xr.grad).abs().max())
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "x".join(map(str, s)))
+def test_wgrad_matches_fp32(cuda_device, shape):
+    from tiresias_b200.ops import native
+    n, cin, cout, hw, k, stride, pad = shape
+    x, w = _case(cuda_device, *shape)
+    wr = w.float().requires_grad_(True)
+    ref_y = torch.nn.functional.conv2d(x.float(), wr, stride=stride, padding=pad)
+    dy = (torch.randn_like(ref_y) / 8).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ref_y.backward(dy.float())
+    dw = native.conv2d_wgrad(x, dy, (k, k), stride, pad, out_dtype=torch.float32)
+    assert dw.shape == w.shape
+    scale = float(wr.grad.abs().max())
+    assert torch.allclose(dw, wr.grad, rtol=2e-2, atol=2e-2 * scale), float((dw - wr.grad).abs().max())
+
+
+def test_module_forward_backward(cuda_device):
+    from tiresias_b200.ops.conv import TcConv2d
+    torch.manual_seed(0)
+    for stride in (1, 2):
+        conv = TcConv2d(64, 128, 3, stride, 1).to(cuda_device).to(torch.bfloat16).to(memory_format=torch.channels_last)
+        x = torch.randn(4, 64, 16, 16, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        x.requires_grad_(True)
+        y = conv(x)
+        dy = torch.randn_like(y)
+        y.backward(dy)
+        xr = x.detach().float().requires_grad_(True)
+        wr = conv.weight.detach().float().requires_grad_(True)
+        yr = torch.nn.functional.conv2d(xr, wr, stride=stride, padding=1)
+        yr.backward(dy.float())
+        assert torch.allclose(y.float(), yr, rtol=3e-2, atol=3e-2)
+        assert torch.allclose(x.grad.float(), xr.grad, rtol=3e-2, atol=6e-2)
+        assert conv.weight.grad.shape == conv.weight.shape
+        assert torch.allclose(conv.weight.grad.float(), wr.grad, rtol=3e-2, atol=3e-2 * float(wr.grad.abs().max()))

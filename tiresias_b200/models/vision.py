@@ -14,7 +14,7 @@ from torch import nn
 
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
-from ..ops.conv import TcConv1x1
+from ..ops.conv import TcConv1x1, TcConv2d
 from ..ops.linear import TcLinear
 from ..ops.pooling import MaxPool3x3S2
 
@@ -25,6 +25,9 @@ import os
 # per ResNet-50 step), so it is opt-in (TB200_TC_CONV1X1=1) until the GEMM grows a BatchNorm-statistics
 # epilogue that removes the separate statistics pass.
 TC_CONV1X1 = os.environ.get("TB200_TC_CONV1X1", "0") == "1"
+# k x k and strided convolutions as implicit GEMMs with im2col-mode TMA loads (ops/conv.py TcConv2d);
+# TB200_TC_CONV=1 turns on both kinds for every convolution whose input has a multiple of 64 channels.
+TC_CONV = os.environ.get("TB200_TC_CONV", "0") == "1"
 
 
 class TorchBNAct(nn.Module):
@@ -54,8 +57,10 @@ def _bn(channels: int, relu: bool, fused: bool) -> nn.Module:
 def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0, fused: bool = False) -> nn.Module:
     """cuDNN convolution, except 1x1 / stride 1 in the fused build: those are plain GEMMs over the NHWC
     pixel rows and run on the tcgen05 kernel (ops/conv.py)."""
-    if fused and TC_CONV1X1 and k == 1 and stride == 1 and pad == 0:
+    if fused and (TC_CONV1X1 or TC_CONV) and k == 1 and stride == 1 and pad == 0 and cin % 8 == 0 and cout % 8 == 0:
         return TcConv1x1(cin, cout)
+    if fused and TC_CONV and cin % 64 == 0 and cout % 8 == 0:
+        return TcConv2d(cin, cout, k, stride, pad)
     return nn.Conv2d(cin, cout, k, stride, pad, bias=False)
 
 
@@ -97,7 +102,7 @@ class ResNet(nn.Module):
         self.pool = nn.AdaptiveAvgPool2d(1)
         self.fc = TcLinear(cin, num_classes) if fused else nn.Linear(cin, num_classes)
         for m in self.modules():
-            if isinstance(m, (nn.Conv2d, TcConv1x1)):
+            if isinstance(m, (nn.Conv2d, TcConv1x1, TcConv2d)):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
         for m in self.modules():
             if isinstance(m, Bottleneck):

@@ -6,7 +6,12 @@ In NHWC a 1x1 / stride-1 convolution *is* a GEMM over the N*H*W pixel rows:
     dW[Cout, Cin] = dy[R, Cout]^T . x[R, Cin]        (dy and x consumed as stored: MN-major A and B)
 so no im2col, no transposes and no layout change are needed — the activations are only re-viewed. Two
 thirds of ResNet-50's convolutions (conv1 / conv3 of every bottleneck, the stride-1 projection) are of
-this kind. Strided 1x1 and k x k convolutions stay on cuDNN for now (known gaps).
+this kind.
+
+k x k and strided convolutions (``TcConv2d``) run as implicit GEMMs on the same mainloop: the producer warp
+gathers the activation operand with im2col-mode TMA loads (``tb200_conv2d_fprop`` / ``_dgrad`` / ``_wgrad``,
+csrc/gemm_tcgen05.cu), so nothing is unfolded in memory. The input gradient of a *strided* convolution is
+the one piece still taken from cuDNN.
 """
 from __future__ import annotations
 
@@ -69,3 +74,58 @@ class TcConv1x1(nn.Module):
 
     def extra_repr(self) -> str:
         return f"{self.in_channels}, {self.out_channels}, kernel_size=(1, 1), tcgen05"
+
+
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        if not weight.is_contiguous(memory_format=torch.channels_last):
+            weight = weight.contiguous(memory_format=torch.channels_last)
+        ctx.save_for_backward(x, weight)
+        ctx.geom = (stride, pad)
+        return native.conv2d_fprop(x, weight, stride, pad)
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        x, weight = ctx.saved_tensors
+        stride, pad = ctx.geom
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            if stride == 1 and weight.shape[0] % 64 == 0:
+                dx = native.conv2d_dgrad(dy, weight, x.shape, stride, pad)
+            else:                                   # strided dgrad: cuDNN (known gaps)
+                dx = torch.ops.aten.convolution_backward(dy, x, weight, None, [stride, stride], [pad, pad],
+                                                         [1, 1], False, [0, 0], 1, [True, False, False])[0]
+        if ctx.needs_input_grad[1]:
+            dw = native.conv2d_wgrad(x, dy, weight.shape[2:], stride, pad)
+        return dx, dw, None, None
+
+
+class TcConv2d(nn.Module):
+    """``nn.Conv2d(cin, cout, k, stride, padding, bias=False)`` as an implicit GEMM on the tcgen05 kernel
+    for bf16 channels-last CUDA inputs (anything else goes to ``F.conv2d``). ``cin`` must be a multiple of
+    64 (one im2col box = 64 channels of one filter tap) and ``cout`` of 8. Same parameter shape as
+    Conv2d."""
+
+    def __init__(self, in_channels: int, out_channels: int, kernel_size: int, stride: int = 1,
+                 padding: int = 0):
+        super().__init__()
+        if in_channels % 64 or out_channels % 8:
+            raise ValueError("TcConv2d needs in_channels % 64 == 0 and out_channels % 8 == 0")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.kernel_size, self.stride, self.padding = kernel_size, stride, padding
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, kernel_size, kernel_size))
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
+            return _Conv2dFn.apply(x, self.weight, self.stride, self.padding)
+        return torch.nn.functional.conv2d(x, self.weight, stride=self.stride, padding=self.padding)
+
+    def extra_repr(self) -> str:
+        return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
+                f"stride={self.stride}, padding={self.padding}, tcgen05 implicit GEMM")

@@ -88,6 +88,13 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_gemm_bf16.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_int, C.c_int, st]
     lib.tb200_gemm_bf16.restype = C.c_int
+    ci = C.c_int
+    lib.tb200_conv2d_fprop.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, st]
+    lib.tb200_conv2d_fprop.restype = ci
+    lib.tb200_conv2d_dgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, st]
+    lib.tb200_conv2d_dgrad.restype = ci
+    lib.tb200_conv2d_wgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, st]
+    lib.tb200_conv2d_wgrad.restype = ci
     lib.tb200_gemm_reserve.argtypes = [sz]
     lib.tb200_gemm_bf16_nt_pull.argtypes = [C.POINTER(World), C.c_int, sz, C.c_int, vp, vp, vp,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -212,6 +219,51 @@ def gemm(a: torch.Tensor, b: torch.Tensor, a_mn_major: bool = False, b_mn_major:
     check(lib().tb200_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), bias_ptr, bias_dt, m, n, k,
                                 int(a_mn_major), int(b_mn_major), dtype_code(out.dtype), act, stream_ptr()))
     return out
+
+
+def _nhwc(t: torch.Tensor) -> torch.Tensor:
+    """Logical NCHW tensor stored channels_last -> its contiguous [N,H,W,C] view."""
+    v = t.permute(0, 2, 3, 1)
+    assert v.is_contiguous(), "expected a channels_last tensor"
+    return v
+
+
+def conv2d_fprop(x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
+    """Implicit-GEMM convolution forward (tb200_conv2d_fprop). ``x`` [N,Cin,H,W] and ``weight``
+    [Cout,Cin,R,S] are bf16 channels_last; returns y [N,Cout,OH,OW] channels_last."""
+    assert x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    xv, wv = _nhwc(x), _nhwc(weight)
+    n, h, w, cin = xv.shape
+    cout, r, s, _ = wv.shape
+    oh, ow = (h + 2 * pad - r) // stride + 1, (w + 2 * pad - s) // stride + 1
+    y = torch.empty((n, oh, ow, cout), dtype=torch.bfloat16, device=x.device)
+    check(lib().tb200_conv2d_fprop(xv.data_ptr(), wv.data_ptr(), y.data_ptr(), n, h, w, cin, cout, r, s,
+                                   stride, pad, stream_ptr()))
+    return y.permute(0, 3, 1, 2)
+
+
+def conv2d_dgrad(dy: torch.Tensor, weight: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:
+    """Gradient w.r.t. the input of a stride-1 convolution (tb200_conv2d_dgrad)."""
+    dyv, wv = _nhwc(dy), _nhwc(weight)
+    n, cin, h, w = x_shape
+    cout, r, s, _ = wv.shape
+    dx = torch.empty((n, h, w, cin), dtype=torch.bfloat16, device=dy.device)
+    check(lib().tb200_conv2d_dgrad(dyv.data_ptr(), wv.data_ptr(), dx.data_ptr(), n, h, w, cin, cout, r, s,
+                                   stride, pad, stream_ptr()))
+    return dx.permute(0, 3, 1, 2)
+
+
+def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, kernel, stride: int, pad: int,
+                 out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """Gradient w.r.t. the weight (tb200_conv2d_wgrad); returns [Cout,Cin,R,S] channels_last."""
+    xv, dyv = _nhwc(x), _nhwc(dy)
+    n, h, w, cin = xv.shape
+    cout = dyv.shape[3]
+    r, s = kernel
+    dw = torch.empty((cout, r, s, cin), dtype=out_dtype, device=x.device)
+    check(lib().tb200_conv2d_wgrad(xv.data_ptr(), dyv.data_ptr(), dw.data_ptr(), n, h, w, cin, cout, r, s,
+                                   stride, pad, dtype_code(out_dtype), stream_ptr()))
+    return dw.permute(0, 3, 1, 2)
 
 
 def transpose(x: torch.Tensor) -> torch.Tensor:
