@@ -16,7 +16,7 @@ from tiresias_b200.ops import native  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn"])
+    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv"])
     args = ap.parse_args()
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
@@ -28,6 +28,11 @@ def main():
         bias = torch.randn(n, device=dev)
         o = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
         run = lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o)  # noqa: E731
+    elif args.kernel == "conv":
+        # ResNet-50 layer2 3x3 at batch 256 as an implicit GEMM (im2col-mode TMA loads)
+        x = torch.randn(256, 128, 28, 28, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(128, 128, 3, 3, device=dev) / 34.0).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        run = lambda: native.conv2d_fprop(x, w, 1, 1)  # noqa: E731
     elif args.kernel == "bn":
         from tiresias_b200.ops.batchnorm import fused_bn_act
         x = torch.randn(64, 256, 56, 56, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)

@@ -1,4 +1,5 @@
 """Model registry and trainer planning logic that need no GPU."""
+import pytest
 import torch
 from torch import nn
 
@@ -63,3 +64,27 @@ def test_bucket_plan_covers_every_parameter_once_and_shards_evenly():
             assert lo + n == b.offset + b.length
         assert len(seen) == len(list(model.parameters())) and total >= sum(p.numel() for p in model.parameters())
         assert buckets[-1].offset + buckets[-1].length <= total
+
+
+def test_conv_pass_routing_spec():
+    from tiresias_b200.ops.conv import _parse_ops
+    assert _parse_ops("") == {"p": set(), "k": set()}
+    assert _parse_ops("1") == {"p": set("fdw"), "k": set("fdw")}
+    assert _parse_ops("p:fw,k:f") == {"p": {"f", "w"}, "k": {"f"}}
+    with pytest.raises(ValueError):
+        _parse_ops("q:f")
+    with pytest.raises(ValueError):
+        _parse_ops("p:x")
+
+
+def test_tc_conv_modules_fall_back_to_torch_on_cpu():
+    """Off the GPU the tcgen05 convolution modules are plain convolutions with Conv2d's parameter shape."""
+    from tiresias_b200.ops.conv import TcConv1x1, TcConv2d
+    torch.manual_seed(0)
+    x = torch.randn(2, 64, 9, 9)
+    c1, c3 = TcConv1x1(64, 16), TcConv2d(64, 24, 3, 2, 1)
+    assert c1.weight.shape == (16, 64, 1, 1) and c3.weight.shape == (24, 64, 3, 3)
+    assert torch.allclose(c1(x), torch.nn.functional.conv2d(x, c1.weight))
+    assert torch.allclose(c3(x), torch.nn.functional.conv2d(x, c3.weight, stride=2, padding=1))
+    with pytest.raises(ValueError):
+        TcConv2d(48, 64, 3)

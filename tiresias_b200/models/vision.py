@@ -14,7 +14,7 @@ from torch import nn
 
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
-from ..ops.conv import TcConv1x1, TcConv2d
+from ..ops.conv import TcConv1x1, TcConv2d, _parse_ops
 from ..ops.linear import TcLinear
 from ..ops.pooling import MaxPool3x3S2
 
@@ -27,7 +27,10 @@ import os
 TC_CONV1X1 = os.environ.get("TB200_TC_CONV1X1", "0") == "1"
 # k x k and strided convolutions as implicit GEMMs with im2col-mode TMA loads (ops/conv.py TcConv2d);
 # TB200_TC_CONV=1 turns on both kinds for every convolution whose input has a multiple of 64 channels.
-TC_CONV = os.environ.get("TB200_TC_CONV", "0") == "1"
+# Per-pass routing: TB200_TC_CONV="p:fw,k:f" (see ops.conv._parse_ops).
+TC_CONV = _parse_ops(os.environ.get("TB200_TC_CONV", ""))
+if TC_CONV1X1:
+    TC_CONV["p"] = set("fdw")
 
 
 class TorchBNAct(nn.Module):
@@ -57,10 +60,10 @@ def _bn(channels: int, relu: bool, fused: bool) -> nn.Module:
 def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0, fused: bool = False) -> nn.Module:
     """cuDNN convolution, except 1x1 / stride 1 in the fused build: those are plain GEMMs over the NHWC
     pixel rows and run on the tcgen05 kernel (ops/conv.py)."""
-    if fused and (TC_CONV1X1 or TC_CONV) and k == 1 and stride == 1 and pad == 0 and cin % 8 == 0 and cout % 8 == 0:
-        return TcConv1x1(cin, cout)
-    if fused and TC_CONV and cin % 64 == 0 and cout % 8 == 0:
-        return TcConv2d(cin, cout, k, stride, pad)
+    if fused and TC_CONV["p"] and k == 1 and stride == 1 and pad == 0 and cin % 8 == 0 and cout % 8 == 0:
+        return TcConv1x1(cin, cout, TC_CONV["p"])
+    if fused and TC_CONV["k"] and not (k == 1 and stride == 1) and cin % 64 == 0 and cout % 8 == 0:
+        return TcConv2d(cin, cout, k, stride, pad, TC_CONV["k"])
     return nn.Conv2d(cin, cout, k, stride, pad, bias=False)
 
 
@@ -74,7 +77,7 @@ class Bottleneck(nn.Module):
         super().__init__()
         cout = width * self.expansion
         self.conv1, self.bn1 = _conv(cin, width, 1, fused=fused), _bn(width, True, fused)
-        self.conv2, self.bn2 = _conv(width, width, 3, stride, 1), _bn(width, True, fused)
+        self.conv2, self.bn2 = _conv(width, width, 3, stride, 1, fused=fused), _bn(width, True, fused)
         self.conv3, self.bn3 = _conv(width, cout, 1, fused=fused), _bn(cout, True, fused)
         self.down_conv = self.down_bn = None
         if stride != 1 or cin != cout:

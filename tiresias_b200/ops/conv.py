@@ -25,7 +25,7 @@ from . import native
 
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, ops: frozenset = frozenset("fdw")) -> torch.Tensor:
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         n, cin, h, w = x.shape
@@ -34,9 +34,12 @@ class _Conv1x1Fn(torch.autograd.Function):
         w2d = weight.permute(0, 2, 3, 1).reshape(cout, cin)
         if not w2d.is_contiguous():
             w2d = w2d.contiguous()
-        y2d = native.gemm_nt(x2d, w2d)
         ctx.save_for_backward(x2d, w2d)
         ctx.shape = (n, cin, h, w, cout)
+        ctx.ops = ops
+        if "f" not in ops:
+            return torch.nn.functional.conv2d(x, w2d.view(cout, 1, 1, cin).permute(0, 3, 1, 2))
+        y2d = native.gemm_nt(x2d, w2d)
         return y2d.view(n, h, w, cout).permute(0, 3, 1, 2)
 
     @staticmethod
@@ -46,12 +49,23 @@ class _Conv1x1Fn(torch.autograd.Function):
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dy2d = dy.permute(0, 2, 3, 1).reshape(n * h * w, cout)
+        ops = ctx.ops
+        want_dx, want_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        own_dx, own_dw = want_dx and "d" in ops, want_dw and "w" in ops
         dx = dw = None
-        if ctx.needs_input_grad[0]:
+        if own_dx:
             dx = native.gemm(dy2d, w2d, b_mn_major=True).view(n, h, w, cin).permute(0, 3, 1, 2)
-        if ctx.needs_input_grad[1]:
+        if own_dw:
             dw = native.gemm(dy2d, x2d, a_mn_major=True, b_mn_major=True).view(cout, 1, 1, cin).permute(0, 3, 1, 2)
-        return dx, dw
+        if (want_dx and not own_dx) or (want_dw and not own_dw):
+            x4 = x2d.view(n, h, w, cin).permute(0, 3, 1, 2)
+            w4 = w2d.view(cout, 1, 1, cin).permute(0, 3, 1, 2)
+            lib_dx, lib_dw, _ = torch.ops.aten.convolution_backward(
+                dy, x4, w4, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                [want_dx and not own_dx, want_dw and not own_dw, False])
+            dx = dx if own_dx else lib_dx
+            dw = dw if own_dw else lib_dw
+        return dx, dw, None
 
 
 class TcConv1x1(nn.Module):
@@ -59,73 +73,109 @@ class TcConv1x1(nn.Module):
     channels-last CUDA inputs (anything else goes to ``F.conv2d``). The weight keeps Conv2d's shape
     ``[cout, cin, 1, 1]``, so checkpoints and the trainer's flat parameter layout are unchanged."""
 
-    def __init__(self, in_channels: int, out_channels: int):
+    def __init__(self, in_channels: int, out_channels: int, ops=("f", "d", "w")):
         super().__init__()
         if in_channels % 8 or out_channels % 8:
             raise ValueError("channel counts must be multiples of 8 (TMA 16-byte stride rule)")
         self.in_channels, self.out_channels = in_channels, out_channels
+        self.ops = frozenset(ops)
         self.weight = nn.Parameter(torch.empty(out_channels, in_channels, 1, 1))
         nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
-            return _Conv1x1Fn.apply(x, self.weight)
+            return _Conv1x1Fn.apply(x, self.weight, self.ops)
         return torch.nn.functional.conv2d(x, self.weight)
 
     def extra_repr(self) -> str:
         return f"{self.in_channels}, {self.out_channels}, kernel_size=(1, 1), tcgen05"
 
 
+def _parse_ops(spec: str):
+    """``TB200_TC_CONV`` -> {kind: set of passes}. kind ``p`` = pointwise (1x1, stride 1), ``k`` = every
+    other geometry; passes ``f`` forward, ``d`` input gradient, ``w`` weight gradient. ``1`` = everything,
+    e.g. ``p:fw,k:f`` = pointwise forward + weight gradient and k x k forward on the tcgen05 kernels, the
+    rest on cuDNN."""
+    out = {"p": set(), "k": set()}
+    spec = (spec or "").strip()
+    if spec in ("", "0"):
+        return out
+    if spec == "1":
+        return {"p": set("fdw"), "k": set("fdw")}
+    for part in spec.split(","):
+        kind, _, passes = part.partition(":")
+        if kind not in out or not set(passes) <= set("fdw"):
+            raise ValueError(f"bad TB200_TC_CONV entry {part!r}")
+        out[kind] |= set(passes)
+    return out
+
+
+def _aten_backward(dy, x, weight, stride, pad, want_dx, want_dw):
+    return torch.ops.aten.convolution_backward(dy, x, weight, None, [stride, stride], [pad, pad], [1, 1], False,
+                                               [0, 0], 1, [want_dx, want_dw, False])
+
+
 class _Conv2dFn(torch.autograd.Function):
+    """One convolution whose three passes are individually routed to the tcgen05 implicit GEMM (``ops``
+    names them) or to cuDNN."""
+
     @staticmethod
-    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int, ops: frozenset) -> torch.Tensor:
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         if not weight.is_contiguous(memory_format=torch.channels_last):
             weight = weight.contiguous(memory_format=torch.channels_last)
         ctx.save_for_backward(x, weight)
-        ctx.geom = (stride, pad)
-        return native.conv2d_fprop(x, weight, stride, pad)
+        ctx.geom = (stride, pad, ops)
+        if "f" in ops:
+            return native.conv2d_fprop(x, weight, stride, pad)
+        return torch.nn.functional.conv2d(x, weight, stride=stride, padding=pad)
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor):
         x, weight = ctx.saved_tensors
-        stride, pad = ctx.geom
+        stride, pad, ops = ctx.geom
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
+        want_dx, want_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        # strided dgrad is the one pass without a kernel of ours yet (DESIGN.md, known gaps)
+        own_dx = want_dx and "d" in ops and stride == 1 and weight.shape[0] % 64 == 0
+        own_dw = want_dw and "w" in ops
         dx = dw = None
-        if ctx.needs_input_grad[0]:
-            if stride == 1 and weight.shape[0] % 64 == 0:
-                dx = native.conv2d_dgrad(dy, weight, x.shape, stride, pad)
-            else:                                   # strided dgrad: cuDNN (DESIGN.md, known gaps)
-                dx = torch.ops.aten.convolution_backward(dy, x, weight, None, [stride, stride], [pad, pad],
-                                                         [1, 1], False, [0, 0], 1, [True, False, False])[0]
-        if ctx.needs_input_grad[1]:
+        if own_dx:
+            dx = native.conv2d_dgrad(dy, weight, x.shape, stride, pad)
+        if own_dw:
             dw = native.conv2d_wgrad(x, dy, weight.shape[2:], stride, pad)
-        return dx, dw, None, None
+        if (want_dx and not own_dx) or (want_dw and not own_dw):
+            lib_dx, lib_dw, _ = _aten_backward(dy, x, weight, stride, pad, want_dx and not own_dx,
+                                               want_dw and not own_dw)
+            dx = dx if own_dx else lib_dx
+            dw = dw if own_dw else lib_dw
+        return dx, dw, None, None, None
 
 
 class TcConv2d(nn.Module):
     """``nn.Conv2d(cin, cout, k, stride, padding, bias=False)`` as an implicit GEMM on the tcgen05 kernel
     for bf16 channels-last CUDA inputs (anything else goes to ``F.conv2d``). ``cin`` must be a multiple of
     64 (one im2col box = 64 channels of one filter tap) and ``cout`` of 8. Same parameter shape as
-    Conv2d."""
+    Conv2d. ``ops`` picks the passes that run on our kernels (default: all three)."""
 
     def __init__(self, in_channels: int, out_channels: int, kernel_size: int, stride: int = 1,
-                 padding: int = 0):
+                 padding: int = 0, ops=("f", "d", "w")):
         super().__init__()
         if in_channels % 64 or out_channels % 8:
             raise ValueError("TcConv2d needs in_channels % 64 == 0 and out_channels % 8 == 0")
         self.in_channels, self.out_channels = in_channels, out_channels
         self.kernel_size, self.stride, self.padding = kernel_size, stride, padding
+        self.ops = frozenset(ops)
         self.weight = nn.Parameter(torch.empty(out_channels, in_channels, kernel_size, kernel_size))
         nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
-            return _Conv2dFn.apply(x, self.weight, self.stride, self.padding)
+            return _Conv2dFn.apply(x, self.weight, self.stride, self.padding, self.ops)
         return torch.nn.functional.conv2d(x, self.weight, stride=self.stride, padding=self.padding)
 
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
-                f"stride={self.stride}, padding={self.padding}, tcgen05 implicit GEMM")
+                f"stride={self.stride}, padding={self.padding}, tcgen05 implicit GEMM passes={sorted(self.ops)}")
