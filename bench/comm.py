@@ -65,10 +65,15 @@ def main():
     sizes = [1 << 20, 12 << 20, 48 << 20, 264 << 20]           # 2 MB .. 528 MB (VGG-16) of bf16 gradients
     nmax = max(sizes)
     symm = SymmetricWorld.from_env(dev)
-    symm.alloc("grad", nmax * 2)
-    symm.alloc("param", nmax * 2)
+    symm.alloc("grad", nmax * 2, multicast=True)       # NVLS view where the box has one
+    symm.alloc("param", nmax * 2, multicast=True)
     symm.alloc("flags", native.FLAG_WORDS * 4)
-    ws = symm.native_world("grad", "param", "flags")
+    ws_mc = symm.native_world("grad", "param", "flags")
+    has_mc = bool(ws_mc.grad_mc and ws_mc.param_mc)
+    ws_p2p = symm.native_world("grad", "param", "flags")
+    ws_p2p.grad_mc = None
+    ws_p2p.param_mc = None
+    ws = ws_p2p
     grad = symm.buffers["grad"].view(torch.bfloat16)
     param = symm.buffers["param"].view(torch.bfloat16)
     grad.normal_()
@@ -85,18 +90,22 @@ def main():
     rows = []
     for n in sizes:
         shard = n // world
-        for ctas in (32, 148):
+        for ctas, wsv, how in [(32, ws_p2p, "P2P"), (148, ws_p2p, "P2P")] + \
+                ([(32, ws_mc, "NVLS"), (148, ws_mc, "NVLS")] if has_mc else []):
             def ours_ps():
-                native.check(lib.tb200_ps_push_pull(C.byref(ws), 0, rank * shard, shard, native.BF16,
+                native.check(lib.tb200_ps_push_pull(C.byref(wsv), 0, rank * shard, shard, native.BF16,
                                                     master.data_ptr(), mom.data_ptr(), hyper.data_ptr(),
                                                     epoch.data_ptr(), counters.data_ptr(), status.data_ptr(),
                                                     400_000_000, ctas, 1, st))
-                native.check(lib.tb200_step_end(C.byref(ws), 1, epoch.data_ptr(), status.data_ptr(), 400_000_000, st))
+                native.check(lib.tb200_step_end(C.byref(wsv), 1, epoch.data_ptr(), status.data_ptr(), 400_000_000, st))
             ms = timed(ours_ps, dev)
+            # P2P: a GPU receives the other W-1 slices of its shard and sends its new shard W-1 times;
+            # NVLS: the switch reduces / replicates, a GPU sends its W-1 foreign slices once and receives
+            # the W-1 foreign shards once — the same bytes per direction, but no (W-1)-fold fan-in/out
             link_bytes = (world - 1) / world * n * 2                      # in (push) == out (pull), per direction
             hbm_bytes = shard * 16 + shard * 2 + shard * 2 + link_bytes  # master+mom r/w, local grad, local param, remote-served reads
             roof_ms = max(link_bytes / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6)) if world > 1 else hbm_bytes / (hbm * 1e6)
-            rows.append({"op": "ps_push_pull+sgd (fused)", "impl": "ours", "ctas": ctas, "elems": n, "world": world,
+            rows.append({"op": f"ps_push_pull+sgd (fused, {how})", "impl": "ours", "ctas": ctas, "elems": n, "world": world,
                          "ms": round(ms, 4), "nvlink_gbs_per_dir": round(link_bytes / ms / 1e6, 1),
                          "roofline_ms": round(roof_ms, 4), "frac_of_roofline": round(roof_ms / ms, 3)})
         g, p = grad[:n], param[:n]
@@ -121,9 +130,11 @@ def main():
         rows.append({"op": "reduce_scatter + torch SGD + all_gather", "impl": "nccl", "elems": n, "world": world,
                      "ms": round(ms_n, 4), "nvlink_gbs_per_dir": round((world - 1) / world * n * 2 / ms_n / 1e6, 1)})
         if world > 1:
-            for algo, name in ((0, "ring"), (1, "direct")):
+            for algo, name in ((0, "ring"), (1, "direct")) + (((2, "NVLS one-shot"),) if has_mc else ()):
+                wsa = ws_mc if algo == 2 else ws_p2p
+
                 def ours_ar():
-                    native.check(lib.tb200_allreduce(C.byref(ws), ptrs, n, native.BF16, 1.0 / world, algo,
+                    native.check(lib.tb200_allreduce(C.byref(wsa), ptrs, n, native.BF16, 1.0 / world, algo,
                                                      seq.data_ptr(), status.data_ptr(), 400_000_000, 64, st))
                 ms_a = timed(ours_ar, dev)
                 link = 2 * (world - 1) / world * n * 2

@@ -74,6 +74,22 @@ __device__ __forceinline__ void st_stream_16(void* p, const uint4& v) {
                : "memory");
 }
 
+// NVLS: loads/stores through a multicast address (csrc/nvls.cu). The load returns the sum of all GPUs'
+// copies of 8 bf16 (reduced in the NVSwitch, fp32 accumulation), the store writes all copies.
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc_ptr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc_ptr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_16(void* mc_ptr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_ptr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
 // System-scope release/acquire on 32-bit flags living in (possibly peer-mapped) global memory.
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

@@ -160,7 +160,24 @@ struct PushArgs {
   int broadcast;      // 1: store new params to every worker; 0: only to this PS's own buffer
 };
 
-template <typename GT, int W>
+__device__ __forceinline__ F8 unpack_bf16x8(const uint4& r) {
+  F8 f;
+  f.v[0] = bf16_lo(r.x); f.v[1] = bf16_hi(r.x); f.v[2] = bf16_lo(r.y); f.v[3] = bf16_hi(r.y);
+  f.v[4] = bf16_lo(r.z); f.v[5] = bf16_hi(r.z); f.v[6] = bf16_lo(r.w); f.v[7] = bf16_hi(r.w);
+  return f;
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const F8& x) {
+  uint4 o;
+  o.x = pack_bf16(x.v[0], x.v[1]); o.y = pack_bf16(x.v[2], x.v[3]);
+  o.z = pack_bf16(x.v[4], x.v[5]); o.w = pack_bf16(x.v[6], x.v[7]);
+  return o;
+}
+constexpr int kMcUnroll = 8;     // multicast loads in flight per thread
+
+// MC = NVLS: the W gradient slices are summed inside the NVSwitch by one multimem.ld_reduce per 16 bytes
+// (this GPU receives n/W bytes instead of (W-1) n/W) and the new parameters reach all W workers with one
+// multimem.st (this GPU sends n/W bytes instead of (W-1) n/W). bf16 gradients only.
+template <typename GT, int W, bool MC = false>
 __global__ void __launch_bounds__(kCommThreads) ps_push_pull_kernel(const PushArgs a) {
   const int rank = a.w.rank;
   const uint32_t epoch = *a.epoch;
@@ -190,6 +207,29 @@ __global__ void __launch_bounds__(kCommThreads) ps_push_pull_kernel(const PushAr
   const tb200_sgd_hyper_t h = *a.hyper;
   const size_t voff = a.shard_off / 8;  // shard_off is a multiple of 8 elements
   const size_t stride = (size_t)gridDim.x * blockDim.x;
+  if constexpr (MC) {
+    const uint4* gmc = reinterpret_cast<const uint4*>(a.w.grad_mc) + voff;
+    uint4* pmc = reinterpret_cast<uint4*>(a.w.param_mc) + voff;
+    for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < a.nvec; i0 += stride * kMcUnroll) {
+      uint4 raw[kMcUnroll];
+#pragma unroll
+      for (int u = 0; u < kMcUnroll; ++u) {
+        const size_t i = i0 + (size_t)u * stride;
+        if (i < a.nvec) raw[u] = multimem_ld_reduce_bf16x8(gmc + i);
+      }
+#pragma unroll
+      for (int u = 0; u < kMcUnroll; ++u) {
+        const size_t i = i0 + (size_t)u * stride;
+        if (i < a.nvec) {
+          F8 g = unpack_bf16x8(raw[u]);
+          F8 p;
+          sgd_update8(g, a.master, a.mom, i * 8, h, p);
+          if (a.broadcast) multimem_st_16(pmc + i, pack_bf16x8(p));
+          else VecIO<__nv_bfloat16>::store(a.w.param[rank], voff + i, p);
+        }
+      }
+    }
+  } else {
   constexpr int U = CommUnroll<GT, W>::value;
   for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < a.nvec; i0 += stride * U) {
     RawVec<GT> raw[U][W];
@@ -215,6 +255,7 @@ __global__ void __launch_bounds__(kCommThreads) ps_push_pull_kernel(const PushAr
           if (a.broadcast || w == rank) VecIO<__nv_bfloat16>::store(a.w.param[w], voff + i, p);
       }
     }
+  }
   }
 
   // 5. Publish: all CTAs' stores must be visible system-wide before the flag.
@@ -362,6 +403,7 @@ __global__ void bump_seq_kernel(uint32_t* seq) { *seq += 1; }
 // Uses the bucket-0 GRAD_READY / PARAM_DONE flag slots of bucket index TB200_MAX_BUCKETS-1.
 struct DirectArgs {
   tb200_world_t w;
+  void* mc;                     // NVLS multicast view of bufs[0..W-1] (algo 2), else NULL
   void* bufs[TB200_MAX_WORLD];
   size_t n;
   float scale;
@@ -371,7 +413,7 @@ struct DirectArgs {
   unsigned long long budget;
 };
 
-template <typename T, int W>
+template <typename T, int W, bool MC = false>
 __global__ void __launch_bounds__(kCommThreads) direct_allreduce_kernel(const DirectArgs a) {
   const int rank = a.w.rank;
   const int slot = TB200_MAX_BUCKETS - 1;
@@ -392,6 +434,28 @@ __global__ void __launch_bounds__(kCommThreads) direct_allreduce_kernel(const Di
   const size_t slice_vec = a.n / 8 / W;
   const size_t vbase = (size_t)rank * slice_vec;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
+  if constexpr (MC) {
+    // one-shot NVLS: the switch sums my slice of everybody's buffer; one multicast store returns it
+    uint4* mc = reinterpret_cast<uint4*>(a.mc) + vbase;
+    for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < slice_vec; i0 += stride * kMcUnroll) {
+      uint4 raw[kMcUnroll];
+#pragma unroll
+      for (int u = 0; u < kMcUnroll; ++u) {
+        const size_t i = i0 + (size_t)u * stride;
+        if (i < slice_vec) raw[u] = multimem_ld_reduce_bf16x8(mc + i);
+      }
+#pragma unroll
+      for (int u = 0; u < kMcUnroll; ++u) {
+        const size_t i = i0 + (size_t)u * stride;
+        if (i < slice_vec) {
+          F8 acc = unpack_bf16x8(raw[u]);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc.v[k] *= a.scale;
+          multimem_st_16(mc + i, pack_bf16x8(acc));
+        }
+      }
+    }
+  } else {
   constexpr int U = CommUnroll<T, W>::value;
   for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < slice_vec; i0 += stride * U) {
     RawVec<T> raw[U][W];
@@ -416,6 +480,7 @@ __global__ void __launch_bounds__(kCommThreads) direct_allreduce_kernel(const Di
         for (int w = 0; w < W; ++w) VecIO<T>::store(a.bufs[w], vbase + i, acc);
       }
     }
+  }
   }
   __threadfence_system();
   __syncthreads();
@@ -680,7 +745,18 @@ int tb200_ps_push_pull(const tb200_world_t* world, int bucket, size_t shard_off,
     TB_CASE(GT, 1); TB_CASE(GT, 2); TB_CASE(GT, 3); TB_CASE(GT, 4);           \
     TB_CASE(GT, 5); TB_CASE(GT, 6); TB_CASE(GT, 7); TB_CASE(GT, 8);           \
   }
-  if (grad_dtype == TB200_BF16) { TB_SWITCH(__nv_bfloat16) }
+  if (grad_dtype == TB200_BF16 && world->world > 1 && world->grad_mc && world->param_mc) {
+    // NVLS path: in-switch reduction and multicast stores
+    switch (world->world) {
+#define TB_MC_CASE(WW)                                                                    \
+  case WW:                                                                                \
+    ps_push_pull_kernel<__nv_bfloat16, WW, true><<<grid, kCommThreads, 0, stream>>>(a);   \
+    break
+      TB_MC_CASE(2); TB_MC_CASE(3); TB_MC_CASE(4); TB_MC_CASE(5); TB_MC_CASE(6); TB_MC_CASE(7); TB_MC_CASE(8);
+#undef TB_MC_CASE
+    }
+  }
+  else if (grad_dtype == TB200_BF16) { TB_SWITCH(__nv_bfloat16) }
   else if (grad_dtype == TB200_F32) { TB_SWITCH(float) }
   else return fail("tb200_ps_push_pull: bad grad dtype%s");
 #undef TB_SWITCH
@@ -728,6 +804,20 @@ int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD
   }
   DirectArgs a;
   a.w = *world;
+  a.mc = nullptr;
+  if (algo == 2) {
+    // NVLS: `bufs` must be the gradient buffers of `world` (their multicast view is world->grad_mc)
+    if (dtype != TB200_BF16) return fail("tb200_allreduce: the NVLS algorithm reduces bf16 only%s");
+    if (W > 1) {
+      // `bufs` must point into the gradient buffers of `world` (same offset on every rank): their
+      // multicast view is world->grad_mc + that offset
+      if (!world->grad_mc) return fail("tb200_allreduce: algo 2 needs world->grad_mc%s");
+      const ptrdiff_t off = reinterpret_cast<const char*>(bufs[world->rank]) -
+                            reinterpret_cast<const char*>(world->grad[world->rank]);
+      if (off < 0 || off % 16) return fail("tb200_allreduce: algo 2: bufs must lie inside world->grad%s");
+      a.mc = const_cast<char*>(reinterpret_cast<const char*>(world->grad_mc)) + off;
+    }
+  }
   for (int i = 0; i < TB200_MAX_WORLD; ++i) a.bufs[i] = i < W ? bufs[i] : nullptr;
   a.n = n;
   a.scale = scale;
@@ -745,7 +835,17 @@ int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD
     TB_CASE(T, 1); TB_CASE(T, 2); TB_CASE(T, 3); TB_CASE(T, 4);               \
     TB_CASE(T, 5); TB_CASE(T, 6); TB_CASE(T, 7); TB_CASE(T, 8);               \
   }
-  if (dtype == TB200_BF16) { TB_SWITCH(__nv_bfloat16) }
+  if (a.mc && W > 1) {
+    switch (W) {
+#define TB_MC_CASE(WW)                                                                          \
+  case WW:                                                                                      \
+    direct_allreduce_kernel<__nv_bfloat16, WW, true><<<grid, kCommThreads, 0, stream>>>(a);     \
+    break
+      TB_MC_CASE(2); TB_MC_CASE(3); TB_MC_CASE(4); TB_MC_CASE(5); TB_MC_CASE(6); TB_MC_CASE(7); TB_MC_CASE(8);
+#undef TB_MC_CASE
+    }
+  }
+  else if (dtype == TB200_BF16) { TB_SWITCH(__nv_bfloat16) }
   else if (dtype == TB200_F32) { TB_SWITCH(float) }
   else return fail("tb200_allreduce: bad dtype%s");
 #undef TB_SWITCH

@@ -63,6 +63,8 @@ typedef struct {
   const void* grad[TB200_MAX_WORLD];       /* flat gradient buffers (grad_dtype)        */
   void* param[TB200_MAX_WORLD];            /* flat parameter buffers (bf16)             */
   uint32_t* flags[TB200_MAX_WORLD];        /* flag pads, TB200_FLAG_WORDS each          */
+  const void* grad_mc;                     /* NVLS multicast view of the W gradient buffers, or NULL */
+  void* param_mc;                          /* NVLS multicast view of the W parameter buffers, or NULL */
 } tb200_world_t;
 
 /* Hyper-parameters live in device memory so a captured CUDA graph picks up changes. */
@@ -111,7 +113,9 @@ int tb200_step_end(const tb200_world_t* world, int num_buckets, uint32_t* epoch_
 /* ---- K3: all-reduce mode (README.md:6 "All-reduce not yet implemented") ---------------- */
 /* In-place sum over `n` elements of the symmetric buffers buf[0..W-1] (same offset on every
  * rank). algo 0 = ring (reduce-scatter + all-gather, 2(W-1) flag-synchronised steps),
- * algo 1 = direct two-shot through NVSwitch. seq_dev: device counter bumped per call.     */
+ * algo 1 = direct two-shot through NVSwitch, algo 2 = one-shot NVLS (multimem.ld_reduce + multimem.st;
+ * bf16, bufs must lie inside world->grad and world->grad_mc be set). seq_dev: device counter bumped
+ * per call.                                                                                   */
 int tb200_allreduce(const tb200_world_t* world, void* const bufs[TB200_MAX_WORLD], size_t n,
                     int dtype, float scale, int algo, uint32_t* seq_dev, int* status_dev,
                     unsigned long long spin_budget, int num_ctas, cudaStream_t stream);
@@ -132,6 +136,30 @@ int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, 
  * The contiguous dimension of every operand must be a multiple of 8.                               */
 int tb200_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
                     int K, int a_mn_major, int b_mn_major, int d_dtype, int act, cudaStream_t stream);
+
+/* ---- NVLS (NVLink SHARP) multicast: in-switch reduce / broadcast through multimem.* instructions ----
+ * tb200_nvls_supported: 1 when `device` can join a multicast object, 0 when not, <0 on error.
+ * tb200_nvls_selftest: single-process check and timing of multimem.ld_reduce (sum of all GPUs' copies),
+ * multimem.st (store into all copies) and the one-shot all-reduce built from them, over GPUs 0..ndev-1
+ * with `bytes` of bf16 per GPU and `ctas` CTAs of 512 threads; `report` receives one JSON object.
+ * Returns 0 = all values correct, 2 = NVLS unavailable on this box, 1 = error.                      */
+int tb200_nvls_supported(int device);
+int tb200_nvls_selftest(int ndev, size_t bytes, int ctas, char* report, size_t report_len);
+
+/* Multi-process symmetric memory that can carry an NVLS view: physical allocations (cuMemCreate) shared
+ * between the ranks' processes as POSIX file descriptors (the caller passes them over a unix socket).
+ * Order, with the rank's device current: every rank tb200_vmm_round + tb200_vmm_alloc; rank 0
+ * tb200_mc_create, the others tb200_mc_import(fd); every rank tb200_mc_add_device; BARRIER; every rank
+ * tb200_mc_bind -> multicast pointer; every rank tb200_vmm_import of each peer's fd -> peer pointers.   */
+int tb200_vmm_round(int world, size_t bytes, size_t* rounded);
+int tb200_vmm_alloc(size_t rounded, unsigned long long* phys, void** ptr, int* fd);
+int tb200_vmm_import(int fd, size_t rounded, unsigned long long* phys, void** ptr);
+int tb200_vmm_release(unsigned long long phys, void* ptr, size_t rounded);
+int tb200_mc_create(int world, size_t rounded, unsigned long long* mc, int* fd);
+int tb200_mc_import(int fd, unsigned long long* mc);
+int tb200_mc_add_device(unsigned long long mc);
+int tb200_mc_bind(unsigned long long mc, unsigned long long phys, size_t rounded, void** mc_ptr);
+int tb200_mc_release(unsigned long long mc, void* mc_ptr, size_t rounded);
 
 /* Implicit-GEMM convolutions on the same tcgen05 mainloop (K5): one operand is gathered by im2col-mode
  * TMA loads instead of tiled ones. x [n,h,w,cin], y/dy [n,oh,ow,cout] NHWC bf16 (torch channels_last),

@@ -46,14 +46,17 @@ TINY = ModelSpec("tiny", TinyNet, "image", (16, 16, 3), 16)
 def check_allreduce(rank, world, dev):
     symm = SymmetricWorld.from_env(dev)
     n = 1 << 20
-    symm.alloc("buf", n * 4)
+    symm.alloc("buf", n * 4, multicast=True)           # NVLS view where the box has one
     symm.alloc("flags", native.FLAG_WORDS * 4)
-    ws = symm.native_world(None, None, "flags")
+    ws = symm.native_world("buf", None, "flags")
+    has_mc = bool(symm.buffers["buf"].mc_ptr)
     seq = torch.zeros(2, dtype=torch.int32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     lib = native.lib()
-    for algo in (0, 1):
+    for algo in (0, 1, 2):
         for dt, code in ((torch.float32, native.F32), (torch.bfloat16, native.BF16)):
+            if algo == 2 and (not has_mc or dt != torch.bfloat16):
+                continue                                   # NVLS all-reduce: bf16, needs the multicast view
             cnt = n if dt == torch.float32 else 2 * n
             view = symm.buffers["buf"].view(dt)
             g = torch.Generator(device=dev).manual_seed(17 * rank + algo)
@@ -75,6 +78,7 @@ def check_allreduce(rank, world, dev):
             assert err <= tol * max(1.0, want.abs().max().item()), (algo, dt, err)
             dist.barrier()
     symm.close()
+    return has_mc
 
 
 def run_trainer(mode, rank, dev, steps=5, use_graph=False, pull=False, **kw):
@@ -89,6 +93,7 @@ def run_trainer(mode, rank, dev, steps=5, use_graph=False, pull=False, **kw):
     params = tr.param_flat.float().clone()
     n_pull = sum(1 for b in tr.buckets if b.pull_layer is not None)
     launches = tr.native_launches
+    run_trainer.last_nvls = tr.nvls
     tr.close()
     return losses, params, n_pull, launches
 
@@ -106,14 +111,29 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
-    check_allreduce(rank, world, dev)
+    has_mc = check_allreduce(rank, world, dev)
 
     l_ref, p_ref, _, _ = run_trainer("nccl", rank, dev)
-    l_ps, p_ps, n_pull, launches = run_trainer("ps", rank, dev)
-    assert n_pull == 0 and launches > 0
+    l_ps, p_ps, n_pull, launches = run_trainer("ps", rank, dev, nvls=False)       # peer loads / stores
+    assert n_pull == 0 and launches > 0 and not run_trainer.last_nvls
     assert all(abs(a - b) < 5e-2 for a, b in zip(l_ps, l_ref)), (l_ps, l_ref)
     assert torch.allclose(p_ps, p_ref, rtol=2e-2, atol=2e-2), (p_ps - p_ref).abs().max().item()
     assert same_on_all_ranks(p_ps, world), "PS broadcast left ranks with different parameters"
+
+    if has_mc:
+        # the same job with the reduction done inside the NVSwitch and multicast parameter stores
+        l_mc, p_mc, _, _ = run_trainer("ps", rank, dev, nvls=True)
+        assert run_trainer.last_nvls, "NVLS available but the trainer did not use it"
+        assert all(abs(a - b) < 5e-2 for a, b in zip(l_mc, l_ps)), (l_mc, l_ps)
+        assert torch.allclose(p_mc, p_ps, rtol=2e-2, atol=2e-2), (p_mc - p_ps).abs().max().item()
+        assert same_on_all_ranks(p_mc, world), "NVLS broadcast left ranks with different parameters"
+        l_mg, p_mg, _, _ = run_trainer("ps", rank, dev, steps=8, use_graph=True, nvls=True)
+        l_me, p_me, _, _ = run_trainer("ps", rank, dev, steps=8, use_graph=False, nvls=True)
+        assert all(abs(a - b) < 5e-2 for a, b in zip(l_mg, l_me)), (l_mg, l_me)
+        l_mr, p_mr, _, _ = run_trainer("ring", rank, dev, nvls=True)
+        assert run_trainer.last_nvls
+        assert torch.allclose(p_mr, p_ps, rtol=2e-2, atol=2e-2)
+        assert same_on_all_ranks(p_mr, world), "NVLS all-reduce: ranks diverged"
 
     # pull-GEMM: fc1's weight is row-sharded over the PS ranks and gathered inside its GEMM.
     # The local copy of a pulled weight is refreshed by the GEMM's own TMA stores, so compare
@@ -135,7 +155,7 @@ def main():
 
     dist.barrier()
     if rank == 0:
-        print("MULTI OK", flush=True)
+        print(f"MULTI OK (nvls={has_mc})", flush=True)
     dist.destroy_process_group()
 
 

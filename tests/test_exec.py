@@ -3,6 +3,8 @@
 executed JCT comparison."""
 import json
 import os
+import subprocess
+import sys
 
 import pytest
 import torch
@@ -95,3 +97,17 @@ def test_failed_job_is_reported_and_the_pool_keeps_serving(tmp_path):
     recs = {r["job_id"]: r for r in res["records"]}
     assert recs["0"]["status"] == "FAILED" and recs["1"]["status"] == "DONE"
     assert hasattr(loopback, "LoopbackTrainer")
+
+
+def test_fd_exchange_between_ranks():
+    """File descriptors (the handles of VMM / multicast allocations) travel between the ranks of a host
+    as SCM_RIGHTS over unix sockets: three gloo ranks swap pipes and read each other's message."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=3",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port),
+                          os.path.join(root, "tests", "fd_worker.py")], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0 and "FD OK" in res.stdout, (res.stdout + res.stderr)[-2000:]

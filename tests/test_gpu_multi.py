@@ -34,3 +34,21 @@ def test_in_kernel_collectives(native_lib, world):
     tail = (res.stdout + "\n" + res.stderr)[-4000:]
     assert res.returncode == 0, tail
     assert "MULTI OK" in res.stdout, tail
+
+
+def test_nvls_multimem_primitives(native_lib):
+    """multimem.ld_reduce / multimem.st through an NVLS multicast object: sums and broadcasts must be exact
+    (small integers in bf16), on as many GPUs as the box has."""
+    from tiresias_b200.ops import native
+    ndev = min(torch.cuda.device_count(), 8)
+    if ndev < 2:
+        pytest.skip("needs 2 GPUs")
+    if not native.nvls_supported(0):
+        pytest.skip("this box has no NVLS multicast support")
+    rep = native.nvls_selftest(ndev, 32 << 20)
+    if rep is None:
+        pytest.skip("NVLS unavailable: " + native.lib().tb200_last_error().decode(errors="replace"))
+    assert rep["ok"] and "error" not in rep, rep
+    want = ndev * (ndev + 1) / 2
+    assert rep["reduce_first"] == want and rep["bcast_min"] == want == rep["bcast_max"]
+    assert rep["allreduce_min"] == want == rep["allreduce_max"]

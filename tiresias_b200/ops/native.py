@@ -43,6 +43,8 @@ class World(C.Structure):
         ("grad", C.c_void_p * MAX_WORLD),
         ("param", C.c_void_p * MAX_WORLD),
         ("flags", C.c_void_p * MAX_WORLD),
+        ("grad_mc", C.c_void_p),
+        ("param_mc", C.c_void_p),
     ]
 
 
@@ -95,6 +97,23 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_conv2d_dgrad.restype = ci
     lib.tb200_conv2d_wgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, st]
     lib.tb200_conv2d_wgrad.restype = ci
+    ull, ullp, vpp, ip_ = C.c_ulonglong, C.POINTER(C.c_ulonglong), C.POINTER(vp), C.POINTER(C.c_int)
+    lib.tb200_vmm_round.argtypes = [ci, sz, C.POINTER(sz)]
+    lib.tb200_vmm_alloc.argtypes = [sz, ullp, vpp, ip_]
+    lib.tb200_vmm_import.argtypes = [ci, sz, ullp, vpp]
+    lib.tb200_vmm_release.argtypes = [ull, vp, sz]
+    lib.tb200_mc_create.argtypes = [ci, sz, ullp, ip_]
+    lib.tb200_mc_import.argtypes = [ci, ullp]
+    lib.tb200_mc_add_device.argtypes = [ull]
+    lib.tb200_mc_bind.argtypes = [ull, ull, sz, vpp]
+    lib.tb200_mc_release.argtypes = [ull, vp, sz]
+    for fn in ("tb200_vmm_round", "tb200_vmm_alloc", "tb200_vmm_import", "tb200_vmm_release", "tb200_mc_create",
+               "tb200_mc_import", "tb200_mc_add_device", "tb200_mc_bind", "tb200_mc_release"):
+        getattr(lib, fn).restype = ci
+    lib.tb200_nvls_supported.argtypes = [ci]
+    lib.tb200_nvls_supported.restype = ci
+    lib.tb200_nvls_selftest.argtypes = [ci, sz, ci, C.c_char_p, sz]
+    lib.tb200_nvls_selftest.restype = ci
     lib.tb200_gemm_reserve.argtypes = [sz]
     lib.tb200_gemm_bf16_nt_pull.argtypes = [C.POINTER(World), C.c_int, sz, C.c_int, vp, vp, vp,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -219,6 +238,27 @@ def gemm(a: torch.Tensor, b: torch.Tensor, a_mn_major: bool = False, b_mn_major:
     check(lib().tb200_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), bias_ptr, bias_dt, m, n, k,
                                 int(a_mn_major), int(b_mn_major), dtype_code(out.dtype), act, stream_ptr()))
     return out
+
+
+def nvls_supported(device: int = 0) -> bool:
+    """Can this GPU join an NVLS multicast object (NVSwitch fabric)?"""
+    return lib().tb200_nvls_supported(device) == 1
+
+
+def nvls_selftest(ndev: int, nbytes: int = 64 << 20, ctas: int = 148) -> Optional[dict]:
+    """Checks and times multimem.ld_reduce / multimem.st / the one-shot NVLS all-reduce over GPUs
+    0..ndev-1 of this process (csrc/nvls.cu). Returns the report, or None when the box has no NVLS."""
+    import json
+    buf = C.create_string_buffer(2048)
+    rc = lib().tb200_nvls_selftest(ndev, nbytes, ctas, buf, len(buf))
+    if rc == 2:
+        return None
+    if rc != 0 and not buf.value:
+        check(rc)
+    rep = json.loads(buf.value.decode())
+    if rc != 0:
+        rep["error"] = lib().tb200_last_error().decode(errors="replace")
+    return rep
 
 
 def _nhwc(t: torch.Tensor) -> torch.Tensor:

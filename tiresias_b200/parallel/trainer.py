@@ -114,8 +114,8 @@ class Trainer:
                  weight_decay: float = 1e-4, bucket_mb: float = 8.0, use_graph: bool = True,
                  pull_gemm: bool = True, pull_min_mb: float = 4.0, comm_ctas: int = 32,
                  spin_budget: int = 50_000_000, seed: int = 0, device: Optional[torch.device] = None,
-                 model: Optional[nn.Module] = None, allreduce_algo: int = 1, comm_group=None,
-                 stem_pad8: bool = False):
+                 model: Optional[nn.Module] = None, allreduce_algo: Optional[int] = None, comm_group=None,
+                 stem_pad8: bool = False, nvls: Optional[bool] = None):
         if mode not in ("ps", "ring", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
         self.spec, self.mode, self.batch_size = spec, mode, batch_size
@@ -124,7 +124,13 @@ class Trainer:
         self.world, self.rank = self.symm.world, self.symm.rank
         self.use_graph = use_graph
         self.comm_ctas, self.spin_budget = comm_ctas, spin_budget
-        self.allreduce_algo = allreduce_algo
+        # NVLS (in-switch reduction / multicast stores): None = the world's default (SymmetricWorld.
+        # nvls_preferred: every GPU supports multicast objects and the job spans >= 4 GPUs; TB200_NVLS=0/1
+        # forces it off/on); the buffers then come from the VMM allocator
+        self.nvls = (self.symm.nvls_preferred() if nvls is None else
+                     (bool(nvls) and self.symm.nvls_available())) if mode != "nccl" else False
+        self._allreduce_algo_arg = allreduce_algo
+        self.allreduce_algo = 1 if allreduce_algo is None else allreduce_algo
         self.comm_group = comm_group          # NCCL group of this job's ranks (mode "nccl" only)
         self.stem_pad8 = stem_pad8
         self._lib = native.lib()
@@ -164,9 +170,12 @@ class Trainer:
             self.param_flat = torch.zeros(n, dtype=torch.bfloat16, device=dev)
             self.grad_flat = torch.zeros(n, dtype=torch.bfloat16, device=dev)
         else:
-            self.symm.alloc("param", n * 2)
-            self.symm.alloc("grad", n * 2)
+            self.symm.alloc("param", n * 2, multicast=self.nvls)
+            self.symm.alloc("grad", n * 2, multicast=self.nvls)
             self.symm.alloc("flags", native.FLAG_WORDS * 4)
+            self.nvls = bool(self.symm.buffers["grad"].mc_ptr and self.symm.buffers["param"].mc_ptr)
+            if self._allreduce_algo_arg is None and self.nvls:
+                self.allreduce_algo = 2              # one-shot multimem.ld_reduce + multimem.st
             self.param_flat = self.symm.buffers["param"].view(torch.bfloat16)
             self.grad_flat = self.symm.buffers["grad"].view(torch.bfloat16)
             self._world_struct = self.symm.native_world("grad", "param", "flags")
