@@ -183,15 +183,11 @@ class SymmetricWorld:
             self._nvls_ok = all(votes)
         return self._nvls_ok
 
-    # Jobs spanning fewer GPUs than this keep the peer load/store kernels unless TB200_NVLS=1: at 2 GPUs the
-    # switch has nothing to save and the measured multicast rates are lower (profiles/COMM_r1.md).
-    NVLS_MIN_WORLD = 4
-
     def nvls_preferred(self) -> bool:
-        """Collective: should a trainer on this world default to the NVLS kernels?"""
-        if not self.nvls_available():
-            return False
-        return os.environ.get("TB200_NVLS", "auto") == "1" or self.world >= self.NVLS_MIN_WORLD
+        """Collective: should a trainer on this world default to the NVLS kernels? Only on request
+        (TB200_NVLS=1) for now: at 2 GPUs the switch has nothing to save and the peer load/store kernels
+        measure faster (profiles/COMM_r1.md)."""
+        return self.nvls_available() and os.environ.get("TB200_NVLS", "auto") == "1"
 
     def _alloc_vmm(self, name: str, nbytes: int) -> SymmBuffer:
         import torch.distributed as dist

@@ -125,8 +125,8 @@ class Trainer:
         self.use_graph = use_graph
         self.comm_ctas, self.spin_budget = comm_ctas, spin_budget
         # NVLS (in-switch reduction / multicast stores): None = the world's default (SymmetricWorld.
-        # nvls_preferred: every GPU supports multicast objects and the job spans >= 4 GPUs; TB200_NVLS=0/1
-        # forces it off/on); the buffers then come from the VMM allocator
+        # nvls_preferred: TB200_NVLS=1 and every GPU supports multicast objects); the buffers then come
+        # from the VMM allocator
         self.nvls = (self.symm.nvls_preferred() if nvls is None else
                      (bool(nvls) and self.symm.nvls_available())) if mode != "nccl" else False
         self._allreduce_algo_arg = allreduce_algo
