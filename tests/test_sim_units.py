@@ -312,3 +312,38 @@ def test_calibrated_mode_makes_interference_real(tmp_path):
     f2 = define_simulator_flags(); f2.parse(base + ["--mode", "calibrated", "--calibration", str(cal)])
     s2 = run(f2, output_dir=str(tmp_path / "cal"))
     assert s2["avg_jct"] > s1["avg_jct"]
+
+
+def test_calibrated_mode_uses_measured_utilisation_and_memory(tmp_path):
+    """K7: with a calibration that carries measured per-model GPU utilisation and peak memory, calibrated
+    mode reports those instead of drawing from N(avg, (max-avg)/2); parity mode ignores the tables."""
+    import csv as _csv
+    import json as _json
+    from tiresias_b200.cli.run_sim import run
+    trace = tmp_path / "trace.csv"
+    with open(trace, "w") as fh:
+        fh.write("type,normalized_time,minutes,gpu_per_container,used_gpus,gpu_utilization_avg,gpu_utilization_max,"
+                 "memory_max,memory_avg,model_name\n")
+        for i in range(4):
+            fh.write(f"noninteractive,{i * 10000},40,1,1,10,30,{2 << 30},{1 << 30},resnet50\n")
+    cal = tmp_path / "cal.json"
+    cal.write_text(_json.dumps({"gpu_util": {"resnet50": {"avg": 80.0, "max": 100.0}},
+                                "peak_mem_bytes": {"resnet50": 24 << 30}}))
+    base = ["--trace_file", str(trace), "--num_switch", "1", "--num_node_p_switch", "1", "--num_gpu_p_node", "4",
+            "--gpu_memory_capacity", "180", "--seed", "1", "--quiet"]
+
+    def rows(out):
+        with open(os.path.join(out, "cluster.csv")) as fh:
+            return list(_csv.DictReader(fh))
+
+    f1 = define_simulator_flags(); f1.parse(base + ["--mode", "calibrated", "--calibration", str(cal)])
+    run(f1, output_dir=str(tmp_path / "cal"))
+    busy = [r for r in rows(str(tmp_path / "cal")) if int(r["num_busy_gpus"]) == 4]
+    assert busy, "all four jobs should run together at some point"
+    # 4 GPUs each at the measured 80 %, 24 GiB of 180 GiB each: deterministic, printed as plain floats
+    assert all(abs(float(r["avg_gpu_utilization"]) - 80.0) < 1e-9 for r in busy)
+    assert all(abs(float(r["avg_gpu_memory_allocated"]) - 24 / 180) < 1e-6 for r in busy)
+    f2 = define_simulator_flags(); f2.parse(base)
+    run(f2, output_dir=str(tmp_path / "parity"))
+    busy2 = [r for r in rows(str(tmp_path / "parity")) if int(r["num_busy_gpus"]) == 4]
+    assert busy2 and all(float(r["avg_gpu_utilization"].strip("[]")) < 60 for r in busy2)     # draws around 10 %

@@ -46,8 +46,9 @@ def measure(gpus: int, models: Sequence[str], comm: str, iters: int, batch: int,
         if base is None:
             continue
         comm_tab[m] = {g: max(0.0, v - base) for g, v in per.items()}
-    cal.update({"comm_s_per_iter": comm_tab, "source": f"calib.measure gpus={gpus} comm={comm} batch={batch} iters={iters}",
-                "peak_mem_bytes": {r["model"]: r["peak_mem_bytes"] for r in res["records"] if r["num_gpu"] == 1}})
+    cal.update({"comm_s_per_iter": comm_tab, "source": f"calib.measure gpus={gpus} comm={comm} batch={batch} iters={iters}"})
+    if any(r.get("peak_mem_bytes") for r in res["records"]):
+        cal["peak_mem_bytes"] = {r["model"]: r["peak_mem_bytes"] for r in res["records"] if r["num_gpu"] == 1}
     return cal
 
 

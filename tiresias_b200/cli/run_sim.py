@@ -114,6 +114,8 @@ def _run_tick(flags: FlagSet, output_dir: str, rng, calibration) -> Dict:
     jm = JobsManager(flags, jq, rng=rng, trace_reader=reader)
     if calibration and calibration.get("interference_factor") is not None and flags.mode == "calibrated":
         jm.set_interference_factor(float(calibration["interference_factor"]), infrastructure)
+    if calibration and flags.mode == "calibrated":
+        jm.set_measured_profiles(calibration)            # K7: measured utilisation / memory per model
     sched = Scheduler(infrastructure, jm, log_manager, enable_migration=flags.enable_migration,
                       calibration=calibration)
     try:

@@ -24,6 +24,11 @@ from typing import Dict, List, Optional, Sequence, Tuple
 from .buddy import Block, BuddyAllocator, normalize_gpus
 
 
+def _mean(values) -> Optional[float]:
+    vals = [v for v in values if v is not None]
+    return sum(vals) / len(vals) if vals else None
+
+
 @dataclass
 class ExecJob:
     job_id: str
@@ -219,5 +224,7 @@ class Controller:
                         "iter_ms": sum(iter_ms) / len(iter_ms) if iter_ms else None,
                         "startup_s": sum(startup) / len(startup) if startup else None,
                         "snapshot_s": max([x.get("snapshot_s", 0.0) for r in j.results for x in r["ranks"]] or [0.0]),
-                        "peak_mem_bytes": max([x.get("peak_mem_bytes", 0) for r in j.results for x in r["ranks"]] or [0])})
+                        "peak_mem_bytes": max([x.get("peak_mem_bytes", 0) for r in j.results for x in r["ranks"]] or [0]),
+                        "gpu_util_avg": _mean([x.get("gpu_util_avg") for r in j.results for x in r["ranks"]]),
+                        "gpu_util_max": max([x.get("gpu_util_max") or 0.0 for r in j.results for x in r["ranks"]] or [0.0]) or None})
         return out

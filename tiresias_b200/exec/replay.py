@@ -65,7 +65,33 @@ def calibration_from_records(records: Sequence[Dict], reduce: str = "mean") -> D
         start.setdefault(r["model"], {}).setdefault(str(r["num_gpu"]), []).append(r["startup_s"] or 0.0)
     fold = (lambda v: min(v)) if reduce == "min" else (lambda v: sum(v) / len(v))
     table = lambda d: {m: {g: fold(v) for g, v in per.items()} for m, per in d.items()}  # noqa: E731
-    return {"iter_s": table(acc), "startup_s": table(start), "source": "self"}
+    cal = {"iter_s": table(acc), "startup_s": table(start), "source": "self"}
+    cal.update(measured_profiles(records))
+    return cal
+
+
+def measured_profiles(records: Sequence[Dict]) -> Dict:
+    """K7: per-model GPU utilisation (NVML, sampled while the job ran) and peak device memory, the two
+    per-task quantities the reference takes from the trace and perturbs with a random draw
+    (infra/device.py:30-36, model/model_factory.py:68-106). ``{"gpu_util": {model: {"avg", "max"}},
+    "peak_mem_bytes": {model: bytes}}`` — only models that were measured appear."""
+    util: Dict[str, Dict[str, List[float]]] = {}
+    mem: Dict[str, int] = {}
+    for r in records:
+        if r.get("status") != "DONE":
+            continue
+        if r.get("gpu_util_avg") is not None:
+            u = util.setdefault(r["model"], {"avg": [], "max": []})
+            u["avg"].append(float(r["gpu_util_avg"]))
+            u["max"].append(float(r.get("gpu_util_max") or r["gpu_util_avg"]))
+        if r.get("peak_mem_bytes"):
+            mem[r["model"]] = max(mem.get(r["model"], 0), int(r["peak_mem_bytes"]))
+    out: Dict = {}
+    if util:
+        out["gpu_util"] = {m: {"avg": sum(u["avg"]) / len(u["avg"]), "max": max(u["max"])} for m, u in util.items()}
+    if mem:
+        out["peak_mem_bytes"] = mem
+    return out
 
 
 def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:

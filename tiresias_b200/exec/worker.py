@@ -81,6 +81,7 @@ def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, de
     warm_chunk = max(check_every, 8)
     t_steady = None
     steady_from = done
+    util_sampler = None
     while done < iters:
         upto = min(iters, done + (warm_chunk if t_steady is None else check_every))
         for _ in range(upto - done):
@@ -89,6 +90,9 @@ def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, de
         if t_steady is None:
             trainer.synchronize()
             t_steady, steady_from = time.time(), done
+            if not loopback and torch.cuda.is_available():          # K7: measured utilisation of this job
+                from ..utils.clocks import UtilSampler
+                util_sampler = UtilSampler(device.index or 0).start()
         if done < iters:
             flag[0] = 1 if (r == 0 and store.check([preempt_key])) else 0
             if size > 1:
@@ -98,6 +102,7 @@ def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, de
                 break
     trainer.synchronize()
     t_done = time.time()
+    util = util_sampler.stop() if util_sampler is not None else {"gpu_util_avg": None, "gpu_util_max": None}
     run_s = t_done - t_begin
     steady_iters = done - steady_from
     if t_steady is not None and steady_iters >= 5:
@@ -119,7 +124,8 @@ def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, de
     return {"job": cmd["job"], "attempt": cmd["attempt"], "rank": r, "status": "preempted" if preempted else "done",
             "done": done, "iters_run": iters_run, "run_s": run_s, "startup_s": startup_s,
             "iter_ms": iter_ms, "snapshot_s": snapshot_s, "kernel_status": status,
-            "peak_mem_bytes": int(peak), "loss": loss, "t_end": time.time()}
+            "peak_mem_bytes": int(peak), "gpu_util_avg": util["gpu_util_avg"], "gpu_util_max": util["gpu_util_max"],
+            "loss": loss, "t_end": time.time()}
 
 
 def _warm_up(device) -> None:

@@ -60,6 +60,11 @@ class Device:
         total, drawn = 0.0, False
         normal = self._normal
         for t in self.running_tasks.values():
+            if t.measured_profile:
+                total += min(t.gpu_utilization_avg, 100)   # calibrated mode: the measured value, no draw (K7)
+                if 100 < total:
+                    total, drawn = 100.0, False
+                continue
             x = normal(t.gpu_utilization_avg, (t.gpu_utilization_max - t.gpu_utilization_avg) / 2)
             if x < 100:
                 total += x
@@ -121,17 +126,25 @@ def sample_utilizations(devices, rng) -> List[Tuple[float, bool]]:
     scales: List[float] = []
     for d in devices:
         for t in d.running_tasks.values():
+            if t.measured_profile:
+                continue                                # calibrated mode (K7): measured value, no draw
             locs.append(t.gpu_utilization_avg)
             scales.append((t.gpu_utilization_max - t.gpu_utilization_avg) / 2)
     if not locs:
-        return [(0.0, False)] * len(devices)
-    draws = rng.normal(np.asarray(locs, dtype=np.float64), np.asarray(scales, dtype=np.float64)).tolist() \
-        if len(locs) > 1 else [rng.normal(locs[0], scales[0])]
+        draws = []
+    else:
+        draws = rng.normal(np.asarray(locs, dtype=np.float64), np.asarray(scales, dtype=np.float64)).tolist() \
+            if len(locs) > 1 else [rng.normal(locs[0], scales[0])]
     out = []
     i = 0
     for d in devices:
         total, drawn = 0.0, False
-        for _ in range(len(d.running_tasks)):
+        for t in d.running_tasks.values():
+            if t.measured_profile:
+                total += min(t.gpu_utilization_avg, 100)
+                if 100 < total:
+                    total, drawn = 100.0, False
+                continue
             x = draws[i]
             i += 1
             if x < 100:

@@ -43,7 +43,7 @@ class Task(_Ordered):
     __slots__ = ("job_id", "task_id", "cpu", "mem", "gpu", "start_time", "gpu_utilization_avg",
                  "gpu_utilization_max", "gpu_memory_avg", "gpu_memory_max", "pending_time", "duration",
                  "started", "running", "finished", "interfered", "migration_count", "time_processed",
-                 "order", "is_ps")
+                 "order", "is_ps", "measured_profile")
 
     def __init__(self, job_id, task_id, duration, gpu_utilization_avg=0, gpu_utilization_max=0,
                  gpu_mem_avg=0, gpu_mem_max=0, cpu=0, mem=0, gpu=0, order=ORDER_PENDING):
@@ -62,6 +62,7 @@ class Task(_Ordered):
         self.time_processed = 0
         self.order = order
         self.is_ps = False
+        self.measured_profile = False      # calibrated mode: utilisation/memory measured on B200 (K7)
 
     def execute(self, delta_time) -> None:
         self.start_time = delta_time

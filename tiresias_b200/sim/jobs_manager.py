@@ -183,18 +183,47 @@ class JobsManager:
     def total_finished_jobs(self) -> int:
         return len(self.finished_jobs)
 
+    def set_measured_profiles(self, calibration) -> None:
+        """K7, calibrated mode: jobs whose trace row names a model that ``tiresias_b200.calib`` measured
+        take that model's GPU utilisation (NVML) and peak device memory instead of the trace's columns,
+        and their devices report the measured utilisation instead of drawing one (``Device.measured``)."""
+        cal = calibration or {}
+        self.measured_util = dict(cal.get("gpu_util") or {})
+        self.measured_mem = dict(cal.get("peak_mem_bytes") or {})
+
+    def _profile(self, row):
+        """(util_avg, util_max, mem_max_MiB, mem_avg_MiB, measured?) of a trace row."""
+        u_avg, u_max = row.gpu_utilization_avg, row.gpu_utilization_max
+        m_max = util.convert_bytes(row.memory_max, unit="MiB")
+        m_avg = util.convert_bytes(row.memory_avg, unit="MiB")
+        measured = False
+        name = getattr(row, "model_name", None)
+        if self.apply_interference and name:
+            mu = getattr(self, "measured_util", {}).get(name)
+            if mu:
+                u_avg, u_max, measured = float(mu["avg"]), float(mu.get("max", mu["avg"])), True
+            mm = getattr(self, "measured_mem", {}).get(name)
+            if mm:
+                m_max = m_avg = util.convert_bytes(mm, unit="MiB")
+                measured = True
+        return u_avg, u_max, m_max, m_avg, measured
+
     def gen_jobs(self, delta_time, scale_factor=1) -> int:
         rows = self.job_generator.generate_jobs(delta_time)
         jobs = []
         for row in rows:
+            u_avg, u_max, m_max, m_avg, measured = self._profile(row)
             j = Job(row.index, row.minutes * scale_factor, row.normalized_time, row.gpu_per_container,
-                    gpu_utilization_avg=row.gpu_utilization_avg,
-                    gpu_utilization_max=row.gpu_utilization_max,
-                    gpu_memory_max=util.convert_bytes(row.memory_max, unit="MiB"),
-                    gpu_memory_avg=util.convert_bytes(row.memory_avg, unit="MiB"),
+                    gpu_utilization_avg=u_avg,
+                    gpu_utilization_max=u_max,
+                    gpu_memory_max=m_max,
+                    gpu_memory_avg=m_avg,
                     total_gpus=row.used_gpus, order=self.order, model_name=row.model_name,
                     iterations=row.iterations)
             j.arrival_time = row.normalized_time
+            if measured:
+                for t in j.tasks.values():
+                    t.measured_profile = True
             jobs.append(j)
             self.all_jobs[j.job_id] = j
         self.insert(jobs)
