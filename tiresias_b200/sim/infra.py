@@ -35,7 +35,8 @@ def global_rng() -> np.random.RandomState:
 class Device:
     """One GPU. ``running_tasks`` holds every task *placed* on it (reserved or running)."""
 
-    __slots__ = ("device_id", "node_id", "memory", "enable_pack", "running_tasks", "rng", "_normal", "_mem")
+    __slots__ = ("device_id", "node_id", "memory", "enable_pack", "running_tasks", "rng", "_normal", "_mem",
+                 "_ndraw")
 
     def __init__(self, device_id, node_id, memory_cap, enable_pack, rng=None):
         self.device_id = device_id
@@ -46,6 +47,7 @@ class Device:
         self.rng = rng if rng is not None else global_rng()
         self._normal = self.rng.normal
         self._mem = 0                   # cached get_current_memory(); None = recompute
+        self._ndraw = 0                 # resident tasks whose utilisation is drawn (not measured)
 
     def is_idle(self) -> bool:
         return not self.running_tasks
@@ -104,48 +106,55 @@ class Device:
             return False
         if not pack and self.running_tasks:
             return False
+        if task.task_id not in self.running_tasks and not task.measured_profile:
+            self._ndraw += 1
         self.running_tasks[task.task_id] = task
         self._mem = None
         return True
 
     def pop_task(self, task_id):
         self._mem = None
-        return self.running_tasks.pop(task_id, None)
+        task = self.running_tasks.pop(task_id, None)
+        if task is not None and not task.measured_profile:
+            self._ndraw -= 1
+        return task
 
     def reset(self) -> None:
         self.running_tasks = OrderedDict()
         self._mem = 0
+        self._ndraw = 0
+
+
+_IDLE = (0.0, False)
 
 
 def sample_utilizations(devices, rng) -> List[Tuple[float, bool]]:
     """:meth:`Device.sample_utilization` for several devices with ONE call into the generator. The
-    legacy ``RandomState.normal`` fills an array element by element with the same routine a scalar call
-    uses, so drawing all resident tasks (device order, then resident order) at once consumes the stream
-    exactly as the reference's one-call-per-task does — at a fraction of the Python overhead."""
-    locs: List[float] = []
-    scales: List[float] = []
+    legacy ``RandomState.normal(loc, scale)`` is ``loc + scale * gauss()`` on the same Gaussian stream
+    that ``standard_normal(n)`` fills element by element, so drawing all resident tasks' Gaussians at once
+    (device order, then resident order) and applying loc / scale here consumes the stream and produces
+    the doubles exactly as the reference's one-call-per-task does — at a fraction of the overhead (this
+    function is the simulator's hottest: horus scores every candidate node with it)."""
+    n = 0
     for d in devices:
-        for t in d.running_tasks.values():
-            if t.measured_profile:
-                continue                                # calibrated mode (K7): measured value, no draw
-            locs.append(t.gpu_utilization_avg)
-            scales.append((t.gpu_utilization_max - t.gpu_utilization_avg) / 2)
-    if not locs:
-        draws = []
-    else:
-        draws = rng.normal(np.asarray(locs, dtype=np.float64), np.asarray(scales, dtype=np.float64)).tolist() \
-            if len(locs) > 1 else [rng.normal(locs[0], scales[0])]
+        n += d._ndraw
+    gs = rng.standard_normal(n).tolist() if n else ()
     out = []
     i = 0
     for d in devices:
+        tasks = d.running_tasks
+        if not tasks:
+            out.append(_IDLE)
+            continue
         total, drawn = 0.0, False
-        for t in d.running_tasks.values():
+        for t in tasks.values():
             if t.measured_profile:
-                total += min(t.gpu_utilization_avg, 100)
+                total += min(t.gpu_utilization_avg, 100)   # calibrated mode (K7): measured, no draw
                 if 100 < total:
                     total, drawn = 100.0, False
                 continue
-            x = draws[i]
+            avg = t.gpu_utilization_avg
+            x = avg + ((t.gpu_utilization_max - avg) / 2) * gs[i]
             i += 1
             if x < 100:
                 total += x

@@ -166,23 +166,23 @@ class Scheduler:
 
     # -- logging ---------------------------------------------------------------------------------------------------
     def construct_info(self) -> LogInfo:
-        idle_nodes = busy_nodes = idle_gpus = busy_gpus = 0
+        nodes = self.infrastructure.nodes
+        cached = getattr(self, "_device_list", None)
+        if cached is None or cached[0] != len(nodes):
+            # devices never change after the cluster is built: flatten once (node order, device order)
+            devices = [d for n in nodes.values() for d in n.device_cache.values()]
+            cached = self._device_list = (len(nodes), devices, sum(d.memory for d in devices))
+        _, devices, mem_cap = cached
+        idle_nodes = 0
+        for n in nodes.values():
+            if not (n.running_tasks or n.placed_tasks or n.placed_jobs):        # Node.is_idle()
+                idle_nodes += 1
+        busy_nodes = len(nodes) - idle_nodes
+        busy = [d for d in devices if d.running_tasks]
+        busy_gpus = len(busy)
+        idle_gpus = len(devices) - busy_gpus
         util_sum, util_is_array = 0.0, False
         mem_sum = 0
-        mem_cap = 0
-        busy = []
-        for n in self.infrastructure.nodes.values():
-            if n.is_idle():
-                idle_nodes += 1
-            else:
-                busy_nodes += 1
-            for d in n.device_cache.values():
-                if d.running_tasks:
-                    busy.append(d)
-                else:
-                    idle_gpus += 1
-                mem_cap += d.memory
-        busy_gpus = len(busy)
         # one generator call for the whole cluster (same stream order as device-by-device draws)
         for d, (u, drawn) in zip(busy, sample_utilizations(busy, self.infrastructure.rng)):
             util_sum += u
