@@ -66,6 +66,9 @@ def run(flags: FlagSet, output_dir: Optional[str] = None) -> Dict:
             np.random.seed(flags.seed)
             random.seed(flags.seed)
         calibration = load_calibration(flags.calibration)
+        if getattr(flags, "fast", False):
+            from ..sim.infra import MeanRandomState, global_rng
+            rng = MeanRandomState(global_rng())
         if _use_tick_engine(flags):
             summary = _run_tick(flags, output_dir, rng, calibration)
         else:

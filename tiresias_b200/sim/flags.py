@@ -136,4 +136,8 @@ def define_simulator_flags(fs: Optional[FlagSet] = None) -> FlagSet:
     fs.define_string("calibration", None, "calibration json produced by tiresias_b200.calib")
     fs.define_string("comm", "ps", "communication mode priced/executed for distributed jobs: ps | ring")
     fs.define_boolean("quiet", False, "do not mirror the log to stderr")
+    fs.define_boolean("fast", False, "skip the per-task Gaussian utilisation draws (every task reports its "
+                                     "mean): no random stream is consumed, cluster.csv equals the exact "
+                                     "mode's in every column but avg_gpu_utilization whenever the policy "
+                                     "does not score devices (yarn placement)")
     return fs

@@ -32,6 +32,26 @@ def global_rng() -> np.random.RandomState:
     return np.random.mtrand._rand
 
 
+class MeanRandomState:
+    """``--fast``: stands in for the legacy generator wherever utilisation is drawn — every Gaussian is
+    its mean — and hands every other request (k-means' ``randint`` ...) to the real generator, so nothing
+    else changes. SURVEY 7.4 item 2: the exact mode replays the reference's stream, this one trades
+    column 6 of cluster.csv for not touching it."""
+
+    def __init__(self, real: np.random.RandomState):
+        self._real = real
+
+    def standard_normal(self, size=None):
+        return 0.0 if size is None else np.zeros(size)
+
+    def normal(self, loc=0.0, scale=1.0, size=None):
+        return loc if size is None and np.ndim(loc) == 0 else np.broadcast_to(np.asarray(loc, dtype=np.float64),
+                                                                             np.shape(loc) if size is None else size).copy()
+
+    def __getattr__(self, name):
+        return getattr(self._real, name)
+
+
 class Device:
     """One GPU. ``running_tasks`` holds every task *placed* on it (reserved or running)."""
 
