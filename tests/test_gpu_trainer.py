@@ -148,3 +148,27 @@ def test_conv1x1_on_tcgen05_matches_torch(cuda_device):
     assert torch.allclose(x.grad.float(), xr.grad, rtol=3e-2, atol=5e-2)
     assert conv.weight.grad.shape == conv.weight.shape
     assert torch.allclose(conv.weight.grad.float(), wr.grad, rtol=3e-2, atol=2e-1)
+
+
+def test_fit_with_prefetch_equals_step_by_step(cuda_device):
+    """Trainer.fit (next batch copied on its own stream while the current step runs) must train exactly
+    like step(x, y) + loss() on the same batches."""
+    from tiresias_b200.parallel.trainer import Trainer
+    batches = [synthetic_batch(TINY, 32, pinned=True, seed=i % 3) for i in range(7)]
+    tr = Trainer(TINY, batch_size=32, mode="ps", use_graph=True, device=cuda_device, bucket_mb=0.05, lr=0.05)
+    step_losses = []
+    for x, y in batches:
+        tr.step(x, y)
+        step_losses.append(tr.loss())
+    p_step = tr.param_flat.float().clone()
+    tr.close()
+    tr = Trainer(TINY, batch_size=32, mode="ps", use_graph=True, device=cuda_device, bucket_mb=0.05, lr=0.05)
+    fit_losses = list(tr.fit(batches))
+    assert tr.check_status() == 0
+    p_fit = tr.param_flat.float().clone()
+    with pytest.raises(RuntimeError):
+        tr.step()                                   # nothing staged
+    tr.close()
+    assert len(fit_losses) == len(batches)
+    assert fit_losses == step_losses
+    assert torch.equal(p_fit, p_step)

@@ -270,9 +270,21 @@ class Trainer:
         ydim = (bs,) if self.spec.kind == "image" else (bs, *self.spec.sample_shape)
         self.y_dev = torch.zeros(ydim, dtype=torch.int64, device=dev)
         self.loss_dev = torch.zeros(1, dtype=torch.float32, device=dev)
-        self.loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        # two pinned slots, so that step i+1 can be enqueued before step i's loss is read (fit())
+        self.loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self._loss_done = [torch.cuda.Event(), torch.cuda.Event()]
+        self._loss_slot = 0
         self.h2d_bytes = self.x_dev.numel() * self.x_dev.element_size() + self.y_dev.numel() * 8
         self.d2h_bytes = 4
+        # input prefetch (prefetch() / fit()): the next batch lands in a staging pair on its own stream while
+        # the current step computes; the step then pays a device-to-device copy (~10 us) instead of the PCIe
+        # transfer (~0.7 ms for a 256 x 224 x 224 x 3 uint8 batch)
+        self.x_stage = torch.empty_like(self.x_dev)
+        self.y_stage = torch.empty_like(self.y_dev)
+        self.copy_stream = torch.cuda.Stream(dev)
+        self._stage_ready = torch.cuda.Event()
+        self._stage_free = torch.cuda.Event()
+        self._staged = False
 
     # ------------------------------------------------------------------------------------------
     # gradient hooks -> communication
@@ -466,14 +478,66 @@ class Trainer:
             self.native_launches += self.native_per_step
         self._steps += 1
 
-    def step(self, x_host: torch.Tensor, y_host: torch.Tensor) -> None:
-        """Enqueue one training step on host tensors (pinned for asynchronous copies). The loss
-        of this step is read back with :meth:`loss` (device->host copy enqueued here)."""
+    def step(self, x_host: Optional[torch.Tensor] = None, y_host: Optional[torch.Tensor] = None) -> None:
+        """Enqueue one training step on host tensors (pinned for asynchronous copies), or — called without
+        arguments — on the batch a preceding :meth:`prefetch` staged. The loss of this step is read back
+        with :meth:`loss` (device->host copy enqueued here)."""
         with torch.cuda.stream(self.stream):
-            self.x_dev.copy_(x_host, non_blocking=True)
-            self.y_dev.copy_(y_host, non_blocking=True)
+            if x_host is None:
+                if not self._staged:
+                    raise RuntimeError("step() without a batch needs a preceding prefetch()")
+                self.stream.wait_event(self._stage_ready)
+                self.x_dev.copy_(self.x_stage, non_blocking=True)
+                self.y_dev.copy_(self.y_stage, non_blocking=True)
+                self._stage_free.record(self.stream)
+                self._staged = False
+            else:
+                self.x_dev.copy_(x_host, non_blocking=True)
+                self.y_dev.copy_(y_host, non_blocking=True)
             self._advance()
-            self.loss_host.copy_(self.loss_dev, non_blocking=True)
+            self._loss_slot ^= 1
+            self.loss_host[self._loss_slot:self._loss_slot + 1].copy_(self.loss_dev, non_blocking=True)
+            self._loss_done[self._loss_slot].record(self.stream)
+
+    def prefetch(self, x_host: torch.Tensor, y_host: torch.Tensor) -> None:
+        """Start the host->device copy of the NEXT step's batch (pinned memory) on the copy stream; it
+        overlaps whatever the compute stream is running. The next :meth:`step` without arguments uses it."""
+        if self._staged:
+            raise RuntimeError("a prefetched batch is already waiting; call step() first")
+        cs = self.copy_stream
+        cs.wait_event(self._stage_free)                 # the previous consumer has read the staging pair
+        with torch.cuda.stream(cs):
+            self.x_stage.copy_(x_host, non_blocking=True)
+            self.y_stage.copy_(y_host, non_blocking=True)
+            self._stage_ready.record(cs)
+        self._staged = True
+
+    def fit(self, batches):
+        """Train on an iterable of pinned host batches ``(x, y)`` and yield every step's loss. The copy of
+        batch i+1 is in flight while step i computes (double-buffered input), so a step costs its device
+        time plus a device-to-device copy; every batch still crosses PCIe and every loss is read back —
+        step i's loss is read (and yielded) while step i+1 is already running, so the host never leaves the
+        GPU without queued work. Losses come out in step order, one per batch."""
+        it = iter(batches)
+        nxt = next(it, None)
+        if nxt is None:
+            return
+        self.prefetch(*nxt)
+        pending = None                       # slot holding the previous step's loss, not yet read
+        while nxt is not None:
+            self.step()
+            slot = self._loss_slot
+            nxt = next(it, None)
+            if nxt is not None:
+                self.prefetch(*nxt)
+            if pending is not None:          # read step i-1's loss while step i runs: the GPU never idles
+                yield self._read_loss(pending)
+            pending = slot
+        yield self._read_loss(pending)
+
+    def _read_loss(self, slot: int) -> float:
+        self._loss_done[slot].synchronize()
+        return float(self.loss_host[slot])
 
     def step_resident(self) -> None:
         """One step on the batch already resident on the device (device-only timing)."""
@@ -483,11 +547,12 @@ class Trainer:
     def loss(self) -> float:
         """Blocks until the most recent step's loss has landed in pinned host memory."""
         self.stream.synchronize()
-        return float(self.loss_host[0])
+        return float(self.loss_host[self._loss_slot])
 
     def synchronize(self) -> None:
         self.stream.synchronize()
         self.comm_stream.synchronize()
+        self.copy_stream.synchronize()
 
     def check_status(self) -> int:
         """Watchdog hook: non-zero means an in-kernel wait ran out of spin budget (peer lost)."""
