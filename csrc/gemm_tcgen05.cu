@@ -663,6 +663,72 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   }
 }
 
+// ---- probe: shifted K-major operand windows ---------------------------------------------------------
+// Groundwork for convolutions that fetch an input halo tile ONCE and form the R x S filter taps as shifted
+// windows of it in shared memory (profiles/conv_r1g.md: the im2col-TMA kernel re-fetches the tile per tap
+// and is bound by L2->SM traffic). A window that starts `shift` pixel rows (128 bytes each) into a
+// 128-byte-swizzled tile is no longer aligned to the 1024-byte swizzle pattern; the descriptor's "matrix
+// base offset" field (bits 49-51) exists for that case. This one-CTA kernel measures what the hardware
+// does: D[128, 64] = A[shift : shift+128, 0:64] . B[64, 64]^T with the A descriptor advanced by shift*128
+// bytes and base offset = `base_offset`. The host compares against the same product in fp32.
+__global__ void __launch_bounds__(128, 1)
+probe_shift_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   float* __restrict__ D, int shift, int base_offset) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t a_smem = smem_u32(smem_raw);                 // 256 rows x 128 B
+  const uint32_t b_smem = a_smem + 256 * 128;                 // 64 rows x 128 B
+  const uint32_t bar_full = b_smem + 64 * 128;
+  const uint32_t bar_done = bar_full + 8;
+  const uint32_t tmem_slot = bar_full + 16;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (threadIdx.x == 0) {
+    mbar_init(bar_full, 1);
+    mbar_init(bar_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(64)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - a_smem));
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar_full, 256 * 128 + 64 * 128);
+    tma_load_2d(a_smem, &map_a, bar_full, 0, 0);
+    tma_load_2d(a_smem + 128 * 128, &map_a, bar_full, 0, 128);
+    tma_load_2d(b_smem, &map_b, bar_full, 0, 0);
+    mbar_wait(bar_full, 0);
+    tc_fence_after();
+    const uint32_t idesc = make_idesc_bf16(128, 64);
+    const uint64_t adesc = make_kmajor_sw128_desc(a_smem + (uint32_t)shift * 128u) |
+                           ((uint64_t)(base_offset & 7) << 49);
+    const uint64_t bdesc = make_kmajor_sw128_desc(b_smem);
+#pragma unroll
+    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) tc_mma_bf16(tmem_base, adesc + 2u * k, bdesc + 2u * k, idesc, k > 0);
+    tc_commit(bar_done);
+  }
+  mbar_wait(bar_done, 0);
+  tc_fence_after();
+  const int row = warp * 32 + lane;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    uint32_t r[32];
+    tc_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32), r);
+    tc_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) D[(size_t)row * 64 + c * 32 + j] = __uint_as_float(r[j]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(64) : "memory");
+  }
+}
+
 // Split-K second pass: sum the fp32 partials in split order, then bias/activation/cast.
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ partials,
                                                             int splits, size_t mn, int N,
@@ -1114,6 +1180,28 @@ int tb200_conv2d_wgrad(const void* x, const void* dy, void* dw, int n, int h, in
   c.act = x; c.n = n; c.h = h; c.w = wd; c.c = cin; c.pad = pad;
   return gemm_common(nullptr, 0, 0, 0, dy, nullptr, dw, nullptr, 0, cout, R * S * cin, n * oh * ow, dw_dtype, 0,
                      nullptr, nullptr, 0, stream, nullptr, 0, 1, 1, &c);
+}
+
+// Hardware probe (see probe_shift_kernel): A bf16 [256, 64], B bf16 [64, 64], D fp32 [128, 64].
+int tb200_probe_shifted_operand(const void* A, const void* B, float* D, int shift, int base_offset,
+                                cudaStream_t stream) {
+  if (shift < 0 || shift > 128) return fail("tb200_probe_shifted_operand: shift %s(%ld) outside 0..128", "", shift);
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    TB_CUDA_OK(cudaFree(nullptr));
+    ctx_bound = true;
+  }
+  CUtensorMap ma, mb;
+  if (int rc = make_map(&ma, A, 256, 64, 128)) return rc;
+  if (int rc = make_map(&mb, B, 64, 64, 64)) return rc;
+  const int smem = 256 * 128 + 64 * 128 + 64;
+  static bool configured = false;
+  if (!configured) {
+    TB_CUDA_OK(cudaFuncSetAttribute(probe_shift_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  probe_shift_kernel<<<1, 128, smem, stream>>>(ma, mb, D, shift, base_offset);
+  return launched();
 }
 
 // Pre-size the split-K scratch (call before CUDA-graph capture so no allocation happens

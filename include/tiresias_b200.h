@@ -174,6 +174,12 @@ int tb200_conv2d_dgrad(const void* dy, const void* w, void* dx, int n, int h, in
 int tb200_conv2d_wgrad(const void* x, const void* dy, void* dw, int n, int h, int wd, int cin, int cout, int R,
                        int S, int stride, int pad, int dw_dtype, cudaStream_t stream);
 
+/* Hardware probe for halo-tile convolutions: D[128,64] fp32 = A[shift:shift+128, :] . B^T with A bf16 [256,64],
+ * B bf16 [64,64], the A shared-memory descriptor advanced by `shift` 128-byte rows and its matrix-base-offset
+ * field set to `base_offset` (bench/probe_shift.py reports which setting reproduces the fp32 product). */
+int tb200_probe_shifted_operand(const void* A, const void* B, float* D, int shift, int base_offset,
+                                cudaStream_t stream);
+
 /* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
 int tb200_gemm_reserve(size_t bytes);
 

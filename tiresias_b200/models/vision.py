@@ -20,14 +20,14 @@ from ..ops.pooling import MaxPool3x3S2
 
 import os
 
-# 1x1 / stride-1 convolutions on the tcgen05 GEMM: correct (tests/test_gpu_trainer.py) but, measured on B200 at
-# batch 256, 7 % slower end to end than cuDNN's kernels for these thin, memory-bound shapes (26.4 vs 24.6 ms
-# per ResNet-50 step), so it is opt-in (TB200_TC_CONV1X1=1) until the GEMM grows a BatchNorm-statistics
-# epilogue that removes the separate statistics pass.
+# Convolutions on our own tcgen05 kernels (ops/conv.py): 1x1 / stride 1 as plain GEMMs over the NHWC pixel
+# rows, everything else with a multiple of 64 input channels as implicit GEMMs fed by im2col-mode TMA loads.
+# Correct (tests/test_gpu_conv.py, test_gpu_trainer.py) but cuDNN wins every pass in situ on B200 at batch
+# 256 (profiles/conv_r1g.md: +1 % of the ResNet-50 step per pointwise pass, +3-5 % per k x k pass), so the
+# routing is opt-in:  TB200_TC_CONV="p:fdw,k:fdw"  (p = pointwise, k = the rest; f / d / w = forward, input
+# gradient, weight gradient; "1" = everything; see ops.conv._parse_ops). TB200_TC_CONV1X1=1 is the older
+# spelling of "p:fdw".
 TC_CONV1X1 = os.environ.get("TB200_TC_CONV1X1", "0") == "1"
-# k x k and strided convolutions as implicit GEMMs with im2col-mode TMA loads (ops/conv.py TcConv2d);
-# TB200_TC_CONV=1 turns on both kinds for every convolution whose input has a multiple of 64 channels.
-# Per-pass routing: TB200_TC_CONV="p:fw,k:f" (see ops.conv._parse_ops).
 TC_CONV = _parse_ops(os.environ.get("TB200_TC_CONV", ""))
 if TC_CONV1X1:
     TC_CONV["p"] = set("fdw")
@@ -58,8 +58,7 @@ def _bn(channels: int, relu: bool, fused: bool) -> nn.Module:
 
 
 def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0, fused: bool = False) -> nn.Module:
-    """cuDNN convolution, except 1x1 / stride 1 in the fused build: those are plain GEMMs over the NHWC
-    pixel rows and run on the tcgen05 kernel (ops/conv.py)."""
+    """cuDNN convolution unless TB200_TC_CONV routes passes of this geometry to the tcgen05 kernels."""
     if fused and TC_CONV["p"] and k == 1 and stride == 1 and pad == 0 and cin % 8 == 0 and cout % 8 == 0:
         return TcConv1x1(cin, cout, TC_CONV["p"])
     if fused and TC_CONV["k"] and not (k == 1 and stride == 1) and cin % 64 == 0 and cout % 8 == 0:
