@@ -174,6 +174,12 @@ int tb200_conv2d_dgrad(const void* dy, const void* w, void* dx, int n, int h, in
 int tb200_conv2d_wgrad(const void* x, const void* dy, void* dw, int n, int h, int wd, int cin, int cout, int R,
                        int S, int stride, int pad, int dw_dtype, cudaStream_t stream);
 
+/* EXPERIMENTAL (compiles, not yet run on hardware): 3x3 / stride 1 / pad 1 forward convolution that fetches
+ * each input halo tile once and forms the nine taps as shifted shared-memory windows (csrc/conv_halo.cu).
+ * Same tensors as tb200_conv2d_fprop; cin % 64 == 0, cout % 8 == 0, image width <= 126.                   */
+int tb200_conv2d_fprop_halo(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout,
+                            int R, int S, cudaStream_t stream);
+
 /* Hardware probe for halo-tile convolutions: D[128,64] fp32 = A[shift:shift+128, :] . B^T with A bf16 [256,64],
  * B bf16 [64,64], the A shared-memory descriptor advanced by `shift` 128-byte rows and its matrix-base-offset
  * field set to `base_offset` (bench/probe_shift.py reports which setting reproduces the fp32 product). */

@@ -1,5 +1,7 @@
 """Implicit-GEMM convolutions (tb200_conv2d_fprop / _dgrad / _wgrad: im2col-mode TMA loads feeding the
 tcgen05 mainloop) against a plain PyTorch fp32 convolution of the same bf16-rounded operands."""
+import os
+
 import pytest
 import torch
 
@@ -85,3 +87,20 @@ def test_module_forward_backward(cuda_device):
         assert torch.allclose(x.grad.float(), xr.grad, rtol=3e-2, atol=6e-2)
         assert conv.weight.grad.shape == conv.weight.shape
         assert torch.allclose(conv.weight.grad.float(), wr.grad, rtol=3e-2, atol=3e-2 * float(wr.grad.abs().max()))
+
+
+# The halo-tile kernel (csrc/conv_halo.cu) was written after round 1's GPU budget was spent: it compiles but
+# has never run. Its check is therefore opt-in (TB200_TEST_EXPERIMENTAL=1) until it has been brought up.
+@pytest.mark.skipif(os.environ.get("TB200_TEST_EXPERIMENTAL", "0") != "1",
+                    reason="experimental kernel, not yet validated on hardware (TB200_TEST_EXPERIMENTAL=1 runs it)")
+@pytest.mark.parametrize("shape", [(4, 64, 64, 56), (4, 128, 128, 28), (4, 256, 256, 14), (3, 64, 96, 12), (2, 512, 512, 7)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_halo_fprop_matches_fp32(cuda_device, shape):
+    from tiresias_b200.ops import native
+    n, cin, cout, hw = shape
+    x, w = _case(cuda_device, n, cin, cout, hw, 3, 1, 1)
+    y = native.conv2d_fprop_halo(x, w)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.conv2d(x.float(), w.float(), padding=1)
+    assert y.shape == ref.shape
+    assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-2), float((y.float() - ref).abs().max())

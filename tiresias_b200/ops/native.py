@@ -110,6 +110,8 @@ def _declare(lib: C.CDLL) -> None:
     for fn in ("tb200_vmm_round", "tb200_vmm_alloc", "tb200_vmm_import", "tb200_vmm_release", "tb200_mc_create",
                "tb200_mc_import", "tb200_mc_add_device", "tb200_mc_bind", "tb200_mc_release"):
         getattr(lib, fn).restype = ci
+    lib.tb200_conv2d_fprop_halo.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, st]
+    lib.tb200_conv2d_fprop_halo.restype = ci
     lib.tb200_nvls_supported.argtypes = [ci]
     lib.tb200_nvls_supported.restype = ci
     lib.tb200_nvls_selftest.argtypes = [ci, sz, ci, C.c_char_p, sz]
@@ -279,6 +281,19 @@ def conv2d_fprop(x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int) -
     y = torch.empty((n, oh, ow, cout), dtype=torch.bfloat16, device=x.device)
     check(lib().tb200_conv2d_fprop(xv.data_ptr(), wv.data_ptr(), y.data_ptr(), n, h, w, cin, cout, r, s,
                                    stride, pad, stream_ptr()))
+    return y.permute(0, 3, 1, 2)
+
+
+def conv2d_fprop_halo(x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """EXPERIMENTAL halo-tile forward convolution (3x3, stride 1, pad 1; csrc/conv_halo.cu): compiled but
+    not yet validated on hardware — nothing calls it by default."""
+    assert x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    xv, wv = _nhwc(x), _nhwc(weight)
+    n, h, w, cin = xv.shape
+    cout, r, s, _ = wv.shape
+    y = torch.empty((n, h, w, cout), dtype=torch.bfloat16, device=x.device)
+    check(lib().tb200_conv2d_fprop_halo(xv.data_ptr(), wv.data_ptr(), y.data_ptr(), n, h, w, cin, cout, r, s,
+                                        stream_ptr()))
     return y.permute(0, 3, 1, 2)
 
 
