@@ -1,0 +1,66 @@
+"""CPU model of the halo-tile convolution's geometry (csrc/conv_halo.cu), step for step: padded-space
+tiling, whole-padded-row loads with zero fill outside the image, taps as windows shifted by r*Wp+s rows of
+the SAME tile, and stores clipped against the output's real extent. The kernel itself has not run on
+hardware yet; this pins its index arithmetic against a plain convolution so that bring-up on the GPU only
+has to debug the PTX plumbing."""
+import pytest
+import torch
+
+
+def halo_conv_model(x_nhwc: torch.Tensor, w_krsc: torch.Tensor) -> torch.Tensor:
+    n, h, w, c = x_nhwc.shape
+    k, r_, s_, _ = w_krsc.shape
+    pad = (r_ - 1) // 2
+    wp = 8
+    while wp < w + s_ - 1:
+        wp *= 2
+    assert wp <= 128
+    hp, th = h + r_ - 1, 128 // wp
+    a_rows = th + r_ - 1
+    num_m = (n * hp + th - 1) // th
+    store_w = min(32, wp)
+    a_alloc = (a_rows * wp + (s_ - 1) + 7) // 8 * 8
+    y = torch.full((n, h, w, k), float("nan"))
+    for m_tile in range(num_m):
+        acc = torch.zeros(128, k)
+        for cb in range(c // 64):
+            # producer: a_rows whole padded rows {64 ch, Wp, 1, 1} at (cb*64, -pad, hp-pad, n); the rest of the
+            # stage is whatever was there before (poisoned here: only junk outputs may touch it)
+            tile = torch.full((a_alloc, 64), 1e30)
+            row0 = m_tile * th
+            for i in range(a_rows):
+                rg = row0 + i
+                img, hrow = divmod(rg, hp)
+                for j in range(wp):
+                    hh, ww = hrow - pad, j - pad
+                    inside = img < n and 0 <= hh < h and 0 <= ww < w
+                    tile[i * wp + j] = x_nhwc[img, hh, ww, cb * 64:(cb + 1) * 64] if inside else 0.0
+            # MMA issuer: per tap a 128-row window starting (r*Wp + s) rows into the tile
+            for t in range(r_ * s_):
+                r, s = divmod(t, s_)
+                win = tile[r * wp + s: r * wp + s + 128]
+                acc += win @ w_krsc[:, r, s, cb * 64:(cb + 1) * 64].t()
+        # epilogue: per warp 32 rows, TMA stores of store_w positions clipped against (W, H, N)
+        for ew in range(4):
+            for seg in range(32 // store_w):
+                q = m_tile * 128 + ew * 32 + seg * store_w
+                rg, j = divmod(q, wp)
+                img, hrow = divmod(rg, hp)
+                for d in range(store_w):
+                    if img < n and hrow < h and j + d < w:
+                        y[img, hrow, j + d] = acc[ew * 32 + seg * store_w + d]
+    return y
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 8, 14, 3), (1, 128, 16, 28, 3), (3, 64, 8, 7, 3), (2, 64, 8, 12, 3),
+                                   (1, 64, 8, 56, 3), (2, 64, 8, 9, 1)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_halo_geometry_equals_convolution(shape):
+    n, c, k, hw, r = shape
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(n, hw, hw, c, generator=g)
+    w = torch.randn(k, r, r, c, generator=g) / (c * r * r) ** 0.5
+    y = halo_conv_model(x, w)
+    ref = torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), padding=(r - 1) // 2).permute(0, 2, 3, 1)
+    assert not torch.isnan(y).any(), "some real output position was never stored"
+    assert torch.allclose(y, ref, rtol=1e-4, atol=1e-4), float((y - ref).abs().max())
