@@ -38,11 +38,12 @@ def test_in_kernel_collectives(native_lib, world):
 
 def test_nvls_multimem_primitives(native_lib):
     """multimem.ld_reduce / multimem.st through an NVLS multicast object: sums and broadcasts must be exact
-    (small integers in bf16), on as many GPUs as the box has."""
+    (small integers in bf16). Single process, two GPUs (the multi-process path over 2/4/8 GPUs is covered by
+    multi_worker.py through the trainers)."""
     from tiresias_b200.ops import native
-    ndev = min(torch.cuda.device_count(), 8)
-    if ndev < 2:
+    if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
+    ndev = 2
     if not native.nvls_supported(0):
         pytest.skip("this box has no NVLS multicast support")
     rep = native.nvls_selftest(ndev, 32 << 20)

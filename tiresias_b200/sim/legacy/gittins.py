@@ -24,7 +24,19 @@ import csv
 import sys
 from typing import Dict, List, Optional, Sequence
 
-import torch
+
+
+class _LazyTorch:
+    """``torch`` on first use: the priority math (LAS queues, Gittins ranks) is in PyTorch, but importing it
+    costs seconds that fifo / sjf / shortest runs never need."""
+
+    def __getattr__(self, name):
+        import torch as _torch
+        globals()["torch"] = _torch
+        return getattr(_torch, name)
+
+
+torch = _LazyTorch()
 
 MAXSIZE = sys.maxsize
 

@@ -26,7 +26,19 @@ from __future__ import annotations
 import math
 from typing import Callable, Dict, List, Optional, Tuple
 
-import torch
+
+
+class _LazyTorch:
+    """``torch`` on first use: the priority math (LAS queues, Gittins ranks) is in PyTorch, but importing it
+    costs seconds that fifo / sjf / shortest runs never need."""
+
+    def __getattr__(self, name):
+        import torch as _torch
+        globals()["torch"] = _torch
+        return getattr(_torch, name)
+
+
+torch = _LazyTorch()
 
 from . import gittins as gi
 from .jobs import MAXSIZE, JobRegistry, TJob
