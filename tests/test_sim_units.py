@@ -347,3 +347,42 @@ def test_calibrated_mode_uses_measured_utilisation_and_memory(tmp_path):
     run(f2, output_dir=str(tmp_path / "parity"))
     busy2 = [r for r in rows(str(tmp_path / "parity")) if int(r["num_busy_gpus"]) == 4]
     assert busy2 and all(float(r["avg_gpu_utilization"].strip("[]")) < 60 for r in busy2)     # draws around 10 %
+
+
+def test_environment_steps_the_tick_loop(tmp_path):
+    """O4: the reference's RL stub has an empty step(); here Environment drives the same tick loop and must
+    reach the same end state as Scheduler.start()."""
+    import numpy as np
+    from tiresias_b200.cli.run_sim import run
+    from tiresias_b200.sim.env import Environment
+    from tiresias_b200.sim.infra import Infrastructure
+    from tiresias_b200.sim.jobs_manager import JobsManager
+    from tiresias_b200.sim.logs import LogManager
+    from tiresias_b200.sim.queues import JobQueueManager
+    from tiresias_b200.sim.scheduler import Scheduler
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    argv = ["--trace_file", os.path.join(gold, "t12_yarn_fifo.trace.csv"), "--num_switch", "1",
+            "--num_node_p_switch", "4", "--seed", "1", "--quiet"]
+    f = define_simulator_flags(); f.parse(argv)
+    want = run(f, output_dir=str(tmp_path / "direct"))
+
+    f2 = define_simulator_flags(); f2.parse(argv)
+    np.random.seed(1)
+    out = tmp_path / "env"
+    out.mkdir()
+    logs = LogManager(str(out), f2)
+    infra = Infrastructure(f2)
+    logs.init(infra)
+    jm = JobsManager(f2, JobQueueManager(f2, f2.trace_file))
+    sched = Scheduler(infra, jm, logs)
+    env = Environment(sched)
+    assert Environment().step() is None                     # unwrapped: the reference's no-op
+    sched.prime()
+    steps, done = 0, False
+    while not done:
+        obs, reward, done = env.step()
+        assert reward <= 0 and obs is sched.last_info
+        steps += 1
+    logs.close()
+    got = sched.summary()
+    assert steps == want["ticks"] and got["makespan"] == want["makespan"] and got["avg_jct"] == want["avg_jct"]
