@@ -6,7 +6,6 @@ ncu launch list, whose per-kernel cache flush inflates everything that normally 
 """
 import argparse
 import collections
-import json
 import os
 import sys
 

@@ -1,7 +1,6 @@
 """Execution backend without GPUs: buddy placement, the PS/worker protocol on CPU tensors over gloo
 (world_size > 1), the worker pool + real-time controller, preemption and resume, and the simulated-vs-
 executed JCT comparison."""
-import json
 import os
 import subprocess
 import sys

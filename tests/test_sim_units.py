@@ -1,5 +1,4 @@
 """Unit tests of the simulator's components."""
-import math
 import os
 
 import numpy as np

@@ -16,7 +16,6 @@ import json
 import logging
 import os
 import random
-import sys
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
@@ -104,7 +103,7 @@ def _run_tick(flags: FlagSet, output_dir: str, rng, calibration) -> Dict:
     from ..sim.logs import LogManager
     from ..sim.queues import JobQueueManager
     from ..sim.scheduler import Scheduler
-    from ..sim.trace import JobTraceReader, detect_schema
+    from ..sim.trace import detect_schema
 
     log_manager = LogManager(output_dir, flags)
     infrastructure = Infrastructure(flags, rng=rng)

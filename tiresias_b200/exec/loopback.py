@@ -7,7 +7,7 @@ with momentum on the fp32 master shard, all-gather of the new parameters), on ``
 from __future__ import annotations
 
 import time
-from typing import Dict, Optional
+from typing import Dict
 
 import torch
 import torch.distributed as dist

@@ -26,10 +26,9 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import sys
 import time
 import traceback
-from typing import Dict, Optional, Tuple
+from typing import Dict, Tuple
 
 import torch
 import torch.distributed as dist

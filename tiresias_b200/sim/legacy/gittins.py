@@ -22,7 +22,7 @@ from __future__ import annotations
 
 import csv
 import sys
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Optional, Sequence
 
 
 

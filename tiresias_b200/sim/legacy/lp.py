@@ -9,7 +9,7 @@ same constraints. ``prepare_job_info`` / ``prepare_cluster_info`` keep the refer
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import numpy as np
 

@@ -19,7 +19,7 @@ from __future__ import annotations
 
 import math
 from heapq import heappop, heappush
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, List, Tuple
 
 from . import util
 from .scoring import score_fn

@@ -14,10 +14,6 @@ Signature: ``policy(scheme, placement, infrastructure, jobs_manager, delta, **kw
 """
 from __future__ import annotations
 
-from typing import Optional
-
-from . import util
-
 LOOK_AHEAD = 5            # core/scheduling/algorithm.py:204,240
 GANDIVA_QUANTUM = 100     # core/scheduling/algorithm.py:426
 
