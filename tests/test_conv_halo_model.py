@@ -64,3 +64,18 @@ def test_halo_geometry_equals_convolution(shape):
     ref = torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), padding=(r - 1) // 2).permute(0, 2, 3, 1)
     assert not torch.isnan(y).any(), "some real output position was never stored"
     assert torch.allclose(y, ref, rtol=1e-4, atol=1e-4), float((y - ref).abs().max())
+
+
+@pytest.mark.parametrize("k,pad", [(3, 1), (1, 0), (5, 2)])
+def test_dgrad_is_a_forward_convolution_with_the_flipped_filter(k, pad):
+    """ops.native.conv2d_dgrad_halo runs the forward kernel over dy with dgrad_weight(w): check that identity
+    against autograd on the CPU."""
+    from tiresias_b200.ops.native import dgrad_weight
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(2, 8, 9, 9, generator=g, requires_grad=True)
+    w = torch.randn(6, 8, k, k, generator=g)
+    y = torch.nn.functional.conv2d(x, w, padding=pad)
+    dy = torch.randn(y.shape, generator=g)
+    y.backward(dy)
+    dx = torch.nn.functional.conv2d(dy, dgrad_weight(w), padding=k - 1 - pad)
+    assert torch.allclose(dx, x.grad, rtol=1e-4, atol=1e-4)

@@ -297,6 +297,20 @@ def conv2d_fprop_halo(x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
     return y.permute(0, 3, 1, 2)
 
 
+def dgrad_weight(weight: torch.Tensor) -> torch.Tensor:
+    """The filter that turns a stride-1 convolution's input gradient into a forward convolution of dy:
+    ``dx = conv(dy, dgrad_weight(w), padding = R-1-pad)`` — taps flipped, in / out channels swapped.
+    ``weight`` [K,C,R,S] -> [C,K,R,S], channels_last."""
+    return weight.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
+
+
+def conv2d_dgrad_halo(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """EXPERIMENTAL: input gradient of a 3x3 / stride 1 / pad 1 convolution on the halo-tile kernel (a
+    forward pass over dy with the flipped, channel-swapped filter; the filter is rewritten per call, which
+    is one small kernel — weights change every step anyway)."""
+    return conv2d_fprop_halo(dy, dgrad_weight(weight))
+
+
 def conv2d_dgrad(dy: torch.Tensor, weight: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:
     """Gradient w.r.t. the input of a stride-1 convolution (tb200_conv2d_dgrad)."""
     dyv, wv = _nhwc(dy), _nhwc(weight)
