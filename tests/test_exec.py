@@ -63,6 +63,21 @@ def test_replay_preempt_and_resume_loopback(tmp_path):
     assert "(resume)" in log and "preempt job 0" in log
 
 
+@pytest.mark.timeout(300)
+def test_replay_gittins_loopback(tmp_path):
+    """Executed Gittins scheduling: a long job that has already received more GPU-time than the short jobs of
+    the distribution ever need has a lower index than a fresh arrival, so it is preempted for it."""
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(2, 0, 300, "resnet50"), (2, 1, 20, "vgg16"), (2, 1, 20, "vgg16")])
+    res = replay(trace, gpus=2, schedule="gittins", comm="ps", out=str(tmp_path / "o"), loopback=True,
+                 step_sleep=0.01, check_every=5, gittins_delta_s=0.2)
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert all(r["status"] == "DONE" for r in recs.values())
+    assert recs["0"]["preempt"] >= 1                         # the long job made way for a fresh arrival
+    assert recs["2"]["end"] < recs["0"]["end"]               # which finished first
+    assert res["comparison"]["n"] == 3 and os.path.exists(tmp_path / "o" / "sim" / "jobs.csv")
+
+
 def test_loopback_trainer_matches_single_process_sgd():
     """world = 1: the PS protocol degenerates to plain SGD with momentum on the flat parameters."""
     from tiresias_b200.exec.loopback import LoopbackTrainer

@@ -47,6 +47,7 @@ class ExecJob:
     attained: float = 0.0              # seconds of service received (all attempts)
     preempt: int = 0
     q_id: int = 0
+    rank: float = 0.0                  # gittins index of the attained service (policy "gittins")
     results: List[Dict] = field(default_factory=list)
 
     def jct(self) -> Optional[float]:
@@ -57,7 +58,9 @@ class Controller:
     def __init__(self, store, num_gpus: int, rows: Sequence[Dict], policy: str = "fifo", comm: str = "ps",
                  batch: int = 32, time_scale: float = 1.0, ckpt_dir: str = "/dev/shm/tb200_ckpt",
                  queue_limit: Sequence[float] = (20.0,), check_every: int = 10, poll_s: float = 0.02,
-                 job_timeout_s: float = 600.0, step_sleep: float = 0.0, graph: bool = True, log=print):
+                 job_timeout_s: float = 600.0, step_sleep: float = 0.0, graph: bool = True, log=print,
+                 job_dist_s: Optional[Sequence[float]] = None, gittins_delta_s: float = 2.0,
+                 est_iter_s: float = 0.05):
         self.store, self.num_gpus, self.policy, self.comm = store, num_gpus, policy, comm
         self.time_scale, self.ckpt_dir, self.check_every, self.poll_s = time_scale, ckpt_dir, check_every, poll_s
         self.queue_limit = list(queue_limit)
@@ -70,6 +73,15 @@ class Controller:
             self.jobs.append(ExecJob(str(r["job_id"]), r.get("model_name") or "resnet50",
                                      normalize_gpus(r["num_gpu"], num_gpus), max(1, int(r["iterations"])),
                                      float(r["submit_time"]) * time_scale, int(r.get("batch") or batch)))
+        # gittins: the index table over GPU-time samples in milliseconds (sim.legacy.gittins, PyTorch). Without
+        # a distribution the trace's own jobs are the samples: iterations x estimated iteration time x GPUs —
+        # what the simulator falls back to as well (sim/legacy/engine.py).
+        self.gittins_table = None
+        if policy == "gittins":
+            from ..sim.legacy import gittins as gi
+            samples = list(job_dist_s) if job_dist_s else [j.iters * est_iter_s * j.gpus for j in self.jobs]
+            self.gittins_table = gi.gittins_table([max(1, int(round(v * 1000.0))) for v in samples],
+                                                  max(1, int(round(gittins_delta_s * 1000.0))))
         self.t0 = 0.0
         self.pending: List[ExecJob] = []           # fifo: arrived, could not start yet
         self.seen: set = set()
@@ -179,6 +191,18 @@ class Controller:
                 while j.q_id < len(self.queue_limit) and served >= self.queue_limit[j.q_id]:
                     j.q_id += 1
             runnable.sort(key=lambda j: (j.q_id, 0 if j.status != "WAITING" else 1, j.submit))
+        elif self.policy == "gittins":
+            # highest Gittins index of the attained GPU-time first (Tiresias 2D-Gittins; the reference's own
+            # loop sorts ascending, run_sim.py:1082 — the simulator keeps that selectable, --gittins_desc)
+            import torch
+            from ..sim.legacy import gittins as gi
+            if runnable:
+                att = torch.tensor([int((j.attained + (now - j.last_start if j.status == "RUNNING" else 0.0))
+                                        * j.gpus * 1000.0) for j in runnable], dtype=torch.int64)
+                ranks = gi.gittins_ranks(self.gittins_table, att).tolist()
+                for j, r in zip(runnable, ranks):
+                    j.rank = float(r)
+            runnable.sort(key=lambda j: (-j.rank, 0 if j.status != "WAITING" else 1, j.submit))
         else:
             raise NotImplementedError(self.policy)
         free = self.num_gpus
@@ -200,7 +224,8 @@ class Controller:
     # -- main loop --------------------------------------------------------------------------------------------
     def run(self) -> List[ExecJob]:
         """Decisions are taken at the simulator's event instants only — a job arrives, or an attempt
-        ends — plus, for dlas-gpu, on every poll (queue demotions happen between events)."""
+        ends — plus, for dlas-gpu and gittins, on every poll (queue demotions / index changes happen between
+        events)."""
         self.t0 = time.time()
         announced: set = set()
         while any(j.status not in ("DONE", "FAILED") for j in self.jobs):
@@ -208,7 +233,7 @@ class Controller:
             changed = self._collect(now)
             arrivals = [j for j in self.jobs if j.submit <= now and j.job_id not in announced]
             announced.update(j.job_id for j in arrivals)
-            if changed or arrivals or self.policy == "dlas-gpu":
+            if changed or arrivals or self.policy in ("dlas-gpu", "gittins"):
                 self._schedule(now)
             time.sleep(self.poll_s)
         return self.jobs

@@ -31,7 +31,7 @@ from ..sim.trace import read_tiresias_trace
 from .controller import Controller
 
 MS = 1000.0
-SIM_SCHEDULE = {"fifo": "fjf", "sjf": "sjf", "shortest": "shortest", "dlas-gpu": "dlas-gpu"}
+SIM_SCHEDULE = {"fifo": "fjf", "sjf": "sjf", "shortest": "shortest", "dlas-gpu": "dlas-gpu", "gittins": "gittins"}
 
 
 def _free_port() -> int:
@@ -104,7 +104,8 @@ def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:
 
 
 def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, gpus: int, schedule: str,
-             queue_limit_s: Sequence[float], out_dir: str, scheme: str = "buddy") -> Dict[str, Dict]:
+             queue_limit_s: Sequence[float], out_dir: str, scheme: str = "buddy",
+             gittins_delta_s: float = 2.0) -> Dict[str, Dict]:
     """Event simulation in milliseconds on a 1 x 1 x ``gpus`` cluster. ``scheme="buddy"`` places jobs on
     aligned power-of-two GPU blocks like the worker pool does (non-preemptive schedules); the preemptive
     ones hand out GPUs by counting, as their reference loops do."""
@@ -125,6 +126,9 @@ def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, g
             "--num_gpu_p_node", str(gpus), "--quiet"]
     if schedule == "dlas-gpu":
         argv += ["--queue_limit", ",".join(str(int(q * MS)) for q in queue_limit_s)]
+    if schedule == "gittins":
+        # same direction (highest index first) and re-evaluation period as the controller
+        argv += ["--gittins_desc", "--gittins_delta", str(int(round(gittins_delta_s * MS)))]
     if schedule != "fifo":
         # restart cost of a resumed job, measured in this very replay: start-up + shard snapshot
         pre = [r for r in records if r.get("preempt")]
@@ -175,10 +179,21 @@ def compare(records: Sequence[Dict], sim: Dict[str, Dict]) -> Dict:
             "makespan_error_pct": round((mk_sim - mk_exec) / mk_exec * 100.0, 2), "jobs": rows}
 
 
+def _estimated_iter_s(calibration_path: Optional[str], step_sleep: float) -> float:
+    """Iteration time the gittins controller assumes before anything has run: the mean of a given
+    calibration's 1-GPU entries, else the loopback's sleep per step, else 50 ms."""
+    if calibration_path and os.path.exists(calibration_path):
+        with open(calibration_path) as fh:
+            per = [v.get("1") for v in (json.load(fh).get("iter_s") or {}).values() if v.get("1")]
+        if per:
+            return sum(per) / len(per)
+    return step_sleep if step_sleep > 0 else 0.05
+
+
 def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out: str = "replay_out",
            calibration_path: Optional[str] = None, loopback: bool = False, batch: int = 32, time_scale: float = 1.0,
            queue_limit_s: Sequence[float] = (20.0,), check_every: int = 10, step_sleep: float = 0.0,
-           iters_scale: float = 1.0, graph: bool = True) -> Dict:
+           iters_scale: float = 1.0, graph: bool = True, gittins_delta_s: float = 2.0) -> Dict:
     os.makedirs(out, exist_ok=True)
     rows = read_tiresias_trace(trace)
     for r in rows:
@@ -195,7 +210,8 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
         print(msg, flush=True)
     ctl = Controller(store, gpus, rows, policy=schedule, comm=comm, batch=batch, time_scale=time_scale,
                      ckpt_dir=ckpt_dir, queue_limit=queue_limit_s, check_every=check_every, step_sleep=step_sleep,
-                     graph=graph, log=log)
+                     graph=graph, log=log, gittins_delta_s=gittins_delta_s,
+                     est_iter_s=_estimated_iter_s(calibration_path, step_sleep))
     try:
         ctl.wait_ready()
         t_pool = time.time()
@@ -214,7 +230,7 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
     else:
         calibration = calibration_from_records(records)
     sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"),
-                   "buddy" if schedule == "fifo" else "count")
+                   "buddy" if schedule == "fifo" else "count", gittins_delta_s)
     result = {"trace": trace, "gpus": gpus, "schedule": schedule, "comm": comm, "loopback": loopback,
               "queue_limit_s": list(queue_limit_s),
               "wall_s": round(wall, 2), "calibration_source": calibration.get("source", calibration_path),
@@ -253,6 +269,7 @@ def main(argv: Optional[Sequence[str]] = None) -> None:
     ap.add_argument("--gpus", type=int, default=8)
     ap.add_argument("--schedule", default="fifo", choices=sorted(SIM_SCHEDULE))
     ap.add_argument("--comm", default="ps", choices=["ps", "ring", "nccl"])
+    ap.add_argument("--gittins-delta", type=float, default=2.0, help="gittins: service quantum in GPU-seconds")
     ap.add_argument("--out", default="replay_out")
     ap.add_argument("--calibration", default=None)
     ap.add_argument("--loopback", action="store_true")
@@ -270,7 +287,7 @@ def main(argv: Optional[Sequence[str]] = None) -> None:
         return
     res = replay(a.trace, a.gpus, a.schedule, a.comm, a.out, a.calibration, a.loopback, a.batch, a.time_scale,
                  [float(x) for x in a.queue_limit.split(",")], a.check_every, a.step_sleep, a.iters_scale,
-                 not a.no_graph)
+                 not a.no_graph, a.gittins_delta)
     c = res["comparison"]
     print(json.dumps({k: v for k, v in c.items() if k != "jobs"}))
 
