@@ -6,7 +6,7 @@
 #   2. the whole 1-GPU suite, smoke, bench
 mkdir -p gpurun_out
 export TB200_TEST_EXPERIMENTAL=1
-timeout 120 python -m pytest tests/test_gpu_conv.py -m gpu -q -k halo -x > gpurun_out/halo_test.log 2>&1
+timeout 120 python -m pytest tests/test_gpu_conv.py tests/test_gpu_kernels.py -m gpu -q -k "halo or pull_gemm" > gpurun_out/halo_test.log 2>&1
 echo "== halo tests exit $?"; tail -n 15 gpurun_out/halo_test.log | cut -c1-300
 timeout 300 python bench/kernels.py --only conv --iters 10 > gpurun_out/kernels_conv_halo.log 2>&1
 echo "== conv bench exit $?"; grep '^{' gpurun_out/kernels_conv_halo.log | python -c "

@@ -1,6 +1,7 @@
 """Numerics of every hand-written kernel against a plain PyTorch fp32 reference of the same op
 (SURVEY.md §4 item 5)."""
 import ctypes as C
+import os
 
 import pytest
 import torch
@@ -252,3 +253,45 @@ def test_gemm_operand_layouts_match_fp32(cuda_device, m, n, k, a_mn, b_mn):
     got = native.gemm(a_arg, b_arg, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32)
     ref = a.float() @ b.float().t()
     assert torch.allclose(got, ref, rtol=2e-2, atol=2e-2), (got - ref).abs().max().item()
+
+
+# Single-GPU check of the pull GEMM (K2: B tiles TMA-loaded from the shard owners' memory). Written after the
+# round's GPU budget was spent, so it is opt-in until it has run once; the multi-rank trainers
+# (tests/multi_worker.py, 2/4/8 GPUs) cover the same kernel over real peers.
+@pytest.mark.skipif(os.environ.get("TB200_TEST_EXPERIMENTAL", "0") != "1",
+                    reason="not yet run on hardware (TB200_TEST_EXPERIMENTAL=1 runs it)")
+@pytest.mark.parametrize("world", [2, 4])
+def test_pull_gemm_emulated_owners(cuda_device, world):
+    from tiresias_b200.parallel.symm import SymmetricWorld
+    lib = native.lib()
+    m, n, k = 96, 128 * world, 256                        # every owner holds 128 rows of B
+    ranks = SymmetricWorld.emulated(world, cuda_device)
+    for r in ranks:
+        r.alloc("param", n * k * 2)
+        r.alloc("grad", 64)
+        r.alloc("flags", native.FLAG_WORDS * 4)
+    torch.manual_seed(3)
+    a = torch.randn(m, k, device=cuda_device).to(torch.bfloat16)
+    b = (torch.randn(n, k, device=cuda_device) / k ** 0.5).to(torch.bfloat16)
+    rows = n // world
+    for r in ranks:                                        # owner r has only ITS shard up to date
+        buf = r.buffers["param"].view(torch.bfloat16).view(n, k)
+        buf.zero_()
+        buf[r.rank * rows:(r.rank + 1) * rows].copy_(b[r.rank * rows:(r.rank + 1) * rows])
+    epoch = torch.full((1,), 2, dtype=torch.int32, device=cuda_device)      # shards were written in step 1
+    status = torch.zeros(1, dtype=torch.int32, device=cuda_device)
+    me = ranks[0]
+    me.post_flags("flags", native.flag_param_done(0, 0), world, 1)
+    w = me.native_world("grad", "param", "flags")
+    y = torch.empty(m, n, dtype=torch.bfloat16, device=cuda_device)
+    native.check(lib.tb200_gemm_bf16_nt_pull(C.byref(w), 0, 0, rows, a.data_ptr(), y.data_ptr(), None, 0, m, n, k,
+                                             native.BF16, 0, epoch.data_ptr(), status.data_ptr(), 1_000_000,
+                                             native.stream_ptr()))
+    torch.cuda.synchronize()
+    assert status.item() == 0
+    ref = a.float() @ b.float().t()
+    assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-2)
+    # the gather-store warp left the full matrix in rank 0's own buffer
+    assert torch.equal(me.buffers["param"].view(torch.bfloat16).view(n, k), b)
+    for r in ranks:
+        r.close()
