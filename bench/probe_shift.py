@@ -41,6 +41,21 @@ def main():
             rows.append({"shift": shift, "base_offset": bo, "max_abs_err": round(err, 4), "ok": err < 0.05,
                          "rows_matching_some_source_row": exact, "first_sources": src[:12].tolist()})
             print(json.dumps(rows[-1]), flush=True)
+    # MN-major operand shifted along the reduction dimension (halo-tile wgrad): not run yet in round 1
+    if hasattr(lib, "tb200_probe_shifted_mn_operand") and os.environ.get("TB200_TEST_EXPERIMENTAL") == "1":
+        lib.tb200_probe_shifted_mn_operand.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        lib.tb200_probe_shifted_mn_operand.restype = C.c_int
+        a2 = torch.randn(128, 64, device=dev).to(torch.bfloat16)
+        b2 = torch.randn(256, 64, device=dev).to(torch.bfloat16)
+        for shift in (0, 1, 3, 8, 9, 18, 66, 130, 192):
+            out.zero_()
+            native.check(lib.tb200_probe_shifted_mn_operand(a2.data_ptr(), b2.data_ptr(), out.data_ptr(), shift,
+                                                            native.stream_ptr()))
+            torch.cuda.synchronize()
+            want = a2.float() @ b2[shift:shift + 64].float()
+            err = float((out - want).abs().max())
+            rows.append({"operand": "B MN-major", "shift": shift, "max_abs_err": round(err, 4), "ok": err < 0.05})
+            print(json.dumps(rows[-1]), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(rows, open(os.path.join(ROOT, "gpurun_out", "probe_shift.json"), "w"), indent=1)
 

@@ -443,7 +443,101 @@ int launch_halo(const CUtensorMap& mx, const CUtensorMap& mw, const CUtensorMap&
   return launched();
 }
 
+
+// ---- probe: shifted MN-major operand windows (groundwork for a halo-tile wgrad) -----------------------
+// dW[k, (r,s), c] = sum_q dy[q, k] * x_padded[q + r*Wp + s, c]: the reduction runs over pixel rows, so both
+// operands are MN-major (rows = reduction index) and a tap is a window of the x tile shifted ALONG the
+// reduction dimension. One CTA: D[128, 64] = A[128, 64] . B[shift : shift+64, 0:64] with A K-major (as
+// validated) and B stored [256 reduction rows][64 n] bf16, 128-byte swizzled, its MN-major descriptor
+// advanced by shift*128 bytes.
+__global__ void __launch_bounds__(128, 1)
+probe_shift_mn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                      float* __restrict__ D, int shift) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t a_smem = smem_u32(smem_raw);                 // 128 rows x 128 B (K-major A)
+  const uint32_t b_smem = a_smem + 128 * 128;                 // 256 reduction rows x 128 B (MN-major B)
+  const uint32_t bar_full = b_smem + 256 * 128;
+  const uint32_t bar_done = bar_full + 8;
+  const uint32_t tmem_slot = bar_full + 16;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (threadIdx.x == 0) {
+    hb_init(bar_full, 1);
+    hb_init(bar_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(64)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  h_fence_before();
+  __syncthreads();
+  h_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - a_smem));
+  if (threadIdx.x == 0) {
+    hb_expect(bar_full, 128 * 128 + 256 * 128);
+    h_tma_load_2d(a_smem, &map_a, bar_full, 0, 0);
+    h_tma_load_2d(b_smem, &map_b, bar_full, 0, 0);
+    h_tma_load_2d(b_smem + 128 * 128, &map_b, bar_full, 0, 128);
+    hb_wait(bar_full, 0);
+    h_fence_after();
+    const uint32_t idesc = h_idesc(128, 64) | (1u << 16);       // B is MN-major
+    // MN-major descriptor: 8 reduction rows = one 1024-byte atom (stride byte offset), 64-wide MN slabs 8192
+    // bytes apart (leading byte offset; a single slab here)
+    uint64_t bdesc = 0;
+    bdesc |= (uint64_t)(((b_smem + (uint32_t)shift * 128u) & 0x3ffff) >> 4);
+    bdesc |= (uint64_t)(8192 >> 4) << 16;
+    bdesc |= (uint64_t)(1024 >> 4) << 32;
+    bdesc |= (uint64_t)1 << 46;
+    bdesc |= (uint64_t)2 << 61;
+    const uint64_t adesc = h_desc(a_smem);
+#pragma unroll
+    for (int k = 0; k < 64 / kUmmaK; ++k)                       // 16 reduction rows = 2048 bytes = 128 units
+      h_mma(tmem_base, adesc + 2u * k, bdesc + 128u * k, idesc, k > 0);
+    h_commit(bar_done);
+  }
+  hb_wait(bar_done, 0);
+  h_fence_after();
+  const int row = warp * 32 + lane;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    uint32_t r[32];
+    h_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32), r);
+    h_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) D[(size_t)row * 64 + c * 32 + j] = __uint_as_float(r[j]);
+  }
+  h_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    h_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(64) : "memory");
+  }
+}
+
 }  // namespace
+
+// Hardware probe (see probe_shift_mn_kernel): A bf16 [128, 64] (K-major), B bf16 [256, 64] (reduction rows x n),
+// D fp32 [128, 64] = A . B[shift : shift+64, :].
+extern "C" int tb200_probe_shifted_mn_operand(const void* A, const void* B, float* D, int shift, cudaStream_t stream) {
+  if (shift < 0 || shift > 192) return fail("tb200_probe_shifted_mn_operand: shift %s(%ld) outside 0..192", "", shift);
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    TB_CUDA_OK(cudaFree(nullptr));
+    ctx_bound = true;
+  }
+  CUtensorMap ma, mb;
+  if (int rc = halo_map_weights(&ma, A, 128, 64, 128)) return rc;     // [rows, 64 cols], box {64, 128}
+  if (int rc = halo_map_weights(&mb, B, 256, 64, 128)) return rc;
+  const int smem = 128 * 128 + 256 * 128 + 64;
+  static bool configured = false;
+  if (!configured) {
+    TB_CUDA_OK(cudaFuncSetAttribute(probe_shift_mn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  probe_shift_mn_kernel<<<1, 128, smem, stream>>>(ma, mb, D, shift);
+  return launched();
+}
 
 extern "C" int tb200_conv2d_fprop_halo(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout,
                                        int R, int S, cudaStream_t stream) {

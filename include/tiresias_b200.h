@@ -186,6 +186,10 @@ int tb200_conv2d_fprop_halo(const void* x, const void* w, void* y, int n, int h,
 int tb200_probe_shifted_operand(const void* A, const void* B, float* D, int shift, int base_offset,
                                 cudaStream_t stream);
 
+/* EXPERIMENTAL probe for a halo-tile wgrad: D[128,64] fp32 = A[128,64] . B[shift:shift+64, :] with B bf16
+ * [256 reduction rows, 64] read as an MN-major operand whose descriptor starts `shift` rows into the tile. */
+int tb200_probe_shifted_mn_operand(const void* A, const void* B, float* D, int shift, cudaStream_t stream);
+
 /* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
 int tb200_gemm_reserve(size_t bytes);
 
