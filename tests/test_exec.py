@@ -64,6 +64,22 @@ def test_replay_preempt_and_resume_loopback(tmp_path):
 
 
 @pytest.mark.timeout(300)
+def test_replay_dlas_gpu_loopback(tmp_path):
+    """Executed discretised LAS: the long job is demoted to Q1 once its attained GPU-time passes the queue
+    limit, so a later arrival (Q0) preempts it and — staying under the limit itself — runs to the end."""
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(2, 0, 300, "resnet50"), (2, 1, 8, "vgg16")])
+    res = replay(trace, gpus=2, schedule="dlas-gpu", comm="ps", out=str(tmp_path / "o"), loopback=True,
+                 step_sleep=0.01, check_every=5, queue_limit_s=(0.5,))
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert all(r["status"] == "DONE" for r in recs.values())
+    assert recs["0"]["preempt"] >= 1 and recs["1"]["preempt"] == 0
+    assert recs["1"]["end"] < recs["0"]["end"]
+    sim = res["comparison"]
+    assert sim["n"] == 2
+
+
+@pytest.mark.timeout(300)
 def test_replay_gittins_loopback(tmp_path):
     """Executed Gittins scheduling: a long job that has already received more GPU-time than the short jobs of
     the distribution ever need has a lower index than a fresh arrival, so it is preempted for it."""

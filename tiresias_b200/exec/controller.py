@@ -84,6 +84,7 @@ class Controller:
                                                   max(1, int(round(gittins_delta_s * 1000.0))))
         self.t0 = 0.0
         self.pending: List[ExecJob] = []           # fifo: arrived, could not start yet
+        self.queues: List[List[ExecJob]] = []      # dlas-gpu: the MLFQ, as explicit lists like the simulator's
         self.seen: set = set()
 
     # -- pool plumbing -------------------------------------------------------------------------------
@@ -186,11 +187,30 @@ class Controller:
         elif self.policy == "shortest":
             runnable.sort(key=lambda j: (j.iters - j.done, j.submit))
         elif self.policy == "dlas-gpu":
-            for j in runnable:
-                served = (j.attained + (now - j.last_start if j.status == "RUNNING" else 0.0)) * j.gpus
-                while j.q_id < len(self.queue_limit) and served >= self.queue_limit[j.q_id]:
-                    j.q_id += 1
-            runnable.sort(key=lambda j: (j.q_id, 0 if j.status != "WAITING" else 1, j.submit))
+            # the simulator's dlas loop (sim/legacy/schedulers.py::dlas, reference run_sim.py:663-946) on explicit
+            # queue lists: arrivals join the back of Q0; a running job whose attained GPU-time reached its
+            # queue's limit moves to the back of the next queue (one level per pass); GPUs are handed out by
+            # counting, queue by queue in list order; afterwards every queue keeps its running jobs in front
+            # and its waiting ones, in order, behind them.
+            if not self.queues:
+                self.queues = [[] for _ in range(len(self.queue_limit) + 1)]
+            for j in waiting:
+                if j.job_id not in self.seen:
+                    self.seen.add(j.job_id)
+                    self.queues[0].append(j)
+            live = {j.job_id for j in runnable}
+            for q in self.queues:
+                q[:] = [j for j in q if j.job_id in live]
+            for qi in range(len(self.queues) - 1):
+                for j in list(self.queues[qi]):
+                    if j.status != "RUNNING" or j.q_id != qi:
+                        continue
+                    served = (j.attained + (now - j.last_start)) * j.gpus
+                    if served >= self.queue_limit[qi]:
+                        self.queues[qi].remove(j)
+                        self.queues[qi + 1].append(j)
+                        j.q_id = qi + 1
+            runnable = [j for q in self.queues for j in q]
         elif self.policy == "gittins":
             # highest Gittins index of the attained GPU-time first (Tiresias 2D-Gittins; the reference's own
             # loop sorts ascending, run_sim.py:1082 — the simulator keeps that selectable, --gittins_desc)
@@ -220,6 +240,8 @@ class Controller:
         for j in chosen:
             if j.status == "WAITING":
                 self._start(j, now)
+        for q in self.queues:                       # dlas-gpu: waiting jobs go behind the running ones
+            q[:] = [j for j in q if j.status != "WAITING"] + [j for j in q if j.status == "WAITING"]
 
     # -- main loop --------------------------------------------------------------------------------------------
     def run(self) -> List[ExecJob]:
