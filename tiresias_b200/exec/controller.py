@@ -77,10 +77,14 @@ class Controller:
         # a distribution the trace's own jobs are the samples: iterations x estimated iteration time x GPUs —
         # what the simulator falls back to as well (sim/legacy/engine.py).
         self.gittins_table = None
+        self.gittins_delta_s = max(1e-3, float(gittins_delta_s))
+        self._next_unit = self.gittins_delta_s
+        self.gittins_samples_ms: Optional[List[int]] = None
         if policy == "gittins":
             from ..sim.legacy import gittins as gi
             samples = list(job_dist_s) if job_dist_s else [j.iters * est_iter_s * j.gpus for j in self.jobs]
-            self.gittins_table = gi.gittins_table([max(1, int(round(v * 1000.0))) for v in samples],
+            self.gittins_samples_ms = [max(1, int(round(v * 1000.0))) for v in samples]
+            self.gittins_table = gi.gittins_table(self.gittins_samples_ms,
                                                   max(1, int(round(gittins_delta_s * 1000.0))))
         self.t0 = 0.0
         self.pending: List[ExecJob] = []           # fifo: arrived, could not start yet
@@ -246,8 +250,8 @@ class Controller:
     # -- main loop --------------------------------------------------------------------------------------------
     def run(self) -> List[ExecJob]:
         """Decisions are taken at the simulator's event instants only — a job arrives, or an attempt
-        ends — plus, for dlas-gpu and gittins, on every poll (queue demotions / index changes happen between
-        events)."""
+        ends — plus, for dlas-gpu, on every poll (queue demotions happen between events) and, for gittins, every
+        ``gittins_delta`` seconds (the simulator's extra wake-up)."""
         self.t0 = time.time()
         announced: set = set()
         while any(j.status not in ("DONE", "FAILED") for j in self.jobs):
@@ -255,7 +259,11 @@ class Controller:
             changed = self._collect(now)
             arrivals = [j for j in self.jobs if j.submit <= now and j.job_id not in announced]
             announced.update(j.job_id for j in arrivals)
-            if changed or arrivals or self.policy in ("dlas-gpu", "gittins"):
+            tick = False
+            if self.policy == "gittins" and now >= self._next_unit:      # the simulator's extra wake-up
+                self._next_unit = (int(now / self.gittins_delta_s) + 1) * self.gittins_delta_s
+                tick = True
+            if changed or arrivals or tick or self.policy == "dlas-gpu":
                 self._schedule(now)
             time.sleep(self.poll_s)
         return self.jobs

@@ -105,7 +105,7 @@ def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:
 
 def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, gpus: int, schedule: str,
              queue_limit_s: Sequence[float], out_dir: str, scheme: str = "buddy",
-             gittins_delta_s: float = 2.0) -> Dict[str, Dict]:
+             gittins_delta_s: float = 2.0, job_dist_ms: Optional[Sequence[int]] = None) -> Dict[str, Dict]:
     """Event simulation in milliseconds on a 1 x 1 x ``gpus`` cluster. ``scheme="buddy"`` places jobs on
     aligned power-of-two GPU blocks like the worker pool does (non-preemptive schedules); the preemptive
     ones hand out GPUs by counting, as their reference loops do."""
@@ -127,8 +127,15 @@ def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, g
     if schedule == "dlas-gpu":
         argv += ["--queue_limit", ",".join(str(int(q * MS)) for q in queue_limit_s)]
     if schedule == "gittins":
-        # same direction (highest index first) and re-evaluation period as the controller
-        argv += ["--gittins_desc", "--gittins_delta", str(int(round(gittins_delta_s * MS)))]
+        # same direction (highest index first), re-evaluation period, ranking rules and duration samples as the
+        # controller (which knows only estimated iteration times when it builds its table)
+        argv += ["--gittins_desc", "--gittins_clean", "--gittins_delta", str(int(round(gittins_delta_s * MS)))]
+        if job_dist_ms:
+            os.makedirs(out_dir, exist_ok=True)
+            dist_path = os.path.join(out_dir, "job_dist.csv")
+            with open(dist_path, "w") as fh:
+                fh.write("duration\n" + "".join(f"{int(v)}\n" for v in job_dist_ms))
+            argv += ["--job_dist", dist_path]
     if schedule != "fifo":
         # restart cost of a resumed job, measured in this very replay: start-up + shard snapshot
         pre = [r for r in records if r.get("preempt")]
@@ -230,7 +237,7 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
     else:
         calibration = calibration_from_records(records)
     sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"),
-                   "buddy" if schedule == "fifo" else "count", gittins_delta_s)
+                   "buddy" if schedule == "fifo" else "count", gittins_delta_s, ctl.gittins_samples_ms)
     result = {"trace": trace, "gpus": gpus, "schedule": schedule, "comm": comm, "loopback": loopback,
               "queue_limit_s": list(queue_limit_s),
               "wall_s": round(wall, 2), "calibration_source": calibration.get("source", calibration_path),

@@ -130,6 +130,9 @@ def define_simulator_flags(fs: Optional[FlagSet] = None) -> FlagSet:
     fs.define_integer("gittins_delta", 3250, "Gittins service quantum")
     fs.define_boolean("gittins_desc", False, "gittins: highest index first (the reference's loop sorts "
                                              "ascending, its dlas-gpu-gittins variant descending)")
+    fs.define_boolean("gittins_clean", False, "gittins without three accidents of the reference loop: waiting "
+                                              "jobs ranked by attained GPU-time, a wake-up every gittins_delta, "
+                                              "running-first / submit-order tie break (what exec/ executes)")
     fs.define_float("solve_starvation", 0, "DLAS starvation knob: promote when pending >= x * executed")
     fs.define_integer("resume_overhead", 0, "time units charged to a job each time it resumes after a "
                                             "preemption (measured restart cost; 0 = free, as in the reference)")

@@ -453,10 +453,14 @@ def multi_dlas(sim: Sim, gputime: bool = False, solve_starvation: float = 0,
     jobs.completion_check()
 
 
-def gittins(sim: Sim, gputime: bool = False, descending: bool = False) -> None:
+def gittins(sim: Sim, gputime: bool = False, descending: bool = False, clean: bool = False) -> None:
     """gittins (run_sim.py:956-1202). ``descending=False`` is the reference's sort direction
     (ascending rank, run_sim.py:1082); its own dlas-gpu-gittins variant sorts descending (:809) —
-    the ambiguity is kept selectable (``--gittins_desc``)."""
+    the ambiguity is kept selectable (``--gittins_desc``). ``clean`` (``--gittins_clean``, ours) drops
+    three more accidents of the reference loop, which is what the real-time controller executes: a waiting
+    job is ranked by its attained GPU-time like a running one (the reference ranks it by plain seconds), the
+    extra wake-up comes every ``gittins_delta`` (the reference's ``next_unit += now`` makes the period grow
+    with the clock), and equal ranks keep running jobs ahead of waiting ones, then submit order."""
     jobs, cluster, log = sim.jobs, sim.cluster, sim.log
     end_events: List[dict] = []
     next_unit = int(jobs.gittins_delta)
@@ -479,11 +483,16 @@ def gittins(sim: Sim, gputime: bool = False, descending: bool = False) -> None:
         for j in jobs.runnable_jobs:
             _las_clock_update(j, now, gputime, 1, [], jobs.queues, 0)
         if jobs.runnable_jobs:
-            att = torch.tensor([_attained(j, gputime) if j.status == "RUNNING" else j.executed_time
+            att = torch.tensor([_attained(j, gputime) if (j.status == "RUNNING" or clean) else j.executed_time
                                 for j in jobs.runnable_jobs], dtype=torch.int64)
             for j, r in zip(jobs.runnable_jobs, gi.gittins_ranks(jobs.job_dist_data, att).tolist()):
                 j.rank = r
-        jobs.runnable_jobs.sort(key=lambda j: j.rank, reverse=descending)
+        if clean:
+            sign = -1.0 if descending else 1.0
+            jobs.runnable_jobs.sort(key=lambda j: (sign * j.rank, 0 if j.status == "RUNNING" else 1,
+                                                   j.submit_time))
+        else:
+            jobs.runnable_jobs.sort(key=lambda j: j.rank, reverse=descending)
         cluster.empty_infra()
         run_jobs, preempt_jobs = [], []
         for j in jobs.runnable_jobs:
@@ -498,7 +507,10 @@ def gittins(sim: Sim, gputime: bool = False, descending: bool = False) -> None:
         nxt = _earliest_completion(jobs.runnable_jobs, now)
         if nxt is not None:
             end_events.append(nxt)
-        next_unit += now
+        if clean:
+            next_unit = (now // int(jobs.gittins_delta) + 1) * int(jobs.gittins_delta)
+        else:
+            next_unit += now
         log.checkpoint(jobs, now)
         sim.mark(now)
 
@@ -591,7 +603,8 @@ def dispatch(sim: Sim) -> None:
     elif s == "multi-dlas-gpu":
         multi_dlas(sim, gputime=True, solve_starvation=starve)
     elif s == "gittins":
-        gittins(sim, gputime=True, descending=bool(getattr(sim.flags, "gittins_desc", False)))
+        gittins(sim, gputime=True, descending=bool(getattr(sim.flags, "gittins_desc", False)),
+                clean=bool(getattr(sim.flags, "gittins_clean", False)))
     elif s == "gandiva-legacy":
         gandiva_legacy(sim)
     elif s == "gpu-demands":
