@@ -166,3 +166,18 @@ def test_gpu_demands_mode(tmp_path):
     assert rows[0] == ["time", "1-GPU", "2-GPU", "4-GPU", "8-GPU", "12-GPU", "16-GPU", "24-GPU", "32-GPU"]
     demand = {int(r[0]): (int(r[1]), int(r[2])) for r in rows[1:]}
     assert demand[0] == (1, 0) and demand[5] == (1, 2) and demand[6] == (1, 4) and demand[10] == (0, 4)
+
+
+def test_gittins_clean_wakes_every_delta_and_finishes(tmp_path):
+    """--gittins_clean (ours; what the real-time controller executes): highest index first, a wake-up every
+    gittins_delta instead of the reference's growing period. Two 4-GPU jobs on 4 GPUs: a long one that
+    starts alone and a short one arriving later. By then the long job has attained more GPU-time than the
+    short sample of the distribution, so its index has dropped to 0 and the fresh arrival preempts it."""
+    rows, s, _ = _sim(tmp_path, [(4, 0, 1000), (4, 100, 50)], "gittins",
+                      extra=("--gittins_desc", "--gittins_clean", "--gittins_delta", "40"))
+    assert s["finished_jobs"] == 2
+    assert int(rows[1]["end_time"]) == 150                       # ran at once for its 50 units
+    assert int(rows[0]["preempt"]) == 1 and int(rows[0]["end_time"]) == 1050
+    # the reference-faithful loop still completes the same trace
+    rows2, s2, _ = _sim(tmp_path, [(4, 0, 1000), (4, 100, 50)], "gittins", extra=("--gittins_delta", "40"))
+    assert s2["finished_jobs"] == 2
