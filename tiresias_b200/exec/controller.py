@@ -60,7 +60,7 @@ class Controller:
                  queue_limit: Sequence[float] = (20.0,), check_every: int = 10, poll_s: float = 0.02,
                  job_timeout_s: float = 600.0, step_sleep: float = 0.0, graph: bool = True, log=print,
                  job_dist_s: Optional[Sequence[float]] = None, gittins_delta_s: float = 2.0,
-                 est_iter_s: float = 0.05):
+                 est_iter_s: float = 0.05, iter_table: Optional[Dict] = None):
         self.store, self.num_gpus, self.policy, self.comm = store, num_gpus, policy, comm
         self.time_scale, self.ckpt_dir, self.check_every, self.poll_s = time_scale, ckpt_dir, check_every, poll_s
         self.queue_limit = list(queue_limit)
@@ -76,13 +76,17 @@ class Controller:
         # gittins: the index table over GPU-time samples in milliseconds (sim.legacy.gittins, PyTorch). Without
         # a distribution the trace's own jobs are the samples: iterations x estimated iteration time x GPUs —
         # what the simulator falls back to as well (sim/legacy/engine.py).
+        # iteration-time estimates per (model, GPUs): from a calibration when one is given, refined by every
+        # finished attempt; what "shortest" ranks remaining work with and what gittins builds its samples from
+        self.est_iter_s = est_iter_s
+        self.iter_table: Dict[str, Dict[str, float]] = {m: dict(v) for m, v in (iter_table or {}).items()}
         self.gittins_table = None
         self.gittins_delta_s = max(1e-3, float(gittins_delta_s))
         self._next_unit = self.gittins_delta_s
         self.gittins_samples_ms: Optional[List[int]] = None
         if policy == "gittins":
             from ..sim.legacy import gittins as gi
-            samples = list(job_dist_s) if job_dist_s else [j.iters * est_iter_s * j.gpus for j in self.jobs]
+            samples = list(job_dist_s) if job_dist_s else [j.iters * self._iter_s(j) * j.gpus for j in self.jobs]
             self.gittins_samples_ms = [max(1, int(round(v * 1000.0))) for v in samples]
             self.gittins_table = gi.gittins_table(self.gittins_samples_ms,
                                                   max(1, int(round(gittins_delta_s * 1000.0))))
@@ -90,6 +94,14 @@ class Controller:
         self.pending: List[ExecJob] = []           # fifo: arrived, could not start yet
         self.queues: List[List[ExecJob]] = []      # dlas-gpu: the MLFQ, as explicit lists like the simulator's
         self.seen: set = set()
+
+    def _iter_s(self, job: ExecJob) -> float:
+        per = self.iter_table.get(job.model)
+        if not per:
+            return self.est_iter_s
+        keys = sorted(int(k) for k in per)
+        pick = max([k for k in keys if k <= job.gpus], default=keys[0])
+        return float(per[str(pick)])
 
     # -- pool plumbing -------------------------------------------------------------------------------
     def wait_ready(self, timeout_s: float = 600.0) -> None:
@@ -152,6 +164,8 @@ class Controller:
                 self.log(f"[{now:8.2f}s] job {job.job_id} FAILED: {[r.get('error') for r in res if r['status'] == 'failed'][:1]}")
             elif all(r["status"] == "done" for r in res):
                 job.status, job.end, job.done = "DONE", now, job.iters
+                if res[0].get("iter_ms") and str(job.gpus) not in self.iter_table.get(job.model, {}):
+                    self.iter_table.setdefault(job.model, {})[str(job.gpus)] = res[0]["iter_ms"] / 1e3
                 self.log(f"[{now:8.2f}s] job {job.job_id} done (JCT {job.jct():.2f}s, "
                          f"{(res[0].get('iter_ms') or 0.0):.2f} ms/iter)")
             else:
@@ -189,7 +203,7 @@ class Controller:
         if self.policy == "sjf":
             runnable.sort(key=lambda j: (j.gpus, j.submit))
         elif self.policy == "shortest":
-            runnable.sort(key=lambda j: (j.iters - j.done, j.submit))
+            runnable.sort(key=lambda j: ((j.iters - j.done) * self._iter_s(j), j.submit))
         elif self.policy == "dlas-gpu":
             # the simulator's dlas loop (sim/legacy/schedulers.py::dlas, reference run_sim.py:663-946) on explicit
             # queue lists: arrivals join the back of Q0; a running job whose attained GPU-time reached its

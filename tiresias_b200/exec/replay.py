@@ -197,6 +197,13 @@ def _estimated_iter_s(calibration_path: Optional[str], step_sleep: float) -> flo
     return step_sleep if step_sleep > 0 else 0.05
 
 
+def _iter_table(calibration_path: Optional[str]) -> Optional[Dict]:
+    if calibration_path and os.path.exists(calibration_path):
+        with open(calibration_path) as fh:
+            return json.load(fh).get("iter_s")
+    return None
+
+
 def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out: str = "replay_out",
            calibration_path: Optional[str] = None, loopback: bool = False, batch: int = 32, time_scale: float = 1.0,
            queue_limit_s: Sequence[float] = (20.0,), check_every: int = 10, step_sleep: float = 0.0,
@@ -218,7 +225,8 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
     ctl = Controller(store, gpus, rows, policy=schedule, comm=comm, batch=batch, time_scale=time_scale,
                      ckpt_dir=ckpt_dir, queue_limit=queue_limit_s, check_every=check_every, step_sleep=step_sleep,
                      graph=graph, log=log, gittins_delta_s=gittins_delta_s,
-                     est_iter_s=_estimated_iter_s(calibration_path, step_sleep))
+                     est_iter_s=_estimated_iter_s(calibration_path, step_sleep),
+                     iter_table=_iter_table(calibration_path))
     try:
         ctl.wait_ready()
         t_pool = time.time()
