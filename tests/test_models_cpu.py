@@ -88,3 +88,16 @@ def test_tc_conv_modules_fall_back_to_torch_on_cpu():
     assert torch.allclose(c3(x), torch.nn.functional.conv2d(x, c3.weight, stride=2, padding=1))
     with pytest.raises(ValueError):
         TcConv2d(48, 64, 3)
+
+
+def test_samplers_degrade_without_nvml():
+    """On a box without NVML (this CPU container) the clock / utilisation samplers report nothing instead of
+    failing, so the loopback executor and CPU runs keep working."""
+    from tiresias_b200.utils.clocks import ClockSampler, UtilSampler, rejected
+    u = UtilSampler(0).start().stop()
+    c = ClockSampler(0).start().stop()
+    if u["samples"] == 0:                       # no NVML here
+        assert u["gpu_util_avg"] is None and u["gpu_util_max"] is None
+    else:                                       # a GPU box: values are percentages
+        assert 0 <= u["gpu_util_avg"] <= 100
+    assert "reasons" in c and not rejected({"reasons": ["sw_power_cap"]}) and rejected({"reasons": ["hw_slowdown"]})
