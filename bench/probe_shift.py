@@ -56,6 +56,23 @@ def main():
             err = float((out - want).abs().max())
             rows.append({"operand": "B MN-major", "shift": shift, "max_abs_err": round(err, 4), "ok": err < 0.05})
             print(json.dumps(rows[-1]), flush=True)
+    # TMA boxes landing at 128-byte (not 1024-byte) aligned shared-memory offsets: needed for halo tiles whose
+    # padded rows are not multiples of 8 pixels
+    if hasattr(lib, "tb200_probe_tma_dst_shift"):
+        lib.tb200_probe_tma_dst_shift.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        lib.tb200_probe_tma_dst_shift.restype = C.c_int
+        a3 = torch.randn(128, 64, device=dev).to(torch.bfloat16)
+        want = a3.float() @ b.float().t()
+        for shift in (0, 1, 2, 5, 8, 9, 30, 58, 120):
+            for piece in (128, 2, 1):
+                out.zero_()
+                native.check(lib.tb200_probe_tma_dst_shift(a3.data_ptr(), b.data_ptr(), out.data_ptr(), shift, piece,
+                                                           native.stream_ptr()))
+                torch.cuda.synchronize()
+                err = float((out - want).abs().max())
+                rows.append({"probe": "tma_dst", "shift": shift, "piece_rows": piece, "max_abs_err": round(err, 4),
+                             "ok": err < 0.05})
+                print(json.dumps(rows[-1]), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(rows, open(os.path.join(ROOT, "gpurun_out", "probe_shift.json"), "w"), indent=1)
 

@@ -465,16 +465,7 @@ __global__ void __launch_bounds__(kTX * kTY, 2) bn_bwd_apply_kernel(const BwdArg
   }
 }
 
-int sm_count_bn() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+int sm_count_bn() { return device_sm_count(); }
 
 // Row chunks so that the grid is ~`per_sm` CTAs per SM, every chunk holds >= one 32-row step, and the
 // partials fit the scratch. Reductions use fewer, longer chunks (their last CTA folds one partial

@@ -50,6 +50,52 @@ inline int launched() {
 
 enum DType : int { kF32 = 0, kBF16 = 1 };
 
+// Per-device one-time set-up. Function attributes (cudaFuncAttributeMaxDynamicSharedMemorySize) and the SM
+// count belong to a device, not to the process: a host that drives several GPUs from one process must
+// configure every kernel on every GPU it launches on. `DeviceOnce` remembers, per kernel instantiation,
+// which devices are done (lock-free; a race only repeats the cheap, idempotent call).
+constexpr int kMaxDevices = 64;
+
+inline int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 0;
+  return dev;
+}
+
+struct DeviceOnce {
+  std::atomic<bool> done[kMaxDevices];
+  bool need(int dev) const { return !done[dev].load(std::memory_order_acquire); }
+  void mark(int dev) { done[dev].store(true, std::memory_order_release); }
+};
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, device).
+template <typename Kern>
+inline int ensure_dynamic_smem(DeviceOnce& once, Kern kern, int bytes) {
+  const int dev = current_device();
+  if (once.need(dev)) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) {
+      snprintf(g_last_error, sizeof(g_last_error), "cudaFuncSetAttribute(max dynamic smem %d) failed: %s", bytes,
+               cudaGetErrorString(e));
+      return 2;
+    }
+    once.mark(dev);
+  }
+  return 0;
+}
+
+// SM count of the CURRENT device (cached per device).
+inline int device_sm_count() {
+  static std::atomic<int> cache[kMaxDevices];
+  const int dev = current_device();
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n <= 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Device helpers
 // ---------------------------------------------------------------------------------------------

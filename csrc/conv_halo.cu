@@ -429,15 +429,9 @@ int launch_halo(const CUtensorMap& mx, const CUtensorMap& mw, const CUtensorMap&
   sm.bar_off = sm.epi_off + HaloCfg<BLOCK_N>::kEpiBytes;
   sm.total = sm.bar_off + 1024;
   auto kern = conv_halo_kernel<BLOCK_N>;
-  static bool configured = false;
-  if (!configured) {
-    TB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
-    configured = true;
-  }
-  int sms = 0, dev = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (sms <= 0) sms = 148;
+  static DeviceOnce configured;      // one per template instantiation
+  if (int rc = ensure_dynamic_smem(configured, kern, kSmemMax)) return rc;
+  const int sms = device_sm_count();
   const int items = p.num_m * p.num_n;
   kern<<<items < sms ? items : sms, kThreadsHalo, sm.total, stream>>>(mx, mw, my, p, sm);
   return launched();
@@ -515,7 +509,87 @@ probe_shift_mn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   }
 }
 
+
+// ---- probe: TMA destination that is 128-byte but not 1024-byte aligned -------------------------------
+// A halo tile whose padded rows are not multiples of 8 pixels puts each row's TMA box at a shared-memory
+// offset that is a multiple of 128 bytes only. This one-CTA kernel loads A[128, 64] (128-byte swizzle) to
+// a_smem + shift*128 as `pieces` row boxes and multiplies it from a descriptor at the same address:
+// D = A . B^T must come out unchanged if the swizzle of both the TMA write and the MMA read follows the
+// absolute shared-memory address.
+__global__ void __launch_bounds__(128, 1)
+probe_tma_dst_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                     float* __restrict__ D, int shift, int piece_rows) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t a_smem = smem_u32(smem_raw);                 // 256 rows x 128 B
+  const uint32_t b_smem = a_smem + 256 * 128;                 // 64 rows x 128 B
+  const uint32_t bar_full = b_smem + 64 * 128;
+  const uint32_t bar_done = bar_full + 8;
+  const uint32_t tmem_slot = bar_full + 16;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (threadIdx.x == 0) {
+    hb_init(bar_full, 1);
+    hb_init(bar_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(64)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  h_fence_before();
+  __syncthreads();
+  h_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - a_smem));
+  if (threadIdx.x == 0) {
+    hb_expect(bar_full, 128 * 128 + 64 * 128);
+    for (int r0 = 0; r0 < 128; r0 += piece_rows)              // map_a's box is piece_rows rows
+      h_tma_load_2d(a_smem + (uint32_t)(shift + r0) * 128u, &map_a, bar_full, 0, r0);
+    h_tma_load_2d(b_smem, &map_b, bar_full, 0, 0);
+    hb_wait(bar_full, 0);
+    h_fence_after();
+    const uint32_t idesc = h_idesc(128, 64);
+    const uint64_t adesc = h_desc(a_smem + (uint32_t)shift * 128u);
+    const uint64_t bdesc = h_desc(b_smem);
+#pragma unroll
+    for (int k = 0; k < 64 / kUmmaK; ++k) h_mma(tmem_base, adesc + 2u * k, bdesc + 2u * k, idesc, k > 0);
+    h_commit(bar_done);
+  }
+  hb_wait(bar_done, 0);
+  h_fence_after();
+  const int row = warp * 32 + lane;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    uint32_t r[32];
+    h_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32), r);
+    h_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) D[(size_t)row * 64 + c * 32 + j] = __uint_as_float(r[j]);
+  }
+  h_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    h_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(64) : "memory");
+  }
+}
+
 }  // namespace
+
+// Hardware probe (see probe_tma_dst_kernel): A bf16 [128, 64], B bf16 [64, 64], D fp32 [128, 64] = A . B^T with A
+// landed `shift` 128-byte rows into shared memory, as boxes of `piece_rows` rows (must divide 128).
+extern "C" int tb200_probe_tma_dst_shift(const void* A, const void* B, float* D, int shift, int piece_rows,
+                                         cudaStream_t stream) {
+  if (shift < 0 || shift > 120) return fail("tb200_probe_tma_dst_shift: shift %s(%ld) outside 0..120", "", shift);
+  if (piece_rows <= 0 || 128 % piece_rows) return fail("tb200_probe_tma_dst_shift: piece_rows must divide 128%s");
+  TB_CUDA_OK(cudaFree(nullptr));
+  CUtensorMap ma, mb;
+  if (int rc = halo_map_weights(&ma, A, 128, 64, piece_rows)) return rc;
+  if (int rc = halo_map_weights(&mb, B, 64, 64, 64)) return rc;
+  const int smem = 256 * 128 + 64 * 128 + 64;
+  TB_CUDA_OK(cudaFuncSetAttribute(probe_tma_dst_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  probe_tma_dst_kernel<<<1, 128, smem, stream>>>(ma, mb, D, shift, piece_rows);
+  return launched();
+}
 
 // Hardware probe (see probe_shift_mn_kernel): A bf16 [128, 64] (K-major), B bf16 [256, 64] (reduction rows x n),
 // D fp32 [128, 64] = A . B[shift : shift+64, :].
@@ -530,11 +604,8 @@ extern "C" int tb200_probe_shifted_mn_operand(const void* A, const void* B, floa
   if (int rc = halo_map_weights(&ma, A, 128, 64, 128)) return rc;     // [rows, 64 cols], box {64, 128}
   if (int rc = halo_map_weights(&mb, B, 256, 64, 128)) return rc;
   const int smem = 128 * 128 + 256 * 128 + 64;
-  static bool configured = false;
-  if (!configured) {
-    TB_CUDA_OK(cudaFuncSetAttribute(probe_shift_mn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  static DeviceOnce configured;
+  if (int rc = ensure_dynamic_smem(configured, probe_shift_mn_kernel, smem)) return rc;
   probe_shift_mn_kernel<<<1, 128, smem, stream>>>(ma, mb, D, shift);
   return launched();
 }

@@ -882,16 +882,7 @@ struct Workspace {
 std::mutex g_ws_mutex;
 std::unordered_map<int, Workspace> g_ws;  // per device split-K scratch, grown on demand
 
-int sm_count() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+int sm_count() { return device_sm_count(); }
 
 int get_workspace(size_t bytes, float** out) {
   int dev = 0;
@@ -911,16 +902,55 @@ int get_workspace(size_t bytes, float** out) {
   return 0;
 }
 
+// Tile width and split-K factor of a problem (shared by the launcher and tb200_gemm_plan_splits).
+//   block_n: 256 when that still yields at least one full wave of CTAs, else 128.
+//   splits : 1 when the tile grid fills the machine. Otherwise the count whose work-item total packs best
+//            into whole waves of `sms` CTAs (ties go to fewer splits), bounded by
+//              - at least 4 k-blocks (256 reduction elements) per split:  splits <= ceil(K/64) / 4
+//              - one split per SM:                                          splits <= sms
+//              - the fp32 partial planes may add at most ~10 % to the bf16 input traffic, with a floor of
+//                16 (a long-reduction, tiny-output GEMM such as a 1x1 convolution's dW wants one split per
+//                SM; a square-ish problem wants few):   splits <= max(16, 0.1 * in_bytes / plane_bytes)
+int plan_tiles(int M, int N, int K, bool pull, int rows_per_rank, int sms, int* block_n_out, int* splits_out) {
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  const int num_m = (M + BLOCK_M - 1) / BLOCK_M;
+  int block_n = 256;
+  if (N <= 128 || (long long)num_m * ((N + 255) / 256) < sms) block_n = 128;
+  if (pull && rows_per_rank % block_n) {
+    block_n = 128;
+    if (rows_per_rank % 128)
+      return fail("tb200_gemm_pull: rows_per_rank %s(%ld) must be a multiple of 128", "", rows_per_rank);
+  }
+  const int tiles = num_m * ((N + block_n - 1) / block_n);
+  int splits = 1;
+  if (tiles < sms) {
+    int max_splits = num_kb / 4;
+    if (max_splits > sms) max_splits = sms;
+    const double in_bytes = 2.0 * ((double)M * K + (double)N * K);
+    const double plane_bytes = 4.0 * (double)M * N;
+    int by_traffic = (int)(0.1 * in_bytes / plane_bytes);
+    if (by_traffic < 16) by_traffic = 16;
+    if (max_splits > by_traffic) max_splits = by_traffic;
+    double best = 0.0;
+    for (int s = 1; s <= max_splits; ++s) {
+      const int it = tiles * s;
+      const int waves = (it + sms - 1) / sms;
+      const double eff = (double)it / ((double)waves * sms);
+      if (eff > best + 1e-9) { best = eff; splits = s; }
+    }
+  }
+  *block_n_out = block_n;
+  *splits_out = splits;
+  return 0;
+}
+
 template <int BLOCK_N, bool kPull, bool THIN>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const PullMaps& pull,
                 const GemmParams& p, int grid, cudaStream_t stream) {
   using C = Cfg<BLOCK_N, THIN>;
   auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull, THIN>;
-  static bool configured = false;
-  if (!configured) {
-    TB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    configured = true;
-  }
+  static DeviceOnce configured;      // one per template instantiation
+  if (int rc = ensure_dynamic_smem(configured, kern, C::kSmemBytes)) return rc;
   kern<<<grid, kGemmThreads, C::kSmemBytes, stream>>>(ma, mb, md, pull, p);
   return launched();
 }
@@ -965,41 +995,11 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
 
-  // Tile width: 256 when that still yields at least one full wave, else 128.
   const int sms = sm_count();
-  int block_n = 256;
-  if (N <= 128 || (long long)p.num_m * ((N + 255) / 256) < sms) block_n = 128;
-  if (pull && rows_per_rank % block_n) {
-    block_n = 128;
-    if (rows_per_rank % 128)
-      return fail("tb200_gemm_pull: rows_per_rank %s(%ld) must be a multiple of 128", "", rows_per_rank);
-  }
+  int block_n = 0, splits = 1;
+  if (int rc = plan_tiles(M, N, K, pull, rows_per_rank, sms, &block_n, &splits)) return rc;
   p.num_n = (N + block_n - 1) / block_n;
   const int tiles = p.num_m * p.num_n;
-  // Split K when the tile grid cannot fill the machine (small-batch FC layers are weight-
-  // bandwidth bound: every SM should be streaming a slice of B).
-  int splits = 1;
-  if (tiles < sms) {
-    // Pick the split count whose work-item total packs best into whole waves of `sms` CTAs
-    // (ties go to fewer splits); keep at least 4 k-blocks per split.
-    // ... and no more splits than SMs, nor so many that the fp32 partial planes add more than ~10 % to the
-    // bf16 input traffic, with a floor of 16 (a long-reduction, tiny-output GEMM such as a 1x1 convolution's
-    // dW — K = N*H*W pixels, output Cout x Cin — wants one split per SM; a square-ish problem wants few).
-    int max_splits = p.num_kb / 4;
-    if (max_splits > sms) max_splits = sms;
-    const double in_bytes = 2.0 * ((double)M * K + (double)N * K);
-    const double plane_bytes = 4.0 * (double)M * N;
-    int by_traffic = (int)(0.1 * in_bytes / plane_bytes);
-    if (by_traffic < 16) by_traffic = 16;
-    if (max_splits > by_traffic) max_splits = by_traffic;
-    double best = 0.0;
-    for (int s = 1; s <= max_splits; ++s) {
-      const int it = tiles * s;
-      const int waves = (it + sms - 1) / sms;
-      const double eff = (double)it / ((double)waves * sms);
-      if (eff > best + 1e-9) { best = eff; splits = s; }
-    }
-  }
   p.splits = splits;
   if (splits > 1) {
     const size_t need = (size_t)splits * M * N * sizeof(float);
@@ -1195,13 +1195,19 @@ int tb200_probe_shifted_operand(const void* A, const void* B, float* D, int shif
   if (int rc = make_map(&ma, A, 256, 64, 128)) return rc;
   if (int rc = make_map(&mb, B, 64, 64, 64)) return rc;
   const int smem = 256 * 128 + 64 * 128 + 64;
-  static bool configured = false;
-  if (!configured) {
-    TB_CUDA_OK(cudaFuncSetAttribute(probe_shift_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  static DeviceOnce configured;
+  if (int rc = ensure_dynamic_smem(configured, probe_shift_kernel, smem)) return rc;
   probe_shift_kernel<<<1, 128, smem, stream>>>(ma, mb, D, shift, base_offset);
   return launched();
+}
+
+// How many split-K partial planes tb200_gemm_bf16_nt / _noalloc would use for this problem on the current
+// device (1 = no scratch needed). Scratch bytes = splits * M * N * 4.
+int tb200_gemm_plan_splits(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  int block_n = 0, splits = 1;
+  if (plan_tiles(M, N, K, false, 0, sm_count(), &block_n, &splits)) return 0;
+  return splits;
 }
 
 // Pre-size the split-K scratch (call before CUDA-graph capture so no allocation happens
@@ -1232,7 +1238,6 @@ static __device__ __align__(256) float tb200_noalloc_splitk_scratch[TB200_GEMM_N
 
 namespace {
 
-constexpr int kMaxDevices = 64;
 std::mutex g_noalloc_mutex;
 float* g_noalloc_ptr[kMaxDevices] = {};
 

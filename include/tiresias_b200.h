@@ -199,14 +199,20 @@ int tb200_gemm_reserve(size_t bytes);
  * Who needs it: a job that shares its GPU with other jobs (cudaMalloc/cudaFree synchronise the
  * whole device, so an allocation by one tenant stalls the others, and on a fully subscribed GPU
  * it can fail mid-step), and plain C hosts of this ABI that bring no allocator and want the
- * memory footprint fixed at load time. This entry point never calls cudaMalloc, cudaFree or any
- * allocating routine: when the problem is split along K, the fp32 partial sums go to a scratch
- * array that is built into the library, TB200_GEMM_NOALLOC_SCRATCH_BYTES per GPU, held by every
- * GPU that loads the library until the process exits.
+ * memory footprint fixed at load time. This entry point never calls cudaMalloc or any
+ * allocating routine and frees nothing (the first call a thread makes into the GEMM issues one
+ * cudaFree(NULL), which releases nothing: it only binds the CUDA context to that thread): when
+ * the problem is split along K, the fp32 partial sums go to a scratch array that is built into
+ * the library, TB200_GEMM_NOALLOC_SCRATCH_BYTES per GPU, held by every GPU that loads the
+ * library until the process exits.
  *
- *  - Limit: splits * M * N * 4 bytes must fit in the scratch (splits is chosen as in
- *    tb200_gemm_bf16_nt, at most 16). Larger problems are refused with an error that names
- *    both sizes; nothing is launched in that case. Problems that need no split use no scratch.
+ *  - Limit: splits * M * N * 4 bytes must fit in the scratch. splits is chosen as in
+ *    tb200_gemm_bf16_nt: 1 when the 128 x {128,256} tile grid already fills the GPU, otherwise
+ *    up to min(ceil(K/64)/4, SM count, max(16, 0.1 * (M+N)*K*2 / (M*N*4))) - so a long-K,
+ *    small-output problem can use one split per SM (148 on a B200), not 16.
+ *    tb200_gemm_plan_splits(M, N, K) returns the count for the current device, so a caller can
+ *    check the fit in advance. Larger problems are refused with an error that names both sizes;
+ *    nothing is launched in that case. Problems that need no split use no scratch.
  *  - The first call on each device looks up the scratch's device address (one
  *    cudaGetSymbolAddress with that device current). Make that first call during set-up,
  *    before any stream capture is started on the device.
@@ -218,6 +224,11 @@ int tb200_gemm_reserve(size_t bytes);
 int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void* bias,
                                int bias_dtype, int M, int N, int K, int d_dtype, int act,
                                cudaStream_t stream);
+
+/* Split-K partial planes tb200_gemm_bf16_nt / _noalloc use for an [M,K] x [N,K]^T problem on the
+ * current device (1 = no scratch; 0 = empty problem). Scratch bytes = splits * M * N * 4.
+ * No counterpart in the reference.                                                           */
+int tb200_gemm_plan_splits(int M, int N, int K);
 
 /* ---- K2 (load side): PS->worker pull fused into the first GEMM that consumes the weights.
  * B is sharded by rows across the world: rank s owns rows [s*rows_per_rank, ...) inside its

@@ -9,7 +9,7 @@ export TB200_TEST_EXPERIMENTAL=1
 timeout 120 python -m pytest tests/test_gpu_conv.py tests/test_gpu_kernels.py -m gpu -q -k "halo or pull_gemm" > gpurun_out/halo_test.log 2>&1
 echo "== halo tests exit $?"; tail -n 15 gpurun_out/halo_test.log | cut -c1-300
 timeout 60 python bench/probe_shift.py > gpurun_out/probe_shift.log 2>&1
-echo "== probes exit $?"; grep "MN-major" gpurun_out/probe_shift.log | cut -c1-160
+echo "== probes exit $?"; grep -E "MN-major|tma_dst" gpurun_out/probe_shift.log | cut -c1-160
 timeout 300 python bench/kernels.py --only conv --iters 10 > gpurun_out/kernels_conv_halo.log 2>&1
 echo "== conv bench exit $?"; grep '^{' gpurun_out/kernels_conv_halo.log | python -c "
 import sys, json

@@ -24,7 +24,9 @@ def test_gemm_nt_matches_fp32(cuda_device, m, n, k):
     got = native.gemm_nt(a, b, out_dtype=torch.float32)
     ref = a.float() @ b.float().t()
     torch.cuda.synchronize()
-    assert torch.allclose(got, ref, rtol=2e-2, atol=2e-2), (got - ref).abs().max().item()
+    # fp32 output of bf16 operands against the fp32 product of the same operands: only the summation order
+    # differs, so a mis-addressed k-slice (1/32 of K and up) cannot hide inside the tolerance
+    assert torch.allclose(got, ref, rtol=1e-3, atol=1e-3), (got - ref).abs().max().item()
 
 
 @pytest.mark.parametrize("act", [native.ACT_NONE, native.ACT_RELU, native.ACT_GELU])
@@ -252,7 +254,7 @@ def test_gemm_operand_layouts_match_fp32(cuda_device, m, n, k, a_mn, b_mn):
     b_arg = b.t().contiguous() if b_mn else b
     got = native.gemm(a_arg, b_arg, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32)
     ref = a.float() @ b.float().t()
-    assert torch.allclose(got, ref, rtol=2e-2, atol=2e-2), (got - ref).abs().max().item()
+    assert torch.allclose(got, ref, rtol=1e-3, atol=1e-3), (got - ref).abs().max().item()
 
 
 # Single-GPU check of the pull GEMM (K2: B tiles TMA-loaded from the shard owners' memory). Written after the
