@@ -12,9 +12,18 @@ the PS shards, synthetic uint8 images and random-init weights (no network for da
 Prints ONE JSON line on rank 0. ``value`` is device-timed (CUDA events, max over ranks) with the
 batch resident on the GPU; ``e2e`` goes through the public ``Trainer.step`` API including the
 pinned host->device copy of every step's inputs and the device->host read of every step's loss.
-``nccl_baseline`` is the PyTorch+NCCL PS/worker arm (same model, same buckets) measured in the
-same process right after, as BASELINE.json prescribes. ``--impl reference`` reports that the
-reference itself cannot produce this metric (it is a CPU-only scheduling simulator).
+Two NCCL arms are measured in the same process right after:
+``nccl_baseline``      the stock PyTorch + NCCL PS/worker job BASELINE.json prescribes (nn.BatchNorm2d, cuDNN /
+                       cuBLAS, eager, per-parameter gradient accumulation, torch optimizer ops);
+``nccl_same_compute``  the SAME fused network, gradient packing, optimizer kernel and CUDA graph as ours —
+                       only the communication differs (NCCL reduce_scatter + all_gather instead of the fused
+                       push/pull kernel). ours / nccl_same_compute is what the in-kernel push/pull buys;
+                       nccl_same_compute / nccl_baseline is what the compute kernels and the graph buy.
+``sim`` carries the other half of BASELINE's metric (makespan per scheduler): the UNMODIFIED reference
+simulator from ``baseline/_ref`` driven through its own ``run_sim.py`` next to this simulator on the same
+trace and seed — wall time of both, makespans, and whether the two cluster.csv files are byte-identical.
+``--impl reference`` runs only the reference: it has no execution path, so it reports the samples/s metric as
+unavailable and emits the same ``sim`` keys.
 """
 from __future__ import annotations
 
@@ -42,19 +51,36 @@ def parse_args() -> argparse.Namespace:
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (weak scaling)")
     ap.add_argument("--bucket-mb", type=float, default=8.0)
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--skip-nccl", action="store_true", help="do not run the NCCL baseline arm")
+    ap.add_argument("--skip-nccl", action="store_true", help="do not run the NCCL baseline arms")
+    ap.add_argument("--skip-sim", action="store_true", help="do not run the simulator comparison")
     return ap.parse_args()
 
 
+def sim_block(ours: bool, reference: bool):
+    """Simulator comparison (rank 0 only, CPU): see tiresias_b200/utils/refsim.py."""
+    try:
+        from tiresias_b200.utils import refsim
+        return refsim.compare(ours=ours, reference=reference)
+    except Exception as e:  # noqa: BLE001 - context for the headline, never a reason to lose it
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+
 def reference_arm(args: argparse.Namespace) -> None:
-    # Install outcome: `pip install --target baseline/_ref /root/reference` fails with
-    # "Neither 'setup.py' nor 'pyproject.toml' found"; beyond packaging, the reference has no
-    # code path that executes a model, so samples/s cannot be produced by it at all.
-    print(json.dumps({
+    # Install outcome (DESIGN.md section 2): `pip install --target baseline/_ref /root/reference` fails with
+    # "Neither 'setup.py' nor 'pyproject.toml' found", so baseline/_ref is an untouched copy of the tree. The
+    # reference has no code path that executes a model (CPU-only scheduling simulator), so the samples/s
+    # metric cannot be produced by it; what it CAN produce — makespan per scheduler through its own
+    # run_sim.py — is measured here.
+    line = {
         "impl": "reference",
-        "unavailable": "reference is a CPU-only scheduling simulator with no training/execution "
-                       "path (no samples/s metric) and no setup.py/pyproject.toml to install",
-    }))
+        "unavailable": "reference is a CPU-only scheduling simulator with no training/execution path: it cannot "
+                       "produce samples/s (and has no setup.py/pyproject.toml; baseline/_ref is an unmodified copy)",
+        "metric": f"{args.model}_ps_sync_sgd_samples_per_s", "value": None, "n_gpus": args.gpus,
+    }
+    if int(os.environ.get("RANK", "0")) == 0:
+        if not args.skip_sim:
+            line["sim"] = sim_block(ours=False, reference=True)
+        print(json.dumps(line))
 
 
 def init_dist(args: argparse.Namespace):
@@ -96,7 +122,7 @@ def timed_region(fn_step, steps: int, device, sampler=None):
     return float(ms.item()), wall, clocks
 
 
-def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, world: int):
+def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, world: int, same_compute: bool = False):
     import torch
     from tiresias_b200.models import zoo
     from tiresias_b200.ops import native
@@ -106,7 +132,7 @@ def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, wor
     device = torch.device("cuda", local_rank)
     spec = zoo.resolve(args.model)
     trainer = Trainer(spec, args.batch, mode=mode, bucket_mb=args.bucket_mb,
-                      use_graph=not args.no_graph, device=device)
+                      use_graph=not args.no_graph, device=device, nccl_same_compute=same_compute)
     # distinct pinned host batches so every step's H2D copy moves fresh bytes
     host = [zoo.synthetic_batch(spec, args.batch, pinned=True, seed=1000 * rank + i) for i in range(4)]
 
@@ -132,7 +158,7 @@ def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, wor
         cur.wait_stream(trainer.copy_stream)
 
     # warm-up through the public API: covers allocator growth, cuDNN autotune and graph capture
-    e2e(max(args.warmup, 5 if trainer.use_graph and mode != "nccl" else args.warmup))
+    e2e(max(args.warmup, 5 if trainer.use_graph and (mode != "nccl" or same_compute) else args.warmup))
     if trainer.check_status() != 0:
         raise SystemExit("in-kernel wait timed out during warm-up")
 
@@ -167,10 +193,17 @@ def main() -> None:
     import torch.distributed as dist
     rank, local_rank, world = init_dist(args)
     mode = {"ours": "ps", "nccl": "nccl", "ring": "ring"}[args.impl]
+    sim = None
+    if rank == 0 and args.impl == "ours" and not args.skip_sim:
+        sim = sim_block(ours=True, reference=True)     # CPU only; the other ranks wait at the first barrier
     res = run_arm(mode, args, rank, local_rank, world)
-    base, base_error = None, None
+    base, fair, base_error = None, None, None
     if args.impl == "ours" and not args.skip_nccl:
-        # the PyTorch + NCCL arm is context for the headline number, never a reason to lose it
+        # the PyTorch + NCCL arms are context for the headline number, never a reason to lose it
+        try:
+            fair = run_arm("nccl", args, rank, local_rank, world, same_compute=True)
+        except Exception as e:  # noqa: BLE001
+            base_error = f"nccl_same_compute: {type(e).__name__}: {e}"[:300]
         try:
             base = run_arm("nccl", args, rank, local_rank, world)
         except Exception as e:  # noqa: BLE001
@@ -202,13 +235,24 @@ def main() -> None:
         }
         if base is not None:
             line["nccl_baseline"] = {
+                "what": "stock PyTorch network (nn.BatchNorm2d, cuDNN/cuBLAS), eager, NCCL reduce_scatter + torch SGD + all_gather",
                 "value": round(base["value"], 2), "ms_per_step": round(base["ms_per_step"], 4),
                 "e2e_value": round(base["e2e_value"], 2),
                 "speedup_device": round(res["value"] / base["value"], 4),
                 "speedup_e2e": round(res["e2e_value"] / base["e2e_value"], 4),
             }
+        if fair is not None:
+            line["nccl_same_compute"] = {
+                "what": "same fused network, gradient packing, SGD kernel and CUDA graph as ours; only the collectives are NCCL",
+                "value": round(fair["value"], 2), "ms_per_step": round(fair["ms_per_step"], 4),
+                "e2e_value": round(fair["e2e_value"], 2), "cuda_graph": fair["graph"],
+                "speedup_device": round(res["value"] / fair["value"], 4),
+                "speedup_e2e": round(res["e2e_value"] / fair["e2e_value"], 4),
+            }
         if base_error is not None:
-            line["nccl_baseline"] = {"error": base_error}
+            line["nccl_error"] = base_error
+        if sim is not None:
+            line["sim"] = sim
         print(json.dumps(line))
         sys.stdout.flush()
     dist.barrier()

@@ -261,6 +261,17 @@ def conv_cases(iters):
                 row.update({"fprop_halo_ms": round(halo, 4), "fprop_halo_max_abs_diff_vs_cudnn": round(herr, 4)})
             except Exception as e:  # noqa: BLE001 - bring-up: report, keep benchmarking
                 row["fprop_halo_error"] = str(e)[:200]
+        if k == 3 and stride == 1 and cout % 64 == 0:
+            # second-generation halo-tile kernel (csrc/conv3x3.cu), with and without the BatchNorm-statistics epilogue
+            try:
+                c3, _ = timeit(lambda: native.conv3x3_fprop(x, w), iters)
+                c3s, _ = timeit(lambda: native.conv3x3_fprop(x, w, stats=True), iters)
+                c3d, _ = timeit(lambda: native.conv3x3_dgrad(dy, w), iters)
+                err3 = (native.conv3x3_fprop(x, w).float() - y.float()).abs().max().item()
+                row.update({"fprop_c3_ms": round(c3, 4), "fprop_c3_stats_ms": round(c3s, 4), "dgrad_c3_ms": round(c3d, 4),
+                            "fprop_c3_max_abs_diff_vs_cudnn": round(err3, 4), "fprop_c3_tflops": round(flops / c3 / 1e9, 1)})
+            except Exception as e:  # noqa: BLE001
+                row["fprop_c3_error"] = str(e)[:200]
         if stride == 1:
             ours, _ = timeit(lambda: native.conv2d_dgrad(dy, w, x.shape, stride, pad), iters)
             lib, _ = timeit(lambda: aten(dy, x, w, None, [stride] * 2, [pad] * 2, [1, 1], False, [0, 0], 1,

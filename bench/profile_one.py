@@ -16,7 +16,7 @@ from tiresias_b200.ops import native  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv", "halo1", "halo2", "halo3"])
+    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv", "halo1", "halo2", "halo3", "c3_1", "c3_2", "c3_3", "c3_4"])
     args = ap.parse_args()
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
@@ -39,6 +39,12 @@ def main():
         x = torch.randn(256, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         w = (torch.randn(c, c, 3, 3, device=dev) / (3.0 * c ** 0.5)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         run = lambda: native.conv2d_fprop_halo(x, w)  # noqa: E731
+    elif args.kernel.startswith("c3_"):
+        # ResNet-50 3x3 / stride 1 convolutions at batch 256 on the second-generation halo-tile kernel
+        c, hw = {"c3_1": (64, 56), "c3_2": (128, 28), "c3_3": (256, 14), "c3_4": (512, 7)}[args.kernel]
+        x = torch.randn(256, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(c, c, 3, 3, device=dev) / (3.0 * c ** 0.5)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        run = lambda: native.conv3x3_fprop(x, w)  # noqa: E731
     elif args.kernel == "bn":
         from tiresias_b200.ops.batchnorm import fused_bn_act
         x = torch.randn(64, 256, 56, 56, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)

@@ -20,7 +20,23 @@
 #include "common.cuh"
 #include "../include/tiresias_b200.h"
 
+#include <stdlib.h>
+
 using namespace tb200;
+
+// csrc/bn_stream.cu: the TMA-streamed second generation (power-of-two channel counts up to 2048)
+namespace tb200 {
+bool bn_stream_eligible(size_t rows, int C);
+int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamma, const void* beta, int param_dtype,
+                  float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                  float* save_invstd, float* partials, float* coef, const float* conv_partials, int conv_nparts,
+                  size_t rows, int C, int relu, cudaStream_t stream);
+int bn_stream_apply(const void* x, const void* residual, void* y, const float* scale_shift, size_t rows, int C, int relu,
+                    cudaStream_t stream);
+int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta, int param_dtype,
+                  const float* save_mean, const float* save_invstd, void* dx, void* dres, void* dgamma, void* dbeta,
+                  float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream);
+}  // namespace tb200
 
 namespace {
 
@@ -31,7 +47,18 @@ constexpr int kCounterWords = 1024;
 constexpr int kMaxPartialFloats = 2 * 64 * 1024;
 constexpr int kMaxC = 4096;
 constexpr int kCoefFloats = 4 * kMaxC;
-static_assert(TB200_BN_SCRATCH_FLOATS == kCounterWords + kMaxPartialFloats + kCoefFloats, "scratch layout");
+constexpr int kStreamPartialFloats = 2 * 1024 * 1024;   // [<= 3 CTAs x SMs][C <= 2048][2] of the streamed kernels
+static_assert(TB200_BN_SCRATCH_FLOATS == kCounterWords + kMaxPartialFloats + kCoefFloats + kStreamPartialFloats,
+              "scratch layout");
+
+// TB200_BN_STREAM=0 keeps every layer on the first-generation kernels (A/B measurements).
+bool use_stream(size_t rows, int C) {
+  static const bool enabled = [] {
+    const char* e = getenv("TB200_BN_STREAM");
+    return !(e && e[0] == '0');
+  }();
+  return enabled && bn_stream_eligible(rows, C) && (size_t)device_sm_count() * 3 * C * 2 <= (size_t)kStreamPartialFloats;
+}
 
 __device__ __forceinline__ void unpack8(const uint4& r, float (&f)[8]) {
   f[0] = bf16_lo(r.x); f[1] = bf16_hi(r.x); f[2] = bf16_lo(r.y); f[3] = bf16_hi(r.y);
@@ -504,6 +531,10 @@ int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void*
                        float momentum, float eps, float* save_mean, float* save_invstd,
                        float* scratch, size_t rows, int C, int relu, cudaStream_t stream) {
   if (int rc = check_shape("tb200_bn_fwd_train", rows, C)) return rc;
+  if (use_stream(rows, C))
+    return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
+                         save_invstd, scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
+                         scratch + kCounterWords + kMaxPartialFloats, nullptr, 0, rows, C, relu, stream);
   const int groups = (C + kGroup - 1) / kGroup;
   FwdArgs f{};
   f.x = reinterpret_cast<const uint4*>(x);
@@ -527,9 +558,28 @@ int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void*
   return launched();
 }
 
+// Training forward whose batch statistics come from the producing convolution's epilogue (per-channel
+// (sum, sum of squares) partials, csrc/conv3x3.cu / gemm_tcgen05.cu): fold + apply, no statistics pass.
+int tb200_bn_fwd_train_stats(const void* x, const void* residual, void* y, const void* gamma, const void* beta,
+                             int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
+                             float* save_mean, float* save_invstd, float* scratch, const float* conv_partials,
+                             int conv_nparts, size_t rows, int C, int relu, cudaStream_t stream) {
+  if (int rc = check_shape("tb200_bn_fwd_train_stats", rows, C)) return rc;
+  if (!conv_partials || conv_nparts <= 0) return fail("tb200_bn_fwd_train_stats: no statistics partials%s");
+  float* coef = scratch + kCounterWords + kMaxPartialFloats;
+  if (use_stream(rows, C))
+    return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
+                         save_invstd, nullptr, coef, conv_partials, conv_nparts, rows, C, relu, stream);
+  if (int rc = tb200_bn_finalize(conv_partials, conv_nparts, (double)rows, C, gamma, beta, param_dtype, running_mean,
+                                 running_var, momentum, eps, save_mean, save_invstd, coef, stream))
+    return rc;
+  return tb200_bn_apply(x, residual, y, coef, rows, C, relu, stream);
+}
+
 int tb200_bn_apply(const void* x, const void* residual, void* y, const float* scale_shift,
                    size_t rows, int C, int relu, cudaStream_t stream) {
   if (int rc = check_shape("tb200_bn_apply", rows, C)) return rc;
+  if (use_stream(rows, C)) return bn_stream_apply(x, residual, y, scale_shift, rows, C, relu, stream);
   const int groups = (C + kGroup - 1) / kGroup;
   ApplyArgs ap{};
   ap.x = reinterpret_cast<const uint4*>(x); ap.res = reinterpret_cast<const uint4*>(residual);
@@ -546,6 +596,10 @@ int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma
   if (int rc = check_shape("tb200_bn_bwd", rows, C)) return rc;
   if (relu && !y && !beta) return fail("tb200_bn_bwd: relu needs the forward output, or beta to recompute it%s");
   if (relu && !y && dres) return fail("tb200_bn_bwd: a layer with a residual input must pass its forward output%s");
+  if (use_stream(rows, C))
+    return bn_stream_bwd(dy, x, y, gamma, beta, param_dtype, save_mean, save_invstd, dx, dres, dgamma, dbeta,
+                         scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
+                         scratch + kCounterWords + kMaxPartialFloats, rows, C, relu, stream);
   const int groups = (C + kGroup - 1) / kGroup;
   BwdArgs b{};
   b.dy = reinterpret_cast<const uint4*>(dy); b.x = reinterpret_cast<const uint4*>(x);

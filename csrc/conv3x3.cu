@@ -1,0 +1,502 @@
+// 3x3 / stride 1 / pad 1 convolution, forward and input gradient, as a halo-tile implicit GEMM on tcgen05
+// (K5: "convs as implicit GEMM on the same mainloop"; the trace's model zoo is convolutional —
+// /root/reference model/model_factory.py:31-55, per-tensor tables core/models.py:8-20).
+//
+//   y[n,h,w,k] = sum_{r,s,c} x[n, h+r-1, w+s-1, c] * wt[k,r,s,c]          x, y NHWC bf16, fp32 accumulation
+//
+// Second generation of csrc/conv_halo.cu. What the first one measured on B200 (profiles/conv_r2a.md): the
+// numerics were right, but the tensor pipe sat idle 65-79 % of the time because the single MMA-issuing thread
+// needed ~640 cycles of integer divisions, descriptor construction and per-tap barrier traffic for every 4
+// MMAs. This version
+//   * runs the producer and MMA warps converged, with single-thread instructions under elect.sync, so the
+//     descriptors live in uniform registers; the nine taps are unrolled with compile-time (r, s); all
+//     divisions are multiplications by host-computed reciprocals
+//   * groups the weight tiles of three taps behind one barrier pair (BLOCK_N <= 128)
+//   * lays positions out with a pitch of W+1 / H+1 (the zero column / row between two image rows / images is
+//     shared by both neighbours) instead of a power of two: 3-15 % junk positions at 56x56..14x14 and 31 % at
+//     7x7, where the power-of-two layout wasted 18-31 % and 194 %. Tiles are 128 consecutive positions of that
+//     flat space; the producer fetches the padded rows a tile touches ONCE per 64-channel block (TMA boxes
+//     {64 ch, W+1 px} landing at 128-byte-aligned offsets; out-of-range rows / columns arrive zero-filled =
+//     the padding) and every tap is a descriptor start shifted by ((r-1)*(W+1) + (s-1)) rows
+//   * can emit per-channel sum / sum of squares of the bf16 outputs from the epilogue (BatchNorm statistics),
+//     which removes the statistics pass of the following fused BatchNorm (a full read of the activation)
+//   * dgrad mode: the same kernel over dy with the taps flipped and the forward weight read as MN-major
+//     B slabs (no transposed copy of the weights).
+#include "common.cuh"
+#include "tc_ptx.cuh"
+#include "../include/tiresias_b200.h"
+
+#include <cuda.h>
+#include <mutex>
+
+using namespace tb200;
+using namespace tb200::ptx;
+
+namespace {
+
+constexpr int kC3Threads = 256;
+constexpr int kC3Acc = 2;          // TMEM accumulator stages
+constexpr int kEpiBytes = 4 * 2 * 4096;   // 4 epilogue warps x 2 staging tiles of 32 rows x 128 B
+
+struct C3Params {
+  int N, H, W, C, K;               // batch, image, reduction channels, output channels
+  int Wp, Hp;                      // pitches of the flat padded space: W+1, H+1
+  int NR;                          // padded rows fetched per A stage
+  int cblocks;                     // C / 64
+  int num_m, num_n;
+  int total_pos;                   // N * Hp * Wp
+  unsigned long long mWp, mHp;     // fastdiv multipliers
+  int a_stage_bytes, a_stages;
+  int b_groups;                    // ring depth in groups of taps (1 when resident)
+  int epi_off, bar_off;
+  int resident;                    // all weight tiles of the (single) n block stay in shared memory
+  __nv_bfloat16* y;
+  float* stats;                    // [gridDim.x * 4][K][2] per-channel (sum, sum of squares) partials, or null
+};
+
+template <int BLOCK_N, int TPG, bool DGRAD>
+__global__ void __launch_bounds__(kC3Threads, 1)
+conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w, const C3Params p) {
+  constexpr int kTileBytes = BLOCK_N * 128;               // one (tap, 64-channel block) weight tile
+  constexpr int kGroups = 9 / TPG;
+  constexpr int kTmemCols = kC3Acc * BLOCK_N;
+  static_assert(9 % TPG == 0, "taps per group");
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  const uint32_t a_smem = base;
+  const uint32_t b_smem = base + (uint32_t)(p.a_stages * p.a_stage_bytes);
+  const uint32_t epi_smem = base + (uint32_t)p.epi_off;
+  const uint32_t bar = base + (uint32_t)p.bar_off;
+  auto a_full = [&](int s) { return bar + 8u * s; };
+  auto a_empty = [&](int s) { return bar + 8u * (p.a_stages + s); };
+  auto b_full = [&](int s) { return bar + 8u * (2 * p.a_stages + s); };
+  auto b_empty = [&](int s) { return bar + 8u * (2 * p.a_stages + p.b_groups + s); };
+  const uint32_t t_base = bar + 8u * (2 * p.a_stages + 2 * p.b_groups);
+  auto t_full = [&](int s) { return t_base + 8u * s; };
+  auto t_empty = [&](int s) { return t_base + 8u * (kC3Acc + s); };
+  const uint32_t tmem_slot = t_base + 8u * 2 * kC3Acc;
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_x);
+    prefetch_tensormap(&map_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.a_stages; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
+    for (int s = 0; s < p.b_groups; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
+    for (int s = 0; s < kC3Acc; ++s) { mbar_init(t_full(s), 1); mbar_init(t_empty(s), 4); }
+    mbar_init_fence();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - base));
+
+  // Work items: n block outermost (a CTA's consecutive tiles share the weights).
+  const int items = p.num_m * p.num_n;
+  const uint32_t row_bytes = (uint32_t)p.Wp * 128u;       // one padded row of 64 channels
+
+  // weight tile of (tap t, reduction block cb, n block): forward = box {64 c, BLOCK_N k} of wt[k][t][c];
+  // dgrad = BLOCK_N/64 slabs {64 k_out, 64 c_red} of the forward weight wf[c_red][8-t][k_out] (MN-major)
+  auto load_b_tile = [&](uint32_t dst, uint32_t bar_addr, int t, int cb, int n_blk) {
+    if constexpr (!DGRAD) {
+      tma_load_2d(dst, &map_w, bar_addr, t * p.C + cb * 64, n_blk * BLOCK_N);
+    } else {
+#pragma unroll
+      for (int sl = 0; sl < BLOCK_N / 64; ++sl)
+        tma_load_2d(dst + sl * 8192, &map_w, bar_addr, (8 - t) * p.K + n_blk * BLOCK_N + sl * 64, cb * 64);
+    }
+  };
+
+  if (warp == 0) {
+    // ================= producer (converged warp, one elected lane issues) =================
+    if (p.resident) {
+      if (elect_one()) {
+        mbar_expect_tx(b_full(0), (uint32_t)(9 * p.cblocks) * kTileBytes);
+        for (int cb = 0; cb < p.cblocks; ++cb)
+          for (int t = 0; t < 9; ++t) load_b_tile(b_smem + (uint32_t)(cb * 9 + t) * kTileBytes, b_full(0), t, cb, 0);
+      }
+      __syncwarp();
+    }
+    int as = 0, bg = 0;
+    uint32_t aph = 0, bph = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int m_tile = it % p.num_m, n_blk = it / p.num_m;
+      const uint32_t q0 = (uint32_t)m_tile * 128u;
+      // first padded row the tile's windows touch: floor((q0 - Wp - 1) / Wp), can be -1 or -2 for the first tile
+      const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
+      for (int cb = 0; cb < p.cblocks; ++cb) {
+        mbar_wait(a_empty(as), aph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(a_full(as), (uint32_t)p.NR * row_bytes);
+          int n, hp;
+          if (rho0 < 0) { n = -1; hp = rho0 + p.Hp; }
+          else { n = (int)fastdiv((uint32_t)rho0, p.mHp); hp = rho0 - n * p.Hp; }
+          uint32_t dst = a_smem + (uint32_t)as * p.a_stage_bytes;
+          for (int i = 0; i < p.NR; ++i) {
+            // whole padded row: columns 0..W (column W, row H and images outside [0, N) arrive as zeros)
+            tma_load_4d(dst, &map_x, a_full(as), cb * 64, 0, hp, n);
+            dst += row_bytes;
+            if (++hp == p.Hp) { hp = 0; ++n; }
+          }
+        }
+        __syncwarp();
+        if (++as == p.a_stages) { as = 0; aph ^= 1; }
+        if (!p.resident) {
+#pragma unroll 1
+          for (int g = 0; g < kGroups; ++g) {
+            mbar_wait(b_empty(bg), bph ^ 1);
+            if (elect_one()) {
+              mbar_expect_tx(b_full(bg), TPG * kTileBytes);
+#pragma unroll
+              for (int tt = 0; tt < TPG; ++tt)
+                load_b_tile(b_smem + (uint32_t)(bg * TPG + tt) * kTileBytes, b_full(bg), g * TPG + tt, cb, n_blk);
+            }
+            __syncwarp();
+            if (++bg == p.b_groups) { bg = 0; bph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (converged warp, one elected lane issues) =================
+    constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, 0, DGRAD ? 1 : 0);
+    constexpr uint64_t kBDesc = DGRAD ? kDescMNMajor : kDescKMajor;
+    constexpr uint32_t kBStep = DGRAD ? 128u : 2u;        // 16 reduction elements, in 16-byte units
+    const int wp8 = p.Wp * 8;                             // one padded row, in 16-byte units
+    int as = 0, bg = 0, acc = 0;
+    uint32_t aph = 0, bph = 0, accph = 0;
+    if (p.resident) {
+      mbar_wait(b_full(0), 0);
+      tc_fence_after();
+    }
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int m_tile = it % p.num_m;
+      const uint32_t q0 = (uint32_t)m_tile * 128u;
+      const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
+      // rows between the stage's first position and the tile's first position: in [Wp+1, 2*Wp]
+      const uint32_t woff8 = (uint32_t)((int)q0 - rho0 * p.Wp) * 8u;
+      mbar_wait(t_empty(acc), accph ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BLOCK_N);
+      uint32_t accumulate = 0;
+      for (int cb = 0; cb < p.cblocks; ++cb) {
+        mbar_wait(a_full(as), aph);
+        tc_fence_after();
+        // descriptor (low word) of the window of tap (1, 1): the tile's own positions
+        const uint32_t a_mid = desc_units(a_smem + (uint32_t)as * p.a_stage_bytes) + woff8;
+#pragma unroll
+        for (int g = 0; g < kGroups; ++g) {
+          uint32_t b_units;
+          if (p.resident) {
+            b_units = desc_units(b_smem + (uint32_t)(cb * 9 + g * TPG) * kTileBytes);
+          } else {
+            mbar_wait(b_full(bg), bph);
+            tc_fence_after();
+            b_units = desc_units(b_smem + (uint32_t)(bg * TPG) * kTileBytes);
+          }
+#pragma unroll
+          for (int tt = 0; tt < TPG; ++tt) {
+            constexpr int kUnitsPerTile = kTileBytes / 16;
+            const int t = g * TPG + tt, r = t / 3, s = t % 3;           // compile-time after unrolling
+            const uint32_t a_units = a_mid + (uint32_t)((r - 1) * wp8 + (s - 1) * 8);
+            const uint64_t adesc = kDescKMajor | (uint64_t)a_units;
+            const uint64_t bdesc = kBDesc | (uint64_t)(b_units + (uint32_t)(tt * kUnitsPerTile));
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tc_mma_bf16(tmem_d, adesc + 2u * k, bdesc + kBStep * k, idesc, (k == 0) ? accumulate : 1u);
+            }
+            __syncwarp();
+            accumulate = 1;
+          }
+          if (!p.resident) {
+            if (elect_one()) tc_commit(b_empty(bg));
+            __syncwarp();
+            if (++bg == p.b_groups) { bg = 0; bph ^= 1; }
+          }
+        }
+        if (elect_one()) tc_commit(a_empty(as));
+        __syncwarp();
+        if (++as == p.a_stages) { as = 0; aph ^= 1; }
+      }
+      if (elect_one()) tc_commit(t_full(acc));
+      __syncwarp();
+      if (++acc == kC3Acc) { acc = 0; accph ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue =================
+    // Warp ew owns tile rows [32*ew, +32); lane = row for the TMEM loads. Per 64 output channels:
+    // TMEM -> registers -> bf16 -> swizzled staging tile (32 rows x 128 B) -> (statistics from the staged
+    // bf16 values) -> coalesced 16-byte global stores of the valid rows (4 rows x 128 B per instruction).
+    const int ew = warp - 4;
+    int acc = 0;
+    uint32_t accph = 0;
+    const uint32_t bufs = epi_smem + (uint32_t)(ew * 2) * 4096u;
+    const uint32_t swz = (uint32_t)(lane & 7);
+    constexpr int kChunks = BLOCK_N / 64;
+    float st[kChunks][4];
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
+    int cur_n = -1;
+    auto flush_stats = [&](int n_blk) {
+      const size_t part = (size_t)blockIdx.x * 4 + ew;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        const int k = n_blk * BLOCK_N + c * 64 + 2 * lane;
+        if (k < p.K)
+          *reinterpret_cast<float4*>(p.stats + (part * p.K + k) * 2) = make_float4(st[c][0], st[c][1], st[c][2], st[c][3]);
+        st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
+      }
+    };
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const int m_tile = it % p.num_m, n_blk = it / p.num_m;
+      if (p.stats && n_blk != cur_n) {
+        if (cur_n >= 0) flush_stats(cur_n);
+        cur_n = n_blk;
+      }
+      // this lane's row: flat padded position -> (image, row, column); junk positions get pix = -1
+      const uint32_t q = (uint32_t)m_tile * 128u + (uint32_t)(ew * 32 + lane);
+      const uint32_t rho = fastdiv(q, p.mWp), j = q - rho * (uint32_t)p.Wp;
+      const uint32_t n = fastdiv(rho, p.mHp), h = rho - n * (uint32_t)p.Hp;
+      const bool valid = q < (uint32_t)p.total_pos && j < (uint32_t)p.W && h < (uint32_t)p.H;
+      const int pix = valid ? (int)((n * (uint32_t)p.H + h) * (uint32_t)p.W + j) : -1;
+      const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+      mbar_wait(t_full(acc), accph);
+      tc_fence_after();
+      const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BLOCK_N);
+      int nchunks = (p.K - n_blk * BLOCK_N + 63) / 64;
+      if (nchunks > kChunks) nchunks = kChunks;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        if (c < nchunks) {
+          const int k0 = n_blk * BLOCK_N + c * 64;
+          uint32_t v[64];
+          tc_ld_32x32(tcol + c * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          tc_ld_32x32(tcol + c * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          tc_ld_wait();
+          if (c == nchunks - 1) {
+            // the accumulator has been read: hand the TMEM stage back before the stores
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(t_empty(acc));
+          }
+          const uint32_t buf = bufs + (uint32_t)(c & 1) * 4096u;
+          __syncwarp();                                    // readers of this staging tile (chunk c-2) are done
+          const uint32_t row_addr = buf + (uint32_t)lane * 128u;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(v[8 * u]), __uint_as_float(v[8 * u + 1]));
+            o.y = pack_bf16(__uint_as_float(v[8 * u + 2]), __uint_as_float(v[8 * u + 3]));
+            o.z = pack_bf16(__uint_as_float(v[8 * u + 4]), __uint_as_float(v[8 * u + 5]));
+            o.w = pack_bf16(__uint_as_float(v[8 * u + 6]), __uint_as_float(v[8 * u + 7]));
+            st_shared_16(row_addr + (((uint32_t)u ^ swz) << 4), o);
+          }
+          __syncwarp();
+          if (p.stats) {
+            // lane l sums channels k0 + 2l, +1 over the valid rows: word l of every staged row
+            const uint32_t col = (uint32_t)(lane >> 2), wsel = (uint32_t)(lane & 3) * 4u;
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) {
+              const uint32_t w = ld_shared_4(buf + (uint32_t)rr * 128u + ((col ^ (uint32_t)(rr & 7)) << 4) + wsel);
+              if ((vmask >> rr) & 1u) {
+                const float a = bf16_lo(w), b = bf16_hi(w);
+                st[c][0] += a; st[c][1] = fmaf(a, a, st[c][1]);
+                st[c][2] += b; st[c][3] = fmaf(b, b, st[c][3]);
+              }
+            }
+          }
+          // stores: lane -> (row (lane/8) + 4i, 16-byte unit lane%8)
+          const bool unit_ok = k0 + (int)swz * 8 < p.K;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = (lane >> 3) + 4 * i;
+            const int pr = __shfl_sync(0xffffffffu, pix, rr);
+            const uint4 o = ld_shared_16(buf + (uint32_t)rr * 128u + ((swz ^ (uint32_t)(rr & 7)) << 4));
+            if (pr >= 0 && unit_ok)
+              *reinterpret_cast<uint4*>(p.y + (size_t)pr * p.K + k0 + swz * 8) = o;
+          }
+        }
+      }
+      if (++acc == kC3Acc) { acc = 0; accph ^= 1; }
+    }
+    if (p.stats && cur_n >= 0) flush_stats(cur_n);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+  }
+}
+
+// ---- host ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                             const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                             CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeFn c3_encode() {
+  static EncodeFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeFn>(p);
+  });
+  return fn;
+}
+
+// NHWC bf16 tensor [n,h,w,c] as a 4-D map {c, w, h, n}; box = {64 channels, box_w pixels, 1, 1}.
+int c3_map_nhwc(CUtensorMap* out, const void* base, int n, int h, int w, int c, int box_w) {
+  EncodeFn enc = c3_encode();
+  if (!enc) return fail("cuTensorMapEncodeTiled entry point not available%s");
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_w, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled (NHWC) failed (%s code %ld)", "", (long)r);
+  return 0;
+}
+
+// row-major bf16 [rows, cols], box = {64 cols, box_rows}
+int c3_map_2d(CUtensorMap* out, const void* base, int rows, int cols, int box_rows) {
+  EncodeFn enc = c3_encode();
+  if (!enc) return fail("cuTensorMapEncodeTiled entry point not available%s");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled (weights) failed (%s code %ld)", "", (long)r);
+  return 0;
+}
+
+template <int BLOCK_N, int TPG, bool DGRAD>
+int launch_c3(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* nparts_out, cudaStream_t stream) {
+  constexpr int kSmemMax = 227 * 1024;
+  constexpr int kTile = BLOCK_N * 128;
+  const int row_bytes = p.Wp * 128;
+  p.a_stage_bytes = (p.NR * row_bytes + 1023) / 1024 * 1024;
+  const int fixed = kEpiBytes + 1024;
+  const int resident_bytes = 9 * p.cblocks * kTile;
+  p.resident = (p.num_n == 1 && resident_bytes + 2 * p.a_stage_bytes + fixed <= kSmemMax) ? 1 : 0;
+  int b_bytes;
+  if (p.resident) {
+    p.b_groups = 1;
+    b_bytes = resident_bytes;
+    p.a_stages = (kSmemMax - fixed - b_bytes) / p.a_stage_bytes;
+  } else {
+    // at least two A stages, then as many weight groups as fit (2..4), then a third A stage if there is room
+    p.a_stages = 2;
+    p.b_groups = (kSmemMax - fixed - 2 * p.a_stage_bytes) / (TPG * kTile);
+    const int max_groups = TPG == 1 ? 6 : 3;
+    if (p.b_groups > max_groups) p.b_groups = max_groups;
+    if (p.b_groups < 2) return fail("tb200_conv3x3: tile does not fit shared memory (W %s%ld)", "", p.W);
+    b_bytes = p.b_groups * TPG * kTile;
+    p.a_stages = (kSmemMax - fixed - b_bytes) / p.a_stage_bytes;
+  }
+  if (p.a_stages > 3) p.a_stages = 3;
+  if (p.a_stages < 2) return fail("tb200_conv3x3: tile does not fit shared memory (W %s%ld)", "", p.W);
+  p.epi_off = p.a_stages * p.a_stage_bytes + b_bytes;
+  p.bar_off = p.epi_off + kEpiBytes;
+  const int total = p.bar_off + 1024;
+  auto kern = conv3x3_kernel<BLOCK_N, TPG, DGRAD>;
+  static DeviceOnce configured;
+  if (int rc = ensure_dynamic_smem(configured, kern, kSmemMax)) return rc;
+  const int sms = device_sm_count();
+  const int items = p.num_m * p.num_n;
+  const int grid = items < sms ? items : sms;
+  if (p.stats) {
+    // CTAs that see no tile of some n block leave its slots untouched: start from zero
+    TB_CUDA_OK(cudaMemsetAsync(p.stats, 0, (size_t)grid * 4 * p.K * 2 * sizeof(float), stream));
+    if (nparts_out) *nparts_out = grid * 4;
+  }
+  kern<<<grid, kC3Threads, total, stream>>>(mx, mw, p);
+  return launched();
+}
+
+int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, int c_red, int k_out, bool dgrad,
+                   float* stats, size_t stats_floats, int* nparts_out, cudaStream_t stream) {
+  const char* who = dgrad ? "tb200_conv3x3_dgrad" : "tb200_conv3x3_fprop";
+  if (n <= 0 || h <= 0 || wd <= 0 || c_red <= 0 || k_out <= 0) return fail("%s: empty problem", who);
+  if (c_red % 64) return fail("%s: the reduction channel count (%ld) must be a multiple of 64", who, c_red);
+  if (k_out % 8) return fail("%s: the output channel count (%ld) must be a multiple of 8", who, k_out);
+  if (wd + 1 > 256) return fail("%s: image width %ld exceeds one TMA box (255)", who, wd);
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    TB_CUDA_OK(cudaFree(nullptr));       // binds the primary context to this thread for the driver-API encode
+    ctx_bound = true;
+  }
+  C3Params p{};
+  p.N = n; p.H = h; p.W = wd; p.C = c_red; p.K = k_out;
+  p.Wp = wd + 1; p.Hp = h + 1;
+  const long long total = (long long)n * p.Hp * p.Wp;
+  if (total + 4 * p.Wp >= (1ll << 24) || p.Wp >= 4096 || p.Hp >= 4096)
+    return fail("%s: problem too large for the position arithmetic (%ld positions)", who, (long)total);
+  p.total_pos = (int)total;
+  p.mWp = fastdiv_magic((unsigned)p.Wp);
+  p.mHp = fastdiv_magic((unsigned)p.Hp);
+  p.NR = (3 * p.Wp + 129 + p.Wp - 1) / p.Wp;
+  p.cblocks = c_red / 64;
+  p.num_m = (int)((total + 127) / 128);
+  p.y = reinterpret_cast<__nv_bfloat16*>(y);
+  p.stats = stats;
+  const int block_n = k_out <= 64 ? 64 : (k_out <= 128 ? 128 : 256);
+  p.num_n = (k_out + block_n - 1) / block_n;
+  if (stats) {
+    const int sms = device_sm_count();
+    const long long items = (long long)p.num_m * p.num_n;
+    const size_t need = (size_t)(items < sms ? items : sms) * 4 * k_out * 2;
+    if (stats_floats < need)
+      return fail("%s: statistics buffer too small (%ld floats needed)", who, (long)need);
+  }
+  CUtensorMap mx, mw;
+  if (int rc = c3_map_nhwc(&mx, x, n, h, wd, c_red, p.Wp)) return rc;
+  if (!dgrad) {
+    // wt [k_out][9][c_red] as [k_out rows, 9*c_red cols]
+    if (int rc = c3_map_2d(&mw, w, k_out, 9 * c_red, block_n)) return rc;
+    if (block_n == 64) return launch_c3<64, 3, false>(mx, mw, p, nparts_out, stream);
+    if (block_n == 128) return launch_c3<128, 3, false>(mx, mw, p, nparts_out, stream);
+    return launch_c3<256, 1, false>(mx, mw, p, nparts_out, stream);
+  }
+  // forward weight wf [c_red][9][k_out] as [c_red rows, 9*k_out cols]; boxes of 64 x 64
+  if (int rc = c3_map_2d(&mw, w, c_red, 9 * k_out, 64)) return rc;
+  if (block_n == 64) return launch_c3<64, 3, true>(mx, mw, p, nparts_out, stream);
+  if (block_n == 128) return launch_c3<128, 3, true>(mx, mw, p, nparts_out, stream);
+  return launch_c3<256, 1, true>(mx, mw, p, nparts_out, stream);
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t tb200_conv_stats_floats(int cout) { return (size_t)device_sm_count() * 4 * (size_t)cout * 2; }
+
+int tb200_conv3x3_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, float* stats,
+                        size_t stats_floats, int* nparts, cudaStream_t stream) {
+  return conv3x3_common(x, w, y, n, h, wd, cin, cout, false, stats, stats_floats, nparts, stream);
+}
+
+int tb200_conv3x3_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout,
+                        cudaStream_t stream) {
+  // dx[n,h,w,ci] = sum_{r,s,co} dy[n, h+1-r, w+1-s, co] * wt[co,r,s,ci]: a forward pass over dy (reduction over
+  // cout) with flipped taps whose B tiles are read out of the forward weight as stored
+  return conv3x3_common(dy, w, dx, n, h, wd, cout, cin, true, nullptr, 0, nullptr, stream);
+}
+
+}  // extern "C"

@@ -236,7 +236,15 @@ struct ConvGeom {
   int R, S;          // filter taps
   int cblocks;       // 64-channel blocks per tap of the im2col operand
   int flip;          // mode 1: weights are read as tap (R-1-r, S-1-s) through a 3-D map, MN-major (dgrad)
+  // n / d as (n * ceil(2^40 / d)) >> 40, exact for n * d < 2^40 (host-computed): the producer is ONE thread, and
+  // a hardware-less integer division costs it ~40 dependent instructions — six of them per k-block made the
+  // wgrad producer slower than the MMAs it feeds (profiles/conv_r2a.md)
+  unsigned long long m_plane, m_ow, m_cblocks, m_s;
 };
+
+__device__ __forceinline__ int cdiv40(int n, unsigned long long magic) {
+  return (int)(((unsigned long long)(unsigned)n * magic) >> 40);
+}
 
 struct GemmParams {
   int M, N, K;
@@ -411,18 +419,46 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       int cv_n = 0, cv_h = 0, cv_w = 0;
       if (p.conv.mode == 1) {
         const int pix = m_blk * BLOCK_M, plane = p.conv.OH * p.conv.OW;
-        cv_n = pix / plane;
-        const int rem = pix - cv_n * plane, oh = rem / p.conv.OW;
+        cv_n = cdiv40(pix, p.conv.m_plane);
+        const int rem = pix - cv_n * plane, oh = cdiv40(rem, p.conv.m_ow);
         cv_h = oh * p.conv.stride + p.conv.lower;
         cv_w = (rem - oh * p.conv.OW) * p.conv.stride + p.conv.lower;
+      }
+      // mode 1: (tap row, tap column, channel block) of the first k-block, then advanced incrementally
+      int t_r = 0, t_s = 0, t_cb = 0;
+      if (p.conv.mode == 1) {
+        const int tap = cdiv40(kb0, p.conv.m_cblocks);
+        t_cb = kb0 - tap * p.conv.cblocks;
+        t_r = cdiv40(tap, p.conv.m_s);
+        t_s = tap - t_r * p.conv.S;
+      }
+      // mode 2: the (tap, channel block) of each 64-column slab of this tile does not depend on the k-block
+      int sl_c[BLOCK_N / 64], sl_s[BLOCK_N / 64], sl_r[BLOCK_N / 64];
+      int w_n = 0, w_oh = 0, w_ow = 0;             // mode 2: image / output row / column of the k-block's first pixel
+      if (p.conv.mode == 2) {
+#pragma unroll
+        for (int sl = 0; sl < BLOCK_N / 64; ++sl) {
+          const int blk = (b_row >> 6) + sl;                   // 64-column block index along (tap, c)
+          const int tap = cdiv40(blk, p.conv.m_cblocks), cb = blk - tap * p.conv.cblocks;
+          const int r = cdiv40(tap, p.conv.m_s), sx = tap - r * p.conv.S;
+          // slabs past the last tap (N tail) still have to deliver their bytes: clamp to a valid tap,
+          // the epilogue's store clips those columns
+          const bool in = tap < p.conv.R * p.conv.S;
+          sl_c[sl] = in ? cb * 64 : 0; sl_s[sl] = in ? sx : 0; sl_r[sl] = in ? r : 0;
+        }
+        const int pix = kb0 * BLOCK_K, plane = p.conv.OH * p.conv.OW;
+        w_n = cdiv40(pix, p.conv.m_plane);
+        const int rem = pix - w_n * plane;
+        w_oh = cdiv40(rem, p.conv.m_ow);
+        w_ow = rem - w_oh * p.conv.OW;
       }
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1);
         mbar_expect_tx(full_bar(stage), C::kStageBytes);
         if (p.conv.mode == 1) {
           // reduction block kb = (tap, 64-channel block); taps in (r, s) order like the weight's K axis
-          const int tap = kb / p.conv.cblocks, cb = kb - tap * p.conv.cblocks;
-          const int r = tap / p.conv.S, sx = tap - r * p.conv.S;
+          const int cb = t_cb, r = t_r, sx = t_s;
+          if (++t_cb == p.conv.cblocks) { t_cb = 0; if (++t_s == p.conv.S) { t_s = 0; ++t_r; } }
           tma_load_im2col_4d(a_smem + stage * C::kABytes, &map_a, full_bar(stage), cb * 64, cv_w, cv_h, cv_n,
                              sx, r);
           if (!p.conv.flip) {
@@ -451,21 +487,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         if (p.conv.mode == 2) {
           // wgrad: reduction block kb = 64 consecutive output pixels; each 64-column slab of the tile is
           // one (tap, 64-channel block) of the im2col matrix
-          const int pix = kb * BLOCK_K, plane = p.conv.OH * p.conv.OW;
-          const int n = pix / plane, rem = pix - n * plane, oh = rem / p.conv.OW;
-          const int h = oh * p.conv.stride + p.conv.lower;
-          const int w = (rem - oh * p.conv.OW) * p.conv.stride + p.conv.lower;
+          const int h = w_oh * p.conv.stride + p.conv.lower;
+          const int w = w_ow * p.conv.stride + p.conv.lower;
 #pragma unroll
-          for (int sl = 0; sl < BLOCK_N / 64; ++sl) {
-            const int blk = (b_row >> 6) + sl;                 // 64-column block index along (tap, c)
-            const int tap = blk / p.conv.cblocks, cb = blk - tap * p.conv.cblocks;
-            const int r = tap / p.conv.S, sx = tap - r * p.conv.S;
-            // slabs past the last tap (N tail) still have to deliver their bytes: clamp to a valid tap,
-            // the epilogue's store clips those columns
-            const bool in = tap < p.conv.R * p.conv.S;
-            tma_load_im2col_4d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage),
-                               in ? cb * 64 : 0, w, h, n, in ? sx : 0, in ? r : 0);
-          }
+          for (int sl = 0; sl < BLOCK_N / 64; ++sl)
+            tma_load_im2col_4d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage), sl_c[sl], w, h, w_n,
+                               sl_s[sl], sl_r[sl]);
+          // next k-block starts 64 output pixels further (row-major over ow, oh, n)
+          w_ow += BLOCK_K;
+          while (w_ow >= p.conv.OW) { w_ow -= p.conv.OW; if (++w_oh == p.conv.OH) { w_oh = 0; ++w_n; } }
         } else if (!p.b_mn) {
           tma_load_2d(b_smem + stage * C::kBBytes, bmap, full_bar(stage), kb * BLOCK_K, b_row);
         } else {
@@ -991,7 +1021,17 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   p.M = M; p.N = N; p.K = K;
   p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
   p.a_mn = a_mn; p.b_mn = b_mn;
-  if (conv) p.conv = conv->g;
+  if (conv) {
+    p.conv = conv->g;
+    auto magic40 = [](long long d) { return (unsigned long long)(((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d); };
+    const long long plane = (long long)conv->g.OH * conv->g.OW;
+    if ((double)M * (double)plane >= 1.0e12 && conv->g.mode == 1) return fail("tb200_conv2d: problem too large%s");
+    if ((double)K * (double)plane >= 1.0e12 && conv->g.mode == 2) return fail("tb200_conv2d: problem too large%s");
+    p.conv.m_plane = magic40(plane);
+    p.conv.m_ow = magic40(conv->g.OW);
+    p.conv.m_cblocks = magic40(conv->g.cblocks);
+    p.conv.m_s = magic40(conv->g.S);
+  }
   p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
 

@@ -180,6 +180,26 @@ int tb200_conv2d_wgrad(const void* x, const void* dy, void* dw, int n, int h, in
 int tb200_conv2d_fprop_halo(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout,
                             int R, int S, cudaStream_t stream);
 
+/* ---- 3x3 / stride 1 / pad 1 convolutions as halo-tile implicit GEMMs (csrc/conv3x3.cu; model zoo of
+ * model/model_factory.py:31-55). x [n,h,w,cin], y / dy [n,h,w,cout] NHWC bf16, w [cout,3,3,cin] bf16.
+ * cin % 64 == 0 and cout % 8 == 0 for fprop; cout % 64 == 0 and cin % 8 == 0 for dgrad; w <= 255.
+ * The input rows a 128-position output tile needs are fetched once per 64-channel block and the nine taps
+ * are shifted shared-memory windows of that tile. dgrad reads the forward weight as stored.
+ * `stats` (optional, fprop): the epilogue also writes per-channel (sum, sum of squares) of the bf16 outputs
+ * as *nparts partial rows [nparts][cout][2] (fp32) for tb200_bn_finalize - the statistics pass of a following
+ * BatchNorm comes for free. The buffer must hold tb200_conv_stats_floats(cout) floats.                     */
+size_t tb200_conv_stats_floats(int cout);
+int tb200_conv3x3_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, float* stats,
+                        size_t stats_floats, int* nparts, cudaStream_t stream);
+int tb200_conv3x3_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout,
+                        cudaStream_t stream);
+/* Per-channel statistics partials [nparts][C][2] over `count` values per channel -> batch mean / invstd,
+ * scale_shift = [gamma*invstd | beta - mean*gamma*invstd] for tb200_bn_apply, running statistics (may be NULL).
+ * Summed in double in a fixed order: bitwise reproducible.                                                */
+int tb200_bn_finalize(const float* partials, int nparts, double count, int C, const void* gamma, const void* beta,
+                      int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
+                      float* save_mean, float* save_invstd, float* scale_shift, cudaStream_t stream);
+
 /* Hardware probe for halo-tile convolutions: D[128,64] fp32 = A[shift:shift+128, :] . B^T with A bf16 [256,64],
  * B bf16 [64,64], the A shared-memory descriptor advanced by `shift` 128-byte rows and its matrix-base-offset
  * field set to `base_offset` (bench/probe_shift.py reports which setting reproduces the fp32 product). */
@@ -282,12 +302,18 @@ int tb200_sumsq(const void* x, int dtype, size_t n, float* partials, float* out,
  *   bwd:       g = dy * (y > 0 if relu); dx, dres = g (may be NULL), dgamma, dbeta. For a ReLU layer
  *              WITHOUT residual input, y may be NULL: the mask is then recomputed from x with the
  *              forward's own fp32 fma (needs beta), which saves one activation read per pass.      */
-#define TB200_BN_SCRATCH_FLOATS (1024 + 2 * 64 * 1024 + 4 * 4096)
+#define TB200_BN_SCRATCH_FLOATS (1024 + 2 * 64 * 1024 + 4 * 4096 + 2 * 1024 * 1024)
 size_t tb200_bn_scratch_floats(void);
 int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void* gamma,
                        const void* beta, int param_dtype, float* running_mean, float* running_var,
                        float momentum, float eps, float* save_mean, float* save_invstd,
                        float* scratch, size_t rows, int C, int relu, cudaStream_t stream);
+/* fwd_train whose statistics come from the producing convolution's epilogue (tb200_conv3x3_fprop `stats`):
+ * no statistics pass over x. conv_partials [conv_nparts][C][2] as written by the convolution.            */
+int tb200_bn_fwd_train_stats(const void* x, const void* residual, void* y, const void* gamma, const void* beta,
+                             int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
+                             float* save_mean, float* save_invstd, float* scratch, const float* conv_partials,
+                             int conv_nparts, size_t rows, int C, int relu, cudaStream_t stream);
 int tb200_bn_apply(const void* x, const void* residual, void* y, const float* scale_shift,
                    size_t rows, int C, int relu, cudaStream_t stream);
 int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,

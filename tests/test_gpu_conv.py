@@ -104,3 +104,73 @@ def test_halo_fprop_matches_fp32(cuda_device, shape):
     ref = torch.nn.functional.conv2d(x.float(), w.float(), padding=1)
     assert y.shape == ref.shape
     assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-2), float((y.float() - ref).abs().max())
+
+
+# ---- second-generation halo-tile kernel (csrc/conv3x3.cu): flat padded space with pitch W+1 / H+1 ----------
+C3_SHAPES = [(4, 64, 64, 56), (4, 128, 128, 28), (4, 256, 256, 14), (2, 512, 512, 7), (3, 64, 96, 12),
+             (2, 128, 64, 9), (1, 64, 8, 5), (5, 192, 320, 10), (1, 64, 64, 1)]
+
+
+@pytest.mark.parametrize("shape", C3_SHAPES, ids=lambda s: "x".join(map(str, s)))
+def test_conv3x3_fprop_matches_fp32(cuda_device, shape):
+    from tiresias_b200.ops import native
+    n, cin, cout, hw = shape
+    x, w = _case(cuda_device, n, cin, cout, hw, 3, 1, 1)
+    y, stats = native.conv3x3_fprop(x, w, stats=True)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.conv2d(x.float(), w.float(), padding=1)
+    assert y.shape == ref.shape
+    assert torch.allclose(y.float(), ref, rtol=1e-2, atol=1e-2), float((y.float() - ref).abs().max())
+    # the statistics are those of the bf16 outputs the kernel stored (what a following BatchNorm reads)
+    yf = y.float().permute(1, 0, 2, 3).reshape(cout, -1).double()
+    sums = stats.sums()
+    assert stats.count == n * hw * hw
+    assert torch.allclose(sums[:, 0], yf.sum(1), rtol=1e-4, atol=1e-2), float((sums[:, 0] - yf.sum(1)).abs().max())
+    assert torch.allclose(sums[:, 1], (yf * yf).sum(1), rtol=1e-4, atol=1e-2)
+    y2 = native.conv3x3_fprop(x, w)                       # without the statistics: same output, bit for bit
+    assert torch.equal(y2, y)
+
+
+@pytest.mark.parametrize("shape", C3_SHAPES[:-2], ids=lambda s: "x".join(map(str, s)))
+def test_conv3x3_dgrad_matches_fp32(cuda_device, shape):
+    from tiresias_b200.ops import native
+    n, cin, cout, hw = shape
+    if cout % 64:
+        pytest.skip("dgrad reduces over cout: needs a multiple of 64")
+    x, w = _case(cuda_device, n, cin, cout, hw, 3, 1, 1)
+    xr = x.float().requires_grad_(True)
+    ref_y = torch.nn.functional.conv2d(xr, w.float(), padding=1)
+    dy = (torch.randn_like(ref_y) / 8).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ref_y.backward(dy.float())
+    dx = native.conv3x3_dgrad(dy, w)
+    torch.cuda.synchronize()
+    assert dx.shape == x.shape
+    assert torch.allclose(dx.float(), xr.grad, rtol=1e-2, atol=1e-2), float((dx.float() - xr.grad).abs().max())
+
+
+def test_bn_finalize_from_conv_stats(cuda_device):
+    """conv epilogue statistics -> tb200_bn_finalize -> tb200_bn_apply == batch_norm(conv(x)) of torch."""
+    import ctypes as C
+    from tiresias_b200.ops import native
+    n, cin, cout, hw = 8, 64, 128, 14
+    x, w = _case(cuda_device, n, cin, cout, hw, 3, 1, 1)
+    y, stats = native.conv3x3_fprop(x, w, stats=True)
+    gamma = (torch.rand(cout, device=cuda_device) + 0.5).to(torch.bfloat16)
+    beta = torch.randn(cout, device=cuda_device).to(torch.bfloat16)
+    rm, rv = torch.zeros(cout, device=cuda_device), torch.ones(cout, device=cuda_device)
+    mean, invstd = torch.empty(cout, device=cuda_device), torch.empty(cout, device=cuda_device)
+    coef = torch.empty(2 * cout, device=cuda_device)
+    native.check(native.lib().tb200_bn_finalize(
+        stats.partials.data_ptr(), stats.nparts, float(stats.count), cout, gamma.data_ptr(), beta.data_ptr(),
+        native.BF16, rm.data_ptr(), rv.data_ptr(), 0.1, 1e-5, mean.data_ptr(), invstd.data_ptr(), coef.data_ptr(),
+        native.stream_ptr()))
+    torch.cuda.synchronize()
+    yf = y.float()
+    ref_mean = yf.mean((0, 2, 3))
+    ref_var = yf.var((0, 2, 3), unbiased=False)
+    assert torch.allclose(mean, ref_mean, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(invstd, torch.rsqrt(ref_var + 1e-5), rtol=1e-4, atol=1e-5)
+    assert torch.allclose(rm, 0.1 * ref_mean, rtol=1e-4, atol=1e-6)
+    assert torch.allclose(rv, 0.9 + 0.1 * yf.var((0, 2, 3), unbiased=True), rtol=1e-4, atol=1e-6)
+    assert torch.allclose(coef[:cout], gamma.float() * invstd, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(coef[cout:], beta.float() - mean * gamma.float() * invstd, rtol=1e-5, atol=1e-5)

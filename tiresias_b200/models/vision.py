@@ -28,7 +28,7 @@ import os
 # gradient, weight gradient; "1" = everything; see ops.conv._parse_ops). TB200_TC_CONV1X1=1 is the older
 # spelling of "p:fdw".
 TC_CONV1X1 = os.environ.get("TB200_TC_CONV1X1", "0") == "1"
-TC_CONV = _parse_ops(os.environ.get("TB200_TC_CONV", ""))
+TC_CONV = _parse_ops(os.environ.get("TB200_TC_CONV", "1"))
 if TC_CONV1X1:
     TC_CONV["p"] = set("fdw")
 
@@ -62,7 +62,7 @@ def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0, fused: boo
     if fused and TC_CONV["p"] and k == 1 and stride == 1 and pad == 0 and cin % 8 == 0 and cout % 8 == 0:
         return TcConv1x1(cin, cout, TC_CONV["p"])
     if fused and TC_CONV["k"] and not (k == 1 and stride == 1) and cin % 64 == 0 and cout % 8 == 0:
-        return TcConv2d(cin, cout, k, stride, pad, TC_CONV["k"])
+        return TcConv2d(cin, cout, k, stride, pad, TC_CONV["k"], emit_stats=True)
     return nn.Conv2d(cin, cout, k, stride, pad, bias=False)
 
 

@@ -37,7 +37,7 @@ def _rows_channels(x: torch.Tensor):
 
 class _FusedBNFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, momentum, eps, relu):
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, momentum, eps, relu, stats_partials=None):
         x, rows, c = _rows_channels(x)
         if residual is not None:
             residual, _, _ = _rows_channels(residual)
@@ -45,13 +45,17 @@ class _FusedBNFn(torch.autograd.Function):
         save_mean = torch.empty(c, dtype=torch.float32, device=x.device)
         save_invstd = torch.empty(c, dtype=torch.float32, device=x.device)
         scratch = _get_scratch(x.device)
-        native.check(native.lib().tb200_bn_fwd_train(
-            x.data_ptr(), residual.data_ptr() if residual is not None else 0, y.data_ptr(),
-            gamma.data_ptr(), beta.data_ptr(), native.dtype_code(gamma.dtype),
-            running_mean.data_ptr() if running_mean is not None else 0,
-            running_var.data_ptr() if running_var is not None else 0,
-            float(momentum), float(eps), save_mean.data_ptr(), save_invstd.data_ptr(),
-            scratch.data_ptr(), rows, c, int(relu), native.stream_ptr()))
+        common = (x.data_ptr(), residual.data_ptr() if residual is not None else 0, y.data_ptr(),
+                  gamma.data_ptr(), beta.data_ptr(), native.dtype_code(gamma.dtype),
+                  running_mean.data_ptr() if running_mean is not None else 0,
+                  running_var.data_ptr() if running_var is not None else 0,
+                  float(momentum), float(eps), save_mean.data_ptr(), save_invstd.data_ptr(), scratch.data_ptr())
+        if stats_partials is not None:
+            # the producing convolution's epilogue summed x already: fold + apply, no statistics pass
+            native.check(native.lib().tb200_bn_fwd_train_stats(
+                *common, stats_partials.data_ptr(), stats_partials.shape[0], rows, c, int(relu), native.stream_ptr()))
+        else:
+            native.check(native.lib().tb200_bn_fwd_train(*common, rows, c, int(relu), native.stream_ptr()))
         ctx.relu, ctx.has_res, ctx.rows, ctx.c = bool(relu), residual is not None, rows, c
         # the ReLU mask of a layer without residual input is recomputed from x in the backward
         ctx.save_for_backward(x, y if (relu and residual is not None) else None, gamma, beta, save_mean, save_invstd)
@@ -71,16 +75,21 @@ class _FusedBNFn(torch.autograd.Function):
             beta.data_ptr(), native.dtype_code(gamma.dtype), save_mean.data_ptr(), save_invstd.data_ptr(), dx.data_ptr(),
             dres.data_ptr() if dres is not None else 0, dgamma.data_ptr(), dbeta.data_ptr(),
             scratch.data_ptr(), ctx.rows, ctx.c, int(ctx.relu), native.stream_ptr()))
-        return dx, dres, dgamma, dbeta, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
 
 
 def fused_bn_act(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
                  running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
                  residual: Optional[torch.Tensor] = None, relu: bool = False, momentum: float = 0.1,
-                 eps: float = 1e-5) -> torch.Tensor:
-    """Training-mode ``relu?(batch_norm(x) + residual?)`` (bf16 NHWC, CUDA)."""
+                 eps: float = 1e-5, stats=None) -> torch.Tensor:
+    """Training-mode ``relu?(batch_norm(x) + residual?)`` (bf16 NHWC, CUDA). ``stats``: the
+    :class:`native.ConvStats` the convolution that produced ``x`` emitted from its epilogue (skips the
+    statistics pass over ``x``)."""
     assert x.dtype == torch.bfloat16 and x.dim() == 4
-    return _FusedBNFn.apply(x, residual, gamma, beta, running_mean, running_var, momentum, eps, relu)
+    partials = None
+    if stats is not None and stats.count == x.shape[0] * x.shape[2] * x.shape[3] and stats.partials.shape[1] == x.shape[1]:
+        partials = stats.partials
+    return _FusedBNFn.apply(x, residual, gamma, beta, running_mean, running_var, momentum, eps, relu, partials)
 
 
 def bn_apply(x: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor,
@@ -130,7 +139,8 @@ class FusedBatchNormAct(nn.Module):
         if x.is_cuda and x.dtype == torch.bfloat16:
             if self.training:
                 return fused_bn_act(x, self.weight, self.bias, self.running_mean, self.running_var,
-                                    residual, self.relu, self.momentum, self.eps)
+                                    residual, self.relu, self.momentum, self.eps,
+                                    stats=getattr(x, "_tb200_stats", None))
             invstd = torch.rsqrt(self.running_var + self.eps)
             scale = self.weight.float() * invstd
             return bn_apply(x, scale, self.bias.float() - self.running_mean * scale, residual, self.relu)

@@ -116,23 +116,39 @@ def _aten_backward(dy, x, weight, stride, pad, want_dx, want_dw):
 
 
 class _Conv2dFn(torch.autograd.Function):
-    """One convolution whose three passes are individually routed to the tcgen05 implicit GEMM (``ops``
-    names them) or to cuDNN."""
+    """One convolution whose three passes are individually routed to our tcgen05 kernels (``ops`` names them)
+    or to cuDNN. 3x3 / stride 1 / pad 1 forward and input gradient run on the halo-tile kernel
+    (csrc/conv3x3.cu); every other geometry on the im2col-TMA implicit GEMM (csrc/gemm_tcgen05.cu).
+    Returns ``(y, stats_partials)``: with ``want_stats`` the forward's epilogue also emits the per-channel
+    (sum, sum of squares) partials a following fused BatchNorm turns into its batch statistics."""
 
     @staticmethod
-    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int, ops: frozenset) -> torch.Tensor:
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int, ops: frozenset, want_stats: bool):
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         if not weight.is_contiguous(memory_format=torch.channels_last):
             weight = weight.contiguous(memory_format=torch.channels_last)
         ctx.save_for_backward(x, weight)
         ctx.geom = (stride, pad, ops)
+        ctx.halo = weight.shape[2] == 3 and weight.shape[3] == 3 and stride == 1 and pad == 1 and x.shape[3] < 256
+        empty = x.new_empty(0, dtype=torch.float32)
+        ctx.nparts = 0
         if "f" in ops:
-            return native.conv2d_fprop(x, weight, stride, pad)
-        return torch.nn.functional.conv2d(x, weight, stride=stride, padding=pad)
+            if ctx.halo:
+                if want_stats:
+                    y, st = native.conv3x3_fprop(x, weight, stats=True)
+                    ctx.nparts = st.nparts
+                    ctx.mark_non_differentiable(st.partials)
+                    return y, st.partials
+            ctx.mark_non_differentiable(empty)
+            if ctx.halo:
+                return native.conv3x3_fprop(x, weight), empty
+            return native.conv2d_fprop(x, weight, stride, pad), empty
+        ctx.mark_non_differentiable(empty)
+        return torch.nn.functional.conv2d(x, weight, stride=stride, padding=pad), empty
 
     @staticmethod
-    def backward(ctx, dy: torch.Tensor):
+    def backward(ctx, dy: torch.Tensor, _dstats=None):
         x, weight = ctx.saved_tensors
         stride, pad, ops = ctx.geom
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -143,7 +159,7 @@ class _Conv2dFn(torch.autograd.Function):
         own_dw = want_dw and "w" in ops
         dx = dw = None
         if own_dx:
-            dx = native.conv2d_dgrad(dy, weight, x.shape, stride, pad)
+            dx = native.conv3x3_dgrad(dy, weight) if ctx.halo else native.conv2d_dgrad(dy, weight, x.shape, stride, pad)
         if own_dw:
             dw = native.conv2d_wgrad(x, dy, weight.shape[2:], stride, pad)
         if (want_dx and not own_dx) or (want_dw and not own_dw):
@@ -151,7 +167,7 @@ class _Conv2dFn(torch.autograd.Function):
                                                want_dw and not own_dw)
             dx = dx if own_dx else lib_dx
             dw = dw if own_dw else lib_dw
-        return dx, dw, None, None, None
+        return dx, dw, None, None, None, None
 
 
 class TcConv2d(nn.Module):
@@ -161,8 +177,9 @@ class TcConv2d(nn.Module):
     Conv2d. ``ops`` picks the passes that run on our kernels (default: all three)."""
 
     def __init__(self, in_channels: int, out_channels: int, kernel_size: int, stride: int = 1,
-                 padding: int = 0, ops=("f", "d", "w")):
+                 padding: int = 0, ops=("f", "d", "w"), emit_stats: bool = False):
         super().__init__()
+        self.emit_stats = emit_stats          # a fused BatchNorm follows: hand it the epilogue's statistics
         if in_channels % 64 or out_channels % 8:
             raise ValueError("TcConv2d needs in_channels % 64 == 0 and out_channels % 8 == 0")
         self.in_channels, self.out_channels = in_channels, out_channels
@@ -173,7 +190,12 @@ class TcConv2d(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
-            return _Conv2dFn.apply(x, self.weight, self.stride, self.padding, self.ops)
+            want = self.emit_stats and self.training and torch.is_grad_enabled()
+            y, partials = _Conv2dFn.apply(x, self.weight, self.stride, self.padding, self.ops, want)
+            if partials.numel():
+                n, _, h, w = y.shape
+                y._tb200_stats = native.ConvStats(partials, partials.shape[0], n * h * w)
+            return y
         return torch.nn.functional.conv2d(x, self.weight, stride=self.stride, padding=self.padding)
 
     def extra_repr(self) -> str:

@@ -18,7 +18,7 @@ MAX_BUCKETS = 256
 MAX_RING_CTAS = 64
 IPC_HANDLE_BYTES = 64
 FLAG_WORDS = 2 * MAX_BUCKETS * MAX_WORLD + 2 * MAX_RING_CTAS
-BN_SCRATCH_FLOATS = 1024 + 2 * 64 * 1024 + 4 * 4096
+BN_SCRATCH_FLOATS = 1024 + 2 * 64 * 1024 + 4 * 4096 + 2 * 1024 * 1024   # TB200_BN_SCRATCH_FLOATS
 
 F32, BF16 = 0, 1
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
@@ -112,6 +112,17 @@ def _declare(lib: C.CDLL) -> None:
         getattr(lib, fn).restype = ci
     lib.tb200_conv2d_fprop_halo.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, st]
     lib.tb200_conv2d_fprop_halo.restype = ci
+    lib.tb200_conv_stats_floats.argtypes = [ci]
+    lib.tb200_conv_stats_floats.restype = sz
+    lib.tb200_conv3x3_fprop.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp, sz, ip_, st]
+    lib.tb200_conv3x3_fprop.restype = ci
+    lib.tb200_conv3x3_dgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, st]
+    lib.tb200_conv3x3_dgrad.restype = ci
+    lib.tb200_bn_fwd_train_stats.argtypes = [vp, vp, vp, vp, vp, ci, vp, vp, C.c_float, C.c_float, vp, vp, vp, vp, ci,
+                                             sz, ci, ci, st]
+    lib.tb200_bn_fwd_train_stats.restype = ci
+    lib.tb200_bn_finalize.argtypes = [vp, ci, C.c_double, ci, vp, vp, ci, vp, vp, C.c_float, C.c_float, vp, vp, vp, st]
+    lib.tb200_bn_finalize.restype = ci
     lib.tb200_nvls_supported.argtypes = [ci]
     lib.tb200_nvls_supported.restype = ci
     lib.tb200_nvls_selftest.argtypes = [ci, sz, ci, C.c_char_p, sz]
@@ -309,6 +320,57 @@ def conv2d_dgrad_halo(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
     forward pass over dy with the flipped, channel-swapped filter; the filter is rewritten per call, which
     is one small kernel — weights change every step anyway)."""
     return conv2d_fprop_halo(dy, dgrad_weight(weight))
+
+
+class ConvStats:
+    """Per-channel (sum, sum of squares) partials a convolution's epilogue wrote next to its output:
+    ``partials`` fp32 [nparts, C, 2] over ``count`` values per channel. A following fused BatchNorm turns
+    them into its scale / shift with one tiny kernel (``bn_finalize``) instead of re-reading the activation."""
+
+    __slots__ = ("partials", "nparts", "count")
+
+    def __init__(self, partials: torch.Tensor, nparts: int, count: int):
+        self.partials, self.nparts, self.count = partials, nparts, count
+
+    def sums(self) -> torch.Tensor:
+        """[C, 2] totals in fp64 (tests / debugging)."""
+        return self.partials[: self.nparts].double().sum(0)
+
+
+def conv_stats_buffer(cout: int, device) -> torch.Tensor:
+    parts = lib().tb200_conv_stats_floats(cout) // (2 * cout)
+    return torch.empty((parts, cout, 2), dtype=torch.float32, device=device)
+
+
+def conv3x3_fprop(x: torch.Tensor, weight: torch.Tensor, stats: bool = False):
+    """3x3 / stride 1 / pad 1 convolution forward on the halo-tile kernel (tb200_conv3x3_fprop). ``x``
+    [N,Cin,H,W] and ``weight`` [Cout,Cin,3,3] bf16 channels_last. With ``stats`` returns ``(y, ConvStats)``."""
+    assert x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    xv, wv = _nhwc(x), _nhwc(weight)
+    n, h, w, cin = xv.shape
+    cout = wv.shape[0]
+    assert wv.shape[1:] == (3, 3, cin)
+    y = torch.empty((n, h, w, cout), dtype=torch.bfloat16, device=x.device)
+    nparts = C.c_int(0)
+    buf = conv_stats_buffer(cout, x.device) if stats else None
+    check(lib().tb200_conv3x3_fprop(xv.data_ptr(), wv.data_ptr(), y.data_ptr(), n, h, w, cin, cout,
+                                    buf.data_ptr() if stats else 0, buf.numel() if stats else 0,
+                                    C.byref(nparts), stream_ptr()))
+    y = y.permute(0, 3, 1, 2)
+    return (y, ConvStats(buf[: nparts.value], nparts.value, n * h * w)) if stats else y
+
+
+def conv3x3_dgrad(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """Input gradient of a 3x3 / stride 1 / pad 1 convolution (tb200_conv3x3_dgrad): the halo-tile kernel over
+    dy with flipped taps, reading the forward ``weight`` [Cout,Cin,3,3] (channels_last) as stored."""
+    assert dy.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    dyv, wv = _nhwc(dy), _nhwc(weight)
+    n, h, w, cout = dyv.shape
+    cin = wv.shape[3]
+    assert wv.shape[:3] == (cout, 3, 3)
+    dx = torch.empty((n, h, w, cin), dtype=torch.bfloat16, device=dy.device)
+    check(lib().tb200_conv3x3_dgrad(dyv.data_ptr(), wv.data_ptr(), dx.data_ptr(), n, h, w, cin, cout, stream_ptr()))
+    return dx.permute(0, 3, 1, 2)
 
 
 def conv2d_dgrad(dy: torch.Tensor, weight: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:

@@ -19,7 +19,13 @@ job runs for real:
                 634 GB/s bus bandwidth at 2 GPUs vs 529 for NCCL; ``allreduce_algo=0`` is the classic
                 neighbour ring with 2(W-1) flag-synchronised steps.
 ``mode="nccl"``  the baseline named by BASELINE.json: bucketed ``reduce_scatter`` + torch SGD on the
-                shard + ``all_gather`` through NCCL, same model code, same buckets.
+                shard + ``all_gather`` through NCCL, same buckets, the STOCK network (nn.BatchNorm2d,
+                cuDNN / cuBLAS everywhere), eager.
+                ``nccl_same_compute=True`` is the like-for-like arm: the SAME fused network, gradient packing,
+                optimizer kernel and CUDA-graph capture as ``ps``; only the communication differs (NCCL
+                ``reduce_scatter`` -> ``tb200_sgd_momentum`` on the shard -> NCCL ``all_gather`` instead of the
+                fused push/pull kernel). The gap between that arm and ``ps`` is what the in-kernel push/pull
+                buys; the gap between the two NCCL arms is what the compute kernels buy.
 """
 from __future__ import annotations
 
@@ -115,10 +121,11 @@ class Trainer:
                  pull_gemm: bool = True, pull_min_mb: float = 4.0, comm_ctas: int = 32,
                  spin_budget: int = 50_000_000, seed: int = 0, device: Optional[torch.device] = None,
                  model: Optional[nn.Module] = None, allreduce_algo: Optional[int] = None, comm_group=None,
-                 stem_pad8: bool = False, nvls: Optional[bool] = None):
+                 stem_pad8: bool = False, nvls: Optional[bool] = None, nccl_same_compute: bool = False):
         if mode not in ("ps", "ring", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
         self.spec, self.mode, self.batch_size = spec, mode, batch_size
+        self.nccl_same_compute = bool(nccl_same_compute) and mode == "nccl"
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.symm = world if world is not None else SymmetricWorld.from_env(self.device)
         self.world, self.rank = self.symm.world, self.symm.rank
@@ -138,13 +145,14 @@ class Trainer:
         torch.manual_seed(seed)           # identical initial weights on every rank
         with torch.device(self.device):
             # the NCCL arm is the stock-PyTorch network (nn.BatchNorm2d / nn.Linear, cuDNN + cuBLAS)
-            self.model = (model if model is not None else zoo_build(spec, fused=(mode != "nccl"))).to(self.device)
+            self.model = (model if model is not None else
+                          zoo_build(spec, fused=(mode != "nccl" or self.nccl_same_compute))).to(self.device)
         self.model.train()
         self.buckets, self.total = plan_buckets(
             self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
             allow_pull=(pull_gemm and mode == "ps"))
 
-        self.pack_grads = mode != "nccl"
+        self.pack_grads = mode != "nccl" or self.nccl_same_compute
         self._grad_view: Dict[int, torch.Tensor] = {}
         self._alloc_state()
         self._flatten_model()
@@ -154,6 +162,7 @@ class Trainer:
         self.stream = torch.cuda.Stream(self.device)
         self.comm_stream = torch.cuda.Stream(self.device)
         self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graph_failed = False
         self._steps = 0
         self.native_per_step = 0
         self.native_launches = 0
@@ -371,6 +380,17 @@ class Trainer:
         else:
             b._shard_grad.copy_(g[:n])
         base = self._shard_base[b.index]
+        if self.nccl_same_compute:
+            # same optimizer kernel as the ring / ps paths: only the collectives come from NCCL
+            native.check(self._lib.tb200_sgd_momentum(
+                self.master.data_ptr() + 4 * base, self.mom.data_ptr() + 4 * base, b._shard_grad.data_ptr(), native.BF16,
+                b._shard_param.data_ptr(), native.BF16, n, self.hyper.data_ptr(), native.stream_ptr(self.comm_stream)))
+            p = self.param_flat[b.offset: b.offset + b.length]
+            if dist.is_initialized() and self.world > 1:
+                dist.all_gather_into_tensor(p, b._shard_param, group=self.comm_group)
+            else:
+                p[:n].copy_(b._shard_param)
+            return
         m, v = self.master[base: base + n], self.mom[base: base + n]
         # plain torch SGD(momentum, weight decay) on the fp32 master shard
         grad = b._shard_grad.float().mul_(1.0 / self.world).add_(m, alpha=self.weight_decay)
@@ -461,12 +481,18 @@ class Trainer:
 
     def _advance(self) -> None:
         """Run one device-side step on ``self.stream`` (eager, or capture-then-replay)."""
-        graphable = self.use_graph and self.mode != "nccl"
+        graphable = self.use_graph and (self.mode != "nccl" or self.nccl_same_compute) and not self._graph_failed
         if graphable and self._graph is None and self._steps >= 3:
             torch.cuda.synchronize(self.device)
             self.symm.barrier()
             before = native.launch_count()
-            self._capture()
+            try:
+                self._capture()
+            except Exception:  # noqa: BLE001 - NCCL builds that cannot be captured: stay eager, say so
+                if self.mode != "nccl":
+                    raise
+                self._graph, self._graph_failed = None, True
+                torch.cuda.synchronize(self.device)
             self.native_per_step = native.launch_count() - before
         if graphable and self._graph is not None:
             self._graph.replay()
