@@ -83,8 +83,9 @@ def main():
         from tiresias_b200.models import zoo
         from tiresias_b200.parallel.trainer import Trainer
         spec = zoo.resolve("resnet50")
-        tr = Trainer(spec, batch_size=64, mode="ps", use_graph=False, device=dev)
-        x, y = zoo.synthetic_batch(spec, 64)
+        bs = int(os.environ.get("TB200_PROFILE_BATCH", "64"))
+        tr = Trainer(spec, batch_size=bs, mode="ps", use_graph=False, device=dev)
+        x, y = zoo.synthetic_batch(spec, bs)
 
         def run():
             tr.step(x, y)

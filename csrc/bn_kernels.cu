@@ -30,12 +30,13 @@ bool bn_stream_eligible(size_t rows, int C);
 int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamma, const void* beta, int param_dtype,
                   float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                   float* save_invstd, float* partials, float* coef, const float* conv_partials, int conv_nparts,
-                  size_t rows, int C, int relu, cudaStream_t stream);
+                  size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters);
 int bn_stream_apply(const void* x, const void* residual, void* y, const float* scale_shift, size_t rows, int C, int relu,
                     cudaStream_t stream);
 int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta, int param_dtype,
                   const float* save_mean, const float* save_invstd, void* dx, void* dres, void* dgamma, void* dbeta,
-                  float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream);
+                  float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp,
+                  unsigned* counters);
 }  // namespace tb200
 
 namespace {
@@ -534,7 +535,8 @@ int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void*
   if (use_stream(rows, C))
     return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
                          save_invstd, scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
-                         scratch + kCounterWords + kMaxPartialFloats, nullptr, 0, rows, C, relu, stream);
+                         scratch + kCounterWords + kMaxPartialFloats, nullptr, 0, rows, C, relu, stream,
+                         scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch));
   const int groups = (C + kGroup - 1) / kGroup;
   FwdArgs f{};
   f.x = reinterpret_cast<const uint4*>(x);
@@ -569,7 +571,8 @@ int tb200_bn_fwd_train_stats(const void* x, const void* residual, void* y, const
   float* coef = scratch + kCounterWords + kMaxPartialFloats;
   if (use_stream(rows, C))
     return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
-                         save_invstd, nullptr, coef, conv_partials, conv_nparts, rows, C, relu, stream);
+                         save_invstd, nullptr, coef, conv_partials, conv_nparts, rows, C, relu, stream,
+                         scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch));
   if (int rc = tb200_bn_finalize(conv_partials, conv_nparts, (double)rows, C, gamma, beta, param_dtype, running_mean,
                                  running_var, momentum, eps, save_mean, save_invstd, coef, stream))
     return rc;
@@ -599,7 +602,8 @@ int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma
   if (use_stream(rows, C))
     return bn_stream_bwd(dy, x, y, gamma, beta, param_dtype, save_mean, save_invstd, dx, dres, dgamma, dbeta,
                          scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
-                         scratch + kCounterWords + kMaxPartialFloats, rows, C, relu, stream);
+                         scratch + kCounterWords + kMaxPartialFloats, rows, C, relu, stream, scratch + kCounterWords,
+                         reinterpret_cast<unsigned*>(scratch));
   const int groups = (C + kGroup - 1) / kGroup;
   BwdArgs b{};
   b.dy = reinterpret_cast<const uint4*>(dy); b.x = reinterpret_cast<const uint4*>(x);

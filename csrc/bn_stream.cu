@@ -14,7 +14,7 @@
 // A CTA owns a contiguous row range (all channels), so its traffic is one sequential stream per tensor. Thread
 // t of the 256 consumers always sees the same 8 channels (vector column t % (C/8)), which keeps the
 // per-channel coefficients in registers. Reductions write per-CTA partials that a small second kernel folds in
-// a fixed order in double precision: results are bitwise reproducible.
+// a fixed order (compensated fp32 sums): results are bitwise reproducible.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 #include "../include/tiresias_b200.h"
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(kBlock, 2) bn_bwd_apply_stream_kernel(const St
   });
 }
 
-// ---- second pass of the reductions: fold the per-CTA partials (fixed order, double precision) -------------
+// ---- second pass of the reductions: fold the per-CTA partials (fixed order) -------------------------------
 struct FoldArgs {
   const float* partials;      // [nparts][C][2]
   int nparts, C;
@@ -298,28 +298,40 @@ struct FoldArgs {
   const float* invstd_in;     // backward: the forward's invstd
 };
 
+// 64 channels x 16 slices per CTA. Each thread folds every 16th partial of its channel with compensated (Kahan)
+// fp32 sums — double-precision adds and float->double conversions run at a small fraction of the fp32 rate on
+// B200 and made a first version of this 4-CTA kernel take longer (36 us) than the statistics pass it finishes —
+// then the 16 slice results are combined in slice order. Only the last handful of operations per channel
+// (mean, E[x^2] - mean^2) use double. The order is a function of nparts only: bitwise reproducible.
+constexpr int kFoldSlices = 16;
+
 template <bool BWD>
-__global__ void __launch_bounds__(256) bn_fold_kernel(const FoldArgs a) {
-  __shared__ double sh[2][4][64];
+__global__ void __launch_bounds__(64 * kFoldSlices) bn_fold_kernel(const FoldArgs a) {
+  __shared__ float sh[2][kFoldSlices][64];
   const int chl = threadIdx.x % 64, slice = threadIdx.x / 64;
   const int ch = blockIdx.x * 64 + chl;
-  double s = 0.0, q = 0.0;
+  float s = 0.f, cs = 0.f, q = 0.f, cq = 0.f;
   if (ch < a.C) {
-    for (int part = slice; part < a.nparts; part += 4) {
-      const float2 v = __ldg(reinterpret_cast<const float2*>(a.partials + ((size_t)part * a.C + ch) * 2));
-      s += (double)v.x;
-      q += (double)v.y;
+    const float2* p = reinterpret_cast<const float2*>(a.partials) + ch;
+#pragma unroll 4
+    for (int part = slice; part < a.nparts; part += kFoldSlices) {
+      const float2 v = __ldg(p + (size_t)part * a.C);
+      float y = v.x - cs, t = s + y;
+      cs = (t - s) - y; s = t;
+      y = v.y - cq; t = q + y;
+      cq = (t - q) - y; q = t;
     }
   }
   sh[0][slice][chl] = s;
   sh[1][slice][chl] = q;
   __syncthreads();
   if (slice != 0 || ch >= a.C) return;
-  s = (sh[0][0][chl] + sh[0][1][chl]) + (sh[0][2][chl] + sh[0][3][chl]);
-  q = (sh[1][0][chl] + sh[1][1][chl]) + (sh[1][2][chl] + sh[1][3][chl]);
+  double S = 0.0, Q = 0.0;
+#pragma unroll
+  for (int i = 0; i < kFoldSlices; ++i) { S += (double)sh[0][i][chl]; Q += (double)sh[1][i][chl]; }
   if constexpr (!BWD) {
-    const double mean = s / a.count;
-    double var = q / a.count - mean * mean;
+    const double mean = S / a.count;
+    double var = Q / a.count - mean * mean;
     if (var < 0.0) var = 0.0;
     const float invstd = rsqrtf((float)var + a.eps);
     a.save_mean[ch] = (float)mean;
@@ -333,12 +345,96 @@ __global__ void __launch_bounds__(256) bn_fold_kernel(const FoldArgs a) {
       a.running_var[ch] = (1.f - a.momentum) * a.running_var[ch] + a.momentum * (float)unbiased;
     }
   } else {
-    store_param(a.dbeta, a.param_dtype, ch, (float)s);
-    store_param(a.dgamma, a.param_dtype, ch, (float)q);
+    store_param(a.dbeta, a.param_dtype, ch, (float)S);
+    store_param(a.dgamma, a.param_dtype, ch, (float)Q);
     a.coef[ch] = load_param(a.gamma, a.param_dtype, ch) * a.invstd_in[ch];
-    a.coef[a.C + ch] = (float)(s / a.count);
-    a.coef[2 * a.C + ch] = (float)(q / a.count);
+    a.coef[a.C + ch] = (float)(S / a.count);
+    a.coef[2 * a.C + ch] = (float)(Q / a.count);
   }
+}
+
+// Two-level variant for the hot path (53 + 53 launches per ResNet-50 step): the single-level kernel above walks
+// 444-592 partials per channel with 16 slices, i.e. ~37 dependent global-load round trips per thread, and took
+// 9-15 us per call on B200 — latency, not bandwidth. Here grid.y CTAs each fold a 128-part range of one 64-channel
+// group (every thread issues its 8 loads at once), write one combined row to `tmp`, and the CTA that arrives last
+// at the group's counter folds the grid.y rows in index order and finishes the channel. The order is a function
+// of nparts only, whichever CTA arrives last: bitwise reproducible.
+constexpr int kFoldRange = kFoldSlices * 8;      // partials per CTA
+
+template <bool BWD>
+__global__ void __launch_bounds__(64 * kFoldSlices) bn_fold2_kernel(const FoldArgs a, float* __restrict__ tmp,
+                                                                    unsigned* __restrict__ counters) {
+  __shared__ float sh[2][kFoldSlices][64];
+  __shared__ int s_last;
+  const int chl = threadIdx.x % 64, slice = threadIdx.x / 64;
+  const int ch = blockIdx.x * 64 + chl;
+  const int p0 = blockIdx.y * kFoldRange;
+  float s = 0.f, q = 0.f;
+  if (ch < a.C) {
+    const float2* p = reinterpret_cast<const float2*>(a.partials) + ch;
+    float2 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int part = p0 + slice + u * kFoldSlices;
+      v[u] = part < a.nparts ? __ldg(p + (size_t)part * a.C) : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { s += v[u].x; q += v[u].y; }
+  }
+  sh[0][slice][chl] = s;
+  sh[1][slice][chl] = q;
+  __syncthreads();
+  if (slice == 0 && ch < a.C) {
+    float S = 0.f, Q = 0.f;
+#pragma unroll
+    for (int i = 0; i < kFoldSlices; ++i) { S += sh[0][i][chl]; Q += sh[1][i][chl]; }
+    reinterpret_cast<float2*>(tmp)[(size_t)blockIdx.y * a.C + ch] = make_float2(S, Q);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(counters + blockIdx.x, 1u);
+    s_last = (prev == gridDim.y - 1);
+    if (s_last) counters[blockIdx.x] = 0;          // self-resetting: ready for the next launch on the stream
+  }
+  __syncthreads();
+  if (!s_last || slice != 0 || ch >= a.C) return;
+  __threadfence();
+  double S = 0.0, Q = 0.0;
+  for (unsigned g = 0; g < gridDim.y; ++g) {
+    const float2 v = __ldcg(reinterpret_cast<const float2*>(tmp) + (size_t)g * a.C + ch);
+    S += (double)v.x;
+    Q += (double)v.y;
+  }
+  if constexpr (!BWD) {
+    const double mean = S / a.count;
+    double var = Q / a.count - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float invstd = rsqrtf((float)var + a.eps);
+    a.save_mean[ch] = (float)mean;
+    a.save_invstd[ch] = invstd;
+    const float scale = load_param(a.gamma, a.param_dtype, ch) * invstd;
+    a.coef[ch] = scale;
+    a.coef[a.C + ch] = load_param(a.beta, a.param_dtype, ch) - (float)mean * scale;
+    if (a.running_mean) {
+      const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
+      a.running_mean[ch] = (1.f - a.momentum) * a.running_mean[ch] + a.momentum * (float)mean;
+      a.running_var[ch] = (1.f - a.momentum) * a.running_var[ch] + a.momentum * (float)unbiased;
+    }
+  } else {
+    store_param(a.dbeta, a.param_dtype, ch, (float)S);
+    store_param(a.dgamma, a.param_dtype, ch, (float)Q);
+    a.coef[ch] = load_param(a.gamma, a.param_dtype, ch) * a.invstd_in[ch];
+    a.coef[a.C + ch] = (float)(S / a.count);
+    a.coef[2 * a.C + ch] = (float)(Q / a.count);
+  }
+}
+
+template <bool BWD>
+int launch_fold(const FoldArgs& f, float* tmp, unsigned* counters, cudaStream_t stream) {
+  const dim3 grid((f.C + 63) / 64, (f.nparts + kFoldRange - 1) / kFoldRange);
+  bn_fold2_kernel<BWD><<<grid, 64 * kFoldSlices, 0, stream>>>(f, tmp, counters);
+  return launched();
 }
 
 // ---- host -------------------------------------------------------------------------------------------------
@@ -386,7 +482,7 @@ int bn_stream_max_parts() { return device_sm_count() * 3; }
 int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamma, const void* beta, int param_dtype,
                   float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                   float* save_invstd, float* partials, float* coef, const float* conv_partials, int conv_nparts,
-                  size_t rows, int C, int relu, cudaStream_t stream) {
+                  size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters) {
   FoldArgs f{};
   f.C = C; f.count = (double)rows; f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype;
   f.running_mean = running_mean; f.running_var = running_var; f.momentum = momentum; f.eps = eps;
@@ -407,8 +503,7 @@ int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamm
     f.partials = partials;
     f.nparts = grid;
   }
-  bn_fold_kernel<false><<<(C + 63) / 64, 256, 0, stream>>>(f);
-  if (int rc = launched()) return rc;
+  if (int rc = launch_fold<false>(f, fold_tmp, counters, stream)) return rc;
   StreamArgs ap{};
   int grid = 0;
   ap.in[0] = reinterpret_cast<const uint8_t*>(x);
@@ -447,7 +542,8 @@ int bn_stream_apply(const void* x, const void* residual, void* y, const float* s
 
 int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta, int param_dtype,
                   const float* save_mean, const float* save_invstd, void* dx, void* dres, void* dgamma, void* dbeta,
-                  float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream) {
+                  float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp,
+                  unsigned* counters) {
   const int mask = !relu ? 0 : (y ? 1 : 2);
   StreamArgs a{};
   int grid = 0;
@@ -476,8 +572,7 @@ int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamm
   f.partials = partials; f.nparts = grid; f.C = C; f.count = (double)rows;
   f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype; f.coef = coef;
   f.dgamma = dgamma; f.dbeta = dbeta; f.invstd_in = save_invstd;
-  bn_fold_kernel<true><<<(C + 63) / 64, 256, 0, stream>>>(f);
-  if (int rc2 = launched()) return rc2;
+  if (int rc2 = launch_fold<true>(f, fold_tmp, counters, stream)) return rc2;
   a.out[0] = reinterpret_cast<uint4*>(dx);
   a.out[1] = reinterpret_cast<uint4*>(dres);
 #define TB_BWD_APPLY(M, D, NINV)                                                                              \
@@ -504,6 +599,6 @@ extern "C" int tb200_bn_finalize(const float* partials, int nparts, double count
   f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype;
   f.running_mean = running_mean; f.running_var = running_var; f.momentum = momentum; f.eps = eps;
   f.save_mean = save_mean; f.save_invstd = save_invstd; f.coef = scale_shift;
-  bn_fold_kernel<false><<<(C + 63) / 64, 256, 0, stream>>>(f);
+  bn_fold_kernel<false><<<(C + 63) / 64, 64 * kFoldSlices, 0, stream>>>(f);
   return launched();
 }

@@ -240,6 +240,12 @@ struct ConvGeom {
   // a hardware-less integer division costs it ~40 dependent instructions — six of them per k-block made the
   // wgrad producer slower than the MMAs it feeds (profiles/conv_r2a.md)
   unsigned long long m_plane, m_ow, m_cblocks, m_s;
+  int lower_w;       // lower corner along w (== lower except for the parity classes of a strided dgrad)
+  // flip mode: window tap (r, s) reads forward-weight tap (wt_rb - wt_rs*r) * wt_S + (wt_sb - wt_ss*s)
+  int wt_rb, wt_rs, wt_sb, wt_ss, wt_S;
+  // scatter mode (strided dgrad): GEMM row (n, a, b) over the OH x OW class grid is stored to pixel
+  // (n, a*sc_stride + sc_ph, b*sc_stride + sc_pw) of an sc_H x sc_W image
+  int sc_on, sc_H, sc_W, sc_stride, sc_ph, sc_pw;
 };
 
 __device__ __forceinline__ int cdiv40(int n, unsigned long long magic) {
@@ -258,6 +264,8 @@ struct GemmParams {
   int act;
   int direct_store;   // 1: per-thread global stores (row stride not 16-byte aligned); 0: TMA store
   int a_mn, b_mn;     // operand is stored [K, M] / [K, N] (non-reduction dimension contiguous)
+  float* stats;       // optional: per-channel (sum, sum of squares) partials of the bf16 output,
+                      // [gridDim.x * 4][N][2] (BatchNorm statistics from the epilogue; bf16, no bias / activation)
   // pull variant
   int rows_per_rank;
   int world;
@@ -278,10 +286,11 @@ struct PullMaps {
 // (64 bf16 or 32 fp32 columns) TMEM -> registers, + bias (the tile's bias row sits in shared memory, loaded
 // by the epilogue warps while the tile's MMAs were still running; every lane reads it with broadcast
 // 16-byte loads), activation, pack, swizzled st.shared, TMA store.
-template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32>
+template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32, bool STATS = false>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* map_d, uint32_t tcol,
                                               uint32_t bufs, uint32_t tile_bytes, int& epi_buf, float* bias_s,
-                                              int row0, int col_base, int ks, int lane) {
+                                              int row0, int col_base, int ks, int lane,
+                                              float (*st)[4] = nullptr) {
   constexpr int kCols = F32 ? 32 : 64;
   if (row0 >= p.M) return;
   const uint32_t swz = (uint32_t)(lane & 7);
@@ -330,6 +339,23 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
       if (p.splits > 1) tma_store_3d(map_d, buf, col0, row0, ks);
       else tma_store_2d(map_d, buf, col0, row0);
       tma_store_commit();
+    }
+    if constexpr (STATS) {
+      // BatchNorm statistics of the values just staged (bf16, what the next layer reads): lane l sums
+      // channels col0 + 2l, +1 over the tile's 32 rows = word l of every staged row (rows past M were
+      // zero-filled by the loads and add nothing). The staging tile is reused only EPI_BUFS chunks later.
+      const uint32_t ucol = (uint32_t)(lane >> 2), wsel = (uint32_t)(lane & 3) * 4u;
+      float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+#pragma unroll
+      for (int rr = 0; rr < 32; ++rr) {
+        uint32_t w;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w)
+                     : "r"(buf + (uint32_t)rr * 128u + ((ucol ^ (uint32_t)(rr & 7)) << 4) + wsel) : "memory");
+        const float a = bf16_lo(w), b = bf16_hi(w);
+        s0 += a; q0 = fmaf(a, a, q0);
+        s1 += b; q1 = fmaf(b, b, q1);
+      }
+      st[c][0] += s0; st[c][1] += q0; st[c][2] += s1; st[c][3] += q1;
     }
     epi_buf = (epi_buf + 1) % EPI_BUFS;
   }
@@ -422,7 +448,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         cv_n = cdiv40(pix, p.conv.m_plane);
         const int rem = pix - cv_n * plane, oh = cdiv40(rem, p.conv.m_ow);
         cv_h = oh * p.conv.stride + p.conv.lower;
-        cv_w = (rem - oh * p.conv.OW) * p.conv.stride + p.conv.lower;
+        cv_w = (rem - oh * p.conv.OW) * p.conv.stride + p.conv.lower_w;
       }
       // mode 1: (tap row, tap column, channel block) of the first k-block, then advanced incrementally
       int t_r = 0, t_s = 0, t_cb = 0;
@@ -466,7 +492,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           } else {
             // dgrad: dx[., ci] += dy[. + (pad' - r, pad' - s), co] * W[co, R-1-r, S-1-s, ci]; the weight
             // is a 3-D tensor (ci, tap, co): 64 co rows x 64 ci columns per box, MN-major B slabs
-            const int wtap = (p.conv.R - 1 - r) * p.conv.S + (p.conv.S - 1 - sx);
+            const int wtap = (p.conv.wt_rb - p.conv.wt_rs * r) * p.conv.wt_S + (p.conv.wt_sb - p.conv.wt_ss * sx);
 #pragma unroll
             for (int sl = 0; sl < BLOCK_N / 64; ++sl)
               tma_load_3d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage), b_row + sl * 64,
@@ -488,7 +514,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           // wgrad: reduction block kb = 64 consecutive output pixels; each 64-column slab of the tile is
           // one (tap, 64-channel block) of the im2col matrix
           const int h = w_oh * p.conv.stride + p.conv.lower;
-          const int w = w_ow * p.conv.stride + p.conv.lower;
+          const int w = w_ow * p.conv.stride + p.conv.lower_w;
 #pragma unroll
           for (int sl = 0; sl < BLOCK_N / 64; ++sl)
             tma_load_im2col_4d(b_smem + stage * C::kBBytes + sl * 8192, bmap, full_bar(stage), sl_c[sl], w, h, w_n,
@@ -570,10 +596,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     int epi_buf = 0;
+    // BatchNorm-statistics epilogue: per-lane (sum, sum of squares) of two channels per 64-column chunk, carried
+    // across this CTA's tiles of one n block and written as one partial row per (CTA, warp) when it changes
+    float st[BLOCK_N / 64][4];
+#pragma unroll
+    for (int c = 0; c < BLOCK_N / 64; ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
+    int st_n = -1;
+    auto flush_stats = [&](int n_blk) {
+      const size_t part = (size_t)blockIdx.x * 4 + ew;
+#pragma unroll
+      for (int c = 0; c < BLOCK_N / 64; ++c) {
+        const int col = n_blk * BLOCK_N + c * 64 + 2 * lane;
+        if (col < p.N)
+          *reinterpret_cast<float4*>(p.stats + (part * p.N + col) * 2) = make_float4(st[c][0], st[c][1], st[c][2], st[c][3]);
+        st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
+      }
+    };
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       const int ks = it % p.splits;
       const int tile = it / p.splits;
       const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      if (p.stats && n_blk != st_n) {
+        if (st_n >= 0) flush_stats(st_n);
+        st_n = n_blk;
+      }
       if (p.bias && p.splits == 1 && !p.direct_store) {
         // Stage this tile's bias row (fp32) before waiting for the accumulator: the loads overlap the
         // MMAs. Buffer `as` was last read two tiles ago; the barrier of the tile in between orders it.
@@ -588,6 +634,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       tc_fence_after();
       const int row = m_blk * BLOCK_M + ew * 32 + lane;
       const bool row_ok = row < p.M;
+      size_t orow = (size_t)(row_ok ? row : 0);      // output row (scatter mode: the pixel of the strided image)
+      if (p.conv.sc_on && row_ok) {
+        const int plane = p.conv.OH * p.conv.OW;
+        const int n = cdiv40(row, p.conv.m_plane), rem = row - n * plane;
+        const int a = cdiv40(rem, p.conv.m_ow), b = rem - a * p.conv.OW;
+        orow = ((size_t)n * p.conv.sc_H + (size_t)(a * p.conv.sc_stride + p.conv.sc_ph)) * p.conv.sc_W +
+               (size_t)(b * p.conv.sc_stride + p.conv.sc_pw);
+      }
       if (!p.direct_store) {
         // ---- TMEM -> registers -> swizzled smem tile -> TMA store (coalesced, clipped at M / N) ----
         const int row0 = m_blk * BLOCK_M + ew * 32;
@@ -598,8 +652,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         const int col_base = n_blk * BLOCK_N;
         // One compact instruction stream per (activation, bias, output type): the element loop must not
         // carry per-element branches (a first version did and was instruction-fetch bound).
-        const int variant = (p.splits > 1) ? 12 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0));
+        const int variant = (p.splits > 1) ? 12 : (p.stats ? 13 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0)));
         switch (variant) {
+          case 13:
+            epilogue_tile<BLOCK_N, C::kEpiBufs, 0, false, false, true>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf,
+                                                                       bias_s, row0, col_base, ks, lane, st);
+            break;
 #define TB_EPI(ID, ACT, BIAS, F32)                                                                        \
   case ID:                                                                                                \
     epilogue_tile<BLOCK_N, C::kEpiBufs, ACT, BIAS, F32>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf, bias_s, row0, \
@@ -648,7 +706,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           v[j] = apply_act(x, p.act);
         }
         if (p.d_dtype == kBF16) {
-          __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.D) + (size_t)row * p.N + col0;
+          __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.D) + orow * p.N + col0;
           if (col0 + 32 <= p.N && (p.N % 8) == 0) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
@@ -663,7 +721,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
               if (col0 + j < p.N) out[j] = __float2bfloat16(v[j]);
           }
         } else {
-          float* out = reinterpret_cast<float*>(p.D) + (size_t)row * p.N + col0;
+          float* out = reinterpret_cast<float*>(p.D) + orow * p.N + col0;
           if (col0 + 32 <= p.N && (p.N % 4) == 0) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4)
@@ -680,6 +738,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       if (lane == 0) mbar_arrive(tempty_bar(as));
       if (++as == kAccumStages) { as = 0; aphase ^= 1; }
     }
+    if (p.stats && st_n >= 0) flush_stats(st_n);
     if (lane == 0) tma_store_wait_all();     // smem must outlive the last bulk stores
   }
 
@@ -818,13 +877,14 @@ EncodeIm2colFn get_encode_im2col() {
 // Bounding box of window corners: lower = -pad, upper = pad - (taps - 1) (cuTensorMapEncodeIm2col's
 // convention: corners relative to the tensor's first / last element).
 int make_im2col_map(CUtensorMap* out, const void* base, int n, int h, int w, int c, int R, int S, int stride,
-                    int pad, int pixels) {
+                    int pad, int pixels, const int* corners = nullptr /* lower_w, lower_h, upper_w, upper_h */) {
   EncodeIm2colFn enc = get_encode_im2col();
   if (!enc) return fail("cuTensorMapEncodeIm2col entry point not available%s");
   cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
   cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
   int lower[2] = {-pad, -pad};
   int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  if (corners) { lower[0] = corners[0]; lower[1] = corners[1]; upper[0] = corners[2]; upper[1] = corners[3]; }
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower,
                    upper, 64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -992,14 +1052,18 @@ struct ConvHost {
   int n, h, w, c;           // its extent
   int pad;                  // padding of the walk (dgrad: taps - 1 - pad)
   int wcout, wtaps, wcin;   // weight extent (flip only)
+  int has_corners;          // explicit im2col bounding box (strided-dgrad classes)
+  int corners[4];
 };
 
 int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_per_rank,
                 const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M,
                 int N, int K, int d_dtype, int act, const uint32_t* epoch_dev, int* status_dev,
                 unsigned long long budget, cudaStream_t stream, float* fixed_scratch = nullptr,
-                size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0, const ConvHost* conv = nullptr) {
+                size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0, const ConvHost* conv = nullptr,
+                float* stats = nullptr, size_t stats_floats = 0, int* stats_parts = nullptr) {
   const bool pull = world != nullptr;
+  if (stats_parts) *stats_parts = 0;
   if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
   // cuTensorMapEncodeTiled is a driver call and needs the primary context bound to THIS thread; a thread
   // that has made no runtime call yet (e.g. autograd's backward thread, when the GEMM is the first thing
@@ -1031,6 +1095,10 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
     p.conv.m_ow = magic40(conv->g.OW);
     p.conv.m_cblocks = magic40(conv->g.cblocks);
     p.conv.m_s = magic40(conv->g.S);
+    if (!conv->has_corners) p.conv.lower_w = conv->g.lower;
+    if (conv->g.flip && !conv->g.wt_S) {          // stride-1 dgrad: plain flip of both tap axes
+      p.conv.wt_rb = conv->g.R - 1; p.conv.wt_rs = 1; p.conv.wt_sb = conv->g.S - 1; p.conv.wt_ss = 1; p.conv.wt_S = conv->g.S;
+    }
   }
   p.num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
@@ -1060,7 +1128,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   }
   // TMA-store epilogue needs a 16-byte aligned row stride; odd widths fall back to direct stores.
   const bool f32_out = splits > 1 || d_dtype == TB200_F32;
-  p.direct_store = (N % (f32_out ? 4 : 8)) != 0;
+  p.direct_store = (N % (f32_out ? 4 : 8)) != 0 || (conv && conv->g.sc_on);
 
   CUtensorMap ma, mb, md;
   memset(&md, 0, sizeof(md));
@@ -1075,7 +1143,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   memset(&pm, 0, sizeof(pm));
   if (conv && conv->g.mode == 1) {
     if (int rc = make_im2col_map(&ma, conv->act, conv->n, conv->h, conv->w, conv->c, conv->g.R, conv->g.S,
-                                 conv->g.stride, conv->pad, BLOCK_M))
+                                 conv->g.stride, conv->pad, BLOCK_M, conv->has_corners ? conv->corners : nullptr))
       return rc;
   } else if (int rc = a_mn ? make_map_mn(&ma, A, K, M) : make_map(&ma, A, M, K, BLOCK_M)) {
     return rc;
@@ -1114,6 +1182,15 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
 
   const int items = tiles * splits;
   const int grid = items < sms ? items : sms;
+  // BatchNorm-statistics epilogue: only the plain bf16 TMA-store epilogue carries it; a problem that had to be
+  // split along K (tiny batch) simply reports no statistics and the caller runs its own pass
+  if (stats && splits == 1 && !p.direct_store && d_dtype == TB200_BF16 && !bias && act == 0 && !pull) {
+    const size_t need = (size_t)grid * 4 * N * 2;
+    if (stats_floats < need) return fail("tb200_gemm: statistics buffer too small (%s%ld floats needed)", "", (long)need);
+    TB_CUDA_OK(cudaMemsetAsync(stats, 0, need * sizeof(float), stream));
+    p.stats = stats;
+    if (stats_parts) *stats_parts = grid * 4;
+  }
   int rc;
   const bool thin = !pull && p.num_kb <= 4 && splits == 1;   // store-bound: deeper epilogue pipeline
   if (block_n == 256) {
@@ -1145,6 +1222,14 @@ int tb200_gemm_bf16_nt(const void* A, const void* B, void* D, const void* bias, 
                        int M, int N, int K, int d_dtype, int act, cudaStream_t stream) {
   return gemm_common(nullptr, 0, 0, 0, A, B, D, bias, bias_dtype, M, N, K, d_dtype, act, nullptr,
                      nullptr, 0, stream);
+}
+
+// D (bf16) = A . B^T plus, from the epilogue, per-channel (sum, sum of squares) partials of D for a following
+// BatchNorm: *nparts rows of [N][2] floats in `stats` (0 rows when the problem had to be split along K).
+int tb200_gemm_bf16_nt_stats(const void* A, const void* B, void* D, int M, int N, int K, float* stats,
+                             size_t stats_floats, int* nparts, cudaStream_t stream) {
+  return gemm_common(nullptr, 0, 0, 0, A, B, D, nullptr, 0, M, N, K, TB200_BF16, 0, nullptr, nullptr, 0, stream, nullptr,
+                     0, 0, 0, nullptr, stats, stats_floats, nparts);
 }
 
 int tb200_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
@@ -1179,24 +1264,90 @@ static int conv_check(const char* who, int n, int h, int w, int cin, int cout, i
   return 0;
 }
 
+static int conv2d_fprop_impl(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
+                             int S, int stride, int pad, float* stats, size_t stats_floats, int* nparts,
+                             cudaStream_t stream);
+
 int tb200_conv2d_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
                        int S, int stride, int pad, cudaStream_t stream) {
+  return conv2d_fprop_impl(x, w, y, n, h, wd, cin, cout, R, S, stride, pad, nullptr, 0, nullptr, stream);
+}
+
+int tb200_conv2d_fprop_stats(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
+                             int S, int stride, int pad, float* stats, size_t stats_floats, int* nparts,
+                             cudaStream_t stream) {
+  return conv2d_fprop_impl(x, w, y, n, h, wd, cin, cout, R, S, stride, pad, stats, stats_floats, nparts, stream);
+}
+
+static int conv2d_fprop_impl(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
+                             int S, int stride, int pad, float* stats, size_t stats_floats, int* nparts,
+                             cudaStream_t stream) {
+  if (nparts) *nparts = 0;
   if (int rc = conv_check("tb200_conv2d_fprop", n, h, wd, cin, cout, R, S, stride, pad, cin)) return rc;
   const int oh = conv_out(h, R, stride, pad), ow = conv_out(wd, S, stride, pad);
   ConvHost c{};
   c.g = ConvGeom{1, oh, ow, stride, -pad, R, S, cin / 64, 0};
   c.act = x; c.n = n; c.h = h; c.w = wd; c.c = cin; c.pad = pad;
   return gemm_common(nullptr, 0, 0, 0, nullptr, w, y, nullptr, 0, n * oh * ow, cout, R * S * cin, TB200_BF16, 0,
-                     nullptr, nullptr, 0, stream, nullptr, 0, 0, 0, &c);
+                     nullptr, nullptr, 0, stream, nullptr, 0, 0, 0, &c, stats, stats_floats, nparts);
+}
+
+// Strided input gradient as stride x stride parity classes: output pixels with
+// (h % stride, w % stride) == (ph, pw) only ever see the taps r = (ph + pad) mod stride, + stride, ..., so each class
+// is a stride-1 correlation of dy with a dense R' x S' sub-filter whose rows land on every stride-th pixel of dx.
+// One launch per class on the same im2col mainloop; the epilogue scatters its rows to the class's pixels.
+static int conv2d_dgrad_strided(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout, int R,
+                                int S, int stride, int pad, cudaStream_t stream) {
+  const int oh = conv_out(h, R, stride, pad), ow = conv_out(wd, S, stride, pad);
+  struct Axis { int taps, tmax, off, count; };
+  auto axis = [&](int ph, int extent, int k) {
+    Axis a{};
+    a.count = (extent - ph + stride - 1) / stride;             // pixels of this parity
+    int tmax = -1;
+    for (int t = k - 1; t >= 0; --t)
+      if ((ph + pad - t) % stride == 0) { tmax = t; break; }
+    a.tmax = tmax;
+    a.taps = tmax < 0 ? 0 : tmax / stride + 1;
+    a.off = tmax < 0 ? 0 : (ph + pad - tmax) / stride;         // first dy row/column of the window of pixel 0
+    return a;
+  };
+  bool any_empty = false;
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const Axis ah = axis(ph, h, R), aw = axis(pw, wd, S);
+      if (ah.count > 0 && aw.count > 0 && (ah.taps == 0 || aw.taps == 0)) any_empty = true;
+    }
+  // classes no tap reaches (e.g. the odd pixels of a 1x1 / stride-2 convolution) are zero
+  if (any_empty) TB_CUDA_OK(cudaMemsetAsync(dx, 0, (size_t)n * h * wd * cin * 2, stream));
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const Axis ah = axis(ph, h, R), aw = axis(pw, wd, S);
+      if (ah.count <= 0 || aw.count <= 0 || ah.taps == 0 || aw.taps == 0) continue;
+      ConvHost c{};
+      c.g = ConvGeom{1, ah.count, aw.count, 1, ah.off, ah.taps, aw.taps, cout / 64, 1};
+      c.g.lower_w = aw.off;
+      c.g.wt_rb = ah.tmax; c.g.wt_rs = stride; c.g.wt_sb = aw.tmax; c.g.wt_ss = stride; c.g.wt_S = S;
+      c.g.sc_on = 1; c.g.sc_H = h; c.g.sc_W = wd; c.g.sc_stride = stride; c.g.sc_ph = ph; c.g.sc_pw = pw;
+      c.act = dy; c.n = n; c.h = oh; c.w = ow; c.c = cout; c.pad = 0;
+      c.wcout = cout; c.wtaps = R * S; c.wcin = cin;
+      // window corners run over [off, off + count): count = extent + upper - lower
+      c.has_corners = 1;
+      c.corners[0] = aw.off; c.corners[1] = ah.off;
+      c.corners[2] = aw.count - ow + aw.off; c.corners[3] = ah.count - oh + ah.off;
+      if (int rc = gemm_common(nullptr, 0, 0, 0, nullptr, w, dx, nullptr, 0, n * ah.count * aw.count, cin,
+                               ah.taps * aw.taps * cout, TB200_BF16, 0, nullptr, nullptr, 0, stream, nullptr, 0, 0, 1, &c))
+        return rc;
+    }
+  return 0;
 }
 
 int tb200_conv2d_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout, int R,
                        int S, int stride, int pad, cudaStream_t stream) {
-  if (stride != 1) return fail("tb200_conv2d_dgrad: only stride 1 is implemented%s");
   if (pad > R - 1 || pad > S - 1) return fail("tb200_conv2d_dgrad: padding larger than the filter%s");
   if (int rc = conv_check("tb200_conv2d_dgrad", n, h, wd, cin, cout, R, S, stride, pad, cout)) return rc;
-  if (R != S) return fail("tb200_conv2d_dgrad: square filters only%s");
   if (cin % 8) return fail("tb200_conv2d_dgrad: cin %s(%ld) must be a multiple of 8", "", cin);
+  if (stride != 1) return conv2d_dgrad_strided(dy, w, dx, n, h, wd, cin, cout, R, S, stride, pad, stream);
+  if (R != S) return fail("tb200_conv2d_dgrad: square filters only%s");
   const int oh = conv_out(h, R, 1, pad), ow = conv_out(wd, S, 1, pad);
   // dx = "full" correlation of dy with the flipped filter: an fprop over dy with padding taps-1-pad whose
   // output grid is x's

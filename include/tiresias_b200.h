@@ -189,13 +189,20 @@ int tb200_conv2d_fprop_halo(const void* x, const void* w, void* y, int n, int h,
  * as *nparts partial rows [nparts][cout][2] (fp32) for tb200_bn_finalize - the statistics pass of a following
  * BatchNorm comes for free. The buffer must hold tb200_conv_stats_floats(cout) floats.                     */
 size_t tb200_conv_stats_floats(int cout);
+/* The same statistics from the GEMM / im2col-convolution epilogue (1x1 and strided convolutions): D bf16 [M,N] =
+ * A . B^T. *nparts = 0 when the problem had to be split along K (tiny batch): the caller then runs its own pass. */
+int tb200_gemm_bf16_nt_stats(const void* A, const void* B, void* D, int M, int N, int K, float* stats,
+                             size_t stats_floats, int* nparts, cudaStream_t stream);
+int tb200_conv2d_fprop_stats(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, int R,
+                             int S, int stride, int pad, float* stats, size_t stats_floats, int* nparts,
+                             cudaStream_t stream);
 int tb200_conv3x3_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, float* stats,
                         size_t stats_floats, int* nparts, cudaStream_t stream);
 int tb200_conv3x3_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout,
                         cudaStream_t stream);
 /* Per-channel statistics partials [nparts][C][2] over `count` values per channel -> batch mean / invstd,
  * scale_shift = [gamma*invstd | beta - mean*gamma*invstd] for tb200_bn_apply, running statistics (may be NULL).
- * Summed in double in a fixed order: bitwise reproducible.                                                */
+ * Compensated sums in a fixed order: bitwise reproducible.                                                */
 int tb200_bn_finalize(const float* partials, int nparts, double count, int C, const void* gamma, const void* beta,
                       int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
                       float* save_mean, float* save_invstd, float* scale_shift, cudaStream_t stream);
@@ -270,6 +277,15 @@ int tb200_u8_to_bf16_norm(const uint8_t* src, void* dst, size_t pixels, const fl
  * 8-channel-aligned tensor-core path; dst holds pixels * 8 bf16.                                   */
 int tb200_u8_to_bf16_norm_pad8(const uint8_t* src, void* dst, size_t pixels, const float mean[3],
                                const float inv_std[3], cudaStream_t stream);
+/* ResNet stem on the tensor cores (csrc/stem.cu): the 7x7 / stride 2 / pad 3 convolution over 3 channels becomes a
+ * 4x1 / stride-1 convolution over a packed 64-channel tensor. pack: uint8 NHWC [n,h,w,3] -> normalised bf16
+ * Y [n, oh+3, ow, 64] (oh = (h-1)/2+1, ow = (w-1)/2+1); weight_pack: bf16 [cout][7][7][3] -> [cout][4][64];
+ * wgrad_unpack: fp32 [cout][4][64] -> [cout][7][7][3] in dw_dtype. Then
+ * tb200_conv2d_fprop(Y, Wp, y, n, oh+3, ow, 64, cout, 4, 1, 1, 0) and tb200_conv2d_wgrad with the same geometry. */
+int tb200_stem7x7_pack(const uint8_t* src, void* dst, int n, int h, int w, const float mean[3], const float inv_std[3],
+                       cudaStream_t stream);
+int tb200_stem7x7_weight_pack(const void* w, void* wp, int cout, cudaStream_t stream);
+int tb200_stem7x7_wgrad_unpack(const float* dwp, void* dw, int cout, int dw_dtype, cudaStream_t stream);
 /* Copy up to any number of bf16 tensors into their destinations with one launch per TB200_PACK_MAX
  * items (gathers per-parameter gradients into the flat symmetric gradient buffer of a bucket).      */
 #define TB200_PACK_MAX 64

@@ -5,7 +5,10 @@ Checks, on real peer memory over NVLink:
   2. the fused PS push/pull trainer against the PyTorch+NCCL PS/worker trainer (same buckets),
      eager and CUDA-graph replay, and that every rank ends with bit-identical parameters,
   3. the pull-GEMM path (weights gathered inside the first forward GEMM),
-  4. ring all-reduce mode against the PS mode.
+  4. ring all-reduce mode against the PS mode,
+  5. checkpoint / resume at world > 1 (every rank restores only its PS shard; all ranks must continue from the
+     full restored parameters) against an uninterrupted run, with and without pull-GEMM layers,
+  6. the like-for-like NCCL arm (same fused compute, NCCL collectives), eager and captured in a CUDA graph.
 Prints ``MULTI OK`` from rank 0 when everything held.
 """
 import ctypes as C
@@ -98,6 +101,35 @@ def run_trainer(mode, rank, dev, steps=5, use_graph=False, pull=False, **kw):
     return losses, params, n_pull, launches
 
 
+def check_resume(rank, dev, world, pull):
+    """Interrupt after 3 of 6 steps, restore into a trainer built from ANOTHER seed, compare with 6 straight steps."""
+    kw = dict(batch_size=32, mode="ps", use_graph=False, device=dev, bucket_mb=0.05, lr=0.05, pull_gemm=pull,
+              pull_min_mb=0.25)
+    batches = [synthetic_batch(TINY, 32, seed=100 * rank + (i % 2)) for i in range(6)]
+    tr = Trainer(TINY, **kw)
+    for x, y in batches[:3]:
+        tr.step(x, y)
+    state = tr.state_dict()
+    want = []
+    for x, y in batches[3:]:
+        tr.step(x, y)
+        want.append(tr.loss())
+    p_want = tr.param_flat.float().clone()
+    tr.close()
+    tr2 = Trainer(TINY, seed=4321, **kw)                       # different initial weights on purpose
+    tr2.load_state_dict(state)
+    got = []
+    for x, y in batches[3:]:
+        tr2.step(x, y)
+        got.append(tr2.loss())
+    assert tr2.check_status() == 0
+    assert all(abs(a - b) < 5e-2 for a, b in zip(got, want)), (pull, got, want)
+    if not pull:                                               # (a pulled weight's local copy lags by one forward)
+        assert torch.allclose(tr2.param_flat.float(), p_want, rtol=2e-2, atol=2e-2)
+        assert same_on_all_ranks(tr2.param_flat.float().clone(), world), "resume left ranks with different parameters"
+    tr2.close()
+
+
 def same_on_all_ranks(t, world):
     gathered = [torch.empty_like(t) for _ in range(world)]
     dist.all_gather(gathered, t)
@@ -152,6 +184,16 @@ def main():
         assert all(abs(a - b) < 5e-2 for a, b in zip(l_r, l_ps)), (algo, l_r, l_ps)
         assert torch.allclose(p_r, p_ps, rtol=2e-2, atol=2e-2), algo
         assert same_on_all_ranks(p_r, world), f"ring algo {algo}: ranks diverged"
+
+    check_resume(rank, dev, world, pull=False)
+    check_resume(rank, dev, world, pull=True)
+
+    # like-for-like NCCL arm: same fused model / packing / optimizer kernel, NCCL collectives; eager and graph
+    l_f, p_f, _, _ = run_trainer("nccl", rank, dev, nccl_same_compute=True)
+    assert all(abs(a - b) < 5e-2 for a, b in zip(l_f, l_ps)), (l_f, l_ps)
+    assert torch.allclose(p_f, p_ps, rtol=2e-2, atol=2e-2)
+    l_fg, p_fg, _, _ = run_trainer("nccl", rank, dev, steps=8, use_graph=True, nccl_same_compute=True)
+    assert all(abs(a - b) < 5e-2 for a, b in zip(l_fg, l_e)), (l_fg, l_e)
 
     dist.barrier()
     if rank == 0:

@@ -181,3 +181,158 @@ def test_gittins_clean_wakes_every_delta_and_finishes(tmp_path):
     # the reference-faithful loop still completes the same trace
     rows2, s2, _ = _sim(tmp_path, [(4, 0, 1000), (4, 100, 50)], "gittins", extra=("--gittins_delta", "40"))
     assert s2["finished_jobs"] == 2
+
+
+# ---- decision oracles for the rest of the Tiresias family (each schedule worked out by hand from the rules of
+# ---- the reference's dead loops; the comments carry the derivation) ----------------------------------------------
+
+def test_lpjf_serves_longest_waiting_and_stops_at_first_failure(tmp_path):
+    # run_sim.py:1474-1531. j0 2G@0 x100, j1 4G@10 x50, j2 1G@20 x10 on 4 GPUs. Arrivals always queue; the queue is
+    # sorted by waiting time (longest first) and served until the first job that does not fit.
+    # t=0  [j0] -> runs 0-100.   t=10 [j1]: 4 GPUs wanted, 2 free -> stop.
+    # t=20 [j1 (waited 10), j2 (0)]: j1 fails -> stop; j2 is NOT tried although 2 GPUs are free
+    #      (fjf, sorted by num_gpu, would start it at 20).
+    # t=100 j0 ends: j1 fits -> 100-150 (removing it while iterating skips j2, which would not fit anyway).
+    # t=150 j2 -> 150-160.
+    rows, s, _ = _sim(tmp_path, [(2, 0, 100), (4, 10, 50), (1, 20, 10)], "lpjf")
+    assert _ints(rows[0], "start_time", "end_time") == (0, 100)
+    assert _ints(rows[1], "start_time", "end_time", "pending_time") == (100, 150, 90)
+    assert _ints(rows[2], "start_time", "end_time", "JCT", "pending_time") == (150, 160, 140, 130)
+    assert s["makespan"] == 160
+
+
+def _dist(tmp_path, samples):
+    path = tmp_path / "dist.csv"
+    path.write_text("duration\n" + "".join(f"{v}\n" for v in samples))
+    return str(path)
+
+
+def test_gittins_faithful_ascending_sort_vs_descending(tmp_path):
+    # Distribution {10, 20, 100, 200}, delta 50. Index table (run_sim.py:1649-1680), a = sample - 1:
+    #   a=9  : idx 0, idx_delta 2 -> p = 2/4,   e = (10+20+50*2)/4 = 32.5 -> 15384.6154
+    #   a=19 : idx 1, idx_delta 2 -> p = .33333, e = (20+50*2)/3   = 40   ->  8333.25
+    #   a=99 : idx 2, idx_delta 3 -> p = 1/2,   e = (100+50)/2     = 75   ->  6666.6667
+    #   a=199: past the last sample                                        ->     0
+    # j0 4G@0 x300, j1 4G@100 x30 on 4 GPUs. The reference's loop (run_sim.py:948-1202) sorts ASCENDING (:1082):
+    # at t=100 j0 has attained 400 GPU-s (rank 0) and the fresh j1 ranks 15384.6, so j0 sorts first and keeps the
+    # GPUs; j1 only starts when j0 ends. Wake-ups: next_unit = 50, then += now each pass: 50, 100, 200, (400).
+    dist = _dist(tmp_path, [10, 20, 100, 200])
+    from tiresias_b200.sim.legacy import gittins as gi
+    table = gi.parse_job_dist(dist, 50)
+    assert table["gittins"][:4] == [15384.6154, 8333.25, 6666.6667, 0.0]
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    rows, s, out = _sim(tmp_path / "a", [(4, 0, 300), (4, 100, 30)], "gittins",
+                        extra=("--job_dist", dist, "--gittins_delta", "50"))
+    assert _ints(rows[0], "start_time", "end_time", "preempt") == (0, 300, 0)
+    assert _ints(rows[1], "start_time", "end_time", "pending_time") == (300, 330, 200)
+    times = [int(r["time"]) for r in csv.DictReader(open(os.path.join(out, "cluster.csv")))]
+    assert times == [0, 50, 100, 200, 300, 330]
+    # --gittins_desc (highest index first, the order of the reference's dlas-gpu-gittins variant, :809): the
+    # fresh job preempts at once.
+    rows, s, _ = _sim(tmp_path / "b", [(4, 0, 300), (4, 100, 30)], "gittins",
+                      extra=("--job_dist", dist, "--gittins_delta", "50", "--gittins_desc"))
+    assert _ints(rows[1], "start_time", "end_time") == (100, 130)
+    assert _ints(rows[0], "end_time", "preempt", "pending_time") == (330, 1, 30)
+
+
+def test_multi_dlas_reserves_gpus_per_class(tmp_path):
+    # run_sim.py:432-661. 10 GPUs; j0 1G@0 x100, j1 4G@0 x100, j2 4G@10 x50. At t=0 the two new classes split the
+    # cluster by demand (1 + 4 = 5 GPUs wanted): 1-GPU class floor(1/5*10) -> min(demand 1, 2) = 1 GPU, 4-GPU class
+    # floor(8/4)*4 -> min(demand 4, 8) = 4 GPUs; the 5 spare GPUs stay unreserved because no class has unmet
+    # demand. j2 arrives into a known class (no re-balance before t=600): its class owns 4 GPUs, all used by j1,
+    # so it waits for j1 (100) although 5 GPUs are idle. Plain dlas-gpu, which counts the whole cluster, starts
+    # it on arrival.
+    jobs = [(1, 0, 100), (4, 0, 100), (4, 10, 50)]
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    rows, s, _ = _sim(tmp_path / "a", jobs, "multi-dlas-gpu", gpus=10)
+    assert _ints(rows[2], "start_time", "end_time", "pending_time") == (100, 150, 90)
+    assert s["makespan"] == 150
+    rows, s, _ = _sim(tmp_path / "b", jobs, "dlas-gpu", gpus=10)
+    assert _ints(rows[2], "start_time", "end_time") == (10, 60)
+
+
+def test_dlas_gpu_pack_shares_gpus_by_model_memory(tmp_path):
+    # run_sim.py:1204-1472 + infra/cluster.py:117-148: a job takes model.mem_util of each of its num_gpu GPUs. The
+    # reference's live table is all ones (core/models.py:22), so packing never engages and the schedule equals
+    # dlas-gpu; with its commented-out measured table (core/models.py:21; resnet50 = 0.50, --pack_mem_util table)
+    # two resnet50 jobs share both GPUs of a 2-GPU cluster and the second starts on arrival.
+    jobs = [(2, 0, 100), (2, 10, 50)]
+    for name in "abc":
+        (tmp_path / name).mkdir()
+    rows, s, _ = _sim(tmp_path / "a", jobs, "dlas-gpu-pack", gpus=2, extra=("--pack_mem_util", "table"))
+    assert _ints(rows[1], "start_time", "end_time") == (10, 60) and s["makespan"] == 100
+    rows, s, _ = _sim(tmp_path / "b", jobs, "dlas-gpu-pack", gpus=2)
+    assert _ints(rows[1], "start_time", "end_time") == (100, 150) and s["makespan"] == 150
+    rows_plain, _, _ = _sim(tmp_path / "c", jobs, "dlas-gpu", gpus=2)
+    assert _ints(rows_plain[1], "start_time", "end_time") == (100, 150)
+
+
+def test_gandiva_legacy_time_slices_an_oversubscribed_node_set(tmp_path):
+    # run_sim.py:101-158 + infra/cluster.py:386-489. One 4-GPU node, two 4-GPU jobs of 100 s at t=0: the node set
+    # of the 4-GPU class has capacity 1, the second job over-subscribes it. The loop steps 10 s; only the head job
+    # advances; heads rotate when the clock hits a multiple of 60:
+    #   j0 advances at t=10..60 (60 s done), rotate at 60; j1 advances t=70..120 (60 s), rotate at 120;
+    #   j0 advances t=130..160 -> 100 s, done at 160; j1 advances t=170..200 -> done at 200.
+    # (fifo would finish j0 at 100.)
+    rows, s, _ = _sim(tmp_path, [(4, 0, 100), (4, 0, 100)], "gandiva-legacy", scheme="gandiva", gpus=4)
+    assert _ints(rows[0], "start_time", "end_time", "JCT") == (0, 160, 160)
+    assert _ints(rows[1], "start_time", "end_time", "JCT") == (0, 200, 200)
+    assert s["makespan"] == 200
+
+
+def test_lp_placement_is_optimal_against_brute_force():
+    # core/lp.py:2-44: minimise the maximum per-node network load; binary p[j, n]; GPU / CPU capacity; every
+    # component placed once. 2 PS shards + 2 workers on 3 nodes with uneven existing load: 81 assignments.
+    import itertools
+    import numpy as np
+    from tiresias_b200.sim.legacy import lp
+    info = {"t": [30.0, 12.5], "num_ps": 2, "num_w": 2, "m_size": 42.5, "ps_c": lp.PS_CPU, "w_c": lp.WORKER_CPU}
+    cl = {"fg": [1, 1, 2], "fc": [16, 6, 16], "ct": [20.0, 0.0, 55.0], "num_n": 3}
+    x = lp._solve_milp(info, cl)
+    assert x is not None and x.shape == (4, 3) and (x.sum(1) == 1).all()
+    t = [info["t"][0] * 2, info["t"][1] * 2, info["m_size"], info["m_size"]]
+    g, c = [0, 0, 1, 1], [lp.PS_CPU, lp.PS_CPU, lp.WORKER_CPU, lp.WORKER_CPU]
+
+    def objective(assign):
+        load, fg, fc = list(cl["ct"]), list(cl["fg"]), list(cl["fc"])
+        for j, n in enumerate(assign):
+            load[n] += t[j]; fg[n] -= g[j]; fc[n] -= c[j]
+        return max(load) if min(fg) >= 0 and min(fc) >= 0 else None
+
+    feasible = [v for v in (objective(a) for a in itertools.product(range(3), repeat=4)) if v is not None]
+    got = objective([int(np.argmax(x[j])) for j in range(4)])
+    assert got is not None and abs(got - min(feasible)) < 1e-6, (got, min(feasible))
+    # capacity is honoured: node 1 has CPUs for either one worker or one PS shard, never both workers
+    assert x[2:, 1].sum() <= 1
+
+
+def test_cross_node_job_network_load_follows_the_switch_formula(tmp_path):
+    # infra/switch.py:97-107 / :122-133: every GPU hosts one worker and one PS shard; per node
+    #   traffic = model_size * local_gpus + sum_{local PS i} ps[i] * (need_gpu - local_gpus) - ps[i] * local_gpus
+    # A 4-GPU resnet50 job on 2 nodes x 2 GPUs under yarn placement: 2 workers + shards (0,1) / (2,3) per node.
+    from tiresias_b200.sim.legacy import engine
+    trace = tmp_path / "t.csv"
+    trace.write_text(HEADER + "0,4,0,100,resnet50,100,30\n")
+    flags = define_simulator_flags()
+    flags.parse(["--trace_file", str(trace), "--schedule", "fjf", "--scheme", "yarn", "--num_switch", "1",
+                 "--num_node_p_switch", "2", "--num_gpu_p_node", "2", "--quiet"])
+    (tmp_path / "o").mkdir()
+    sim = engine.build(flags, str(tmp_path / "o"))
+    job = sim.jobs.job_list[0]
+    assert sim.cluster.try_get_job_res(job)
+    nodes = [nd for pl in job.placements for nd in pl["nodes"]]
+    assert [nd["num_gpu"] for nd in nodes] == [2, 2]
+    size, ps = job.model["total_size"], job.ps_network
+    # resnet50's tensors dealt round-robin over 4 shards (core/models.py:8-20, Job docstring core/jobs/job.py:61-73)
+    shards = [0.0] * 4
+    for i, tsize in enumerate(job.model["tensors"]):
+        shards[i % 4] += tsize
+    assert ps == [round(v, 1) for v in shards] and abs(sum(ps) - size) < 0.5
+    want = []
+    for first in (0, 2):
+        traffic = size * 2
+        for i in (first, first + 1):
+            traffic += ps[i] * (4 - 2) - ps[i] * 2
+        want.append(round(traffic, 1))
+    assert [nd["network"] for nd in nodes] == pytest.approx(want, abs=0.2)
+    assert want[0] == pytest.approx(size * 2, abs=0.2)      # shard terms cancel when half the workers are local

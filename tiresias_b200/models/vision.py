@@ -14,7 +14,7 @@ from torch import nn
 
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
-from ..ops.conv import TcConv1x1, TcConv2d, _parse_ops
+from ..ops.conv import TcConv1x1, TcConv2d, _parse_ops, packed_stem_conv
 from ..ops.linear import TcLinear
 from ..ops.pooling import MaxPool3x3S2
 
@@ -60,7 +60,7 @@ def _bn(channels: int, relu: bool, fused: bool) -> nn.Module:
 def _conv(cin: int, cout: int, k: int, stride: int = 1, pad: int = 0, fused: bool = False) -> nn.Module:
     """cuDNN convolution unless TB200_TC_CONV routes passes of this geometry to the tcgen05 kernels."""
     if fused and TC_CONV["p"] and k == 1 and stride == 1 and pad == 0 and cin % 8 == 0 and cout % 8 == 0:
-        return TcConv1x1(cin, cout, TC_CONV["p"])
+        return TcConv1x1(cin, cout, TC_CONV["p"], emit_stats=True)
     if fused and TC_CONV["k"] and not (k == 1 and stride == 1) and cin % 64 == 0 and cout % 8 == 0:
         return TcConv2d(cin, cout, k, stride, pad, TC_CONV["k"], emit_stats=True)
     return nn.Conv2d(cin, cout, k, stride, pad, bias=False)
@@ -92,6 +92,7 @@ class Bottleneck(nn.Module):
 class ResNet(nn.Module):
     def __init__(self, depths: Sequence[int], num_classes: int = 1000, fused: bool = True):
         super().__init__()
+        self.fused = fused
         self.stem_conv, self.stem_bn = _conv(3, 64, 7, 2, 3), _bn(64, True, fused)
         self.stem_pool = MaxPool3x3S2() if fused else nn.MaxPool2d(3, 2, 1)
         blocks: List[nn.Module] = []
@@ -110,13 +111,22 @@ class ResNet(nn.Module):
             if isinstance(m, Bottleneck):
                 nn.init.zeros_(m.bn3.weight)            # zero-init last BN of each block
 
-    input_channels = 3          # the trainer may feed 8 (rgb + 5 zero channels): see _stem
+    input_channels = 3          # the trainer may feed 8 (rgb + 5 zero channels) or the packed 64: see _stem
+
+    @property
+    def packed_stem(self) -> bool:
+        """True when the trainer should feed ``native.stem7x7_pack`` output (the stem then runs on the tcgen05
+        implicit GEMM, csrc/stem.cu) instead of the normalised image."""
+        return self.fused and bool(TC_CONV["k"] >= {"f", "w"})
 
     def _stem(self, x: torch.Tensor) -> torch.Tensor:
-        """7x7/2 convolution. An 8-channel input (rgb00000, written by tb200_u8_to_bf16_norm_pad8) is
+        """7x7/2 convolution. A 64-channel input is the packed tensor of csrc/stem.cu: 4x1 / stride-1 implicit
+        GEMM on our kernels. An 8-channel input (rgb00000, written by tb200_u8_to_bf16_norm_pad8) is
         convolved with the 3-channel weight zero-padded to 8 input channels — same result, but cuDNN can
         use its 8-channel-aligned sm_100 kernels instead of the legacy 3-channel one."""
         conv = self.stem_conv
+        if x.shape[1] == 64 and x.is_cuda:
+            return packed_stem_conv(x, conv.weight, emit_stats=self.training)
         if x.shape[1] == 8:
             w8 = torch.nn.functional.pad(conv.weight, (0, 0, 0, 0, 0, 5))
             return torch.nn.functional.conv2d(x, w8, None, conv.stride, conv.padding)

@@ -8,10 +8,13 @@ so no im2col, no transposes and no layout change are needed — the activations 
 thirds of ResNet-50's convolutions (conv1 / conv3 of every bottleneck, the stride-1 projection) are of
 this kind.
 
-k x k and strided convolutions (``TcConv2d``) run as implicit GEMMs on the same mainloop: the producer warp
-gathers the activation operand with im2col-mode TMA loads (``tb200_conv2d_fprop`` / ``_dgrad`` / ``_wgrad``,
-csrc/gemm_tcgen05.cu), so nothing is unfolded in memory. The input gradient of a *strided* convolution is
-the one piece still taken from cuDNN.
+3x3 / stride 1 / pad 1 convolutions (``TcConv2d``) run forward and input gradient on the halo-tile kernel of
+csrc/conv3x3.cu (the input rows a tile needs are fetched once, the nine taps are shifted shared-memory windows;
+dgrad reads the forward weight as stored). Every other geometry is an implicit GEMM on the GEMM mainloop
+(``tb200_conv2d_fprop`` / ``_dgrad`` / ``_wgrad``, csrc/gemm_tcgen05.cu): the producer warp gathers the activation
+operand with im2col-mode TMA loads, so nothing is unfolded in memory; a strided input gradient runs as stride x
+stride parity classes on that kernel. Forward passes can emit the per-channel sum / sum of squares of their output
+from the epilogue; the fused BatchNorm that follows then skips its statistics pass (``emit_stats``).
 """
 from __future__ import annotations
 
@@ -25,7 +28,7 @@ from . import native
 
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, ops: frozenset = frozenset("fdw")) -> torch.Tensor:
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, ops: frozenset = frozenset("fdw"), want_stats: bool = False):
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         n, cin, h, w = x.shape
@@ -37,13 +40,21 @@ class _Conv1x1Fn(torch.autograd.Function):
         ctx.save_for_backward(x2d, w2d)
         ctx.shape = (n, cin, h, w, cout)
         ctx.ops = ops
+        empty = x.new_empty(0, dtype=torch.float32)
         if "f" not in ops:
-            return torch.nn.functional.conv2d(x, w2d.view(cout, 1, 1, cin).permute(0, 3, 1, 2))
+            ctx.mark_non_differentiable(empty)
+            return torch.nn.functional.conv2d(x, w2d.view(cout, 1, 1, cin).permute(0, 3, 1, 2)), empty
+        if want_stats:
+            y2d, st = native.gemm_nt_stats(x2d, w2d)
+            partials = st.partials if st is not None else empty
+            ctx.mark_non_differentiable(partials)
+            return y2d.view(n, h, w, cout).permute(0, 3, 1, 2), partials
+        ctx.mark_non_differentiable(empty)
         y2d = native.gemm_nt(x2d, w2d)
-        return y2d.view(n, h, w, cout).permute(0, 3, 1, 2)
+        return y2d.view(n, h, w, cout).permute(0, 3, 1, 2), empty
 
     @staticmethod
-    def backward(ctx, dy: torch.Tensor):
+    def backward(ctx, dy: torch.Tensor, _dstats=None):
         x2d, w2d = ctx.saved_tensors
         n, cin, h, w, cout = ctx.shape
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -65,7 +76,16 @@ class _Conv1x1Fn(torch.autograd.Function):
                 [want_dx and not own_dx, want_dw and not own_dw, False])
             dx = dx if own_dx else lib_dx
             dw = dw if own_dw else lib_dw
-        return dx, dw, None
+        return dx, dw, None, None
+
+
+def _attach_stats(y: torch.Tensor, partials: torch.Tensor) -> torch.Tensor:
+    """Hang the epilogue's statistics on the activation so that the fused BatchNorm that consumes ``y`` next
+    (``FusedBatchNormAct.forward``) skips its statistics pass."""
+    if partials.numel():
+        n, _, h, w = y.shape
+        y._tb200_stats = native.ConvStats(partials, partials.shape[0], n * h * w)
+    return y
 
 
 class TcConv1x1(nn.Module):
@@ -73,8 +93,9 @@ class TcConv1x1(nn.Module):
     channels-last CUDA inputs (anything else goes to ``F.conv2d``). The weight keeps Conv2d's shape
     ``[cout, cin, 1, 1]``, so checkpoints and the trainer's flat parameter layout are unchanged."""
 
-    def __init__(self, in_channels: int, out_channels: int, ops=("f", "d", "w")):
+    def __init__(self, in_channels: int, out_channels: int, ops=("f", "d", "w"), emit_stats: bool = False):
         super().__init__()
+        self.emit_stats = emit_stats          # a fused BatchNorm follows: hand it the epilogue's statistics
         if in_channels % 8 or out_channels % 8:
             raise ValueError("channel counts must be multiples of 8 (TMA 16-byte stride rule)")
         self.in_channels, self.out_channels = in_channels, out_channels
@@ -84,7 +105,8 @@ class TcConv1x1(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
-            return _Conv1x1Fn.apply(x, self.weight, self.ops)
+            want = self.emit_stats and self.training and torch.is_grad_enabled()
+            return _attach_stats(*_Conv1x1Fn.apply(x, self.weight, self.ops, want))
         return torch.nn.functional.conv2d(x, self.weight)
 
     def extra_repr(self) -> str:
@@ -140,6 +162,11 @@ class _Conv2dFn(torch.autograd.Function):
                     ctx.nparts = st.nparts
                     ctx.mark_non_differentiable(st.partials)
                     return y, st.partials
+            if want_stats:
+                y, st = native.conv2d_fprop_stats(x, weight, stride, pad)
+                partials = st.partials if st is not None else empty
+                ctx.mark_non_differentiable(partials)
+                return y, partials
             ctx.mark_non_differentiable(empty)
             if ctx.halo:
                 return native.conv3x3_fprop(x, weight), empty
@@ -154,8 +181,8 @@ class _Conv2dFn(torch.autograd.Function):
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
         want_dx, want_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        # strided dgrad is the one pass without a kernel of ours yet (known gaps)
-        own_dx = want_dx and "d" in ops and stride == 1 and weight.shape[0] % 64 == 0
+        # (a strided input gradient runs as stride x stride parity classes on the same im2col kernel)
+        own_dx = want_dx and "d" in ops and weight.shape[0] % 64 == 0
         own_dw = want_dw and "w" in ops
         dx = dw = None
         if own_dx:
@@ -191,13 +218,45 @@ class TcConv2d(nn.Module):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
             want = self.emit_stats and self.training and torch.is_grad_enabled()
-            y, partials = _Conv2dFn.apply(x, self.weight, self.stride, self.padding, self.ops, want)
-            if partials.numel():
-                n, _, h, w = y.shape
-                y._tb200_stats = native.ConvStats(partials, partials.shape[0], n * h * w)
-            return y
+            return _attach_stats(*_Conv2dFn.apply(x, self.weight, self.stride, self.padding, self.ops, want))
         return torch.nn.functional.conv2d(x, self.weight, stride=self.stride, padding=self.padding)
 
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
                 f"stride={self.stride}, padding={self.padding}, tcgen05 implicit GEMM passes={sorted(self.ops)}")
+
+
+class _PackedStemFn(torch.autograd.Function):
+    """The ResNet stem (7x7 / stride 2 / pad 3 over 3 channels) on the packed input of csrc/stem.cu: a 4x1 /
+    stride-1 implicit GEMM with 64 input channels. ``y_packed`` [N,64,OH+3,OW] comes from
+    ``native.stem7x7_pack`` (the image's uint8 -> bf16 normalisation is fused into that pack) and needs no
+    gradient; the weight keeps its [cout,3,7,7] shape."""
+
+    @staticmethod
+    def forward(ctx, y_packed: torch.Tensor, weight: torch.Tensor, want_stats: bool):
+        if not weight.is_contiguous(memory_format=torch.channels_last):
+            weight = weight.contiguous(memory_format=torch.channels_last)
+        wp = native.stem7x7_weight_pack(weight)
+        ctx.save_for_backward(y_packed)
+        ctx.wdtype = weight.dtype
+        empty = y_packed.new_empty(0, dtype=torch.float32)
+        if want_stats:
+            y, st = native.conv2d_fprop_stats(y_packed, wp, 1, 0)
+            partials = st.partials if st is not None else empty
+            ctx.mark_non_differentiable(partials)
+            return y, partials
+        ctx.mark_non_differentiable(empty)
+        return native.conv2d_fprop(y_packed, wp, 1, 0), empty
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor, _dstats=None):
+        (y_packed,) = ctx.saved_tensors
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dwp = native.conv2d_wgrad(y_packed, dy, (4, 1), 1, 0, out_dtype=torch.float32)
+        return None, native.stem7x7_wgrad_unpack(dwp, ctx.wdtype), None
+
+
+def packed_stem_conv(y_packed: torch.Tensor, weight: torch.Tensor, emit_stats: bool = True) -> torch.Tensor:
+    want = emit_stats and torch.is_grad_enabled() and weight.requires_grad
+    return _attach_stats(*_PackedStemFn.apply(y_packed, weight, want))

@@ -112,6 +112,16 @@ def _declare(lib: C.CDLL) -> None:
         getattr(lib, fn).restype = ci
     lib.tb200_conv2d_fprop_halo.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, st]
     lib.tb200_conv2d_fprop_halo.restype = ci
+    lib.tb200_stem7x7_pack.argtypes = [vp, vp, ci, ci, ci, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
+    lib.tb200_stem7x7_pack.restype = ci
+    lib.tb200_stem7x7_weight_pack.argtypes = [vp, vp, ci, st]
+    lib.tb200_stem7x7_weight_pack.restype = ci
+    lib.tb200_stem7x7_wgrad_unpack.argtypes = [vp, vp, ci, ci, st]
+    lib.tb200_stem7x7_wgrad_unpack.restype = ci
+    lib.tb200_gemm_bf16_nt_stats.argtypes = [vp, vp, vp, ci, ci, ci, vp, sz, ip_, st]
+    lib.tb200_gemm_bf16_nt_stats.restype = ci
+    lib.tb200_conv2d_fprop_stats.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, vp, sz, ip_, st]
+    lib.tb200_conv2d_fprop_stats.restype = ci
     lib.tb200_conv_stats_floats.argtypes = [ci]
     lib.tb200_conv_stats_floats.restype = sz
     lib.tb200_conv3x3_fprop.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp, sz, ip_, st]
@@ -234,6 +244,22 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
     return out
 
 
+def gemm_nt_stats(a: torch.Tensor, b: torch.Tensor):
+    """``a @ b.T`` (bf16 out) plus the per-channel (sum, sum of squares) partials of the output from the
+    epilogue (tb200_gemm_bf16_nt_stats). Returns ``(out, ConvStats or None)`` — None when the problem had to be
+    split along K (tiny batch) and carries no statistics."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.is_contiguous() and b.is_contiguous() and a.shape[1] == b.shape[1]
+    m, k = a.shape
+    n = b.shape[0]
+    out = torch.empty((m, n), dtype=torch.bfloat16, device=a.device)
+    buf = conv_stats_buffer(n, a.device)
+    nparts = C.c_int(0)
+    check(lib().tb200_gemm_bf16_nt_stats(a.data_ptr(), b.data_ptr(), out.data_ptr(), m, n, k, buf.data_ptr(), buf.numel(),
+                                         C.byref(nparts), stream_ptr()))
+    return out, (ConvStats(buf[: nparts.value], nparts.value, m) if nparts.value else None)
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, a_mn_major: bool = False, b_mn_major: bool = False,
          bias: Optional[torch.Tensor] = None, act: int = ACT_NONE, out_dtype: torch.dtype = torch.bfloat16,
          out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -279,6 +305,22 @@ def _nhwc(t: torch.Tensor) -> torch.Tensor:
     v = t.permute(0, 2, 3, 1)
     assert v.is_contiguous(), "expected a channels_last tensor"
     return v
+
+
+def conv2d_fprop_stats(x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int):
+    """:func:`conv2d_fprop` plus the epilogue's BatchNorm statistics: ``(y, ConvStats or None)``."""
+    assert x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    xv, wv = _nhwc(x), _nhwc(weight)
+    n, h, w, cin = xv.shape
+    cout, r, s, _ = wv.shape
+    oh, ow = (h + 2 * pad - r) // stride + 1, (w + 2 * pad - s) // stride + 1
+    y = torch.empty((n, oh, ow, cout), dtype=torch.bfloat16, device=x.device)
+    buf = conv_stats_buffer(cout, x.device)
+    nparts = C.c_int(0)
+    check(lib().tb200_conv2d_fprop_stats(xv.data_ptr(), wv.data_ptr(), y.data_ptr(), n, h, w, cin, cout, r, s, stride, pad,
+                                         buf.data_ptr(), buf.numel(), C.byref(nparts), stream_ptr()))
+    st = ConvStats(buf[: nparts.value], nparts.value, n * oh * ow) if nparts.value else None
+    return y.permute(0, 3, 1, 2), st
 
 
 def conv2d_fprop(x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
@@ -430,6 +472,47 @@ def u8_to_bf16_norm_pad8(src: torch.Tensor, mean: Sequence[float], std: Sequence
     check(lib().tb200_u8_to_bf16_norm_pad8(src.data_ptr(), out.data_ptr(), src.numel() // 3, m, s,
                                            stream_ptr()))
     return out
+
+
+def stem_packed_shape(n: int, h: int, w: int):
+    """Shape [n, oh+3, ow, 64] of the packed stem input for an [n, h, w, 3] image batch (csrc/stem.cu)."""
+    return (n, (h - 1) // 2 + 1 + 3, (w - 1) // 2 + 1, 64)
+
+
+def stem7x7_pack(src: torch.Tensor, mean: Sequence[float], std: Sequence[float],
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 NHWC batch -> the packed, normalised bf16 tensor Y [n, oh+3, ow, 64] over which the 7x7 / stride 2
+    stem convolution is a 4x1 / stride 1 convolution with 64 input channels (tb200_stem7x7_pack)."""
+    assert src.dtype == torch.uint8 and src.is_contiguous() and src.dim() == 4 and src.shape[-1] == 3
+    n, h, w, _ = src.shape
+    if out is None:
+        out = torch.empty(stem_packed_shape(n, h, w), dtype=torch.bfloat16, device=src.device)
+    assert tuple(out.shape) == stem_packed_shape(n, h, w) and out.is_contiguous()
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*[1.0 / v for v in std])
+    check(lib().tb200_stem7x7_pack(src.data_ptr(), out.data_ptr(), n, h, w, m, s, stream_ptr()))
+    return out
+
+
+def stem7x7_weight_pack(weight: torch.Tensor) -> torch.Tensor:
+    """[cout,3,7,7] bf16 channels_last stem weight -> the [cout,64,4,1] channels_last weight of the packed
+    convolution (tb200_stem7x7_weight_pack)."""
+    wv = _nhwc(weight)
+    cout = wv.shape[0]
+    assert wv.shape[1:] == (7, 7, 3) and weight.dtype == torch.bfloat16
+    wp = torch.empty((cout, 4, 1, 64), dtype=torch.bfloat16, device=weight.device)
+    check(lib().tb200_stem7x7_weight_pack(wv.data_ptr(), wp.data_ptr(), cout, stream_ptr()))
+    return wp.permute(0, 3, 1, 2)
+
+
+def stem7x7_wgrad_unpack(dwp: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """fp32 gradient of the packed weight [cout,64,4,1] (channels_last) -> [cout,3,7,7] channels_last."""
+    v = _nhwc(dwp)
+    cout = v.shape[0]
+    assert v.shape[1:] == (4, 1, 64) and dwp.dtype == torch.float32
+    dw = torch.empty((cout, 7, 7, 3), dtype=dtype, device=dwp.device)
+    check(lib().tb200_stem7x7_wgrad_unpack(v.data_ptr(), dw.data_ptr(), cout, dtype_code(dtype), stream_ptr()))
+    return dw.permute(0, 3, 1, 2)
 
 
 def sumsq(x: torch.Tensor, scratch: Optional[torch.Tensor] = None,

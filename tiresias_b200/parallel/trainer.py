@@ -169,6 +169,12 @@ class Trainer:
         self._pending_nccl: List[Tuple[Bucket, object]] = []
         self._phase_events = None
         self._alloc_io()
+        # parameters were flattened / flags zeroed on the current stream: nobody (this rank's step stream, or a
+        # peer's push kernel storing into our buffers) may run ahead of that
+        torch.cuda.synchronize(self.device)
+        if mode != "nccl":
+            self.symm.barrier()
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
 
     # ------------------------------------------------------------------------------------------
     # state
@@ -269,9 +275,15 @@ class Trainer:
         # stem (2.72 ms vs 1.47 ms for the 3-channel kernel), so it stays off; the kernel and the model
         # support are kept for convolution back-ends where it pays.
         self._pad8 = bool(self.stem_pad8) and self.spec.kind == "image" and hasattr(self.model, "_stem")
+        # ResNets on our own convolution kernels take the stem input packed for the tensor cores (csrc/stem.cu):
+        # the uint8 -> bf16 normalisation is fused into the pack
+        self._packed_stem = (self.spec.kind == "image" and bool(getattr(self.model, "packed_stem", False))
+                             and not self._pad8)
         if self.spec.kind == "image":
             self.x_dev = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.uint8, device=dev)
             in_shape = (*self.spec.sample_shape[:-1], 8) if self._pad8 else self.spec.sample_shape
+            if self._packed_stem:
+                in_shape = native.stem_packed_shape(bs, *self.spec.sample_shape[:2])[1:]
             self.x_in = torch.zeros((bs, *in_shape), dtype=torch.bfloat16, device=dev)
         else:
             self.x_dev = torch.zeros((bs, *self.spec.sample_shape), dtype=torch.int64, device=dev)
@@ -408,7 +420,9 @@ class Trainer:
     # ------------------------------------------------------------------------------------------
     def _preprocess(self) -> torch.Tensor:
         if self.spec.kind == "image":
-            if self._pad8:
+            if self._packed_stem:
+                native.stem7x7_pack(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
+            elif self._pad8:
                 native.u8_to_bf16_norm_pad8(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
             else:
                 native.u8_to_bf16_norm(self.x_dev, IMAGENET_MEAN, IMAGENET_STD, out=self.x_in)
@@ -599,11 +613,19 @@ class Trainer:
         return out
 
     def load_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
-        """Restore the optimizer shard; parameters are rebuilt from the fp32 masters."""
+        """Restore the optimizer shard (fp32 masters + momentum), the step counter and the model buffers, then
+        rebuild the FULL bf16 parameter buffer on every rank: in ``ps`` mode a rank only owns 1/world of the
+        masters, so each rank writes its restored shard into every peer's parameter buffer over the symmetric
+        mapping (what the push kernel's broadcast does at the end of a step). A barrier on both sides makes sure
+        no rank starts a step on a mix of restored and freshly initialised weights, and that pull-GEMM layers
+        (whose first wait, for epoch 0, passes at once) find their owners' shards in place."""
         self.synchronize()
+        torch.cuda.synchronize(self.device)
         self.master.copy_(state["master"])
         self.mom.copy_(state["momentum"])
         self._steps = int(state["steps"])
+        # the in-kernel flag protocol restarts at epoch 1 together with the fresh flag pads of this trainer (the
+        # saved "epoch" is bookkeeping only): epochs only have to agree between the ranks of one incarnation
         bufs = dict(self.model.named_buffers())
         for k, v in state.items():
             if k.startswith("buffer."):
@@ -614,9 +636,26 @@ class Trainer:
                 n = b.length if replicated else b.length // self.world
                 lo = 0 if replicated else self.rank * n
                 base = self._shard_base[bi]
-                self.param_flat[b.offset + lo: b.offset + lo + n] = self.master[base: base + n].to(torch.bfloat16)
-        # other ranks' shards are restored by their own load_state_dict; peers then re-gather
-        # on the next step (ps mode broadcasts every shard at the end of each step).
+                shard = self.master[base: base + n].to(torch.bfloat16)
+                self.param_flat[b.offset + lo: b.offset + lo + n] = shard
+                if not replicated and self.world > 1:
+                    if self.mode == "ps":
+                        # peers' parameter buffers are mapped into this process: store the shard there too
+                        from .symm import tensor_from_ptr
+                        pbuf = self.symm.buffers["param"]
+                        for r in range(self.world):
+                            if r == self.rank:
+                                continue
+                            peer = tensor_from_ptr(pbuf.ptrs[r] + 2 * (b.offset + lo), 2 * n, torch.bfloat16, self.device)
+                            peer.copy_(shard)
+                    else:
+                        import torch.distributed as dist
+                        dist.all_gather_into_tensor(self.param_flat[b.offset: b.offset + b.length], shard,
+                                                    group=self.comm_group)
+        self._graph = None                       # captured before the restore: re-capture on the new state
+        torch.cuda.synchronize(self.device)
+        self.symm.barrier()
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
 
     def close(self) -> None:
         self.synchronize()

@@ -133,6 +133,10 @@ def define_simulator_flags(fs: Optional[FlagSet] = None) -> FlagSet:
     fs.define_boolean("gittins_clean", False, "gittins without three accidents of the reference loop: waiting "
                                               "jobs ranked by attained GPU-time, a wake-up every gittins_delta, "
                                               "running-first / submit-order tie break (what exec/ executes)")
+    fs.define_string("pack_mem_util", "unit", "GPU share a job takes under the packing schedulers (dlas-gpu-pack, "
+                                              "gandiva-legacy): unit = 1 per job as in the reference's live table "
+                                              "(packing never engages) | table = the reference's commented-out "
+                                              "per-model shares (core/models.py:21)")
     fs.define_float("solve_starvation", 0, "DLAS starvation knob: promote when pending >= x * executed")
     fs.define_integer("resume_overhead", 0, "time units charged to a job each time it resumes after a "
                                             "preemption (measured restart cost; 0 = free, as in the reference)")

@@ -57,6 +57,8 @@ def apply_calibration(rows: List[dict], calibration: Optional[Dict]) -> None:
 def build(flags, output_dir: str, calibration: Optional[Dict] = None, rows: Optional[List[dict]] = None) -> Sim:
     rows = rows if rows is not None else load_rows(flags)
     apply_calibration(rows, calibration)
+    from .. import models as _models
+    _models.set_mem_table(str(getattr(flags, "pack_mem_util", "unit") or "unit") == "table")
     limits = parse_queue_limit(getattr(flags, "queue_limit", None), flags.num_queue)
     num_queue = flags.num_queue
     if limits is not None and num_queue < len(limits) + 1:

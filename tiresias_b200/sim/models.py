@@ -95,6 +95,16 @@ m_tensors: List[List[float]] = [
     [3.8, 2.1, 1.3, 1.6, 1.9, 1.7, 1.7, 2.2, 5.9, 1.7, 1.7, 2.5, 3.0, 1.7, 1.7, 3.5, 5.9, 1.7, 1.7, 1.5, 7.8],
 ]
 m_mem = [1] * len(m_names)
+# The reference keeps a measured per-model GPU share next to the live table, commented out (core/models.py:21);
+# with the live all-ones table a job takes whole GPUs and `dlas-gpu-pack` degenerates to `dlas-gpu`.
+# ``--pack_mem_util table`` (set_mem_table) switches the packing schedulers to it.
+m_mem_measured = [0.60, 0.55, 0.45, 0.13, 0.85, 0.70, 0.50, 0.85, 0.80]
+_use_measured_mem = False
+
+
+def set_mem_table(measured: bool) -> None:
+    global _use_measured_mem
+    _use_measured_mem = bool(measured)
 
 
 def get_model(model_name: str) -> dict:
@@ -104,7 +114,8 @@ def get_model(model_name: str) -> dict:
     else:
         idx = m_names.index("inception3")
         util.print_fn("No model match, pick %s" % m_names[idx])
-    return {"name": m_names[idx], "ind": idx, "tensors": m_tensors[idx], "mem_util": m_mem[idx]}
+    return {"name": m_names[idx], "ind": idx, "tensors": m_tensors[idx],
+            "mem_util": (m_mem_measured if _use_measured_mem else m_mem)[idx]}
 
 
 def get_model_with_scale(model_name: str, model_scale) -> dict:
