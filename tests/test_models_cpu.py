@@ -101,3 +101,47 @@ def test_samplers_degrade_without_nvml():
     else:                                       # a GPU box: values are percentages
         assert 0 <= u["gpu_util_avg"] <= 100
     assert "reasons" in c and not rejected({"reasons": ["sw_power_cap"]}) and rejected({"reasons": ["hw_slowdown"]})
+
+
+def test_zoo_architectures_carry_the_table_s_gradient_volume():
+    """googlenet / inception3 / the three OpenNMT LSTMs / BERT_Chinese have their own architectures whose fp32
+    parameter bytes sit within ~20 % of the reference's checkpoint-size table (model/model_factory.py:19-55):
+    the quantity the PS/worker cost model is calibrated on. (mobilenet_v1_025 is the real 0.47 M-parameter
+    network; the table's 15 MB is a TF checkpoint with optimizer slots.)"""
+    for name, tol in (("googlenet", 0.05), ("inception3", 0.08), ("2_layers_lstm_gigaword", 0.05),
+                      ("1_layer_bilstm_opennmt", 0.05), ("4_layers_brnn", 0.05), ("BERT_Chinese", 0.2)):
+        spec = zoo.resolve(name)
+        assert spec.name == name, "stand-in where an architecture is expected"
+        with torch.device("meta"):
+            model = zoo.build(spec, fused=False)
+        mb = sum(p.numel() for p in model.parameters()) * 4 / 1e6
+        assert abs(mb - zoo.MODEL_SIZES_MB[name]) <= tol * zoo.MODEL_SIZES_MB[name], (name, mb)
+    with torch.device("meta"):
+        mobile = zoo.build(zoo.resolve("mobilenet_v1_025"), fused=False)
+    assert 0.4e6 < sum(p.numel() for p in mobile.parameters()) < 0.6e6
+    assert zoo.resolve("inception2").name == "googlenet" and zoo.resolve("inception4").name == "inception3"
+
+
+@pytest.mark.parametrize("name,hw", [("googlenet", 64), ("inception3", 96), ("mobilenet_v1_025", 64)])
+def test_new_cnn_architectures_run_fused_and_stock_on_cpu(name, hw):
+    torch.manual_seed(0)
+    spec = zoo.resolve(name)
+    for fused in (True, False):
+        model = zoo.build(spec, fused=fused)
+        y = model(torch.randn(2, 3, hw, hw))
+        assert y.shape == (2, 1000) and torch.isfinite(y).all()
+
+
+def test_seq2seq_lstm_forward_backward_on_cpu():
+    from tiresias_b200.models.rnn import BertEncoder, Seq2SeqLSTM
+    torch.manual_seed(0)
+    for bidir in (False, True):
+        model = Seq2SeqLSTM(vocab=97, emb=16, hidden=32, layers=2, bidirectional=bidir, fused=False)
+        tokens = torch.randint(0, 97, (3, 9))
+        logits = model(tokens)
+        assert logits.shape == (3, 9, 97)
+        torch.nn.functional.cross_entropy(logits.reshape(-1, 97), torch.roll(tokens, -1, 1).reshape(-1)).backward()
+        assert all(p.grad is not None for p in model.parameters())
+    bert = BertEncoder(vocab=101, d_model=32, n_layers=2, n_heads=4, d_ff=64, max_len=16, fused=False)
+    assert bert.head.weight is bert.tok.weight                                   # tied LM head
+    assert bert(torch.randint(0, 101, (2, 7))).shape == (2, 7, 101)

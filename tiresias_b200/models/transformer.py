@@ -32,9 +32,9 @@ def _lin(cin: int, cout: int, fused: bool, relu: bool = False, bias: bool = True
 
 
 class Block(nn.Module):
-    def __init__(self, d_model: int, n_heads: int, d_ff: int, fused: bool = True):
+    def __init__(self, d_model: int, n_heads: int, d_ff: int, fused: bool = True, causal: bool = True):
         super().__init__()
-        self.n_heads = n_heads
+        self.n_heads, self.causal = n_heads, causal
         self.ln1 = nn.LayerNorm(d_model)
         self.qkv = _lin(d_model, 3 * d_model, fused)
         self.proj = _lin(d_model, d_model, fused)
@@ -46,7 +46,7 @@ class Block(nn.Module):
         b, s, d = x.shape
         qkv = self.qkv(self.ln1(x)).view(b, s, 3, self.n_heads, d // self.n_heads)
         q, k, v = (t.transpose(1, 2) for t in qkv.unbind(dim=2))
-        a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=self.causal)
         x = x + self.proj(a.transpose(1, 2).reshape(b, s, d))
         return x + self.ff2(self.ff1(self.ln2(x)))
 

@@ -2,11 +2,12 @@
 (model/model_factory.py:19-55) and per-tensor table (core/models.py:8-20) resolves to an
 executable random-init model plus the synthetic batch shape it trains on.
 
-Names with a hand-built architecture here: resnet50/101/152, vgg11/16/19, alexnet, transformer.
-The remaining names (googlenet, inception2/3/4, mobilenet_v1_025, BERT_Chinese and the three
-OpenNMT RNN checkpoints) are executed as the *size-class stand-in* listed in ``STAND_IN``:
-the architecture here whose gradient volume and compute pattern are closest, so that the
-communication the reference prices as "model size / bandwidth" is exercised at the right scale.
+Names with their own architecture here: resnet50/101/152, vgg11/16/19, alexnet, googlenet, inception3,
+mobilenet_v1_025 (models/vision.py, models/inception.py), transformer, BERT_Chinese and the three OpenNMT
+LSTM checkpoints (models/transformer.py, models/rnn.py) — 15 of the table's 17 names, each within a few per cent
+of its checkpoint size (tests/test_models_cpu.py), so that the communication the reference prices as
+"model size / bandwidth" moves the right number of bytes. inception2 and inception4 remain *size-class
+stand-ins* (``STAND_IN``): the architecture here whose gradient volume is closest.
 """
 from __future__ import annotations
 
@@ -16,7 +17,7 @@ from typing import Callable, Dict, Tuple
 import torch
 from torch import nn
 
-from . import transformer, vision
+from . import inception, rnn, transformer, vision
 
 # Checkpoint sizes in MB, verbatim data from model/model_factory.py:19-55.
 MODEL_SIZES_MB: Dict[str, float] = {
@@ -43,8 +44,8 @@ def _img(name: str, fn: Callable[[], nn.Module]) -> ModelSpec:
     return ModelSpec(name, fn, "image", (224, 224, 3), 1000)
 
 
-def _tok(name: str, fn: Callable[[], nn.Module], seq: int = 128) -> ModelSpec:
-    return ModelSpec(name, fn, "tokens", (seq,), 32000)
+def _tok(name: str, fn: Callable[[], nn.Module], seq: int = 128, vocab: int = 32000) -> ModelSpec:
+    return ModelSpec(name, fn, "tokens", (seq,), vocab)
 
 
 REGISTRY: Dict[str, ModelSpec] = {
@@ -55,17 +56,19 @@ REGISTRY: Dict[str, ModelSpec] = {
     "vgg16": _img("vgg16", vision.vgg16),
     "vgg19": _img("vgg19", vision.vgg19),
     "alexnet": _img("alexnet", vision.alexnet),
+    "googlenet": _img("googlenet", inception.googlenet),
+    "inception3": _img("inception3", inception.inception3),
+    "mobilenet_v1_025": _img("mobilenet_v1_025", inception.mobilenet_v1_025),
+    "2_layers_lstm_gigaword": _tok("2_layers_lstm_gigaword", rnn.lstm_gigaword, seq=64, vocab=50000),
+    "1_layer_bilstm_opennmt": _tok("1_layer_bilstm_opennmt", rnn.bilstm_opennmt, seq=64, vocab=70000),
+    "4_layers_brnn": _tok("4_layers_brnn", rnn.brnn_4_layers, seq=64, vocab=90000),
+    "BERT_Chinese": _tok("BERT_Chinese", rnn.bert_chinese, seq=128, vocab=21128),
     "transformer": _tok("transformer", transformer.transformer_base),
     "transformer_base": _tok("transformer_base", transformer.transformer_base),
     "transformer_big": _tok("transformer_big", transformer.transformer_big),
 }
 
-STAND_IN: Dict[str, str] = {
-    "mobilenet_v1_025": "resnet50", "googlenet": "resnet50", "inception2": "resnet50",
-    "inception3": "resnet50", "inception4": "resnet101", "BERT_Chinese": "transformer_base",
-    "2_layers_lstm_gigaword": "transformer_base", "1_layer_bilstm_opennmt": "transformer_big",
-    "4_layers_brnn": "transformer_big",
-}
+STAND_IN: Dict[str, str] = {"inception2": "googlenet", "inception4": "inception3"}
 
 
 def build(spec: ModelSpec, fused: bool = True) -> nn.Module:
@@ -78,13 +81,13 @@ def build(spec: ModelSpec, fused: bool = True) -> nn.Module:
 
 
 def resolve(name: str) -> ModelSpec:
-    """Model spec for a trace ``model_name``; unknown names fall back to inception3's stand-in,
-    mirroring ``get_model``'s default pick (core/models.py:49-52)."""
+    """Model spec for a trace ``model_name``; unknown names fall back to inception3, mirroring
+    ``get_model``'s default pick (core/models.py:49-52)."""
     if name in REGISTRY:
         return REGISTRY[name]
     if name in STAND_IN:
         return REGISTRY[STAND_IN[name]]
-    return REGISTRY[STAND_IN["inception3"]]
+    return REGISTRY["inception3"]
 
 
 def synthetic_batch(spec: ModelSpec, batch: int, pinned: bool = True, seed: int = 0):
