@@ -16,7 +16,7 @@ from tiresias_b200.ops import native  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv", "halo1", "halo2", "halo3", "c3_1", "c3_2", "c3_3", "c3_4"])
+    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv", "halo1", "halo2", "halo3", "c3_1", "c3_2", "c3_3", "c3_4", "wgrad1", "wgrad3", "thin_stats", "stem"])
     args = ap.parse_args()
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
@@ -45,6 +45,26 @@ def main():
         x = torch.randn(256, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         w = (torch.randn(c, c, 3, 3, device=dev) / (3.0 * c ** 0.5)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         run = lambda: native.conv3x3_fprop(x, w)  # noqa: E731
+    elif args.kernel == "wgrad1":
+        # dW of ResNet-50 layer1 conv3 (1x1, 64 -> 256) at batch 256: dy^T . x with both operands as stored
+        dy = torch.randn(802816, 256, device=dev).to(torch.bfloat16)
+        x = torch.randn(802816, 64, device=dev).to(torch.bfloat16)
+        run = lambda: native.gemm(dy, x, a_mn_major=True, b_mn_major=True)  # noqa: E731
+    elif args.kernel == "wgrad3":
+        x = torch.randn(256, 128, 28, 28, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        dy = torch.randn(256, 128, 28, 28, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        run = lambda: native.conv2d_wgrad(x, dy, (3, 3), 1, 1)  # noqa: E731
+    elif args.kernel == "thin_stats":
+        # forward of layer1 conv3 with the BatchNorm-statistics epilogue
+        x = torch.randn(802816, 64, device=dev).to(torch.bfloat16)
+        w = (torch.randn(256, 64, device=dev) / 8).to(torch.bfloat16)
+        run = lambda: native.gemm_nt_stats(x, w)  # noqa: E731
+    elif args.kernel == "stem":
+        img = torch.randint(0, 256, (256, 224, 224, 3), dtype=torch.uint8, device=dev)
+        w = (torch.randn(64, 3, 7, 7, device=dev) / 12).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        yp = native.stem7x7_pack(img, (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)).permute(0, 3, 1, 2)
+        wp = native.stem7x7_weight_pack(w)
+        run = lambda: native.conv2d_fprop_stats(yp, wp, 1, 0)  # noqa: E731
     elif args.kernel == "bn":
         from tiresias_b200.ops.batchnorm import fused_bn_act
         x = torch.randn(64, 256, 56, 56, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)

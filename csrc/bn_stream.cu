@@ -284,6 +284,8 @@ struct FoldArgs {
   const float* partials;      // [nparts][C][2]
   int nparts, C;
   double count;
+  double inv_count, bessel;   // 1 / count and count / (count - 1): double-precision division costs ~1 us per
+                              // channel thread on B200, so the host does it
   const void* gamma;
   const void* beta;
   int param_dtype;
@@ -330,8 +332,8 @@ __global__ void __launch_bounds__(64 * kFoldSlices) bn_fold_kernel(const FoldArg
 #pragma unroll
   for (int i = 0; i < kFoldSlices; ++i) { S += (double)sh[0][i][chl]; Q += (double)sh[1][i][chl]; }
   if constexpr (!BWD) {
-    const double mean = S / a.count;
-    double var = Q / a.count - mean * mean;
+    const double mean = S * a.inv_count;
+    double var = Q * a.inv_count - mean * mean;
     if (var < 0.0) var = 0.0;
     const float invstd = rsqrtf((float)var + a.eps);
     a.save_mean[ch] = (float)mean;
@@ -340,7 +342,7 @@ __global__ void __launch_bounds__(64 * kFoldSlices) bn_fold_kernel(const FoldArg
     a.coef[ch] = scale;
     a.coef[a.C + ch] = load_param(a.beta, a.param_dtype, ch) - (float)mean * scale;
     if (a.running_mean) {
-      const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
+      const double unbiased = var * a.bessel;
       a.running_mean[ch] = (1.f - a.momentum) * a.running_mean[ch] + a.momentum * (float)mean;
       a.running_var[ch] = (1.f - a.momentum) * a.running_var[ch] + a.momentum * (float)unbiased;
     }
@@ -348,8 +350,8 @@ __global__ void __launch_bounds__(64 * kFoldSlices) bn_fold_kernel(const FoldArg
     store_param(a.dbeta, a.param_dtype, ch, (float)S);
     store_param(a.dgamma, a.param_dtype, ch, (float)Q);
     a.coef[ch] = load_param(a.gamma, a.param_dtype, ch) * a.invstd_in[ch];
-    a.coef[a.C + ch] = (float)(S / a.count);
-    a.coef[2 * a.C + ch] = (float)(Q / a.count);
+    a.coef[a.C + ch] = (float)(S * a.inv_count);
+    a.coef[2 * a.C + ch] = (float)(Q * a.inv_count);
   }
 }
 
@@ -407,8 +409,8 @@ __global__ void __launch_bounds__(64 * kFoldSlices) bn_fold2_kernel(const FoldAr
     Q += (double)v.y;
   }
   if constexpr (!BWD) {
-    const double mean = S / a.count;
-    double var = Q / a.count - mean * mean;
+    const double mean = S * a.inv_count;
+    double var = Q * a.inv_count - mean * mean;
     if (var < 0.0) var = 0.0;
     const float invstd = rsqrtf((float)var + a.eps);
     a.save_mean[ch] = (float)mean;
@@ -417,7 +419,7 @@ __global__ void __launch_bounds__(64 * kFoldSlices) bn_fold2_kernel(const FoldAr
     a.coef[ch] = scale;
     a.coef[a.C + ch] = load_param(a.beta, a.param_dtype, ch) - (float)mean * scale;
     if (a.running_mean) {
-      const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
+      const double unbiased = var * a.bessel;
       a.running_mean[ch] = (1.f - a.momentum) * a.running_mean[ch] + a.momentum * (float)mean;
       a.running_var[ch] = (1.f - a.momentum) * a.running_var[ch] + a.momentum * (float)unbiased;
     }
@@ -425,8 +427,8 @@ __global__ void __launch_bounds__(64 * kFoldSlices) bn_fold2_kernel(const FoldAr
     store_param(a.dbeta, a.param_dtype, ch, (float)S);
     store_param(a.dgamma, a.param_dtype, ch, (float)Q);
     a.coef[ch] = load_param(a.gamma, a.param_dtype, ch) * a.invstd_in[ch];
-    a.coef[a.C + ch] = (float)(S / a.count);
-    a.coef[2 * a.C + ch] = (float)(Q / a.count);
+    a.coef[a.C + ch] = (float)(S * a.inv_count);
+    a.coef[2 * a.C + ch] = (float)(Q * a.inv_count);
   }
 }
 
@@ -485,6 +487,7 @@ int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamm
                   size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters) {
   FoldArgs f{};
   f.C = C; f.count = (double)rows; f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype;
+  f.inv_count = 1.0 / f.count; f.bessel = f.count > 1.0 ? f.count / (f.count - 1.0) : 1.0;
   f.running_mean = running_mean; f.running_var = running_var; f.momentum = momentum; f.eps = eps;
   f.save_mean = save_mean; f.save_invstd = save_invstd; f.coef = coef;
   if (conv_partials) {
@@ -570,6 +573,7 @@ int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamm
   if (rc) return rc;
   FoldArgs f{};
   f.partials = partials; f.nparts = grid; f.C = C; f.count = (double)rows;
+  f.inv_count = 1.0 / f.count; f.bessel = f.count > 1.0 ? f.count / (f.count - 1.0) : 1.0;
   f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype; f.coef = coef;
   f.dgamma = dgamma; f.dbeta = dbeta; f.invstd_in = save_invstd;
   if (int rc2 = launch_fold<true>(f, fold_tmp, counters, stream)) return rc2;
@@ -596,6 +600,7 @@ extern "C" int tb200_bn_finalize(const float* partials, int nparts, double count
   if (!partials || nparts <= 0 || C <= 0 || count <= 0) return fail("tb200_bn_finalize: empty input%s");
   FoldArgs f{};
   f.partials = partials; f.nparts = nparts; f.C = C; f.count = count;
+  f.inv_count = 1.0 / count; f.bessel = count > 1.0 ? count / (count - 1.0) : 1.0;
   f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype;
   f.running_mean = running_mean; f.running_var = running_var; f.momentum = momentum; f.eps = eps;
   f.save_mean = save_mean; f.save_invstd = save_invstd; f.coef = scale_shift;

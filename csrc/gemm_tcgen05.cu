@@ -970,15 +970,17 @@ struct Workspace {
   size_t bytes = 0;
 };
 std::mutex g_ws_mutex;
-std::unordered_map<int, Workspace> g_ws;  // per device split-K scratch, grown on demand
+// split-K scratch, grown on demand, one per (device, stream): jobs that share a GPU (exec/ packs up to three
+// single-GPU jobs per device, each on its own streams) must not share partial sums
+std::unordered_map<unsigned long long, Workspace> g_ws;
 
 int sm_count() { return device_sm_count(); }
 
-int get_workspace(size_t bytes, float** out) {
+int get_workspace(size_t bytes, cudaStream_t stream, float** out) {
   int dev = 0;
   TB_CUDA_OK(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> lock(g_ws_mutex);
-  Workspace& w = g_ws[dev];
+  Workspace& w = g_ws[((unsigned long long)(uintptr_t)stream << 6) ^ (unsigned long long)dev];
   if (w.bytes < bytes) {
     // Growing frees the old block; callers on other streams must not be using it. The
     // Python layer sizes the workspace up-front (tb200_gemm_reserve) before graph capture.
@@ -1106,6 +1108,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   const int sms = sm_count();
   int block_n = 0, splits = 1;
   if (int rc = plan_tiles(M, N, K, pull, rows_per_rank, sms, &block_n, &splits)) return rc;
+  if (conv && conv->g.sc_on) splits = 1;      // the split-K second pass writes rows in order, not scattered
   p.num_n = (N + block_n - 1) / block_n;
   const int tiles = p.num_m * p.num_n;
   p.splits = splits;
@@ -1122,7 +1125,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
         return 4;
       }
       p.partials = fixed_scratch;
-    } else if (int rc = get_workspace(need, &p.partials)) {
+    } else if (int rc = get_workspace(need, stream, &p.partials)) {
       return rc;
     }
   }
@@ -1405,7 +1408,12 @@ int tb200_gemm_plan_splits(int M, int N, int K) {
 // inside the captured region).
 int tb200_gemm_reserve(size_t bytes) {
   float* unused = nullptr;
-  return get_workspace(bytes, &unused);
+  return get_workspace(bytes, nullptr, &unused);
+}
+
+int tb200_gemm_reserve_stream(size_t bytes, cudaStream_t stream) {
+  float* unused = nullptr;
+  return get_workspace(bytes, stream, &unused);
 }
 
 }  // extern "C"

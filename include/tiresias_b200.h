@@ -217,8 +217,11 @@ int tb200_probe_shifted_operand(const void* A, const void* B, float* D, int shif
  * [256 reduction rows, 64] read as an MN-major operand whose descriptor starts `shift` rows into the tile. */
 int tb200_probe_shifted_mn_operand(const void* A, const void* B, float* D, int shift, cudaStream_t stream);
 
-/* Pre-size the per-device split-K scratch of the GEMM (call before CUDA-graph capture). */
+/* Pre-size the split-K scratch of the GEMM (call before CUDA-graph capture). The scratch is kept per
+ * (device, stream) so that jobs sharing a GPU on different streams never share partial sums; this call sizes
+ * the one of the current device's NULL stream, tb200_gemm_reserve_stream the one of `stream`.               */
 int tb200_gemm_reserve(size_t bytes);
+int tb200_gemm_reserve_stream(size_t bytes, cudaStream_t stream);
 
 /* ---- tb200_gemm_bf16_nt without any allocation (no counterpart in the reference, which has
  *      no native code). Same arguments, same kernels and same results as tb200_gemm_bf16_nt.

@@ -141,3 +141,40 @@ def test_fd_exchange_between_ranks():
                           "--master-addr", "127.0.0.1", "--master-port", str(port),
                           os.path.join(root, "tests", "fd_worker.py")], capture_output=True, text=True, timeout=120)
     assert res.returncode == 0 and "FD OK" in res.stdout, (res.stdout + res.stderr)[-2000:]
+
+
+@pytest.mark.timeout(300)
+def test_replay_packed_single_gpu_jobs_loopback(tmp_path):
+    """Executed co-location (reference: up to 3 tasks per device, infra/device.py:49-59): with one GPU slot left
+    busy, a third single-GPU job joins a GPU that already runs one instead of waiting; the workers emulate the
+    slowdown table on the CPU backend and the fifo-pack simulation of the same trace agrees with what ran."""
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(1, 0, 150, "resnet50"), (1, 0, 150, "resnet50"), (1, 0.3, 40, "vgg16")])
+    res = replay(trace, gpus=2, schedule="fifo", comm="ps", out=str(tmp_path / "o"), loopback=True, step_sleep=0.01,
+                 pack=True, max_share=3, interference=[1.0, 1.5, 2.0])
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert all(r["status"] == "DONE" for r in recs.values())
+    assert recs["2"]["start"] < min(recs["0"]["end"], recs["1"]["end"])       # did not wait for a free GPU
+    log = open(tmp_path / "o" / "controller.log").read()
+    assert "shares the GPU with 1" in log
+    # the host of the third job ran slower than the undisturbed one
+    shared_with = "0" if recs["0"]["end"] > recs["1"]["end"] else "1"
+    other = "1" if shared_with == "0" else "0"
+    assert recs[shared_with]["end"] > recs[other]["end"] + 0.1
+    assert res["pack"] and res["comparison"]["n"] == 3
+    assert abs(res["comparison"]["avg_jct_error_pct"]) < 25.0
+
+
+@pytest.mark.timeout(300)
+def test_replay_gandiva_time_slicing_loopback(tmp_path):
+    """Executed Gandiva time slicing (reference core/scheduling/algorithm.py:418-438): two jobs that both need the
+    whole box take turns quantum by quantum; each is preempted at least once and both finish."""
+    from tiresias_b200.exec.replay import replay
+    trace = _write_trace(tmp_path / "t.csv", [(2, 0, 150, "resnet50"), (2, 0.2, 100, "vgg16")])
+    res = replay(trace, gpus=2, schedule="gandiva", comm="ps", out=str(tmp_path / "o"), loopback=True, step_sleep=0.01,
+                 check_every=5, quantum_s=0.5)
+    recs = {r["job_id"]: r for r in res["records"]}
+    assert all(r["status"] == "DONE" for r in recs.values())
+    assert recs["0"]["preempt"] >= 1 and recs["1"]["preempt"] >= 1
+    assert recs["1"]["start"] < recs["0"]["end"]                               # the second job did not wait for the first
+    assert res["comparison"]["n"] == 2

@@ -336,3 +336,28 @@ def test_cross_node_job_network_load_follows_the_switch_formula(tmp_path):
         want.append(round(traffic, 1))
     assert [nd["network"] for nd in nodes] == pytest.approx(want, abs=0.2)
     assert want[0] == pytest.approx(size * 2, abs=0.2)      # shard terms cancel when half the workers are local
+
+
+def test_fifo_pack_shares_a_gpu_at_the_measured_slowdown(tmp_path):
+    # The executor's packing mode, simulated (sim/legacy/schedulers.py::fifo_shared). 2 GPUs, slowdown table
+    # [1, 1.5, 2]: j0, j1 (1 GPU, 100 s) take a GPU each at t=0; j2 (1 GPU, 30 s) arrives at 10 with no GPU free and
+    # joins the shared GPU with the fewest tenants (GPU 0, j0). Both then advance at 1/1.5: j2 needs 45 s -> ends 55;
+    # j0 has done 10 + 45/1.5 = 40 by then and finishes its other 60 alone at 115. j1, undisturbed, ends at 100.
+    jobs = [(1, 0, 100), (1, 0, 100), (1, 10, 30)]
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    rows, s, _ = _sim(tmp_path / "a", jobs, "fifo-pack", gpus=2, extra=("--pack_slowdown", "1,1.5,2"))
+    assert _ints(rows[2], "start_time", "end_time") == (10, 55)
+    assert _ints(rows[0], "end_time") == (115,) and _ints(rows[1], "end_time") == (100,)
+    # one tenant per GPU: the same loop is plain fifo and the late job waits for a GPU
+    rows, s, _ = _sim(tmp_path / "b", jobs, "fifo-pack", gpus=2, extra=("--pack_max_share", "1"))
+    assert _ints(rows[2], "start_time", "end_time") == (100, 130)
+
+
+def test_gandiva_slice_round_robins_while_jobs_wait(tmp_path):
+    # The executor's gandiva policy, simulated: 2 GPUs, quantum 30. j0 (2 GPUs, 100 s) starts at 0; j1 (2 GPUs, 40 s)
+    # arrives at 5 and waits. t=30: j0 has held the GPUs for a quantum -> preempted (30 done), j1 runs; t=60: j1
+    # (30 done) yields to j0; t=90: j0 (60 done) yields to j1, which needs 10 more -> done at 100; j0 then runs its
+    # last 40 s undisturbed (nothing waits, no slicing) -> 140.
+    rows, s, _ = _sim(tmp_path, [(2, 0, 100), (2, 5, 40)], "gandiva-slice", gpus=2, extra=("--slice_quantum", "30"))
+    assert _ints(rows[1], "start_time", "end_time", "preempt") == (30, 100, 1)
+    assert _ints(rows[0], "start_time", "end_time", "preempt") == (0, 140, 2)

@@ -9,6 +9,17 @@ simulator's (tiresias_b200.sim.legacy.schedulers):
 ``sjf``       preemptive, fewest GPUs first
 ``shortest``  preemptive, least remaining iterations first
 ``dlas-gpu``  preemptive two-level (or more) MLFQ on attained GPU-seconds with ``queue_limit`` thresholds
+``gittins``   preemptive, highest Gittins index of the attained GPU-time first
+``gandiva``   fifo with Gandiva's time slicing (reference core/scheduling/algorithm.py:418-438): while jobs are
+              waiting, a job that has held its GPUs for a whole quantum is preempted and re-queued. The reference
+              re-inserts it at the FRONT of its list queue, where its fifo would hand the GPUs
+              straight back to it; the executor re-queues at the BACK, i.e. real round-robin slicing
+
+``pack=True`` executes what the reference's device model allows (infra/device.py:49-59: up to 3 tasks per
+device): single-GPU jobs may share a GPU with up to ``max_share - 1`` other single-GPU jobs — they run as
+threads of that GPU's worker process, same CUDA context, own streams, really concurrent. A free GPU is
+preferred; only when none is left does a job join the shared GPU with the fewest tenants. Multi-GPU jobs
+keep exclusive aligned blocks.
 
 Preemption is executable here (the reference only flips a flag, core/jobs/jobs_manager.py:150-173): the
 job's ranks snapshot their PS shards and the job later resumes from the iteration it reached, possibly on
@@ -60,7 +71,8 @@ class Controller:
                  queue_limit: Sequence[float] = (20.0,), check_every: int = 10, poll_s: float = 0.02,
                  job_timeout_s: float = 600.0, step_sleep: float = 0.0, graph: bool = True, log=print,
                  job_dist_s: Optional[Sequence[float]] = None, gittins_delta_s: float = 2.0,
-                 est_iter_s: float = 0.05, iter_table: Optional[Dict] = None):
+                 est_iter_s: float = 0.05, iter_table: Optional[Dict] = None, pack: bool = False,
+                 max_share: int = 3, quantum_s: float = 10.0, interference: Optional[Sequence[float]] = None):
         self.store, self.num_gpus, self.policy, self.comm = store, num_gpus, policy, comm
         self.time_scale, self.ckpt_dir, self.check_every, self.poll_s = time_scale, ckpt_dir, check_every, poll_s
         self.queue_limit = list(queue_limit)
@@ -90,6 +102,9 @@ class Controller:
             self.gittins_samples_ms = [max(1, int(round(v * 1000.0))) for v in samples]
             self.gittins_table = gi.gittins_table(self.gittins_samples_ms,
                                                   max(1, int(round(gittins_delta_s * 1000.0))))
+        self.pack, self.max_share, self.quantum_s = bool(pack), max(1, int(max_share)), float(quantum_s)
+        self.interference = list(interference) if interference else None   # loopback: emulated slowdown per tenancy
+        self.tenants: Dict[int, List[str]] = {}    # GPU -> ids of the single-GPU jobs sharing it (pack mode)
         self.t0 = 0.0
         self.pending: List[ExecJob] = []           # fifo: arrived, could not start yet
         self.queues: List[List[ExecJob]] = []      # dlas-gpu: the MLFQ, as explicit lists like the simulator's
@@ -116,21 +131,41 @@ class Controller:
             self._send(r, {"op": "exit"})
 
     def _start(self, job: ExecJob, now: float) -> bool:
+        shared = self.pack and job.gpus == 1
         blk = self.alloc.alloc(job.gpus, job.job_id)
+        if blk is None and shared:
+            # no free GPU: join the shared GPU with the fewest tenants, if one has room
+            room = [(len(t), g) for g, t in self.tenants.items() if 0 < len(t) < self.max_share]
+            if room:
+                blk = (min(room)[1], 1)
         if blk is None:
             return False
+        if shared:
+            self.tenants.setdefault(blk[0], []).append(job.job_id)
         job.block, job.status, job.last_start = blk, "RUNNING", now
         if job.first_start is None:
             job.first_start = now
         cmd = {"op": "run", "job": job.job_id, "attempt": job.attempt, "model": job.model, "batch": job.batch,
                "iters": job.iters, "done": job.done, "mode": self.comm, "block": list(blk),
                "resume": job.attempt > 0, "ckpt_dir": self.ckpt_dir, "check_every": self.check_every,
-               "step_sleep": self.step_sleep, "graph": self.graph}
+               "step_sleep": self.step_sleep, "graph": self.graph, "shared": shared,
+               "interference": self.interference}
         for r in range(blk[0], blk[0] + blk[1]):
             self._send(r, cmd)
         self.log(f"[{now:8.2f}s] start job {job.job_id} ({job.model}, {job.gpus} GPU, it {job.done}/{job.iters}) "
-                 f"on GPUs {blk[0]}..{blk[0] + blk[1] - 1}" + (" (resume)" if job.attempt else ""))
+                 f"on GPUs {blk[0]}..{blk[0] + blk[1] - 1}" + (" (resume)" if job.attempt else "")
+                 + (f" (shares the GPU with {len(self.tenants[blk[0]]) - 1})" if shared and len(self.tenants[blk[0]]) > 1 else ""))
         return True
+
+    def _release(self, job: ExecJob) -> None:
+        """Give the job's GPUs back; a shared GPU returns to the allocator when its last tenant leaves."""
+        if self.pack and job.gpus == 1 and job.block is not None and job.job_id in self.tenants.get(job.block[0], ()):
+            left = self.tenants[job.block[0]]
+            left.remove(job.job_id)
+            if not left:
+                self.alloc.free(job.block)
+        elif job.block is not None:
+            self.alloc.free(job.block)
 
     def _request_preempt(self, job: ExecJob, now: float) -> None:
         if job.status == "RUNNING":
@@ -148,14 +183,14 @@ class Controller:
             if not self.store.check(keys):
                 if now - job.last_start > self.job_timeout_s:           # watchdog
                     job.status, job.end = "FAILED", now
-                    self.alloc.free(job.block)
+                    self._release(job)
                     changed = True
                     self.log(f"[{now:8.2f}s] job {job.job_id} timed out")
                 continue
             res = [json.loads(self.store.get(k)) for k in keys]
             job.results.append({"attempt": job.attempt, "block": list(job.block), "ranks": res,
                                 "t_start": job.last_start, "t_end": now})
-            self.alloc.free(job.block)
+            self._release(job)
             job.attained += now - job.last_start
             job.block = None
             changed = True
@@ -197,6 +232,27 @@ class Controller:
                 if j.status == "WAITING" and not self._start(j, now):
                     self.pending.append(j)
             self.pending.sort(key=lambda j: j.gpus)
+            return
+        if self.policy == "gandiva":
+            # fifo over an explicit waiting list + time slicing: preempted jobs come back in `waiting` with
+            # attempt > 0 and rejoin the list at the back; the list is served in order until the first job that
+            # does not fit; then, while anything still waits, every job that has held its GPUs for a whole
+            # quantum is asked to leave.
+            for j in waiting:
+                if j.job_id not in self.seen:
+                    self.seen.add(j.job_id)
+                    self.pending.append(j)
+                elif j not in self.pending:
+                    self.pending.append(j)
+            for j in list(self.pending):
+                if self._start(j, now):
+                    self.pending.remove(j)
+                else:
+                    break
+            if self.pending:
+                for j in running:
+                    if j.status == "RUNNING" and now - j.last_start >= self.quantum_s:
+                        self._request_preempt(j, now)
             return
         # preemptive family: rank all runnable jobs, give GPUs by counting in that order
         runnable = waiting + running
@@ -277,7 +333,7 @@ class Controller:
             if self.policy == "gittins" and now >= self._next_unit:      # the simulator's extra wake-up
                 self._next_unit = (int(now / self.gittins_delta_s) + 1) * self.gittins_delta_s
                 tick = True
-            if changed or arrivals or tick or self.policy == "dlas-gpu":
+            if changed or arrivals or tick or self.policy in ("dlas-gpu", "gandiva"):
                 self._schedule(now)
             time.sleep(self.poll_s)
         return self.jobs

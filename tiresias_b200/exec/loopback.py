@@ -38,6 +38,7 @@ class LoopbackTrainer:
         self.x = torch.randn(16, 32, generator=g)
         self.y = torch.randint(0, 8, (16,), generator=g)
         self._loss = float("nan")
+        self.slowdown = lambda: 1.0               # co-location emulation hook (exec/worker.py)
         self._scatter_back()
 
     def _scatter_back(self) -> None:
@@ -77,7 +78,7 @@ class LoopbackTrainer:
         self._scatter_back()
         self._steps += 1
         if self.step_sleep:
-            time.sleep(self.step_sleep)
+            time.sleep(self.step_sleep * self.slowdown())
 
     def _gloo_reduce_scatter(self, out: torch.Tensor, full: torch.Tensor) -> None:
         buf = full.clone()

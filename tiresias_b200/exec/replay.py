@@ -31,7 +31,8 @@ from ..sim.trace import read_tiresias_trace
 from .controller import Controller
 
 MS = 1000.0
-SIM_SCHEDULE = {"fifo": "fjf", "sjf": "sjf", "shortest": "shortest", "dlas-gpu": "dlas-gpu", "gittins": "gittins"}
+SIM_SCHEDULE = {"fifo": "fjf", "sjf": "sjf", "shortest": "shortest", "dlas-gpu": "dlas-gpu", "gittins": "gittins",
+                "gandiva": "gandiva-slice"}
 
 
 def _free_port() -> int:
@@ -105,7 +106,8 @@ def _lookup(table: Dict, model: str, gpus: int, default: float) -> float:
 
 def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, gpus: int, schedule: str,
              queue_limit_s: Sequence[float], out_dir: str, scheme: str = "buddy",
-             gittins_delta_s: float = 2.0, job_dist_ms: Optional[Sequence[int]] = None) -> Dict[str, Dict]:
+             gittins_delta_s: float = 2.0, job_dist_ms: Optional[Sequence[int]] = None, pack: bool = False,
+             max_share: int = 3, slowdown: Optional[Sequence[float]] = None, quantum_s: float = 10.0) -> Dict[str, Dict]:
     """Event simulation in milliseconds on a 1 x 1 x ``gpus`` cluster. ``scheme="buddy"`` places jobs on
     aligned power-of-two GPU blocks like the worker pool does (non-preemptive schedules); the preemptive
     ones hand out GPUs by counting, as their reference loops do."""
@@ -122,8 +124,15 @@ def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, g
                          "iterations": row["iterations"], "model_name": rec["model"],
                          "duration": max(1, int(round((st + it * row["iterations"]) * MS))), "interval": 0})
     flags = define_simulator_flags()
-    argv = ["--schedule", SIM_SCHEDULE[schedule], "--scheme", scheme, "--num_switch", "1", "--num_node_p_switch", "1",
+    sim_schedule = "fifo-pack" if (pack and schedule == "fifo") else SIM_SCHEDULE[schedule]
+    argv = ["--schedule", sim_schedule, "--scheme", scheme, "--num_switch", "1", "--num_node_p_switch", "1",
             "--num_gpu_p_node", str(gpus), "--quiet"]
+    if sim_schedule == "fifo-pack":
+        # co-located single-GPU jobs advance at the measured rate for their tenancy
+        argv += ["--pack_max_share", str(max_share), "--pack_slowdown",
+                 ",".join(str(v) for v in (slowdown or calibration.get("interference_table") or (1.0, 1.2, 1.2)))]
+    if sim_schedule == "gandiva-slice":
+        argv += ["--slice_quantum", str(int(round(quantum_s * MS)))]
     if schedule == "dlas-gpu":
         argv += ["--queue_limit", ",".join(str(int(q * MS)) for q in queue_limit_s)]
     if schedule == "gittins":
@@ -136,7 +145,7 @@ def simulate(rows: Sequence[Dict], records: Sequence[Dict], calibration: Dict, g
             with open(dist_path, "w") as fh:
                 fh.write("duration\n" + "".join(f"{int(v)}\n" for v in job_dist_ms))
             argv += ["--job_dist", dist_path]
-    if schedule != "fifo":
+    if schedule not in ("fifo",):
         # restart cost of a resumed job, measured in this very replay: start-up + shard snapshot
         pre = [r for r in records if r.get("preempt")]
         if pre:
@@ -207,7 +216,8 @@ def _iter_table(calibration_path: Optional[str]) -> Optional[Dict]:
 def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out: str = "replay_out",
            calibration_path: Optional[str] = None, loopback: bool = False, batch: int = 32, time_scale: float = 1.0,
            queue_limit_s: Sequence[float] = (20.0,), check_every: int = 10, step_sleep: float = 0.0,
-           iters_scale: float = 1.0, graph: bool = True, gittins_delta_s: float = 2.0) -> Dict:
+           iters_scale: float = 1.0, graph: bool = True, gittins_delta_s: float = 2.0, pack: bool = False,
+           max_share: int = 3, quantum_s: float = 10.0, interference: Optional[Sequence[float]] = None) -> Dict:
     os.makedirs(out, exist_ok=True)
     rows = read_tiresias_trace(trace)
     for r in rows:
@@ -226,7 +236,8 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
                      ckpt_dir=ckpt_dir, queue_limit=queue_limit_s, check_every=check_every, step_sleep=step_sleep,
                      graph=graph, log=log, gittins_delta_s=gittins_delta_s,
                      est_iter_s=_estimated_iter_s(calibration_path, step_sleep),
-                     iter_table=_iter_table(calibration_path))
+                     iter_table=_iter_table(calibration_path), pack=pack, max_share=max_share, quantum_s=quantum_s,
+                     interference=interference if loopback else None)
     try:
         ctl.wait_ready()
         t_pool = time.time()
@@ -244,9 +255,16 @@ def replay(trace: str, gpus: int, schedule: str = "fifo", comm: str = "ps", out:
             calibration = json.load(fh)
     else:
         calibration = calibration_from_records(records)
+    if pack and not calibration_path:
+        # self-calibration under packing: a job's own iteration time already contains the sharing it saw, so the
+        # solo time is taken from the fastest attempt of its (model, GPUs) class
+        calibration = calibration_from_records(records, reduce="min")
     sim = simulate(rows, records, calibration, gpus, schedule, queue_limit_s, os.path.join(out, "sim"),
-                   "buddy" if schedule == "fifo" else "count", gittins_delta_s, ctl.gittins_samples_ms)
+                   "buddy" if schedule in ("fifo", "gandiva") else "count", gittins_delta_s, ctl.gittins_samples_ms,
+                   pack=pack, max_share=max_share, slowdown=interference or calibration.get("interference_table"),
+                   quantum_s=quantum_s)
     result = {"trace": trace, "gpus": gpus, "schedule": schedule, "comm": comm, "loopback": loopback,
+              "pack": pack, "max_share": max_share, "quantum_s": quantum_s,
               "queue_limit_s": list(queue_limit_s),
               "wall_s": round(wall, 2), "calibration_source": calibration.get("source", calibration_path),
               "records": records, "comparison": compare(records, sim)}
@@ -295,6 +313,11 @@ def main(argv: Optional[Sequence[str]] = None) -> None:
     ap.add_argument("--check-every", type=int, default=10)
     ap.add_argument("--step-sleep", type=float, default=0.0, help="loopback only: seconds per iteration")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--pack", action="store_true", help="let single-GPU jobs share a GPU (up to --max-share)")
+    ap.add_argument("--max-share", type=int, default=3)
+    ap.add_argument("--quantum", type=float, default=10.0, help="gandiva: time slice in seconds")
+    ap.add_argument("--interference", default=None, help="slowdown per tenancy, comma separated (simulation side; "
+                                                         "on the loopback backend also emulated by the workers)")
     a = ap.parse_args(list(argv) if argv is not None else None)
     if a.resimulate:
         res = resimulate(a.resimulate, a.calibration, a.sim_scheme)
@@ -302,7 +325,8 @@ def main(argv: Optional[Sequence[str]] = None) -> None:
         return
     res = replay(a.trace, a.gpus, a.schedule, a.comm, a.out, a.calibration, a.loopback, a.batch, a.time_scale,
                  [float(x) for x in a.queue_limit.split(",")], a.check_every, a.step_sleep, a.iters_scale,
-                 not a.no_graph, a.gittins_delta)
+                 not a.no_graph, a.gittins_delta, a.pack, a.max_share, a.quantum,
+                 [float(x) for x in a.interference.split(",")] if a.interference else None)
     c = res["comparison"]
     print(json.dumps({k: v for k, v in c.items() if k != "jobs"}))
 

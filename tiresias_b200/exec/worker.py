@@ -14,6 +14,11 @@ Protocol (a ``TCPStore`` served by the controller):
   controller -> job    : key ``preempt/<job>/<attempt>`` (existence = please stop)
   rank -> controller   : key ``res/<job>/<attempt>/<rank_in_block>`` = JSON result
 
+Packing (reference: up to 3 tasks per device, infra/device.py:49-59): a ``run`` command with ``"shared": true``
+(single-GPU jobs only) is executed in a thread of its own inside the GPU's worker process — same CUDA context,
+its own streams — while the command loop keeps listening, so up to three jobs really run concurrently on one
+B200 (kernels of different streams overlap; no context time-slicing). Exclusive jobs run inline as before.
+
 A run trains ``iters - done`` iterations of the job's model on the block's GPUs with the requested
 communication mode (``ps`` fused push/pull kernels, ``ring`` in-kernel all-reduce, ``nccl`` baseline).
 Every ``check_every`` iterations the ranks agree (max over a gloo all-reduce) whether a preemption was
@@ -36,10 +41,18 @@ import torch.distributed as dist
 from .buddy import all_blocks
 
 
+TENANTS = [0]        # single-GPU jobs currently sharing this worker's GPU (threads of this process)
+
+
 def _make_trainer(cmd: Dict, rank_in_block: int, size: int, group, nccl_group, loopback: bool, device):
     if loopback:
         from .loopback import LoopbackTrainer
-        return LoopbackTrainer(cmd["model"], rank_in_block, size, group, step_sleep=cmd.get("step_sleep", 0.0))
+        tr = LoopbackTrainer(cmd["model"], rank_in_block, size, group, step_sleep=cmd.get("step_sleep", 0.0))
+        table = cmd.get("interference")
+        if table and cmd.get("shared"):
+            # emulate co-location on CPU: a step takes slowdown[tenants - 1] times its solo time
+            tr.slowdown = lambda: float(table[min(max(TENANTS[0], 1), len(table)) - 1])
+        return tr
     from ..models import zoo
     from ..parallel.symm import SymmetricWorld
     from ..parallel.trainer import Trainer
@@ -55,6 +68,18 @@ def run_job(cmd: Dict, rank: int, store, groups, nccl_groups, loopback: bool, de
     r = rank - start
     grp = groups[(start, size)]
     t_begin = time.time()
+    shared = bool(cmd.get("shared")) and size == 1
+    if shared:
+        TENANTS[0] += 1
+    try:
+        return _run_job_body(cmd, rank, store, groups, nccl_groups, loopback, device, r, size, grp, t_begin)
+    finally:
+        if shared:
+            TENANTS[0] -= 1
+
+
+def _run_job_body(cmd, rank, store, groups, nccl_groups, loopback, device, r, size, grp, t_begin) -> Dict:
+    start = cmd["block"][0]
     trainer = _make_trainer(cmd, r, size, grp, nccl_groups.get((start, size)), loopback, device)
     ckpt = os.path.join(cmd["ckpt_dir"], f"{cmd['job']}_{r}.pt")
     if cmd.get("resume"):
@@ -168,20 +193,43 @@ def main() -> None:
             nccl_groups[blk] = dist.new_group(ranks, backend="nccl")
     store = dist.TCPStore(args.ctl_host, args.ctl_port, is_master=False, timeout=__import__("datetime").timedelta(days=1))
     store.set(f"ready/{rank}", "1")
+    import threading
+
+    def run_and_report(cmd: Dict, own_client: bool = False) -> None:
+        # a tenant thread talks to the controller over its own connection: the command loop's client is parked
+        # in a blocking get() most of the time
+        st = store
+        if own_client:
+            st = dist.TCPStore(args.ctl_host, args.ctl_port, is_master=False,
+                               timeout=__import__("datetime").timedelta(days=1))
+        try:
+            if device is not None:
+                torch.cuda.set_device(device)                # per thread
+            res = run_job(cmd, rank, st, groups, nccl_groups, args.loopback, device)
+        except Exception as exc:                             # report instead of dying: the pool survives
+            res = {"job": cmd.get("job"), "attempt": cmd.get("attempt"), "rank": rank - cmd["block"][0],
+                   "status": "failed", "error": f"{type(exc).__name__}: {exc}", "trace": traceback.format_exc()[-1500:],
+                   "t_end": time.time()}
+        st.set(f"res/{cmd['job']}/{cmd['attempt']}/{res['rank']}", json.dumps(res))
+
     seq = 0
+    tenants = []
     while True:
         raw = store.get(f"cmd/{rank}/{seq}")              # blocks until the controller posts it
         seq += 1
         cmd = json.loads(raw)
         if cmd["op"] == "exit":
             break
-        try:
-            res = run_job(cmd, rank, store, groups, nccl_groups, args.loopback, device)
-        except Exception as exc:                             # report instead of dying: the pool survives
-            res = {"job": cmd.get("job"), "attempt": cmd.get("attempt"), "rank": rank - cmd["block"][0],
-                   "status": "failed", "error": f"{type(exc).__name__}: {exc}", "trace": traceback.format_exc()[-1500:],
-                   "t_end": time.time()}
-        store.set(f"res/{cmd['job']}/{cmd['attempt']}/{res['rank']}", json.dumps(res))
+        tenants = [t for t in tenants if t.is_alive()]
+        if cmd.get("shared") and cmd["block"][1] == 1:
+            # a packed single-GPU job: runs beside this GPU's other tenants, the loop keeps listening
+            t = threading.Thread(target=run_and_report, args=(cmd, True), daemon=True)
+            t.start()
+            tenants.append(t)
+        else:
+            run_and_report(cmd)
+    for t in tenants:
+        t.join()
     dist.barrier()
     dist.destroy_process_group()
 

@@ -15,11 +15,14 @@ from torch import nn
 
 from . import native
 
-_scratch: Dict[int, torch.Tensor] = {}
+_scratch: Dict[tuple, torch.Tensor] = {}
 
 
 def _get_scratch(device: torch.device) -> torch.Tensor:
-    key = device.index if device.index is not None else torch.cuda.current_device()
+    """One scratch (counters, partials, coefficients) per (device, stream): calls on one stream are ordered,
+    and jobs that share a GPU (exec/ packs single-GPU jobs, each on its own streams) never share one."""
+    dev = device.index if device.index is not None else torch.cuda.current_device()
+    key = (dev, torch.cuda.current_stream(device).cuda_stream)
     buf = _scratch.get(key)
     if buf is None:
         buf = torch.zeros(native.BN_SCRATCH_FLOATS, dtype=torch.float32, device=device)

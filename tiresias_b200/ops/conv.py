@@ -29,6 +29,7 @@ from . import native
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x: torch.Tensor, weight: torch.Tensor, ops: frozenset = frozenset("fdw"), want_stats: bool = False):
+        ctx.set_materialize_grads(False)      # no zeros kernel for the statistics output's (absent) gradient
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         n, cin, h, w = x.shape
@@ -55,6 +56,8 @@ class _Conv1x1Fn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor, _dstats=None):
+        if dy is None:
+            return None, None, None, None
         x2d, w2d = ctx.saved_tensors
         n, cin, h, w, cout = ctx.shape
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -146,6 +149,7 @@ class _Conv2dFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x: torch.Tensor, weight: torch.Tensor, stride: int, pad: int, ops: frozenset, want_stats: bool):
+        ctx.set_materialize_grads(False)
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         if not weight.is_contiguous(memory_format=torch.channels_last):
@@ -176,6 +180,8 @@ class _Conv2dFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor, _dstats=None):
+        if dy is None:
+            return None, None, None, None, None, None
         x, weight = ctx.saved_tensors
         stride, pad, ops = ctx.geom
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -234,6 +240,7 @@ class _PackedStemFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, y_packed: torch.Tensor, weight: torch.Tensor, want_stats: bool):
+        ctx.set_materialize_grads(False)
         if not weight.is_contiguous(memory_format=torch.channels_last):
             weight = weight.contiguous(memory_format=torch.channels_last)
         wp = native.stem7x7_weight_pack(weight)
@@ -250,6 +257,8 @@ class _PackedStemFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor, _dstats=None):
+        if dy is None:
+            return None, None, None
         (y_packed,) = ctx.saved_tensors
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)

@@ -137,6 +137,11 @@ def define_simulator_flags(fs: Optional[FlagSet] = None) -> FlagSet:
                                               "gandiva-legacy): unit = 1 per job as in the reference's live table "
                                               "(packing never engages) | table = the reference's commented-out "
                                               "per-model shares (core/models.py:21)")
+    fs.define_integer("pack_max_share", 3, "fifo-pack: single-GPU jobs per GPU (reference device limit: 3)")
+    fs.define_string("pack_slowdown", "1,1.2,1.2", "fifo-pack: slowdown of a job sharing its GPU with 0, 1, 2 others "
+                                                    "(reference: 1 + interference FACTOR 0.2; measured table from "
+                                                    "calib/interference.py in calibrated runs)")
+    fs.define_integer("slice_quantum", 100, "gandiva-slice: time slice in trace time units (reference: 100 ticks)")
     fs.define_float("solve_starvation", 0, "DLAS starvation knob: promote when pending >= x * executed")
     fs.define_integer("resume_overhead", 0, "time units charged to a job each time it resumes after a "
                                             "preemption (measured restart cost; 0 = free, as in the reference)")

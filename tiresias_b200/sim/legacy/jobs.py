@@ -30,7 +30,7 @@ class TJob:
                  "total_executed_time", "executed_time", "pending_time", "last_pending_time",
                  "remaining_time", "remaining_gputime", "remaining_expected", "q_id", "rank", "preempt",
                  "resume", "promote", "placements", "gpus", "model", "ps_network", "w_network",
-                 "model_scale", "last_start_time")
+                 "model_scale", "last_start_time", "progress", "slice_start")
 
     def __init__(self, row: dict, idx: int):
         self.job_idx = idx

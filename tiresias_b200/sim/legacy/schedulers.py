@@ -584,6 +584,128 @@ def gpu_demands(sim: Sim) -> None:
         sim.mark(now)
 
 
+
+# ---- the execution backend's packing / time-slicing policies, simulated ------------------------------------------------
+
+def fifo_shared(sim: Sim, max_share: int = 1, slowdown: Optional[List[float]] = None, quantum: int = 0) -> None:
+    """``fifo-pack`` and ``gandiva-slice``: the simulated twins of the real-time controller's ``pack`` mode and
+    ``gandiva`` policy (tiresias_b200/exec/controller.py), so that executed and simulated JCTs can be compared.
+
+    The reference models both ideas without executing either: up to 3 tasks share a device and a sharing job runs
+    ``1 + FACTOR`` slower (infra/device.py:49-59, infra/node.py:189-205, infra/interference.py:1); Gandiva preempts a
+    job every 100 ticks while others wait (core/scheduling/algorithm.py:418-438). Here a job's progress is a RATE:
+    a single-GPU job that shares its GPU with k-1 others advances at ``1 / slowdown[k-1]`` (measured table,
+    calib/interference.py; ``slowdown = [1, 1.2, 1.2]`` is the reference's constant), everything else at 1. GPUs are
+    aligned power-of-two blocks (exec/buddy.py) as in the worker pool; single-GPU jobs prefer a free GPU and only join
+    the shared GPU with the fewest tenants when none is left. Waiting jobs are served in list order until the first
+    that does not fit (arrivals join the back; the list is kept sorted by GPU count as in ``sim_job_events``).
+    With ``quantum`` > 0 (and no packing order change) a job that has held its GPUs for a quantum while others wait
+    is preempted and re-queued at the back."""
+    from ...exec.buddy import BuddyAllocator, normalize_gpus
+    jobs, log = sim.jobs, sim.log
+    total = int(sim.cluster.num_gpu)
+    pow2 = 1
+    while pow2 * 2 <= total:
+        pow2 *= 2
+    alloc = BuddyAllocator(pow2)
+    slow = list(slowdown) if slowdown else [1.0]
+    tenants: Dict[int, List[TJob]] = {}
+    arrivals = sorted(jobs.job_list, key=lambda j: (j.submit_time, j.job_idx))
+    for j in arrivals:
+        j.status = "EVENT"
+        j.progress = 0.0
+    pending: List[TJob] = []
+    running: List[TJob] = []
+    now = 0.0
+
+    def rate(j: TJob) -> float:
+        blk = j.placements[0]["buddy"]
+        k = len(tenants.get(blk[0], ())) if (blk[1] == 1 and max_share > 1) else 1
+        return 1.0 / slow[min(max(k, 1), len(slow)) - 1]
+
+    def start(j: TJob) -> bool:
+        need = normalize_gpus(j.num_gpu, pow2)
+        shared = max_share > 1 and need == 1
+        blk = alloc.alloc(need, str(j.job_id))
+        if blk is None and shared:
+            room = [(len(t), g) for g, t in tenants.items() if 0 < len(t) < max_share]
+            if room:
+                blk = (min(room)[1], 1)
+        if blk is None:
+            return False
+        if shared:
+            tenants.setdefault(blk[0], []).append(j)
+        j.placements[:] = [{"buddy": list(blk)}]
+        j.status = "RUNNING"
+        j.slice_start = now
+        if j.start_time == MAXSIZE:
+            j.start_time = int(round(now))
+        running.append(j)
+        return True
+
+    def release(j: TJob) -> None:
+        blk = tuple(j.placements[0]["buddy"])
+        if max_share > 1 and blk[1] == 1 and j in tenants.get(blk[0], ()):
+            tenants[blk[0]].remove(j)
+            if not tenants[blk[0]]:
+                alloc.free(blk)
+        else:
+            alloc.free(blk)
+        running.remove(j)
+
+    while arrivals or pending or running:
+        t_arr = arrivals[0].submit_time if arrivals else MAXSIZE
+        t_end = min((now + (j.duration - j.progress) / rate(j) for j in running), default=MAXSIZE)
+        t_q = MAXSIZE
+        if quantum > 0 and pending:
+            t_q = min((j.slice_start + quantum for j in running), default=MAXSIZE)
+        nxt = min(t_arr, t_end, t_q)
+        if nxt >= MAXSIZE:
+            sim.print_fn(NOT_LARGE_ENOUGH)
+            break
+        nxt = max(nxt, now)
+        for j in running:
+            j.progress += (nxt - now) * rate(j)
+        for j in pending:
+            j.pending_time = int(round(j.pending_time + (nxt - now)))
+        now = nxt
+        for j in [j for j in running if j.progress >= j.duration - 1e-6]:
+            release(j)
+            j.status = "END"
+            log.job_complete(j, int(round(now)))
+        if quantum > 0 and pending:
+            for j in [j for j in running if now - j.slice_start >= quantum - 1e-9]:
+                release(j)
+                j.status = "PENDING"
+                j.preempt = int(j.preempt + 1)
+                pending.append(j)
+        fresh = []
+        while arrivals and arrivals[0].submit_time <= now + 1e-9:
+            j = arrivals.pop(0)
+            j.start_time = MAXSIZE
+            j.pending_time = 0
+            fresh.append(j)
+        if quantum > 0:
+            pending.extend(fresh)
+            for j in list(pending):
+                if start(j):
+                    pending.remove(j)
+                else:
+                    break
+        else:
+            for j in pending:                      # removal while iterating skips the next entry (sim_job_events)
+                if start(j):
+                    pending.remove(j)
+                else:
+                    break
+            for j in fresh:
+                if not start(j):
+                    j.status = "PENDING"
+                    pending.append(j)
+            pending.sort(key=lambda j: j.num_gpu)
+        sim.mark(int(round(now)))
+
+
 def dispatch(sim: Sim) -> None:
     """``--schedule`` -> loop (run_sim.py's README-documented names)."""
     global RESUME_OVERHEAD
@@ -609,10 +731,14 @@ def dispatch(sim: Sim) -> None:
         gandiva_legacy(sim)
     elif s == "gpu-demands":
         gpu_demands(sim)
+    elif s in ("fifo-pack", "gandiva-slice"):
+        table = [float(v) for v in str(getattr(sim.flags, "pack_slowdown", "") or "1,1.2,1.2").split(",")]
+        fifo_shared(sim, max_share=int(getattr(sim.flags, "pack_max_share", 3) or 3) if s == "fifo-pack" else 1,
+                    slowdown=table, quantum=int(getattr(sim.flags, "slice_quantum", 100) or 100) if s == "gandiva-slice" else 0)
     else:
         raise NotImplementedError(f"unknown schedule {s!r}")
 
 
 EVENT_SCHEDULES = ("fifo", "fjf", "lpjf", "sjf", "shortest", "shortest-gpu", "shortest-expected", "dlas",
                    "dlas-gpu", "dlas-gpu-gittins", "dlas-gpu-pack", "multi-dlas-gpu", "gittins",
-                   "gandiva-legacy", "gpu-demands")
+                   "gandiva-legacy", "gpu-demands", "fifo-pack", "gandiva-slice")
