@@ -36,7 +36,7 @@ def _gemm_nt_pull(x2d: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.
     y = torch.empty((m, n), dtype=torch.bfloat16, device=x2d.device)
     bias_ptr, bias_dt = (bias.data_ptr(), native.dtype_code(bias.dtype)) if bias is not None else (0, 0)
     native.check(native.lib().tb200_gemm_bf16_nt_pull(
-        C.byref(trainer._world_struct), bucket.index, bucket.offset, n // trainer.world,
+        C.byref(trainer._world_struct), bucket.index, bucket.offset, bucket.pull_rows,
         x2d.data_ptr(), y.data_ptr(), bias_ptr, bias_dt, m, n, k, native.BF16, act,
         trainer.epoch.data_ptr(), trainer.status.data_ptr(), trainer.spin_budget, native.stream_ptr()))
     return y

@@ -53,6 +53,7 @@ class Bucket:
     length: int                       # padded to a multiple of 8 * world
     params: List[Tuple[nn.Parameter, int]] = field(default_factory=list)   # (param, flat offset)
     pull_layer: Optional[TcLinear] = None
+    pull_rows: int = 0                # rows of the pulled weight every PS rank owns (a multiple of 128)
     pending: int = 0
 
     def shard(self, rank: int, world: int) -> Tuple[int, int]:
@@ -68,14 +69,15 @@ def plan_buckets(model: nn.Module, world: int, bucket_elems: int, pull_min_elems
                  allow_pull: bool) -> Tuple[List[Bucket], int]:
     """Greedy bucketing in reverse registration order (~ the order gradients become ready).
 
-    Large TcLinear weights whose rows split evenly into 128-row tiles per rank get a bucket of
-    their own so they can be row-sharded over the PS ranks and pulled inside the GEMM.
+    Large TcLinear weights get a bucket of their own so that they can be row-sharded over the PS ranks and
+    pulled inside the GEMM. The shard of every rank is a whole number of 128-row GEMM tiles: the bucket is
+    padded with zero rows up to ``world`` x that size (ResNet-50's 1000-row classifier occupies 1024 rows of the
+    flat buffers at 2, 4 and 8 ranks), so no out_features has to divide anything.
     """
     pull_weights: Dict[int, TcLinear] = {}
     if allow_pull and world > 1:
         for m in model.modules():
-            if (isinstance(m, TcLinear) and m.weight.numel() >= pull_min_elems
-                    and m.out_features % (128 * world) == 0):
+            if isinstance(m, TcLinear) and m.weight.numel() >= pull_min_elems:
                 pull_weights[id(m.weight)] = m
     buckets: List[Bucket] = []
     cur: Optional[Bucket] = None
@@ -94,8 +96,9 @@ def plan_buckets(model: nn.Module, world: int, bucket_elems: int, pull_min_elems
         if id(p) in pull_weights:
             close()
             off = _round_up(off, max(_ALIGN, quantum))
-            b = Bucket(len(buckets), off, p.numel(), [(p, off)], pull_weights[id(p)])
-            off += p.numel()
+            rows = _round_up(p.shape[0], 128 * world)
+            b = Bucket(len(buckets), off, rows * p.shape[1], [(p, off)], pull_weights[id(p)], rows // world)
+            off += b.length
             buckets.append(b)
             continue
         if cur is None:
