@@ -53,6 +53,9 @@ def parse_args() -> argparse.Namespace:
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--skip-nccl", action="store_true", help="do not run the NCCL baseline arms")
     ap.add_argument("--skip-sim", action="store_true", help="do not run the simulator comparison")
+    ap.add_argument("--extra-models", default="vgg16:128,transformer_big:32",
+                    help="communication-bound jobs reported next to the headline as model:per-GPU-batch pairs "
+                         "(VGG-16 528 MB and transformer_big 1.1 GB of gradients); '' = none")
     return ap.parse_args()
 
 
@@ -122,7 +125,8 @@ def timed_region(fn_step, steps: int, device, sampler=None):
     return float(ms.item()), wall, clocks
 
 
-def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, world: int, same_compute: bool = False):
+def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, world: int, same_compute: bool = False,
+            model: str = None, batch: int = None, steps: int = None, phases: bool = False):
     import torch
     from tiresias_b200.models import zoo
     from tiresias_b200.ops import native
@@ -130,11 +134,14 @@ def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, wor
     from tiresias_b200.utils.clocks import ClockSampler
 
     device = torch.device("cuda", local_rank)
-    spec = zoo.resolve(args.model)
-    trainer = Trainer(spec, args.batch, mode=mode, bucket_mb=args.bucket_mb,
+    model = model or args.model
+    batch = batch or args.batch
+    steps = steps or args.steps
+    spec = zoo.resolve(model)
+    trainer = Trainer(spec, batch, mode=mode, bucket_mb=args.bucket_mb,
                       use_graph=not args.no_graph, device=device, nccl_same_compute=same_compute)
     # distinct pinned host batches so every step's H2D copy moves fresh bytes
-    host = [zoo.synthetic_batch(spec, args.batch, pinned=True, seed=1000 * rank + i) for i in range(4)]
+    host = [zoo.synthetic_batch(spec, batch, pinned=True, seed=1000 * rank + i) for i in range(4)]
 
     cur = torch.cuda.current_stream(device)
 
@@ -163,15 +170,25 @@ def run_arm(mode: str, args: argparse.Namespace, rank: int, local_rank: int, wor
         raise SystemExit("in-kernel wait timed out during warm-up")
 
     launches0 = trainer.native_launches
-    ms, wall, clocks = timed_region(resident, args.steps, device, ClockSampler(local_rank))
+    ms, wall, clocks = timed_region(resident, steps, device, ClockSampler(local_rank))
     launches = trainer.native_launches - launches0
-    ms_e2e, wall_e2e, _ = timed_region(e2e, args.steps, device)
+    ms_e2e, wall_e2e, _ = timed_region(e2e, steps, device)
     status = trainer.check_status()
+    phase_ms = None
+    if phases:
+        # eager per-phase device times (max over ranks): how much communication is left exposed after backward
+        try:
+            phase_ms = {k: round(v, 3) for k, v in trainer.profile_phases(*host[0], steps=3).items()}
+        except Exception as e:  # noqa: BLE001
+            phase_ms = {"error": f"{type(e).__name__}: {e}"[:200]}
     out = {
-        "ms_per_step": ms / args.steps,
-        "value": args.batch * world * args.steps / (ms / 1e3),
-        "e2e_ms_per_step": ms_e2e / args.steps,
-        "e2e_value": args.batch * world * args.steps / (ms_e2e / 1e3),
+        "ms_per_step": ms / steps,
+        "value": batch * world * steps / (ms / 1e3),
+        "e2e_ms_per_step": ms_e2e / steps,
+        "e2e_value": batch * world * steps / (ms_e2e / 1e3),
+        "phases_ms": phase_ms, "nvls": bool(getattr(trainer, "nvls", False)),
+        "grad_mb": round(sum(p.numel() for p in trainer.model.parameters()) * 2 / 1e6, 1),
+        "pull_layers": sum(1 for b in trainer.buckets if b.pull_layer is not None),
         "wall_s": wall, "clocks": clocks, "gpu_launches": int(launches),
         "h2d_bytes_per_step": trainer.h2d_bytes, "d2h_bytes_per_step": trainer.d2h_bytes,
         "loss_last": losses[-1] if losses else None, "status": status,
@@ -196,7 +213,7 @@ def main() -> None:
     sim = None
     if rank == 0 and args.impl == "ours" and not args.skip_sim:
         sim = sim_block(ours=True, reference=True)     # CPU only; the other ranks wait at the first barrier
-    res = run_arm(mode, args, rank, local_rank, world)
+    res = run_arm(mode, args, rank, local_rank, world, phases=True)
     base, fair, base_error = None, None, None
     if args.impl == "ours" and not args.skip_nccl:
         # the PyTorch + NCCL arms are context for the headline number, never a reason to lose it
@@ -208,6 +225,25 @@ def main() -> None:
             base = run_arm("nccl", args, rank, local_rank, world)
         except Exception as e:  # noqa: BLE001
             base_error = f"{type(e).__name__}: {e}"[:300]
+    extra = []
+    if args.impl == "ours" and not args.skip_nccl and args.extra_models:
+        # where communication is visible: same two arms (ours vs same-compute NCCL) on the big-gradient jobs
+        for item in args.extra_models.split(","):
+            name, _, b = item.partition(":")
+            row = {"model": name, "per_gpu_batch": int(b or args.batch)}
+            try:
+                k = max(5, args.steps // 2)
+                o = run_arm("ps", args, rank, local_rank, world, model=name, batch=row["per_gpu_batch"], steps=k, phases=True)
+                f = run_arm("nccl", args, rank, local_rank, world, same_compute=True, model=name,
+                            batch=row["per_gpu_batch"], steps=k)
+                row.update({"gradient_mb_bf16": o["grad_mb"], "ours_ms_per_step": round(o["ms_per_step"], 3),
+                            "ours_value": round(o["value"], 1), "nccl_same_compute_ms_per_step": round(f["ms_per_step"], 3),
+                            "speedup_device": round(f["ms_per_step"] / o["ms_per_step"], 4),
+                            "speedup_e2e": round(o["e2e_value"] / f["e2e_value"], 4), "phases_ms": o["phases_ms"],
+                            "nvls": o["nvls"], "pull_layers": o["pull_layers"], "steps": k})
+            except Exception as e:  # noqa: BLE001
+                row["error"] = f"{type(e).__name__}: {e}"[:300]
+            extra.append(row)
     if rank == 0:
         line = {
             "metric": f"{args.model}_ps_sync_sgd_samples_per_s",
@@ -232,7 +268,10 @@ def main() -> None:
                     "d2h_bytes_per_step": res["d2h_bytes_per_step"]},
             "gpu_launches": res["gpu_launches"],
             "loss_last": res["loss_last"], "status": res["status"],
+            "phases_ms": res["phases_ms"], "nvls": res["nvls"], "pull_layers": res["pull_layers"],
         }
+        if extra:
+            line["communication_bound_jobs"] = extra
         if base is not None:
             line["nccl_baseline"] = {
                 "what": "stock PyTorch network (nn.BatchNorm2d, cuDNN/cuBLAS), eager, NCCL reduce_scatter + torch SGD + all_gather",

@@ -11,6 +11,9 @@ Per bucket size (bf16 elements, the same on every rank):
   nccl/ps     reduce_scatter_tensor + torch SGD on the shard + all_gather_into_tensor
   ours/ring   tb200_allreduce algo 0 (ring) and algo 1 (direct two-shot)
   nccl/ar     all_reduce
+  pull_gemm   tb200_gemm_bf16_nt_pull (K2): y = x . W^T with W row-sharded over the PS ranks — B tiles are TMA-loaded
+              straight from the owners' memory inside the GEMM and written to the local copy on the way — against
+              NCCL all_gather_into_tensor of the shards followed by a cuBLAS GEMM (``--op pull_gemm``)
 Roofline: per GPU the push moves (W-1)/W * n * 2 bytes in and the pull the same amount out, each direction
 at the measured 770 GB/s peer-copy bandwidth (B200_PROFILING.md); the HBM side (fp32 master + momentum,
 16 bytes per shard element, plus the local bf16 traffic) runs at the measured copy bandwidth. Roofline
@@ -55,7 +58,66 @@ def timed(fn, dev, iters=20, warmup=5):
     return float(t.item())
 
 
+def pull_gemm_cases(symm, ws, rank, world, dev, hbm):
+    """K2 against its NCCL + cuBLAS composite on the FC shapes of the model table (core/models.py:9-11) and the
+    transformer LM head. Roofline = max(2MNK at the measured cuBLAS peak, (W-1)/W of the weight over NVLink at
+    770 GB/s, the weight once through HBM)."""
+    lib = native.lib()
+    try:
+        tf = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]
+    except Exception:
+        tf = 1400.0
+    param = symm.buffers["param"].view(torch.bfloat16)
+    epoch = torch.ones(1, dtype=torch.int32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    rows = []
+    for name, m, n, k in (("vgg fc6", 256, 4096, 25088), ("vgg fc7", 256, 4096, 4096), ("resnet50 fc", 256, 1000, 2048),
+                          ("lm head", 4096, 32000, 1024), ("vgg fc6 b1024", 1024, 4096, 25088)):
+        rpr = (n + 128 * world - 1) // (128 * world) * 128
+        npad = rpr * world
+        if npad * k > param.numel():
+            continue
+        w = param[: npad * k].view(npad, k)
+        w.normal_(0, k ** -0.5)
+        x = torch.randn(m, k, device=dev).to(torch.bfloat16)
+        y = torch.empty(m, n, dtype=torch.bfloat16, device=dev)
+        full = torch.empty(npad, k, dtype=torch.bfloat16, device=dev)
+        shard = w[rank * rpr:(rank + 1) * rpr]
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+
+        def ours():
+            native.check(lib.tb200_gemm_bf16_nt_pull(C.byref(ws), 0, 0, rpr, x.data_ptr(), y.data_ptr(), None, 0, m, n, k,
+                                                     native.BF16, 0, epoch.data_ptr(), status.data_ptr(), 400_000_000,
+                                                     native.stream_ptr()))
+
+        def nccl():
+            dist.all_gather_into_tensor(full, shard.contiguous())
+            torch.matmul(x, full[:n].t(), out=y)
+
+        def local_ours():
+            native.gemm_nt(x, w[:n], out=y)
+
+        def local_cublas():
+            torch.matmul(x, w[:n].t(), out=y)
+        t_ours, t_nccl = timed(ours, dev), timed(nccl, dev)
+        t_lo, t_lc = timed(local_ours, dev), timed(local_cublas, dev)
+        link = (world - 1) / world * n * k * 2
+        roof = max(2.0 * m * n * k / (tf * 1e9), link / (NVLINK_GBS * 1e6), (n * k * 2 + m * k * 2) / (hbm * 1e6))
+        rows.append({"op": "pull_gemm", "shape": name, "M": m, "N": n, "K": k, "world": world, "rows_per_rank": rpr,
+                     "ours_ms": round(t_ours, 4), "nccl_allgather_plus_cublas_ms": round(t_nccl, 4),
+                     "speedup": round(t_nccl / t_ours, 3), "local_gemm_ours_ms": round(t_lo, 4),
+                     "local_gemm_cublas_ms": round(t_lc, 4), "nvlink_rx_gbs": round(link / t_ours / 1e6, 1),
+                     "roofline_ms": round(roof, 4), "frac_of_roofline": round(roof / t_ours, 3)})
+    assert int(status.item()) == 0, "pull GEMM wait timed out"
+    return rows
+
+
 def main():
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--op", default="all", choices=["all", "ps", "pull_gemm"])
+    args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -88,7 +150,9 @@ def main():
     st = native.stream_ptr()
     hbm = hbm_gbs()
     rows = []
-    for n in sizes:
+    if args.op in ("all", "pull_gemm") and world > 1:
+        rows += pull_gemm_cases(symm, ws_p2p, rank, world, dev, hbm)
+    for n in (sizes if args.op in ("all", "ps") else []):
         shard = n // world
         for ctas, wsv, how in [(32, ws_p2p, "P2P"), (148, ws_p2p, "P2P")] + \
                 ([(32, ws_mc, "NVLS"), (148, ws_mc, "NVLS")] if has_mc else []):
@@ -153,7 +217,8 @@ def main():
             print(json.dumps(r), flush=True)
         print(json.dumps({"status_word": bad}))
         os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-        json.dump(rows, open(os.path.join(ROOT, "gpurun_out", f"comm_n{world}.json"), "w"), indent=1)
+        tag = "" if args.op == "all" else "_" + args.op
+        json.dump(rows, open(os.path.join(ROOT, "gpurun_out", f"comm_n{world}{tag}.json"), "w"), indent=1)
     dist.barrier()
     symm.close()
     dist.destroy_process_group()

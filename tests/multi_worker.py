@@ -8,7 +8,11 @@ Checks, on real peer memory over NVLink:
   4. ring all-reduce mode against the PS mode,
   5. checkpoint / resume at world > 1 (every rank restores only its PS shard; all ranks must continue from the
      full restored parameters) against an uninterrupted run, with and without pull-GEMM layers,
-  6. the like-for-like NCCL arm (same fused compute, NCCL collectives), eager and captured in a CUDA graph.
+  6. the like-for-like NCCL arm (same fused compute, NCCL collectives), eager and captured in a CUDA graph,
+  7. a randomised-delay stress of the flag / epoch protocol (the stand-in for compute-sanitizer's racecheck, which is
+     closed on this GPU pool): every rank sleeps a different random time before each of 40 steps, so ranks run up to
+     a whole step apart; reductions are in a fixed order, so ANY race shows up as parameters that are not bit-for-bit
+     those of the undisturbed run.
 Prints ``MULTI OK`` from rank 0 when everything held.
 """
 import ctypes as C
@@ -84,12 +88,17 @@ def check_allreduce(rank, world, dev):
     return has_mc
 
 
-def run_trainer(mode, rank, dev, steps=5, use_graph=False, pull=False, **kw):
+def run_trainer(mode, rank, dev, steps=5, use_graph=False, pull=False, jitter=None, **kw):
     tr = Trainer(TINY, batch_size=32, mode=mode, use_graph=use_graph, device=dev, bucket_mb=0.05,
                  lr=0.05, pull_gemm=pull, pull_min_mb=0.25, **kw)
     losses = []
+    rng = __import__("random").Random(jitter * 1000 + rank) if jitter is not None else None
     for i in range(steps):
         x, y = synthetic_batch(TINY, 32, seed=100 * rank + (i % 2))
+        if rng is not None:
+            __import__("time").sleep(rng.random() * 0.02)       # ranks drift up to a step apart
+            tr.step(x, y)                                        # no loss read-back: nothing else keeps them in step
+            continue
         tr.step(x, y)
         losses.append(tr.loss())
     assert tr.check_status() == 0, f"{mode}: in-kernel wait timed out"
@@ -184,6 +193,15 @@ def main():
         assert all(abs(a - b) < 5e-2 for a, b in zip(l_r, l_ps)), (algo, l_r, l_ps)
         assert torch.allclose(p_r, p_ps, rtol=2e-2, atol=2e-2), algo
         assert same_on_all_ranks(p_r, world), f"ring algo {algo}: ranks diverged"
+
+    # randomised-delay stress: bit-identical parameters with and without per-rank jitter, eager and graph, P2P
+    # and (where present) NVLS; also with pull-GEMM layers, whose owners' shards are read while peers run ahead
+    for kw in ({"nvls": False}, {"nvls": False, "use_graph": True}, {"nvls": False, "pull": True}) + \
+            (({"nvls": True},) if has_mc else ()):
+        _, p_calm, _, _ = run_trainer("ps", rank, dev, steps=40, **kw)
+        _, p_jit, _, _ = run_trainer("ps", rank, dev, steps=40, jitter=7, **kw)
+        assert torch.equal(p_calm, p_jit), ("timing changed the result", kw, (p_calm - p_jit).abs().max().item())
+        assert same_on_all_ranks(p_jit, world) or kw.get("pull"), ("ranks diverged under jitter", kw)
 
     check_resume(rank, dev, world, pull=False)
     check_resume(rank, dev, world, pull=True)

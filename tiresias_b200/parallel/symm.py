@@ -184,10 +184,14 @@ class SymmetricWorld:
         return self._nvls_ok
 
     def nvls_preferred(self) -> bool:
-        """Collective: should a trainer on this world default to the NVLS kernels? Only on request
-        (TB200_NVLS=1) for now: at 2 GPUs the switch has nothing to save and the peer load/store kernels
-        measure faster (profiles/COMM_r1.md)."""
-        return self.nvls_available() and os.environ.get("TB200_NVLS", "auto") == "1"
+        """Collective: should a trainer on this world default to the NVLS kernels? From 4 ranks up, where the
+        in-switch reduction saves (W-1)/W of the reads a rank would otherwise pull over NVLink (8 GPUs, 528 MB
+        bucket: 1.18 ms against 1.65 ms through peer loads, profiles/COMM_r1.md); at 2 GPUs the switch has
+        nothing to save and the peer load/store kernels measure faster. TB200_NVLS=1 / 0 forces it on / off."""
+        env = os.environ.get("TB200_NVLS", "auto")
+        if env == "1":
+            return self.nvls_available()
+        return env != "0" and self.world >= 4 and self.nvls_available()
 
     def _alloc_vmm(self, name: str, nbytes: int) -> SymmBuffer:
         import torch.distributed as dist
