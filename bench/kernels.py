@@ -253,7 +253,7 @@ def conv_cases(iters):
         err = (native.conv2d_fprop(x, w, stride, pad).float() - y.float()).abs().max().item()
         row.update({"fprop_ms": round(ours, 4), "fprop_cudnn_ms": round(lib, 4), "fprop_frac_of_roofline": round(roof_ms / ours, 3),
                     "fprop_tflops": round(flops / ours / 1e9, 1), "fprop_max_abs_diff_vs_cudnn": round(err, 4)})
-        if os.environ.get("TB200_TEST_EXPERIMENTAL") == "1" and k == 3 and stride == 1:
+        if k == 3 and stride == 1:
             # halo-tile kernel (csrc/conv_halo.cu): input tile fetched once, taps as shifted smem windows
             try:
                 halo, _ = timeit(lambda: native.conv2d_fprop_halo(x, w), iters)

@@ -41,8 +41,8 @@ def main():
             rows.append({"shift": shift, "base_offset": bo, "max_abs_err": round(err, 4), "ok": err < 0.05,
                          "rows_matching_some_source_row": exact, "first_sources": src[:12].tolist()})
             print(json.dumps(rows[-1]), flush=True)
-    # MN-major operand shifted along the reduction dimension (halo-tile wgrad): not run yet in round 1
-    if hasattr(lib, "tb200_probe_shifted_mn_operand") and os.environ.get("TB200_TEST_EXPERIMENTAL") == "1":
+    # MN-major operand shifted along the reduction dimension (halo-tile wgrad)
+    if hasattr(lib, "tb200_probe_shifted_mn_operand"):
         lib.tb200_probe_shifted_mn_operand.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         lib.tb200_probe_shifted_mn_operand.restype = C.c_int
         a2 = torch.randn(128, 64, device=dev).to(torch.bfloat16)

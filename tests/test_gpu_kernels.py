@@ -257,11 +257,8 @@ def test_gemm_operand_layouts_match_fp32(cuda_device, m, n, k, a_mn, b_mn):
     assert torch.allclose(got, ref, rtol=1e-3, atol=1e-3), (got - ref).abs().max().item()
 
 
-# Single-GPU check of the pull GEMM (K2: B tiles TMA-loaded from the shard owners' memory). Written after the
-# round's GPU budget was spent, so it is opt-in until it has run once; the multi-rank trainers
-# (tests/multi_worker.py, 2/4/8 GPUs) cover the same kernel over real peers.
-@pytest.mark.skipif(os.environ.get("TB200_TEST_EXPERIMENTAL", "0") != "1",
-                    reason="not yet run on hardware (TB200_TEST_EXPERIMENTAL=1 runs it)")
+# Single-GPU check of the pull GEMM (K2: B tiles TMA-loaded from the shard owners' memory) with emulated owners;
+# the multi-rank trainers (tests/multi_worker.py, 2/4/8 GPUs) cover the same kernel over real peers.
 @pytest.mark.parametrize("world", [2, 4])
 def test_pull_gemm_emulated_owners(cuda_device, world):
     from tiresias_b200.parallel.symm import SymmetricWorld

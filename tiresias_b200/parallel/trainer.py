@@ -151,9 +151,15 @@ class Trainer:
             self.model = (model if model is not None else
                           zoo_build(spec, fused=(mode != "nccl" or self.nccl_same_compute))).to(self.device)
         self.model.train()
+        # Pull layers (K2) fetch every B tile straight from its owner once per 128-row block of the activation, and
+        # peer memory is not cached in the local L2: with more than one row block the weight crosses NVLink that
+        # many times (measured, profiles/comm_pull_r2.md: 0.49x NCCL all_gather + cuBLAS at 256 rows, 0.07x at
+        # 4096). So a layer is pulled only when the whole per-GPU batch is one row block; otherwise the push
+        # kernel broadcasts the updated shard to every rank as for any other bucket.
+        rows_per_step = batch_size * (spec.sample_shape[0] if spec.kind == "tokens" else 1)
         self.buckets, self.total = plan_buckets(
             self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
-            allow_pull=(pull_gemm and mode == "ps"))
+            allow_pull=(pull_gemm and mode == "ps" and rows_per_step <= 128))
 
         self.pack_grads = mode != "nccl" or self.nccl_same_compute
         self._grad_view: Dict[int, torch.Tensor] = {}
