@@ -57,6 +57,18 @@ def main():
                                           native.BF16, mean.data_ptr(), istd.data_ptr(), dx.data_ptr(),
                                           dres.data_ptr() if with_y else 0, dg.data_ptr(), db.data_ptr(), scratch.data_ptr(),
                                           rows, c, 1, st()))
+        mask = torch.zeros(rows * c // 8 + 16, dtype=torch.uint8, device=dev)
+        has_mask = lib.tb200_bn_mask_supported(rows, c) == 1
+
+        def fwd_mask():
+            native.check(lib.tb200_bn_fwd_train_ex(x.data_ptr(), res.data_ptr(), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                                   native.BF16, rm.data_ptr(), rv.data_ptr(), 0.1, 1e-5, mean.data_ptr(),
+                                                   istd.data_ptr(), scratch.data_ptr(), 0, 0, mask.data_ptr(), rows, c, 1, st()))
+
+        def bwd_mask():
+            native.check(lib.tb200_bn_bwd_ex(dy.data_ptr(), x.data_ptr(), 0, mask.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                             native.BF16, mean.data_ptr(), istd.data_ptr(), dx.data_ptr(), dres.data_ptr(),
+                                             dg.data_ptr(), db.data_ptr(), scratch.data_ptr(), rows, c, 1, st()))
         t = x.numel() * 2
         row = {"rows": rows, "C": c, "mb": round(t / 1e6, 1), "stream": os.environ.get("TB200_BN_STREAM", "1")}
         for name, fn, passes in (("fwd", lambda: fwd(None), 3), ("fwd_res", lambda: fwd(res), 4),
@@ -64,6 +76,11 @@ def main():
             ms = timeit(fn)
             row[name + "_ms"] = round(ms, 4)
             row[name + "_frac_hbm"] = round(passes * t / ms / 1e6 / HBM, 3)
+        if has_mask:        # residual + ReLU with the mask as bits: forward writes t/16 more, backward reads 2 * t/16 not 2t
+            for name, fn, passes in (("fwd_res_bits", fwd_mask, 4 + 1 / 16), ("bwd_res_bits", bwd_mask, 6 + 2 / 16)):
+                ms = timeit(fn)
+                row[name + "_ms"] = round(ms, 4)
+                row[name + "_frac_hbm"] = round(passes * t / ms / 1e6 / HBM, 3)
         print(json.dumps(row), flush=True)
 
 

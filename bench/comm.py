@@ -70,6 +70,11 @@ def pull_gemm_cases(symm, ws, rank, world, dev, hbm):
     param = symm.buffers["param"].view(torch.bfloat16)
     epoch = torch.ones(1, dtype=torch.int32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
+    sync = torch.zeros(native.PULL_SYNC_WORDS, dtype=torch.int32, device=dev)
+    # every owner's shard counts as written for all the steps this benchmark will run
+    symm.post_flags("flags", native.flag_param_done(0, 0), native.MAX_WORLD, 1 << 30)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
     rows = []
     for name, m, n, k in (("vgg fc6", 256, 4096, 25088), ("vgg fc7", 256, 4096, 4096), ("resnet50 fc", 256, 1000, 2048),
                           ("lm head", 4096, 32000, 1024), ("vgg fc6 b1024", 1024, 4096, 25088)):
@@ -89,7 +94,8 @@ def pull_gemm_cases(symm, ws, rank, world, dev, hbm):
         def ours():
             native.check(lib.tb200_gemm_bf16_nt_pull(C.byref(ws), 0, 0, rpr, x.data_ptr(), y.data_ptr(), None, 0, m, n, k,
                                                      native.BF16, 0, epoch.data_ptr(), status.data_ptr(), 400_000_000,
-                                                     native.stream_ptr()))
+                                                     sync.data_ptr(), native.stream_ptr()))
+            epoch.add_(1)                              # a new step: the tiles have to be gathered again
 
         def nccl():
             dist.all_gather_into_tensor(full, shard.contiguous())

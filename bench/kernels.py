@@ -76,6 +76,13 @@ def gemm_cases(iters):
         ours, ours_min = timeit(lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o), iters)
         ref = torch.relu(a.float() @ b.float().t() + bias)
         err = (o.float() - ref).abs().max().item()
+        del ref
+        # the same call pinned to the one-CTA kernel and to the 2-CTA kernel (default picks by size)
+        native.lib().tb200_gemm_set_pair_mode(0)
+        one, _ = timeit(lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o), iters)
+        native.lib().tb200_gemm_set_pair_mode(1)
+        two, _ = timeit(lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o), iters)
+        native.lib().tb200_gemm_set_pair_mode(-1)
         bt = b.t()
         lib, lib_min = timeit(lambda: torch.relu_(torch.addmm(bias.to(torch.bfloat16), a, bt)), iters)
         flops = 2.0 * m * n * k
@@ -85,7 +92,8 @@ def gemm_cases(iters):
                     "ms_min": round(ours_min, 4), "tflops": round(flops / ours / 1e9, 1),
                     "gbs": round(byts / ours / 1e6, 1), "roofline_ms": round(roof_ms, 4),
                     "frac_of_roofline": round(roof_ms / ours, 3), "cublas_ms": round(lib, 4),
-                    "speedup_vs_cublas": round(lib / ours, 3), "max_abs_err": round(err, 4), "peaks": SRC})
+                    "speedup_vs_cublas": round(lib / ours, 3), "one_cta_ms": round(one, 4), "two_cta_ms": round(two, 4),
+                    "max_abs_err": round(err, 4), "peaks": SRC})
         print(json.dumps(out[-1]), flush=True)
     return out
 

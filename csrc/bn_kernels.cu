@@ -30,13 +30,14 @@ bool bn_stream_eligible(size_t rows, int C);
 int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamma, const void* beta, int param_dtype,
                   float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                   float* save_invstd, float* partials, float* coef, const float* conv_partials, int conv_nparts,
-                  size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters);
+                  size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters,
+                  uint8_t* mask_out);
 int bn_stream_apply(const void* x, const void* residual, void* y, const float* scale_shift, size_t rows, int C, int relu,
                     cudaStream_t stream);
 int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta, int param_dtype,
                   const float* save_mean, const float* save_invstd, void* dx, void* dres, void* dgamma, void* dbeta,
                   float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp,
-                  unsigned* counters);
+                  unsigned* counters, const uint8_t* mask_in);
 }  // namespace tb200
 
 namespace {
@@ -536,7 +537,7 @@ int tb200_bn_fwd_train(const void* x, const void* residual, void* y, const void*
     return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
                          save_invstd, scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
                          scratch + kCounterWords + kMaxPartialFloats, nullptr, 0, rows, C, relu, stream,
-                         scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch));
+                         scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch), nullptr);
   const int groups = (C + kGroup - 1) / kGroup;
   FwdArgs f{};
   f.x = reinterpret_cast<const uint4*>(x);
@@ -572,11 +573,53 @@ int tb200_bn_fwd_train_stats(const void* x, const void* residual, void* y, const
   if (use_stream(rows, C))
     return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
                          save_invstd, nullptr, coef, conv_partials, conv_nparts, rows, C, relu, stream,
-                         scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch));
+                         scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch), nullptr);
   if (int rc = tb200_bn_finalize(conv_partials, conv_nparts, (double)rows, C, gamma, beta, param_dtype, running_mean,
                                  running_var, momentum, eps, save_mean, save_invstd, coef, stream))
     return rc;
   return tb200_bn_apply(x, residual, y, coef, rows, C, relu, stream);
+}
+
+// 1 when the streamed kernels serve this shape (power-of-two C <= 2048, a tensor worth streaming): only they
+// know the ReLU bit mask of tb200_bn_fwd_train_ex / tb200_bn_bwd_ex.
+int tb200_bn_mask_supported(size_t rows, int C) { return use_stream(rows, C) ? 1 : 0; }
+
+// fwd_train with everything optional: statistics from the producing convolution's epilogue (conv_partials, may
+// be NULL) and, for a residual + ReLU layer, `relu_mask` (rows * C / 8 bytes + 16, may be NULL): one bit per output
+// element, which lets the backward skip re-reading y.
+int tb200_bn_fwd_train_ex(const void* x, const void* residual, void* y, const void* gamma, const void* beta,
+                          int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
+                          float* save_mean, float* save_invstd, float* scratch, const float* conv_partials,
+                          int conv_nparts, uint8_t* relu_mask, size_t rows, int C, int relu, cudaStream_t stream) {
+  if (int rc = check_shape("tb200_bn_fwd_train_ex", rows, C)) return rc;
+  if (relu_mask && !use_stream(rows, C)) return fail("tb200_bn_fwd_train_ex: the ReLU mask needs the streamed kernels%s");
+  if (!use_stream(rows, C)) {
+    if (conv_partials)
+      return tb200_bn_fwd_train_stats(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps,
+                                      save_mean, save_invstd, scratch, conv_partials, conv_nparts, rows, C, relu, stream);
+    return tb200_bn_fwd_train(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps,
+                              save_mean, save_invstd, scratch, rows, C, relu, stream);
+  }
+  return bn_stream_fwd(x, residual, y, gamma, beta, param_dtype, running_mean, running_var, momentum, eps, save_mean,
+                       save_invstd, scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
+                       scratch + kCounterWords + kMaxPartialFloats, conv_partials, conv_nparts, rows, C, relu, stream,
+                       scratch + kCounterWords, reinterpret_cast<unsigned*>(scratch), relu_mask);
+}
+
+// bwd with the ReLU mask as bits (relu_mask, from tb200_bn_fwd_train_ex) instead of the saved output y.
+int tb200_bn_bwd_ex(const void* dy, const void* x, const void* y, const uint8_t* relu_mask, const void* gamma,
+                    const void* beta, int param_dtype, const float* save_mean, const float* save_invstd, void* dx,
+                    void* dres, void* dgamma, void* dbeta, float* scratch, size_t rows, int C, int relu,
+                    cudaStream_t stream) {
+  if (!relu_mask)
+    return tb200_bn_bwd(dy, x, y, gamma, beta, param_dtype, save_mean, save_invstd, dx, dres, dgamma, dbeta, scratch, rows,
+                        C, relu, stream);
+  if (int rc = check_shape("tb200_bn_bwd_ex", rows, C)) return rc;
+  if (!use_stream(rows, C)) return fail("tb200_bn_bwd_ex: the ReLU mask needs the streamed kernels%s");
+  return bn_stream_bwd(dy, x, nullptr, gamma, beta, param_dtype, save_mean, save_invstd, dx, dres, dgamma, dbeta,
+                       scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
+                       scratch + kCounterWords + kMaxPartialFloats, rows, C, relu, stream, scratch + kCounterWords,
+                       reinterpret_cast<unsigned*>(scratch), relu_mask);
 }
 
 int tb200_bn_apply(const void* x, const void* residual, void* y, const float* scale_shift,
@@ -603,7 +646,7 @@ int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma
     return bn_stream_bwd(dy, x, y, gamma, beta, param_dtype, save_mean, save_invstd, dx, dres, dgamma, dbeta,
                          scratch + kCounterWords + kMaxPartialFloats + kCoefFloats,
                          scratch + kCounterWords + kMaxPartialFloats, rows, C, relu, stream, scratch + kCounterWords,
-                         reinterpret_cast<unsigned*>(scratch));
+                         reinterpret_cast<unsigned*>(scratch), nullptr);
   const int groups = (C + kGroup - 1) / kGroup;
   BwdArgs b{};
   b.dy = reinterpret_cast<const uint4*>(dy); b.x = reinterpret_cast<const uint4*>(x);

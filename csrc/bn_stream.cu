@@ -63,15 +63,18 @@ struct StreamArgs {
   int param_dtype;
   int relu;
   float* partials;            // [gridDim.x][C][2]
+  const uint8_t* mask_in;     // backward MASK == 3: one byte per 16-byte vector, bit k = (output element k > 0)
+  uint8_t* mask_out;          // forward with residual + ReLU: the same bits, written next to y
 };
 
 // The pipeline shared by the four kernels. PIECE_VECS 16-byte vectors per tensor per stage. `body(stage_base,
 // first_vec, nvec)` is called by the 256 consumer threads for every piece: tensor i of the stage lives at
 // stage_base + i * PIECE_VECS * 16.
-template <int NIN, int PIECE_VECS, typename Body>
+// MASKBITS adds a byte stream (a.mask_in, one byte per vector) behind the NIN tensors of every stage.
+template <int NIN, int PIECE_VECS, bool MASKBITS = false, typename Body>
 __device__ __forceinline__ void stream_pipeline(const StreamArgs& a, uint8_t* smem_raw, Body&& body) {
   constexpr uint32_t kPieceBytes = PIECE_VECS * 16;
-  constexpr uint32_t kStageBytes = NIN * kPieceBytes;
+  constexpr uint32_t kStageBytes = NIN * kPieceBytes + (MASKBITS ? PIECE_VECS : 0);
   const uint32_t base = smem_u32(smem_raw);
   const uint32_t bars = base + kStages * kStageBytes;
   auto full = [&](int s) { return bars + 8u * s; };
@@ -95,10 +98,13 @@ __device__ __forceinline__ void stream_pipeline(const StreamArgs& a, uint8_t* sm
       if (elect_one()) {
         const size_t pv = v0 + (size_t)i * PIECE_VECS;
         const uint32_t nv = (uint32_t)((v1 - pv) < (size_t)PIECE_VECS ? (v1 - pv) : (size_t)PIECE_VECS);
-        mbar_expect_tx(full(s), NIN * nv * 16u);
+        const uint32_t mbytes = MASKBITS ? ((nv + 15u) & ~15u) : 0u;      // bulk copies move multiples of 16 bytes
+        mbar_expect_tx(full(s), NIN * nv * 16u + mbytes);
 #pragma unroll
         for (int t = 0; t < NIN; ++t)
           bulk_load(base + (uint32_t)s * kStageBytes + (uint32_t)t * kPieceBytes, a.in[t] + pv * 16, nv * 16u, full(s));
+        if constexpr (MASKBITS)
+          bulk_load(base + (uint32_t)s * kStageBytes + NIN * kPieceBytes, a.mask_in + pv, mbytes, full(s));
       }
       __syncwarp();
       if (++s == kStages) { s = 0; ph ^= 1; }
@@ -162,7 +168,7 @@ __global__ void __launch_bounds__(kBlock, 3) bn_stats_stream_kernel(const Stream
   reduce_and_store(a, acc, reinterpret_cast<float*>(smem_raw));
 }
 
-template <int NIN, int PIECE_VECS>
+template <int NIN, int PIECE_VECS, bool WMASK = false>
 __global__ void __launch_bounds__(kBlock, 3) bn_apply_stream_kernel(const StreamArgs a) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const int t = threadIdx.x;
@@ -188,12 +194,20 @@ __global__ void __launch_bounds__(kBlock, 3) bn_apply_stream_kernel(const Stream
           f[j] = relu ? fmaxf(v, 0.f) : v;
         }
         a.out[0][pv + i] = pack8(f);       // default caching: the next layer reads y straight away
+        if constexpr (WMASK) {
+          // the backward's ReLU mask as one bit per element (1/16 of y): a residual layer then never re-reads y
+          uint32_t bits = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bits |= (f[j] > 0.f ? 1u : 0u) << j;
+          a.mask_out[pv + i] = (uint8_t)bits;
+        }
       }
     }
   });
 }
 
-// MASK: 0 = no ReLU, 1 = mask from the saved output y (third stream), 2 = mask recomputed from x.
+// MASK: 0 = no ReLU, 1 = mask from the saved output y (third stream), 2 = mask recomputed from x,
+//       3 = mask bits written by the forward (byte stream, 1/16 of a tensor).
 template <int MASK, int PIECE_VECS>
 __global__ void __launch_bounds__(kBlock, 2) bn_bwd_reduce_stream_kernel(const StreamArgs a) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -215,7 +229,7 @@ __global__ void __launch_bounds__(kBlock, 2) bn_bwd_reduce_stream_kernel(const S
     }
   }
   float acc[2][8] = {};
-  stream_pipeline<NIN, PIECE_VECS>(a, smem_raw, [&](uint32_t stage, size_t, uint32_t nv) {
+  stream_pipeline<NIN, PIECE_VECS, MASK == 3>(a, smem_raw, [&](uint32_t stage, size_t, uint32_t nv) {
 #pragma unroll
     for (int k = 0; k < PIECE_VECS / kConsumers; ++k) {
       const uint32_t i = (uint32_t)t + (uint32_t)k * kConsumers;
@@ -224,6 +238,11 @@ __global__ void __launch_bounds__(kBlock, 2) bn_bwd_reduce_stream_kernel(const S
         unpack8(ld_shared_16(stage + i * 16u), g);
         unpack8(ld_shared_16(stage + PIECE_VECS * 16u + i * 16u), xv);
         if constexpr (MASK == 1) unpack8(ld_shared_16(stage + 2 * PIECE_VECS * 16u + i * 16u), yv);
+        if constexpr (MASK == 3) {
+          const uint32_t bits = smem_raw[(stage - smem_u32(smem_raw)) + 2 * PIECE_VECS * 16u + i];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) yv[j] = ((bits >> j) & 1u) ? 1.f : 0.f;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           if constexpr (MASK == 2) yv[j] = fmaf(xv[j], sc[j], sh[j]);
@@ -256,7 +275,7 @@ __global__ void __launch_bounds__(kBlock, 2) bn_bwd_apply_stream_kernel(const St
       sh[k] = MASK == 2 ? load_param(a.beta, a.param_dtype, ch) - mean[k] * A[k] : 0.f;
     }
   }
-  stream_pipeline<NIN, PIECE_VECS>(a, smem_raw, [&](uint32_t stage, size_t pv, uint32_t nv) {
+  stream_pipeline<NIN, PIECE_VECS, MASK == 3>(a, smem_raw, [&](uint32_t stage, size_t pv, uint32_t nv) {
 #pragma unroll
     for (int k = 0; k < PIECE_VECS / kConsumers; ++k) {
       const uint32_t i = (uint32_t)t + (uint32_t)k * kConsumers;
@@ -265,6 +284,11 @@ __global__ void __launch_bounds__(kBlock, 2) bn_bwd_apply_stream_kernel(const St
         unpack8(ld_shared_16(stage + i * 16u), g);
         unpack8(ld_shared_16(stage + PIECE_VECS * 16u + i * 16u), xv);
         if constexpr (MASK == 1) unpack8(ld_shared_16(stage + 2 * PIECE_VECS * 16u + i * 16u), yv);
+        if constexpr (MASK == 3) {
+          const uint32_t bits = smem_raw[(stage - smem_u32(smem_raw)) + 2 * PIECE_VECS * 16u + i];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) yv[j] = ((bits >> j) & 1u) ? 1.f : 0.f;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           if constexpr (MASK == 2) yv[j] = fmaf(xv[j], A[j], sh[j]);
@@ -443,10 +467,11 @@ int launch_fold(const FoldArgs& f, float* tmp, unsigned* counters, cudaStream_t 
 constexpr int kPiece1 = 1024;      // 16 KB per stage (one stream)
 constexpr int kPiece2 = 512;       // 8 KB per tensor per stage (two or three streams)
 
-template <int NIN, int PIECE_VECS>
+template <int NIN, int PIECE_VECS, bool MASKBITS = false>
 constexpr int stream_smem() {
   // the ring, its barriers, and room for the reduction's [2][256][8] floats (reuses the ring)
-  return (kStages * NIN * PIECE_VECS * 16 > 2 * 256 * 8 * 4 ? kStages * NIN * PIECE_VECS * 16 : 2 * 256 * 8 * 4) + 128;
+  constexpr int ring = kStages * (NIN * PIECE_VECS * 16 + (MASKBITS ? PIECE_VECS : 0));
+  return (ring > 2 * 256 * 8 * 4 ? ring : 2 * 256 * 8 * 4) + 128;
 }
 
 // Row ranges: one wave of CTAs (`per_sm` per SM), each a whole number of pieces.
@@ -484,7 +509,8 @@ int bn_stream_max_parts() { return device_sm_count() * 3; }
 int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamma, const void* beta, int param_dtype,
                   float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                   float* save_invstd, float* partials, float* coef, const float* conv_partials, int conv_nparts,
-                  size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters) {
+                  size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp, unsigned* counters,
+                  uint8_t* mask_out) {
   FoldArgs f{};
   f.C = C; f.count = (double)rows; f.gamma = gamma; f.beta = beta; f.param_dtype = param_dtype;
   f.inv_count = 1.0 / f.count; f.bessel = f.count > 1.0 ? f.count / (f.count - 1.0) : 1.0;
@@ -514,8 +540,13 @@ int bn_stream_fwd(const void* x, const void* residual, void* y, const void* gamm
   ap.out[0] = reinterpret_cast<uint4*>(y);
   ap.coef = coef;
   ap.relu = relu;
+  ap.mask_out = mask_out;
   if (residual) {
     plan_stream(ap, rows, C, kPiece2, 3, &grid);
+    if (mask_out && relu) {
+      static DeviceOnce once;
+      return launch_stream(bn_apply_stream_kernel<2, kPiece2, true>, once, stream_smem<2, kPiece2>(), grid, ap, stream);
+    }
     static DeviceOnce once;
     return launch_stream(bn_apply_stream_kernel<2, kPiece2>, once, stream_smem<2, kPiece2>(), grid, ap, stream);
   }
@@ -546,8 +577,8 @@ int bn_stream_apply(const void* x, const void* residual, void* y, const float* s
 int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta, int param_dtype,
                   const float* save_mean, const float* save_invstd, void* dx, void* dres, void* dgamma, void* dbeta,
                   float* partials, float* coef, size_t rows, int C, int relu, cudaStream_t stream, float* fold_tmp,
-                  unsigned* counters) {
-  const int mask = !relu ? 0 : (y ? 1 : 2);
+                  unsigned* counters, const uint8_t* mask_in) {
+  const int mask = !relu ? 0 : (mask_in ? 3 : (y ? 1 : 2));
   StreamArgs a{};
   int grid = 0;
   plan_stream(a, rows, C, kPiece2, 2, &grid);
@@ -559,8 +590,12 @@ int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamm
   a.partials = partials;
   a.coef = coef;
   a.relu = relu;
+  a.mask_in = mask_in;
   int rc;
-  if (mask == 0) {
+  if (mask == 3) {
+    static DeviceOnce once;
+    rc = launch_stream(bn_bwd_reduce_stream_kernel<3, kPiece2>, once, stream_smem<2, kPiece2, true>(), grid, a, stream);
+  } else if (mask == 0) {
     static DeviceOnce once;
     rc = launch_stream(bn_bwd_reduce_stream_kernel<0, kPiece2>, once, stream_smem<2, kPiece2>(), grid, a, stream);
   } else if (mask == 1) {
@@ -584,6 +619,14 @@ int bn_stream_bwd(const void* dy, const void* x, const void* y, const void* gamm
     static DeviceOnce once;                                                                                   \
     return launch_stream(bn_bwd_apply_stream_kernel<M, D, kPiece2>, once, stream_smem<NINV, kPiece2>(), grid, a, \
                          stream);                                                                             \
+  }
+  if (mask == 3) {
+    if (dres) {
+      static DeviceOnce once;
+      return launch_stream(bn_bwd_apply_stream_kernel<3, true, kPiece2>, once, stream_smem<2, kPiece2, true>(), grid, a, stream);
+    }
+    static DeviceOnce once;
+    return launch_stream(bn_bwd_apply_stream_kernel<3, false, kPiece2>, once, stream_smem<2, kPiece2, true>(), grid, a, stream);
   }
   if (mask == 0) { if (dres) TB_BWD_APPLY(0, true, 2) else TB_BWD_APPLY(0, false, 2) }
   if (mask == 1) { if (dres) TB_BWD_APPLY(1, true, 3) else TB_BWD_APPLY(1, false, 3) }

@@ -4,7 +4,7 @@
 //
 //   y[n,h,w,k] = sum_{r,s,c} x[n, h+r-1, w+s-1, c] * wt[k,r,s,c]          x, y NHWC bf16, fp32 accumulation
 //
-// Second generation of csrc/conv_halo.cu. What the first one measured on B200 (profiles/conv_r2a.md): the
+// Second generation of csrc/conv_halo.cu. What the first one measured on B200 (profiles/conv_r2.md): the
 // numerics were right, but the tensor pipe sat idle 65-79 % of the time because the single MMA-issuing thread
 // needed ~640 cycles of integer divisions, descriptor construction and per-tap barrier traffic for every 4
 // MMAs. This version

@@ -9,14 +9,21 @@
 //                   tcgen05.commit releases smem stages ("empty") and publishes finished
 //                   accumulators ("tmem_full")
 //   warp 2        : TMEM allocator (tcgen05.alloc / dealloc, 2 accumulator stages)
-//   warp 3        : (pull variant) TMA-stores gathered B tiles to the local weight buffer
+//   warp 3        : (pull variant) copy engine: bulk-copies the remote shards of B into the local weight buffer, n tile
+//                   by n tile, and publishes a per-tile "ready" flag the producers wait on
 //   warps 4-7     : epilogue      - tcgen05.ld TMEM -> registers, bias/activation, cast, store
 //
 // The pull variant (K2) is the load side of the parameter pull that the reference only prices
 // as "model_size / bandwidth" (core/network/network_service.py:34-37): B is sharded by rows
-// over the parameter-server ranks, and the producer's TMA reads every tile straight out of the
-// owning rank's memory over NVLink, after that rank's PARAM_DONE flag says the shard is
-// updated. FC layer shapes come from core/models.py:9-20 (VGG fc6 25088x4096 etc.).
+// over the parameter-server ranks. Round 1 let every CTA's TMA read its B tile straight out of the owner's
+// memory; measured at 4 and 8 GPUs that loses to NCCL all_gather + cuBLAS by 2-17x, because peer memory is
+// not cached in the local L2 and every 128-row block of A re-fetched the tile over NVLink
+// (profiles/comm_pull_r2.md). Now every remote byte crosses NVLink ONCE: warp 3 of every CTA is a copy engine
+// (cp.async.bulk owner -> shared -> local weight buffer, 16 KB pieces, double buffered) that walks the n tiles in
+// the order the GEMM consumes them and publishes one flag per tile; the producers wait for a tile's flag and
+// then load it from LOCAL memory like any other GEMM, so the transfer of tile n+1.. overlaps the MMAs of tile
+// n. After the kernel the full gathered matrix is resident locally (backward and the other layers use it).
+// FC layer shapes come from core/models.py:9-20 (VGG fc6 25088x4096 etc.).
 #include "common.cuh"
 #include "../include/tiresias_b200.h"
 
@@ -36,14 +43,17 @@ constexpr int kAccumStages = 2;
 
 // THIN = short reduction (K <= 256): the kernel is bound by its output stores, not by the mainloop, so it
 // trades one mainloop stage for a deeper store pipeline in the epilogue.
-template <int BLOCK_N, bool THIN>
+constexpr int kCopyPiece = 16 * 1024;   // pull variant: bytes per bulk copy of the copy engine (two in flight)
+
+template <int BLOCK_N, bool THIN, bool PULL = false>
 struct Cfg {
-  static constexpr int kStages = (BLOCK_N == 256 ? 4 : 6) - (THIN ? 1 : 0);
+  static constexpr int kStages = (BLOCK_N == 256 ? 4 : 6) - (THIN ? 1 : 0) - (PULL ? 1 : 0);
+  static constexpr int kCopyBytes = PULL ? 2 * kCopyPiece : 0;
   static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = kAccumStages * BLOCK_N;  // 512 or 256 (power of two)
-  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages) * 8 + 16;
+  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages + 2) * 8 + 16;
   // Epilogue staging: per epilogue warp two 32-row x 128-byte tiles (swizzle-128B), TMA-stored.
   static constexpr int kEpiTileBytes = 32 * 128;
   // kEpiBufs staging tiles per epilogue warp: a TMA store occupies its tile for ~1 us, so with two tiles a
@@ -52,7 +62,7 @@ struct Cfg {
   static constexpr int kEpiBytes = 4 * kEpiBufs * kEpiTileBytes;
   static constexpr int kEpiBiasBytes = kAccumStages * 256 * 4;   // the tile's bias row, per accumulator stage
   static constexpr int kSmemBytes =
-      kStages * kStageBytes + kEpiBytes + kEpiBiasBytes + kBarrierBytes;
+      kStages * kStageBytes + kEpiBytes + kEpiBiasBytes + kCopyBytes + kBarrierBytes;
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
@@ -137,6 +147,10 @@ __device__ __forceinline__ void st_shared_16(uint32_t addr, const uint4& v) {
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait_n() {   // all but the N latest bulk groups have completed
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void tma_store_wait_all() {
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -238,7 +252,7 @@ struct ConvGeom {
   int flip;          // mode 1: weights are read as tap (R-1-r, S-1-s) through a 3-D map, MN-major (dgrad)
   // n / d as (n * ceil(2^40 / d)) >> 40, exact for n * d < 2^40 (host-computed): the producer is ONE thread, and
   // a hardware-less integer division costs it ~40 dependent instructions — six of them per k-block made the
-  // wgrad producer slower than the MMAs it feeds (profiles/conv_r2a.md)
+  // wgrad producer slower than the MMAs it feeds (profiles/conv_r2.md)
   unsigned long long m_plane, m_ow, m_cblocks, m_s;
   int lower_w;       // lower corner along w (== lower except for the parity classes of a strided dgrad)
   // flip mode: window tap (r, s) reads forward-weight tap (wt_rb - wt_rs*r) * wt_S + (wt_sb - wt_ss*s)
@@ -275,12 +289,34 @@ struct GemmParams {
   const uint32_t* flags;   // local flag pad
   int* status;
   unsigned long long budget;
+  // copy engine of the pull variant
+  const uint8_t* owner_base[TB200_MAX_WORLD];   // every rank's copy of B (peer mappings), byte address of row 0
+  uint8_t* local_base;                          // this rank's copy
+  uint32_t* pull_cnt;                           // [num_n] arrivals of the CTAs' copy warps (self-resetting)
+  uint32_t* pull_ready;                         // [num_n] epoch at which the tile was last gathered
 };
 
 struct PullMaps {
-  CUtensorMap b[TB200_MAX_WORLD];  // B shard of every owner (peer-mapped addresses)
-  CUtensorMap b_local;             // this rank's full B, written by the gather-store warp
+  CUtensorMap b_local;             // this rank's full B: gathered by the copy engine, read by the producers
 };
+
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store_1d(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 
 // Epilogue of one 32-row slice of an accumulator tile (one epilogue warp): per 128 output bytes per row
 // (64 bf16 or 32 fp32 columns) TMEM -> registers, + bias (the tile's bias row sits in shared memory, loaded
@@ -361,13 +397,22 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
   }
 }
 
+// Pull variant: every rank walks the n tiles starting at its own shard, so the tensor cores work on local tiles
+// while the copy engine gathers the first remote ones.
+template <bool kPull, int BLOCK_N>
+__device__ __forceinline__ int pull_n_order(const GemmParams& p, int t) {
+  if constexpr (!kPull) return t;
+  const int n = t + (p.rank * (p.rows_per_rank / BLOCK_N)) % p.num_n;
+  return n >= p.num_n ? n - p.num_n : n;
+}
+
 template <int BLOCK_N, bool kPull, bool THIN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                     const __grid_constant__ CUtensorMap map_b,
                     const __grid_constant__ CUtensorMap map_d,
                     const __grid_constant__ PullMaps pull, const GemmParams p) {
-  using C = Cfg<BLOCK_N, THIN>;
+  using C = Cfg<BLOCK_N, THIN, kPull>;
   // SWIZZLE_128B tiles need 1024-byte alignment (the kernel has no static shared memory, so the
   // dynamic segment starts at the CTA's 1024-byte aligned shared-memory base).
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -376,12 +421,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t b_smem = smem_base + C::kStages * C::kABytes;
   const uint32_t epi_smem = smem_base + C::kStages * C::kStageBytes;   // 1024-byte aligned
   const uint32_t epi_bias_smem = epi_smem + C::kEpiBytes;
-  const uint32_t bar_base = epi_bias_smem + C::kEpiBiasBytes;
+  const uint32_t copy_smem = epi_bias_smem + C::kEpiBiasBytes;          // pull variant: 2 x kCopyPiece
+  const uint32_t bar_base = copy_smem + C::kCopyBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + s); };
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + kAccumStages + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * C::kStages + 2 * kAccumStages);
+  auto copy_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + 2);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -396,12 +443,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), kPull ? 2 : 1);
+      mbar_init(empty_bar(s), 1);
     }
     for (int s = 0; s < kAccumStages; ++s) {
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), 4);  // one arrive per epilogue warp
     }
+    mbar_init(copy_bar(0), 1);
+    mbar_init(copy_bar(1), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -421,24 +470,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     // ================= TMA producer =================
     int stage = 0;
     uint32_t phase = 0;
-    uint32_t owner_ready = 0;  // bitmask of owners whose PARAM_DONE flag has been observed
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       const int ks = it % p.splits;
       const int tile = it / p.splits;
-      const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      const int m_blk = tile % p.num_m, n_blk = pull_n_order<kPull, BLOCK_N>(p, tile / p.num_m);
       const int kb0 = (int)((long long)ks * p.num_kb / p.splits);
       const int kb1 = (int)((long long)(ks + 1) * p.num_kb / p.splits);
       const CUtensorMap* bmap = &map_b;
       int b_row = n_blk * BLOCK_N;
       if constexpr (kPull) {
+        // a tile another rank owns is readable locally once every CTA's copy warp has finished its share of it
         const int owner = b_row / p.rows_per_rank;
-        bmap = &pull.b[owner];
-        b_row -= owner * p.rows_per_rank;
-        if (!(owner_ready & (1u << owner))) {
-          const uint32_t want = *p.epoch - 1;  // shards written during the step that just ended
-          if (!wait_epoch(p.flags + TB200_FLAG_PARAM_DONE(p.bucket, owner), want, p.budget))
-            atomicExch(p.status, 5);
-          owner_ready |= 1u << owner;
+        if (owner != p.rank) {
+          const uint32_t want = *p.epoch;
+          unsigned long long polls = 0;
+          while (!epoch_reached(ld_acquire_gpu(p.pull_ready + n_blk), want)) {
+            __nanosleep(32);
+            if (p.budget && ++polls > p.budget) { atomicExch(p.status, 5); break; }
+          }
+          asm volatile("fence.proxy.async.global;" ::: "memory");   // the TMA loads below read what bulk stores wrote
         }
       }
       // implicit-GEMM convolution, mode 1: the tile's first output pixel -> (image, window corner)
@@ -567,29 +617,81 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       if (++as == kAccumStages) { as = 0; aphase ^= 1; }
     }
   } else if (kPull && warp == 3 && lane == 0) {
-    // ================= gather-store (pull variant) =================
-    // The CTAs that own m_blk == 0 write each B tile they receive into the local weight
-    // buffer, so that after this GEMM the full gathered matrix is resident locally.
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int it = blockIdx.x; it < items; it += gridDim.x) {
-      const int ks = it % p.splits;
-      const int tile = it / p.splits;
-      const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
-      const int kb0 = (int)((long long)ks * p.num_kb / p.splits);
-      const int kb1 = (int)((long long)(ks + 1) * p.num_kb / p.splits);
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(full_bar(stage), phase);
-        if (m_blk == 0 && (n_blk * BLOCK_N) / p.rows_per_rank != p.rank) {
-          tma_store_2d(&pull.b_local, b_smem + stage * C::kBBytes, kb * BLOCK_K, n_blk * BLOCK_N);
-          tma_store_commit();
-          tma_store_wait_read();
-        }
-        mbar_arrive(empty_bar(stage));
-        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+    // ================= copy engine (pull variant) =================
+    // The remote n tiles (BLOCK_N rows x K, contiguous in the owner's and in the local buffer) in the order the GEMM
+    // consumes them, cut into 16 KB pieces numbered across tiles; this CTA moves pieces blockIdx.x,
+    // blockIdx.x + gridDim.x, ... through a two-deep staging ring: the load of piece i+1 is in flight while piece i
+    // is stored, and a piece is counted into its tile once its store has completed (one group later).
+    uint32_t owner_ready = 0;                     // owners whose PARAM_DONE flag has been observed
+    uint32_t ph[2] = {0, 0};
+    const size_t tile_bytes = (size_t)BLOCK_N * p.K * 2;
+    const int ppt = (int)((tile_bytes + kCopyPiece - 1) / kCopyPiece);      // pieces per tile
+    const int own_blks = p.rows_per_rank / BLOCK_N, own_first = p.rank * own_blks;
+    const int own_cnt = own_first < p.num_n ? (p.num_n - own_first < own_blks ? p.num_n - own_first : own_blks) : 0;
+    const int rot = own_first % p.num_n;          // pull_n_order(): the GEMM starts at this rank's own tiles
+    const int remote_tiles = p.num_n - own_cnt;
+    const long long total = (long long)remote_tiles * ppt;
+    const uint32_t epoch = *p.epoch;
+    auto locate = [&](long long g, int* n_blk, size_t* off, uint32_t* sz) {
+      const int j = (int)(g / ppt);                // j-th remote tile in consumption order
+      int n = rot + own_cnt + j;                   // the tiles after mine, wrapping around
+      if (n >= p.num_n) n -= p.num_n;
+      *n_blk = n;
+      *off = (size_t)(g - (long long)j * ppt) * kCopyPiece;
+      *sz = (uint32_t)(tile_bytes - *off < (size_t)kCopyPiece ? tile_bytes - *off : (size_t)kCopyPiece);
+    };
+    auto issue_load = [&](long long g, int buf) {
+      int n_blk; size_t off; uint32_t sz;
+      locate(g, &n_blk, &off, &sz);
+      const int owner = (n_blk * BLOCK_N) / p.rows_per_rank;
+      if (!(owner_ready & (1u << owner))) {
+        // shards written during the step that just ended
+        if (!wait_epoch(p.flags + TB200_FLAG_PARAM_DONE(p.bucket, owner), epoch - 1, p.budget)) atomicExch(p.status, 5);
+        owner_ready |= 1u << owner;
       }
+      mbar_expect_tx(copy_bar(buf), sz);
+      bulk_load_1d(copy_smem + buf * kCopyPiece, p.owner_base[owner] + (size_t)n_blk * tile_bytes + off, sz, copy_bar(buf));
+    };
+    auto count_in = [&](long long g) {
+      int n_blk; size_t off; uint32_t sz;
+      locate(g, &n_blk, &off, &sz);
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+      __threadfence();
+      const unsigned prev = atomicAdd(p.pull_cnt + n_blk, 1u);
+      if (prev == (unsigned)ppt - 1) {
+        p.pull_cnt[n_blk] = 0;                     // self-resetting: ready for the next launch
+        __threadfence();
+        st_release_gpu(p.pull_ready + n_blk, epoch);
+      }
+    };
+    long long g = blockIdx.x;
+    int buf = 0;
+    long long prev_g = -1;                         // piece whose store is the latest committed group
+    if (g < total) issue_load(g, 0);
+    for (; g < total; g += gridDim.x) {
+      const long long gn = g + gridDim.x;
+      if (gn < total) {
+        if (prev_g >= 0) tma_store_wait_read_n<0>();   // the other buffer's store (piece prev_g) has read it
+        issue_load(gn, buf ^ 1);
+      }
+      int n_blk; size_t off; uint32_t sz;
+      locate(g, &n_blk, &off, &sz);
+      mbar_wait(copy_bar(buf), ph[buf]);
+      ph[buf] ^= 1;
+      fence_proxy_async_smem();
+      bulk_store_1d(p.local_base + (size_t)n_blk * tile_bytes + off, copy_smem + buf * kCopyPiece, sz);
+      tma_store_commit();
+      if (prev_g >= 0) {
+        tma_store_wait_n<1>();                     // every group but the one just committed is complete
+        count_in(prev_g);
+      }
+      prev_g = g;
+      buf ^= 1;
     }
-    tma_store_wait_all();
+    if (prev_g >= 0) {
+      tma_store_wait_all();
+      count_in(prev_g);
+    }
   } else if (warp >= 4) {
     // ================= epilogue =================
     const int ew = warp - 4;  // == warp % 4: the TMEM lane quarter this warp may touch
@@ -615,7 +717,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
       const int ks = it % p.splits;
       const int tile = it / p.splits;
-      const int m_blk = tile % p.num_m, n_blk = tile / p.num_m;
+      const int m_blk = tile % p.num_m, n_blk = pull_n_order<kPull, BLOCK_N>(p, tile / p.num_m);
       if (p.stats && n_blk != st_n) {
         if (st_n >= 0) flush_stats(st_n);
         st_n = n_blk;
@@ -1036,10 +1138,57 @@ int plan_tiles(int M, int N, int K, bool pull, int rows_per_rank, int sms, int* 
   return 0;
 }
 
+}  // namespace
+#include "gemm_2cta.cuh"
+namespace {
+
+// 0 = never, 1 = whenever the problem is eligible, -1 = eligible and large enough to fill the pairs
+// (TB200_GEMM_2CTA or tb200_gemm_set_pair_mode).
+int g_pair_mode = -2;
+int pair_mode() {
+  if (g_pair_mode == -2) {
+    const char* e = getenv("TB200_GEMM_2CTA");
+    g_pair_mode = e ? atoi(e) : -1;
+  }
+  return g_pair_mode;
+}
+
+// Split-K factor of the 2-CTA kernel: 256 x 256 tiles over sms / 2 pairs, same bounds as plan_tiles().
+int plan_pair_splits(int M, int N, int K, int pairs) {
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  const int tiles = ((M + 255) / 256) * ((N + 255) / 256);
+  int splits = 1;
+  if (tiles < pairs) {
+    int max_splits = num_kb / 4;
+    if (max_splits > pairs) max_splits = pairs;
+    const double in_bytes = 2.0 * ((double)M * K + (double)N * K);
+    const double plane_bytes = 4.0 * (double)M * N;
+    int by_traffic = (int)(0.1 * in_bytes / plane_bytes);
+    if (by_traffic < 16) by_traffic = 16;
+    if (max_splits > by_traffic) max_splits = by_traffic;
+    double best = 0.0;
+    for (int s = 1; s <= max_splits; ++s) {
+      const int it = tiles * s;
+      const int waves = (it + pairs - 1) / pairs;
+      const double eff = (double)it / ((double)waves * pairs);
+      if (eff > best + 1e-9) { best = eff; splits = s; }
+    }
+  }
+  return splits;
+}
+
+int launch_gemm_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const GemmParams& p, int pairs,
+                     cudaStream_t stream) {
+  static DeviceOnce configured;
+  if (int rc = ensure_dynamic_smem(configured, pair::gemm2_kernel, pair::kSmemBytes)) return rc;
+  pair::gemm2_kernel<<<2 * pairs, kGemmThreads, pair::kSmemBytes, stream>>>(ma, mb, md, p);
+  return launched();
+}
+
 template <int BLOCK_N, bool kPull, bool THIN>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const PullMaps& pull,
                 const GemmParams& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BLOCK_N, THIN>;
+  using C = Cfg<BLOCK_N, THIN, kPull>;
   auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull, THIN>;
   static DeviceOnce configured;      // one per template instantiation
   if (int rc = ensure_dynamic_smem(configured, kern, C::kSmemBytes)) return rc;
@@ -1063,7 +1212,8 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
                 int N, int K, int d_dtype, int act, const uint32_t* epoch_dev, int* status_dev,
                 unsigned long long budget, cudaStream_t stream, float* fixed_scratch = nullptr,
                 size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0, const ConvHost* conv = nullptr,
-                float* stats = nullptr, size_t stats_floats = 0, int* stats_parts = nullptr) {
+                float* stats = nullptr, size_t stats_floats = 0, int* stats_parts = nullptr,
+                uint32_t* pull_sync = nullptr) {
   const bool pull = world != nullptr;
   if (stats_parts) *stats_parts = 0;
   if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
@@ -1107,7 +1257,23 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
 
   const int sms = sm_count();
   int block_n = 0, splits = 1;
-  if (int rc = plan_tiles(M, N, K, pull, rows_per_rank, sms, &block_n, &splits)) return rc;
+  // 2-CTA kernel (gemm_2cta.cuh): plain GEMMs with a TMA-storable output; the allocation-free entry point keeps
+  // the one-CTA plan its documentation states
+  bool use_pair = false;
+  if (!pull && !conv && !stats && !fixed_scratch && pair_mode() != 0 && sms >= 2) {
+    const int sp = plan_pair_splits(M, N, K, sms / 2);
+    const bool f32 = sp > 1 || d_dtype == TB200_F32;
+    const bool storable = (N % (f32 ? 4 : 8)) == 0;
+    const bool big = M >= 256 && N >= 256 && K >= 256;
+    if (storable && (pair_mode() == 1 || big)) {
+      use_pair = true;
+      block_n = 256;
+      splits = sp;
+      p.num_m = (M + 255) / 256;
+    }
+  }
+  if (!use_pair)
+    if (int rc = plan_tiles(M, N, K, pull, rows_per_rank, sms, &block_n, &splits)) return rc;
   if (conv && conv->g.sc_on) splits = 1;      // the split-K second pass writes rows in order, not scattered
   p.num_n = (N + block_n - 1) / block_n;
   const int tiles = p.num_m * p.num_n;
@@ -1168,19 +1334,22 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
     p.budget = budget;
     if ((long long)rows_per_rank * world->world < N)
       return fail("tb200_gemm_pull: shards do not cover N%s");
-    for (int s = 0; s < world->world; ++s) {
-      const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(world->param[s]) + b_off +
-                                  (size_t)s * rows_per_rank * K;
-      int rows = rows_per_rank;
-      if ((long long)(s + 1) * rows_per_rank > N) rows = N - s * rows_per_rank;
-      if (rows <= 0) rows = 1;
-      if (int rc = make_map(&pm.b[s], base, rows, K, block_n)) return rc;
-    }
+    if (!pull_sync) return fail("tb200_gemm_pull: no synchronisation scratch%s");
+    // every rank's copy of B has the same [rows_per_rank * world, K] layout at element offset b_off of its
+    // parameter buffer; the copy engine moves whole n tiles between them
+    for (int s = 0; s < world->world; ++s)
+      p.owner_base[s] = reinterpret_cast<const uint8_t*>(world->param[s]) + b_off * 2;
+    p.local_base = reinterpret_cast<uint8_t*>(world->param[world->rank]) + b_off * 2;
+    p.pull_cnt = pull_sync;
+    p.pull_ready = pull_sync + TB200_PULL_SYNC_WORDS / 2;
+    if ((N + block_n - 1) / block_n > TB200_PULL_SYNC_WORDS / 2)
+      return fail("tb200_gemm_pull: N %s(%ld) has more column tiles than the synchronisation scratch holds", "", N);
     const __nv_bfloat16* local = reinterpret_cast<const __nv_bfloat16*>(world->param[world->rank]) + b_off;
     if (int rc = make_map(&pm.b_local, local, N, K, block_n)) return rc;
     mb = pm.b_local;
   } else {
-    if (int rc = b_mn ? make_map_mn(&mb, B, K, N) : make_map(&mb, B, N, K, block_n)) return rc;
+    // (the pair kernel's B box is this CTA's 128 rows of the 256-wide tile)
+    if (int rc = b_mn ? make_map_mn(&mb, B, K, N) : make_map(&mb, B, N, K, use_pair ? 128 : block_n)) return rc;
   }
 
   const int items = tiles * splits;
@@ -1196,7 +1365,9 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   }
   int rc;
   const bool thin = !pull && p.num_kb <= 4 && splits == 1;   // store-bound: deeper epilogue pipeline
-  if (block_n == 256) {
+  if (use_pair) {
+    rc = launch_gemm_pair(ma, mb, md, p, items < sms / 2 ? items : sms / 2, stream);
+  } else if (block_n == 256) {
     rc = pull ? launch_gemm<256, true, false>(ma, mb, md, pm, p, grid, stream)
               : (thin ? launch_gemm<256, false, true>(ma, mb, md, pm, p, grid, stream)
                       : launch_gemm<256, false, false>(ma, mb, md, pm, p, grid, stream));
@@ -1245,10 +1416,11 @@ int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off
                             int rows_per_rank, const void* A, void* D, const void* bias,
                             int bias_dtype, int M, int N, int K, int d_dtype, int act,
                             const uint32_t* epoch_dev, int* status_dev,
-                            unsigned long long spin_budget, cudaStream_t stream) {
+                            unsigned long long spin_budget, uint32_t* sync, cudaStream_t stream) {
   if (!world) return fail("tb200_gemm_bf16_nt_pull: null world%s");
   return gemm_common(world, bucket, b_off, rows_per_rank, A, nullptr, D, bias, bias_dtype, M, N, K,
-                     d_dtype, act, epoch_dev, status_dev, spin_budget, stream);
+                     d_dtype, act, epoch_dev, status_dev, spin_budget, stream, nullptr, 0, 0, 0, nullptr, nullptr, 0,
+                     nullptr, sync);
 }
 
 // ---- implicit-GEMM convolutions (K5: "convs as implicit GEMM on the same mainloop") ----------------
@@ -1397,6 +1569,10 @@ int tb200_probe_shifted_operand(const void* A, const void* B, float* D, int shif
 
 // How many split-K partial planes tb200_gemm_bf16_nt / _noalloc would use for this problem on the current
 // device (1 = no scratch needed). Scratch bytes = splits * M * N * 4.
+// -1 (default): the 2-CTA kernel serves eligible problems of at least 256 x 256 x 256; 0: never; 1: every
+// eligible problem (tests). Not part of the reference's surface.
+void tb200_gemm_set_pair_mode(int mode) { g_pair_mode = mode; }
+
 int tb200_gemm_plan_splits(int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   int block_n = 0, splits = 1;

@@ -199,8 +199,15 @@ __global__ void __launch_bounds__(kCommThreads) ps_push_pull_kernel(const PushAr
   }
   __syncthreads();
   if (!s_ok) {
-    if (threadIdx.x == 0) atomicExch(a.status, 1);
-    return;  // leave the shard untouched; the host watchdog sees status != 0
+    // Leave the shard untouched; the host watchdog sees status != 0. Still take part in the arrival counter
+    // (without publishing PARAM_DONE): CTAs that did get through have incremented it, and a counter left
+    // non-zero would let the NEXT launch publish before all of its CTAs have stored their parameters.
+    if (threadIdx.x == 0) {
+      atomicExch(a.status, 1);
+      const unsigned prev = atomicAdd(a.counter, 1u);
+      if (prev == gridDim.x - 1) *a.counter = 0;
+    }
+    return;
   }
 
   // 3-4. Reduce the W gradient slices in rank order, update, broadcast.
@@ -428,7 +435,11 @@ __global__ void __launch_bounds__(kCommThreads) direct_allreduce_kernel(const Di
     s_ok = 0;
   __syncthreads();
   if (!s_ok) {
-    if (threadIdx.x == 0) atomicExch(a.status, 4);
+    if (threadIdx.x == 0) {          // keep the arrival counter consistent for the next launch (see ps_push_pull)
+      atomicExch(a.status, 4);
+      const unsigned prev = atomicAdd(a.counter, 1u);
+      if (prev == gridDim.x - 1) *a.counter = 0;
+    }
     return;
   }
   const size_t slice_vec = a.n / 8 / W;

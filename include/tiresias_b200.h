@@ -260,17 +260,27 @@ int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void
  * No counterpart in the reference.                                                           */
 int tb200_gemm_plan_splits(int M, int N, int K);
 
+/* Plain GEMMs (not the convolutions, the pull variant or the allocation-free entry point) of at least
+ * 256 x 256 x 256 run on the 2-CTA kernel (cta_group::2, 256 x 256 pair tiles; csrc/gemm_2cta.cuh).
+ * mode: -1 that default, 0 never, 1 every eligible problem. Also TB200_GEMM_2CTA. No reference counterpart. */
+void tb200_gemm_set_pair_mode(int mode);
+
 /* ---- K2 (load side): PS->worker pull fused into the first GEMM that consumes the weights.
- * B is sharded by rows across the world: rank s owns rows [s*rows_per_rank, ...) inside its
- * own parameter buffer at element offset b_off. TMA reads each B tile straight from the
- * owner's memory (after its PARAM_DONE flag for `bucket` reaches *epoch_dev - 1, the step that just ended),
- * and the tiles are also written to this rank's parameter buffer so later consumers
- * (backward, the other layers) find the gathered weights locally.                           */
+ * B is sharded by rows across the world: rank s owns rows [s*rows_per_rank, ...) of a [rows_per_rank * world, K]
+ * matrix that every rank holds at element offset b_off of its parameter buffer (rows_per_rank a multiple of 128;
+ * rows past N are padding). One warp per CTA is a copy engine that bulk-copies the other ranks' rows out of
+ * their memory into this rank's copy, column tile by column tile, once the owner's PARAM_DONE flag for
+ * `bucket` has reached *epoch_dev - 1 (the step that just ended), and publishes a flag per tile; the GEMM's
+ * producers wait for a tile's flag and then TMA-load it locally. Every remote byte crosses NVLink once, the
+ * transfer of later tiles overlaps the MMAs of earlier ones, and after the call the gathered matrix is
+ * resident locally for the backward pass. `sync`: TB200_PULL_SYNC_WORDS zero-initialised 32-bit words owned by
+ * this layer (arrival counters + per-tile epochs; the kernels keep them consistent from launch to launch).  */
+#define TB200_PULL_SYNC_WORDS 4096
 int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off,
                             int rows_per_rank, const void* A, void* D, const void* bias,
                             int bias_dtype, int M, int N, int K, int d_dtype, int act,
                             const uint32_t* epoch_dev, int* status_dev,
-                            unsigned long long spin_budget, cudaStream_t stream);
+                            unsigned long long spin_budget, uint32_t* sync, cudaStream_t stream);
 
 /* ---- small fused helpers ----------------------------------------------------------------- */
 /* uint8 NHWC image batch -> normalised bf16 NHWC (mean/std per channel, C == 3).            */
@@ -333,6 +343,19 @@ int tb200_bn_fwd_train_stats(const void* x, const void* residual, void* y, const
                              int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
                              float* save_mean, float* save_invstd, float* scratch, const float* conv_partials,
                              int conv_nparts, size_t rows, int C, int relu, cudaStream_t stream);
+/* The same two with every option: statistics from a convolution's epilogue (conv_partials, may be NULL) and the
+ * ReLU mask as bits. A residual + ReLU layer's backward needs the sign of every output; `relu_mask` (rows*C/8
+ * bytes + 16 of slack) carries it as one bit per element, so the backward reads 1/16 of a tensor instead of y in
+ * both of its passes. Only where tb200_bn_mask_supported(rows, C) (the TMA-streamed kernels).              */
+int tb200_bn_mask_supported(size_t rows, int C);
+int tb200_bn_fwd_train_ex(const void* x, const void* residual, void* y, const void* gamma, const void* beta,
+                          int param_dtype, float* running_mean, float* running_var, float momentum, float eps,
+                          float* save_mean, float* save_invstd, float* scratch, const float* conv_partials,
+                          int conv_nparts, uint8_t* relu_mask, size_t rows, int C, int relu, cudaStream_t stream);
+int tb200_bn_bwd_ex(const void* dy, const void* x, const void* y, const uint8_t* relu_mask, const void* gamma,
+                    const void* beta, int param_dtype, const float* save_mean, const float* save_invstd, void* dx,
+                    void* dres, void* dgamma, void* dbeta, float* scratch, size_t rows, int C, int relu,
+                    cudaStream_t stream);
 int tb200_bn_apply(const void* x, const void* residual, void* y, const float* scale_shift,
                    size_t rows, int C, int relu, cudaStream_t stream);
 int tb200_bn_bwd(const void* dy, const void* x, const void* y, const void* gamma, const void* beta,

@@ -76,6 +76,37 @@ def test_bitwise_repeatable_and_scratch_reuse(cuda_device):
         assert torch.equal(y, outs[0][0]) and torch.equal(rm, outs[0][1]) and torch.equal(rv, outs[0][2])
 
 
+@pytest.mark.parametrize("shape", [(32, 256, 28, 28), (16, 64, 56, 56), (64, 2048, 7, 7), (24, 512, 28, 28)])
+def test_relu_bit_mask_equals_saved_output_path(cuda_device, shape, monkeypatch):
+    """Residual + ReLU layers save one bit per element instead of y: same gradients, bit for bit."""
+    from tiresias_b200.ops import batchnorm, native
+    n, c, h, w = shape
+    assert native.lib().tb200_bn_mask_supported(n * h * w, c) == 1
+    g0 = torch.Generator(device=cuda_device).manual_seed(c)
+    mk = lambda: torch.randn(shape, device=cuda_device, generator=g0).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last)
+    x0, r0, dy = mk(), mk(), mk()
+    gamma0 = (torch.rand(c, device=cuda_device, generator=g0) + 0.5).to(torch.bfloat16)
+    beta0 = (torch.randn(c, device=cuda_device, generator=g0) * 0.3).to(torch.bfloat16)
+    outs = []
+    for use_mask in (True, False):
+        monkeypatch.setattr(batchnorm, "_USE_MASK", use_mask)
+        x, r = x0.clone().requires_grad_(True), r0.clone().requires_grad_(True)
+        gamma, beta = gamma0.clone().requires_grad_(True), beta0.clone().requires_grad_(True)
+        y = fused_bn_act(x, gamma, beta, None, None, r, True)
+        saved = [t for t in y.grad_fn.saved_tensors if t is not None and t.dtype == torch.uint8]
+        assert bool(saved) == use_mask
+        if use_mask:        # the bits are the sign of the output
+            bits = saved[0][: n * h * w * c // 8]
+            want = (y.detach().permute(0, 2, 3, 1).reshape(-1, 8) > 0).to(torch.uint8)
+            want = (want << torch.arange(8, device=cuda_device, dtype=torch.uint8)).sum(dim=1).to(torch.uint8)
+            assert torch.equal(bits, want)
+        y.backward(dy)
+        outs.append((y.detach(), x.grad, r.grad, gamma.grad, beta.grad))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+
+
 def test_module_train_and_eval_match_torch(cuda_device):
     torch.manual_seed(0)
     mod = FusedBatchNormAct(128, relu=True).to(cuda_device).to(torch.bfloat16)

@@ -46,6 +46,74 @@ def test_gemm_epilogue(cuda_device, act, bias_dtype):
     assert torch.allclose(got, ref, rtol=3e-2, atol=3e-2), (got - ref).abs().max().item()
 
 
+@pytest.fixture
+def pair_gemm():
+    """Every eligible GEMM on the 2-CTA (cta_group::2) kernel, whatever its size."""
+    native.lib().tb200_gemm_set_pair_mode(1)
+    yield
+    native.lib().tb200_gemm_set_pair_mode(-1)
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 256, 64), (512, 512, 1024), (300, 520, 200), (128, 264, 72), (1000, 1000, 520),
+                                   (256, 4096, 25088), (2048, 1536, 4096), (64, 256, 8192)])
+def test_pair_gemm_nt_matches_fp32(cuda_device, pair_gemm, m, n, k):
+    """256 x 256 pair tiles (UMMA M = 256 over two SMs): full tiles, M / N / K tails, one tile, split-K."""
+    torch.manual_seed(m + n + k)
+    a = _bf16(torch.randn(m, k, device=cuda_device))
+    b = _bf16(torch.randn(n, k, device=cuda_device) / (k ** 0.5))
+    ref = a.float() @ b.float().t()
+    got = native.gemm_nt(a, b, out_dtype=torch.float32)
+    assert torch.allclose(got, ref, rtol=1e-3, atol=1e-3), (got - ref).abs().max().item()
+    got16 = native.gemm_nt(a, b)
+    assert torch.allclose(got16.float(), ref, rtol=1e-2, atol=1e-2), (got16.float() - ref).abs().max().item()
+    native.lib().tb200_gemm_set_pair_mode(0)
+    one = native.gemm_nt(a, b)
+    native.lib().tb200_gemm_set_pair_mode(1)
+    if native.lib().tb200_gemm_plan_splits(m, n, k) == 1 and k <= 1024:
+        # same k order inside a tile, no split-K on either: the two kernels agree to the bit
+        assert torch.equal(one, got16) or (one.float() - got16.float()).abs().max().item() < 2e-2
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("m,n,k", [(512, 768, 320), (264, 1000, 136)])
+def test_pair_gemm_mn_major(cuda_device, pair_gemm, a_mn, b_mn, m, n, k):
+    torch.manual_seed(5)
+    a = _bf16(torch.randn(m, k, device=cuda_device))
+    b = _bf16(torch.randn(n, k, device=cuda_device) / (k ** 0.5))
+    got = native.gemm(a.t().contiguous() if a_mn else a, b.t().contiguous() if b_mn else b, a_mn_major=a_mn,
+                      b_mn_major=b_mn, out_dtype=torch.float32)
+    ref = a.float() @ b.float().t()
+    assert torch.allclose(got, ref, rtol=1e-3, atol=1e-3), (got - ref).abs().max().item()
+
+
+@pytest.mark.parametrize("act", [native.ACT_NONE, native.ACT_RELU, native.ACT_GELU])
+@pytest.mark.parametrize("bias_dtype", [torch.float32, torch.bfloat16])
+def test_pair_gemm_epilogue(cuda_device, pair_gemm, act, bias_dtype):
+    torch.manual_seed(7)
+    m, n, k = 448, 576, 256
+    a = _bf16(torch.randn(m, k, device=cuda_device))
+    b = _bf16(torch.randn(n, k, device=cuda_device) / 16)
+    bias = torch.randn(n, device=cuda_device).to(bias_dtype)
+    got = native.gemm_nt(a, b, bias, act).float()
+    ref = a.float() @ b.float().t() + bias.float()
+    if act == native.ACT_RELU:
+        ref = torch.relu(ref)
+    elif act == native.ACT_GELU:
+        ref = torch.nn.functional.gelu(ref, approximate="tanh")
+    assert torch.allclose(got, ref, rtol=3e-2, atol=3e-2), (got - ref).abs().max().item()
+
+
+def test_pair_gemm_many_tiles_repeatable(cuda_device, pair_gemm):
+    """More tiles than pairs (persistent loop, both accumulator stages, stage-ring wrap) - twice, same bits."""
+    a = _bf16(torch.randn(4096, 768, device=cuda_device))
+    b = _bf16(torch.randn(5120, 768, device=cuda_device) / 27)
+    x = native.gemm_nt(a, b)
+    y = native.gemm_nt(a, b)
+    ref = a.float() @ b.float().t()
+    assert torch.equal(x, y)
+    assert torch.allclose(x.float(), ref, rtol=1e-2, atol=1e-2)
+
+
 def test_gemm_repeatable(cuda_device):
     a = _bf16(torch.randn(512, 1024, device=cuda_device))
     b = _bf16(torch.randn(768, 1024, device=cuda_device))
@@ -283,14 +351,16 @@ def test_pull_gemm_emulated_owners(cuda_device, world):
     me.post_flags("flags", native.flag_param_done(0, 0), world, 1)
     w = me.native_world("grad", "param", "flags")
     y = torch.empty(m, n, dtype=torch.bfloat16, device=cuda_device)
-    native.check(lib.tb200_gemm_bf16_nt_pull(C.byref(w), 0, 0, rows, a.data_ptr(), y.data_ptr(), None, 0, m, n, k,
-                                             native.BF16, 0, epoch.data_ptr(), status.data_ptr(), 1_000_000,
-                                             native.stream_ptr()))
+    sync = torch.zeros(native.PULL_SYNC_WORDS, dtype=torch.int32, device=cuda_device)
+    for _ in range(2):                                      # twice: the arrival counters reset themselves
+        native.check(lib.tb200_gemm_bf16_nt_pull(C.byref(w), 0, 0, rows, a.data_ptr(), y.data_ptr(), None, 0, m, n, k,
+                                                 native.BF16, 0, epoch.data_ptr(), status.data_ptr(), 1_000_000,
+                                                 sync.data_ptr(), native.stream_ptr()))
     torch.cuda.synchronize()
     assert status.item() == 0
     ref = a.float() @ b.float().t()
     assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-2)
-    # the gather-store warp left the full matrix in rank 0's own buffer
+    # the copy engine left the full matrix in rank 0's own buffer
     assert torch.equal(me.buffers["param"].view(torch.bfloat16).view(n, k), b)
     for r in ranks:
         r.close()

@@ -111,6 +111,10 @@ def _run_job_body(cmd, rank, store, groups, nccl_groups, loopback, device, r, si
         for _ in range(upto - done):
             trainer.step_resident()
         done = upto
+        if not loopback and trainer.check_status() != 0:
+            # an in-kernel wait ran out of its spin budget (a peer is gone): stop now instead of training on
+            # half-updated shards; the controller marks the job failed and frees its GPUs
+            raise RuntimeError(f"in-kernel wait timed out (status {trainer.check_status()}) at iteration {done}")
         if t_steady is None:
             trainer.synchronize()
             t_steady, steady_from = time.time(), done

@@ -8,6 +8,7 @@ kernels are mandatory.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional
 
 import torch
@@ -16,6 +17,7 @@ from torch import nn
 from . import native
 
 _scratch: Dict[tuple, torch.Tensor] = {}
+_USE_MASK = os.environ.get("TB200_BN_MASK", "1") != "0"     # A/B switch for the ReLU bit mask (bench only)
 
 
 def _get_scratch(device: torch.device) -> torch.Tensor:
@@ -53,28 +55,34 @@ class _FusedBNFn(torch.autograd.Function):
                   running_mean.data_ptr() if running_mean is not None else 0,
                   running_var.data_ptr() if running_var is not None else 0,
                   float(momentum), float(eps), save_mean.data_ptr(), save_invstd.data_ptr(), scratch.data_ptr())
-        if stats_partials is not None:
-            # the producing convolution's epilogue summed x already: fold + apply, no statistics pass
-            native.check(native.lib().tb200_bn_fwd_train_stats(
-                *common, stats_partials.data_ptr(), stats_partials.shape[0], rows, c, int(relu), native.stream_ptr()))
-        else:
-            native.check(native.lib().tb200_bn_fwd_train(*common, rows, c, int(relu), native.stream_ptr()))
+        # A residual + ReLU layer's backward needs the sign of every output: as one bit per element where the
+        # streamed kernels serve the shape (the backward then reads 1/16 of a tensor instead of y, twice), else y
+        mask = None
+        if relu and residual is not None and _USE_MASK and native.lib().tb200_bn_mask_supported(rows, c):
+            mask = torch.empty(rows * c // 8 + 16, dtype=torch.uint8, device=x.device)
+        # stats_partials: the producing convolution's epilogue summed x already (fold + apply, no statistics pass)
+        native.check(native.lib().tb200_bn_fwd_train_ex(
+            *common, stats_partials.data_ptr() if stats_partials is not None else 0,
+            stats_partials.shape[0] if stats_partials is not None else 0,
+            mask.data_ptr() if mask is not None else 0, rows, c, int(relu), native.stream_ptr()))
         ctx.relu, ctx.has_res, ctx.rows, ctx.c = bool(relu), residual is not None, rows, c
         # the ReLU mask of a layer without residual input is recomputed from x in the backward
-        ctx.save_for_backward(x, y if (relu and residual is not None) else None, gamma, beta, save_mean, save_invstd)
+        ctx.save_for_backward(x, y if (relu and residual is not None and mask is None) else None, mask, gamma, beta,
+                              save_mean, save_invstd)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, gamma, beta, save_mean, save_invstd = ctx.saved_tensors
+        x, y, mask, gamma, beta, save_mean, save_invstd = ctx.saved_tensors
         dy, _, _ = _rows_channels(dy)
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.has_res else None
         dgamma = torch.empty_like(gamma)
         dbeta = torch.empty_like(gamma)
         scratch = _get_scratch(x.device)
-        native.check(native.lib().tb200_bn_bwd(
-            dy.data_ptr(), x.data_ptr(), y.data_ptr() if y is not None else 0, gamma.data_ptr(),
+        native.check(native.lib().tb200_bn_bwd_ex(
+            dy.data_ptr(), x.data_ptr(), y.data_ptr() if y is not None else 0,
+            mask.data_ptr() if mask is not None else 0, gamma.data_ptr(),
             beta.data_ptr(), native.dtype_code(gamma.dtype), save_mean.data_ptr(), save_invstd.data_ptr(), dx.data_ptr(),
             dres.data_ptr() if dres is not None else 0, dgamma.data_ptr(), dbeta.data_ptr(),
             scratch.data_ptr(), ctx.rows, ctx.c, int(ctx.relu), native.stream_ptr()))

@@ -28,7 +28,7 @@ def _pad_rows(x: torch.Tensor, multiple: int) -> torch.Tensor:
 
 def _gemm_nt_pull(x2d: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act: int,
                   pull_ctx) -> torch.Tensor:
-    """K2: forward GEMM whose B tiles are TMA-loaded from the PS shard owners' memory."""
+    """K2: forward GEMM that gathers its row-sharded weight from the PS shard owners while it runs."""
     import ctypes as C
     trainer, bucket = pull_ctx
     m, k = x2d.shape
@@ -38,7 +38,8 @@ def _gemm_nt_pull(x2d: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.
     native.check(native.lib().tb200_gemm_bf16_nt_pull(
         C.byref(trainer._world_struct), bucket.index, bucket.offset, bucket.pull_rows,
         x2d.data_ptr(), y.data_ptr(), bias_ptr, bias_dt, m, n, k, native.BF16, act,
-        trainer.epoch.data_ptr(), trainer.status.data_ptr(), trainer.spin_budget, native.stream_ptr()))
+        trainer.epoch.data_ptr(), trainer.status.data_ptr(), trainer.spin_budget, bucket.pull_sync.data_ptr(),
+        native.stream_ptr()))
     return y
 
 

@@ -18,6 +18,7 @@ MAX_BUCKETS = 256
 MAX_RING_CTAS = 64
 IPC_HANDLE_BYTES = 64
 FLAG_WORDS = 2 * MAX_BUCKETS * MAX_WORLD + 2 * MAX_RING_CTAS
+PULL_SYNC_WORDS = 4096        # TB200_PULL_SYNC_WORDS
 BN_SCRATCH_FLOATS = 1024 + 2 * 64 * 1024 + 4 * 4096 + 2 * 1024 * 1024   # TB200_BN_SCRATCH_FLOATS
 
 F32, BF16 = 0, 1
@@ -131,17 +132,26 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_bn_fwd_train_stats.argtypes = [vp, vp, vp, vp, vp, ci, vp, vp, C.c_float, C.c_float, vp, vp, vp, vp, ci,
                                              sz, ci, ci, st]
     lib.tb200_bn_fwd_train_stats.restype = ci
+    lib.tb200_bn_mask_supported.argtypes = [sz, ci]
+    lib.tb200_bn_mask_supported.restype = ci
+    lib.tb200_bn_fwd_train_ex.argtypes = [vp, vp, vp, vp, vp, ci, vp, vp, C.c_float, C.c_float, vp, vp, vp, vp, ci,
+                                          vp, sz, ci, ci, st]
+    lib.tb200_bn_fwd_train_ex.restype = ci
+    lib.tb200_bn_bwd_ex.argtypes = [vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, sz, ci, ci, st]
+    lib.tb200_bn_bwd_ex.restype = ci
     lib.tb200_bn_finalize.argtypes = [vp, ci, C.c_double, ci, vp, vp, ci, vp, vp, C.c_float, C.c_float, vp, vp, vp, st]
     lib.tb200_bn_finalize.restype = ci
     lib.tb200_nvls_supported.argtypes = [ci]
     lib.tb200_nvls_supported.restype = ci
     lib.tb200_nvls_selftest.argtypes = [ci, sz, ci, C.c_char_p, sz]
     lib.tb200_nvls_selftest.restype = ci
+    lib.tb200_gemm_set_pair_mode.argtypes = [ci]
+    lib.tb200_gemm_set_pair_mode.restype = None
     lib.tb200_gemm_reserve.argtypes = [sz]
     lib.tb200_gemm_bf16_nt_pull.argtypes = [C.POINTER(World), C.c_int, sz, C.c_int, vp, vp, vp,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                             u32p, ip,
-                                            C.c_ulonglong, st]
+                                            C.c_ulonglong, vp, st]
     lib.tb200_u8_to_bf16_norm.argtypes = [vp, vp, sz, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
     lib.tb200_u8_to_bf16_norm_pad8.argtypes = [vp, vp, sz, C.POINTER(C.c_float), C.POINTER(C.c_float), st]
     lib.tb200_u8_to_bf16_norm_pad8.restype = C.c_int

@@ -54,6 +54,7 @@ class Bucket:
     params: List[Tuple[nn.Parameter, int]] = field(default_factory=list)   # (param, flat offset)
     pull_layer: Optional[TcLinear] = None
     pull_rows: int = 0                # rows of the pulled weight every PS rank owns (a multiple of 128)
+    pull_sync: Optional[torch.Tensor] = None     # the pull GEMM's per-tile arrival counters / epochs
     pending: int = 0
 
     def shard(self, rank: int, world: int) -> Tuple[int, int]:
@@ -275,6 +276,7 @@ class Trainer:
         self.set_hyper(0.1, 0.9, 1e-4)
         for b in self.buckets:
             if b.pull_layer is not None:
+                b.pull_sync = torch.zeros(native.PULL_SYNC_WORDS, dtype=torch.int32, device=self.device)
                 b.pull_layer._pull_ctx = (self, b)
 
     def _alloc_io(self) -> None:
