@@ -289,6 +289,16 @@ def conv_cases(iters):
         lib, _ = timeit(lambda: aten(dy, x, w, None, [stride] * 2, [pad] * 2, [1, 1], False, [0, 0], 1,
                                      [False, True, False]), iters)
         row.update({"wgrad_ms": round(ours, 4), "wgrad_cudnn_ms": round(lib, 4)})
+        if k == 3 and stride == 1 and native.conv3x3_wgrad_eligible(x, cout):
+            # halo-tile weight gradient (csrc/conv3x3.cu conv3x3_wgrad_kernel)
+            try:
+                wh, _ = timeit(lambda: native.conv3x3_wgrad(x, dy), iters)
+                ref = aten(dy, x, w, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1, [False, True, False])[1]
+                werr = (native.conv3x3_wgrad(x, dy).float() - ref.float()).abs().max().item()
+                row.update({"wgrad_halo_ms": round(wh, 4), "wgrad_halo_max_abs_diff_vs_cudnn": round(werr, 4),
+                            "wgrad_halo_rel": round(werr / max(ref.float().abs().max().item(), 1e-9), 5)})
+            except Exception as e:  # noqa: BLE001
+                row["wgrad_halo_error"] = str(e)[:200]
         out.append(row)
         print(json.dumps(row), flush=True)
     return out

@@ -338,6 +338,232 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
   }
 }
 
+
+// =========================================================================================================
+// Weight gradient of the same convolution, also as a halo-tile implicit GEMM:
+//   dW[co, r, s, ci] = sum over positions q of dy[q, co] * x[q + (r-1)*(W+1) + (s-1), ci]
+// in the flat padded space used above (dy is zero at the shared pad column / row because its loads are
+// zero-filled there too). The reduction runs over POSITIONS, so both operands are MN-major as they land:
+// a stage holds, for a super block of 128 positions, the padded rows of dy that cover it (A: M = 64-channel
+// slabs of co, the slab stride goes into the descriptor's leading-dimension field) and the padded rows of x that
+// cover it plus the halo (B: N = 64 channels of ci); a filter tap is the B descriptor advanced by its shift in
+// rows - the same trick as the forward pass, along the reduction dimension this time (probed on B200:
+// profiles/probe_shift_r2a.json, "B MN-major"). The im2col-TMA wgrad fetched x once per tap and dy once per
+// 128-column tile of the 9*Cin-wide output (L2 -> SM traffic 10-18x the tensors, profiles/conv_r2.md); here a
+// work item is (128 output channels, 64 input channels, HALF of the taps - nine 64-column accumulators exceed the
+// 512 TMEM columns - , a split of the positions) and reads x (+ halo) and dy once.
+// Output: fp32 partial planes [splits][Cout][9*Cin], summed and rounded by wgrad_reduce_kernel.
+struct W3Params {
+  int N, H, W, Cin, Cout;
+  int Wp, Hp, total_pos;
+  unsigned long long mWp;
+  unsigned long long mHp;
+  int NRx, NRy;                    // padded rows per stage of x / dy
+  int x_bytes, y_slab_bytes, stage_bytes, stages;
+  int m_slabs;                     // 64-channel slabs of dy per stage: 1 (Cout == 64) or 2
+  int cblocks, mblocks, splits, num_sb;
+  int bar_off;
+  float* partials;
+};
+
+constexpr int kW3Threads = 256;
+constexpr int kW3TmemCols = 512;   // five taps x 64 columns, rounded up to a power of two
+
+__global__ void __launch_bounds__(kW3Threads, 1)
+conv3x3_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
+                     const W3Params p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  const uint32_t bar = base + (uint32_t)p.bar_off;
+  auto full = [&](int s) { return bar + 8u * s; };
+  auto empty = [&](int s) { return bar + 8u * (p.stages + s); };
+  const uint32_t t_full = bar + 8u * (2 * p.stages), t_empty = t_full + 8u;
+  const uint32_t tmem_slot = t_empty + 8u;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_x);
+    prefetch_tensormap(&map_dy);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full(s), 1); mbar_init(empty(s), 1); }
+    mbar_init(t_full, 1);
+    mbar_init(t_empty, 4);
+    mbar_init_fence();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(kW3TmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - base));
+
+  const int per_split = 2 * p.cblocks * p.mblocks;
+  const int items = per_split * p.splits;
+  const uint32_t row_bytes = (uint32_t)p.Wp * 128u;
+  auto decode = [&](int it, int* tg, int* cb, int* mb, int* sb0, int* sb1) {
+    const int ks = it / per_split, r = it - ks * per_split;
+    *tg = r & 1;
+    *cb = (r >> 1) % p.cblocks;
+    *mb = (r >> 1) / p.cblocks;
+    *sb0 = (int)((long long)ks * p.num_sb / p.splits);
+    *sb1 = (int)((long long)(ks + 1) * p.num_sb / p.splits);
+    return ks;
+  };
+
+  if (warp == 0) {
+    // ================= producer =================
+    int st = 0;
+    uint32_t ph = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      int tg, cb, mb, sb0, sb1;
+      decode(it, &tg, &cb, &mb, &sb0, &sb1);
+      for (int sb = sb0; sb < sb1; ++sb) {
+        const uint32_t q0 = (uint32_t)sb * 128u;
+        mbar_wait(empty(st), ph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(full(st), (uint32_t)(p.NRx + p.m_slabs * p.NRy) * row_bytes);
+          // x: padded rows from the one holding q0 - Wp - 1 on (row -1 / -2 of the first block: zero-filled)
+          const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
+          int n, hp;
+          if (rho0 < 0) { n = -1; hp = rho0 + p.Hp; }
+          else { n = (int)fastdiv((uint32_t)rho0, p.mHp); hp = rho0 - n * p.Hp; }
+          uint32_t dst = base + (uint32_t)st * p.stage_bytes;
+          for (int i = 0; i < p.NRx; ++i) {
+            tma_load_4d(dst, &map_x, full(st), cb * 64, 0, hp, n);
+            dst += row_bytes;
+            if (++hp == p.Hp) { hp = 0; ++n; }
+          }
+          // dy: padded rows from the one holding q0 on, one slab per 64 output channels
+          const int rhoy = (int)fastdiv(q0, p.mWp);
+          const int ny0 = (int)fastdiv((uint32_t)rhoy, p.mHp), hy0 = rhoy - ny0 * p.Hp;
+          for (int sl = 0; sl < p.m_slabs; ++sl) {
+            dst = base + (uint32_t)st * p.stage_bytes + (uint32_t)p.x_bytes + (uint32_t)sl * p.y_slab_bytes;
+            n = ny0; hp = hy0;
+            for (int i = 0; i < p.NRy; ++i) {
+              tma_load_4d(dst, &map_dy, full(st), mb * 128 + sl * 64, 0, hp, n);
+              dst += row_bytes;
+              if (++hp == p.Hp) { hp = 0; ++n; }
+            }
+          }
+        }
+        __syncwarp();
+        if (++st == p.stages) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+    // A: MN-major, 64-wide slabs y_slab_bytes apart, 8 reduction rows per 1024-byte atom
+    const uint64_t a_const = ((uint64_t)((uint32_t)p.y_slab_bytes >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+                             ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+    const int wp8 = p.Wp * 8;
+    int st = 0;
+    uint32_t ph = 0, tph = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      int tg, cb, mb, sb0, sb1;
+      decode(it, &tg, &cb, &mb, &sb0, &sb1);
+      mbar_wait(t_empty, tph ^ 1);
+      tc_fence_after();
+      uint32_t accumulate = 0;
+      for (int sb = sb0; sb < sb1; ++sb) {
+        const uint32_t q0 = (uint32_t)sb * 128u;
+        const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
+        const int rhoy = (int)fastdiv(q0, p.mWp);
+        mbar_wait(full(st), ph);
+        tc_fence_after();
+        const uint32_t stage = base + (uint32_t)st * p.stage_bytes;
+        // windows: x at tap (1, 1) = the block's own positions; dy = the block's own positions
+        const uint32_t b_mid = desc_units(stage) + (uint32_t)((int)q0 - rho0 * p.Wp) * 8u;
+        const uint32_t a_units = desc_units(stage + (uint32_t)p.x_bytes) + (uint32_t)((int)q0 - rhoy * p.Wp) * 8u;
+        const uint64_t adesc = a_const | (uint64_t)a_units;
+#pragma unroll
+        for (int tt = 0; tt < 5; ++tt) {
+          if (tt < 5 - tg) {                           // taps 0..4 (tg 0) or 5..8 (tg 1)
+            const int t = tg * 5 + tt, r = t / 3, s2 = t - 3 * r;
+            const uint64_t bdesc = kDescMNMajor | (uint64_t)(b_mid + (uint32_t)((r - 1) * wp8 + (s2 - 1) * 8));
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k)              // 8 x 16 positions; 16 rows = two 1024-byte atoms = 128 units
+                tc_mma_bf16(tmem_base + (uint32_t)(tt * 64), adesc + 128u * k, bdesc + 128u * k, idesc,
+                            (k == 0) ? accumulate : 1u);
+            }
+            __syncwarp();
+          }
+        }
+        accumulate = 1;
+        if (elect_one()) tc_commit(empty(st));
+        __syncwarp();
+        if (++st == p.stages) { st = 0; ph ^= 1; }
+      }
+      if (elect_one()) tc_commit(t_full);
+      __syncwarp();
+      tph ^= 1;
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue: TMEM -> fp32 partial plane of this split =================
+    const int ew = warp - 4;
+    uint32_t tph = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      int tg, cb, mb, sb0, sb1;
+      const int ks = decode(it, &tg, &cb, &mb, &sb0, &sb1);
+      const int co = mb * 128 + ew * 32 + lane;
+      mbar_wait(t_full, tph);
+      tc_fence_after();
+      const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16);
+      float* out_row = p.partials + ((size_t)ks * p.Cout + (size_t)(co < p.Cout ? co : 0)) * (size_t)(9 * p.Cin) + cb * 64;
+#pragma unroll 1
+      for (int tt = 0; tt < 5 - tg; ++tt) {
+        uint32_t v[64];
+        tc_ld_32x32(tcol + tt * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+        tc_ld_32x32(tcol + tt * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+        tc_ld_wait();
+        if (co < p.Cout && sb1 > sb0) {
+          float4* o = reinterpret_cast<float4*>(out_row + (size_t)(tg * 5 + tt) * p.Cin);
+#pragma unroll
+          for (int u = 0; u < 16; ++u)
+            o[u] = make_float4(__uint_as_float(v[4 * u]), __uint_as_float(v[4 * u + 1]), __uint_as_float(v[4 * u + 2]),
+                               __uint_as_float(v[4 * u + 3]));
+        } else if (co < p.Cout) {
+          float4* o = reinterpret_cast<float4*>(out_row + (size_t)(tg * 5 + tt) * p.Cin);
+#pragma unroll
+          for (int u = 0; u < 16; ++u) o[u] = make_float4(0.f, 0.f, 0.f, 0.f);   // a split without positions
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(t_empty);
+      tph ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kW3TmemCols) : "memory");
+  }
+}
+
+// dW (bf16, [Cout][9*Cin]) = sum over the split planes, in split order (deterministic)
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int splits, size_t plane,
+                                                          __nv_bfloat16* __restrict__ dw) {
+  const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
+  if (i >= plane) return;
+  float4 a = *reinterpret_cast<const float4*>(partials + i);
+  for (int s = 1; s < splits; ++s) {
+    const float4 b = *reinterpret_cast<const float4*>(partials + (size_t)s * plane + i);
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  }
+  uint2 o;
+  o.x = pack_bf16(a.x, a.y);
+  o.y = pack_bf16(a.z, a.w);
+  *reinterpret_cast<uint2*>(dw + i) = o;
+}
+
 // ---- host ---------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                              const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -481,9 +707,88 @@ int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, 
   return launch_c3<256, 1, true>(mx, mw, p, nparts_out, stream);
 }
 
+
+// Geometry of the wgrad kernel for a problem: fills p (everything but the pointers), returns 0 / error.
+int w3_plan(W3Params& p, int n, int h, int wd, int cin, int cout) {
+  const char* who = "tb200_conv3x3_wgrad";
+  if (n <= 0 || h <= 0 || wd <= 0 || cin <= 0 || cout <= 0) return fail("%s: empty problem", who);
+  if (cin % 64 || cout % 64) return fail("%s: channel counts must be multiples of 64%s", who);
+  if (wd + 1 > 256) return fail("%s: image width %ld exceeds one TMA box (255)", who, wd);
+  p.N = n; p.H = h; p.W = wd; p.Cin = cin; p.Cout = cout;
+  p.Wp = wd + 1; p.Hp = h + 1;
+  const long long total = (long long)n * p.Hp * p.Wp;
+  if (total + 4 * p.Wp >= (1ll << 24) || p.Wp >= 4096 || p.Hp >= 4096)
+    return fail("%s: problem too large for the position arithmetic (%ld positions)", who, (long)total);
+  p.total_pos = (int)total;
+  p.mWp = fastdiv_magic((unsigned)p.Wp);
+  p.mHp = fastdiv_magic((unsigned)p.Hp);
+  p.NRx = (3 * p.Wp + 129 + p.Wp - 1) / p.Wp;
+  p.NRy = (p.Wp + 127 + p.Wp - 1) / p.Wp;
+  const int row_bytes = p.Wp * 128;
+  p.x_bytes = (p.NRx * row_bytes + 1023) / 1024 * 1024;
+  p.y_slab_bytes = (p.NRy * row_bytes + 1023) / 1024 * 1024;
+  p.m_slabs = cout == 64 ? 1 : 2;
+  if (cout % 128 && cout != 64) return fail("%s: Cout %s(%ld) must be 64 or a multiple of 128", who, cout);
+  // Cout == 64: the MMA still spans 128 rows; its second slab aliases the first one 8 rows further (rows 64-127
+  // of the accumulator are never read), so the stage reserves those 1024 bytes
+  p.stage_bytes = p.x_bytes + p.m_slabs * p.y_slab_bytes + (p.m_slabs == 1 ? 1024 : 0);
+  constexpr int kSmemMax = 227 * 1024;
+  p.stages = (kSmemMax - 1024) / p.stage_bytes;
+  if (p.stages > 4) p.stages = 4;
+  if (p.stages < 2) return fail("%s: a stage does not fit shared memory (W %ld)", who, wd);
+  p.bar_off = p.stages * p.stage_bytes;
+  p.cblocks = cin / 64;
+  p.mblocks = (cout + 127) / 128;
+  p.num_sb = (int)((total + 127) / 128);
+  const int sms = device_sm_count();
+  const int per_split = 2 * p.cblocks * p.mblocks;
+  p.splits = sms / per_split;
+  if (p.splits < 1) p.splits = 1;
+  if (p.splits > p.num_sb) p.splits = p.num_sb;
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
+
+// fp32 scratch (bytes) tb200_conv3x3_wgrad needs for this problem on the current device; 0 = not eligible
+size_t tb200_conv3x3_wgrad_workspace(int n, int h, int wd, int cin, int cout) {
+  W3Params p{};
+  if (w3_plan(p, n, h, wd, cin, cout)) return 0;
+  return (size_t)p.splits * cout * 9 * cin * sizeof(float);
+}
+
+// dw[cout][3][3][cin] (bf16) = weight gradient of the 3x3 / stride 1 / pad 1 convolution y = conv(x, w):
+// x [n,h,wd,cin], dy [n,h,wd,cout] NHWC bf16. workspace: tb200_conv3x3_wgrad_workspace bytes.
+int tb200_conv3x3_wgrad(const void* x, const void* dy, void* dw, int n, int h, int wd, int cin, int cout,
+                        float* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  W3Params p{};
+  if (int rc = w3_plan(p, n, h, wd, cin, cout)) return rc;
+  const size_t plane = (size_t)cout * 9 * cin;
+  if (!workspace || workspace_bytes < (size_t)p.splits * plane * sizeof(float))
+    return fail("tb200_conv3x3_wgrad: workspace too small (%s%ld bytes needed)", "", (long)((size_t)p.splits * plane * 4));
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    TB_CUDA_OK(cudaFree(nullptr));
+    ctx_bound = true;
+  }
+  p.partials = workspace;
+  if (p.m_slabs == 1) p.y_slab_bytes = 1024;          // see w3_plan: the unread second slab aliases the first
+  CUtensorMap mx, my;
+  if (int rc = c3_map_nhwc(&mx, x, n, h, wd, cin, p.Wp)) return rc;
+  if (int rc = c3_map_nhwc(&my, dy, n, h, wd, cout, p.Wp)) return rc;
+  static DeviceOnce configured;
+  if (int rc = ensure_dynamic_smem(configured, conv3x3_wgrad_kernel, 227 * 1024)) return rc;
+  const int items = 2 * p.cblocks * p.mblocks * p.splits;
+  const int sms = device_sm_count();
+  const int grid = items < sms ? items : sms;
+  conv3x3_wgrad_kernel<<<grid, kW3Threads, p.bar_off + 1024, stream>>>(mx, my, p);
+  if (int rc = launched()) return rc;
+  wgrad_reduce_kernel<<<(unsigned)((plane / 4 + 255) / 256), 256, 0, stream>>>(workspace, p.splits, plane,
+                                                                             reinterpret_cast<__nv_bfloat16*>(dw));
+  return launched();
+}
 
 size_t tb200_conv_stats_floats(int cout) { return (size_t)device_sm_count() * 4 * (size_t)cout * 2; }
 

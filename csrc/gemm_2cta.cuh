@@ -231,8 +231,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
       const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * kTileN);
       const uint32_t bufs = epi_smem + (uint32_t)(ew * kEpiBufs) * kEpiTileBytes;
       const int col_base = n_blk * kTileN;
-      const int variant = (p.splits > 1) ? 12 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0));
+      const int variant = (p.splits > 1) ? 12 : (p.addend ? 14 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0)));
       switch (variant) {
+        case 14:
+          epilogue_tile<kTileN, kEpiBufs, 0, false, false, false, true>(p, &map_d, tcol, bufs, kEpiTileBytes, epi_buf,
+                                                                        bias_s, row0, col_base, ks, lane);
+          break;
 #define TB_EPI2(ID, ACT, BIAS, F32)                                                                               \
   case ID:                                                                                                        \
     epilogue_tile<kTileN, kEpiBufs, ACT, BIAS, F32>(p, &map_d, tcol, bufs, kEpiTileBytes, epi_buf, bias_s, row0, \

@@ -278,6 +278,7 @@ struct GemmParams {
   int act;
   int direct_store;   // 1: per-thread global stores (row stride not 16-byte aligned); 0: TMA store
   int a_mn, b_mn;     // operand is stored [K, M] / [K, N] (non-reduction dimension contiguous)
+  const void* addend; // optional: bf16 [M, N] added to the product in the epilogue (residual-gradient fusion)
   float* stats;       // optional: per-channel (sum, sum of squares) partials of the bf16 output,
                       // [gridDim.x * 4][N][2] (BatchNorm statistics from the epilogue; bf16, no bias / activation)
   // pull variant
@@ -322,7 +323,7 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
 // (64 bf16 or 32 fp32 columns) TMEM -> registers, + bias (the tile's bias row sits in shared memory, loaded
 // by the epilogue warps while the tile's MMAs were still running; every lane reads it with broadcast
 // 16-byte loads), activation, pack, swizzled st.shared, TMA store.
-template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32, bool STATS = false>
+template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32, bool STATS = false, bool ADD = false>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* map_d, uint32_t tcol,
                                               uint32_t bufs, uint32_t tile_bytes, int& epi_buf, float* bias_s,
                                               int row0, int col_base, int ks, int lane,
@@ -335,9 +336,30 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
     const int col0 = col_base + c * kCols;
     if (col0 >= p.N) break;
     uint32_t r[kCols];
+    // ADD (bf16 output only): this lane's 128 bytes of the addend row, requested before the accumulator is read
+    uint4 ad[ADD ? 8 : 1];
+    if constexpr (ADD) {
+      const bool row_in = row0 + lane < p.M;
+      const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.addend) +
+                                                       (size_t)(row_in ? row0 + lane : 0) * p.N + col0);
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        ad[q] = (row_in && col0 + 8 * q < p.N) ? __ldg(ap + q) : make_uint4(0u, 0u, 0u, 0u);
+    }
     tc_ld_32x32(tcol + c * kCols, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
     if constexpr (!F32) tc_ld_32x32(tcol + c * kCols + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
     tc_ld_wait();
+    if constexpr (ADD) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const uint32_t w[4] = {ad[q].x, ad[q].y, ad[q].z, ad[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          r[8 * q + 2 * e] = __float_as_uint(__uint_as_float(r[8 * q + 2 * e]) + bf16_lo(w[e]));
+          r[8 * q + 2 * e + 1] = __float_as_uint(__uint_as_float(r[8 * q + 2 * e + 1]) + bf16_hi(w[e]));
+        }
+      }
+    }
 #pragma unroll
     for (int q = 0; q < kCols / 4; ++q) {
       float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -754,8 +776,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         const int col_base = n_blk * BLOCK_N;
         // One compact instruction stream per (activation, bias, output type): the element loop must not
         // carry per-element branches (a first version did and was instruction-fetch bound).
-        const int variant = (p.splits > 1) ? 12 : (p.stats ? 13 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0)));
+        const int variant = (p.splits > 1) ? 12 : (p.stats ? 13 : (p.addend ? 14 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0))));
         switch (variant) {
+          case 14:
+            epilogue_tile<BLOCK_N, C::kEpiBufs, 0, false, false, false, true>(p, &map_d, tcol, bufs, C::kEpiTileBytes,
+                                                                              epi_buf, bias_s, row0, col_base, ks, lane);
+            break;
           case 13:
             epilogue_tile<BLOCK_N, C::kEpiBufs, 0, false, false, true>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf,
                                                                        bias_s, row0, col_base, ks, lane, st);
@@ -1213,7 +1239,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
                 unsigned long long budget, cudaStream_t stream, float* fixed_scratch = nullptr,
                 size_t fixed_scratch_bytes = 0, int a_mn = 0, int b_mn = 0, const ConvHost* conv = nullptr,
                 float* stats = nullptr, size_t stats_floats = 0, int* stats_parts = nullptr,
-                uint32_t* pull_sync = nullptr) {
+                uint32_t* pull_sync = nullptr, const void* addend = nullptr) {
   const bool pull = world != nullptr;
   if (stats_parts) *stats_parts = 0;
   if (M <= 0 || N <= 0 || K <= 0) return fail("tb200_gemm: empty problem%s");
@@ -1237,6 +1263,9 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   p.M = M; p.N = N; p.K = K;
   p.D = D; p.bias = bias; p.bias_dtype = bias_dtype; p.d_dtype = d_dtype; p.act = act;
   p.a_mn = a_mn; p.b_mn = b_mn;
+  p.addend = addend;
+  if (addend && (bias || act || d_dtype != TB200_BF16 || N % 8 || stats || pull || (conv && conv->g.sc_on)))
+    return fail("tb200_gemm: the addend epilogue takes a bf16 output with N %% 8 == 0, no bias, no activation%s");
   if (conv) {
     p.conv = conv->g;
     auto magic40 = [](long long d) { return (unsigned long long)(((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d); };
@@ -1275,6 +1304,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   if (!use_pair)
     if (int rc = plan_tiles(M, N, K, pull, rows_per_rank, sms, &block_n, &splits)) return rc;
   if (conv && conv->g.sc_on) splits = 1;      // the split-K second pass writes rows in order, not scattered
+  if (addend) splits = 1;                     // the addend is applied by the GEMM's own epilogue
   p.num_n = (N + block_n - 1) / block_n;
   const int tiles = p.num_m * p.num_n;
   p.splits = splits;
@@ -1410,6 +1440,15 @@ int tb200_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int
                     int K, int a_mn_major, int b_mn_major, int d_dtype, int act, cudaStream_t stream) {
   return gemm_common(nullptr, 0, 0, 0, A, B, D, bias, bias_dtype, M, N, K, d_dtype, act, nullptr, nullptr, 0,
                      stream, nullptr, 0, a_mn_major ? 1 : 0, b_mn_major ? 1 : 0);
+}
+
+// D = A . B^T + addend (all bf16, addend and D [M, N]; D may alias addend): the residual-gradient add of a
+// bottleneck block folded into the dgrad GEMM of its first convolution.
+int tb200_gemm_bf16_add(const void* A, const void* B, void* D, const void* addend, int M, int N, int K, int a_mn_major,
+                        int b_mn_major, cudaStream_t stream) {
+  if (!addend) return fail("tb200_gemm_bf16_add: null addend%s");
+  return gemm_common(nullptr, 0, 0, 0, A, B, D, nullptr, 0, M, N, K, TB200_BF16, 0, nullptr, nullptr, 0, stream, nullptr, 0,
+                     a_mn_major ? 1 : 0, b_mn_major ? 1 : 0, nullptr, nullptr, 0, nullptr, nullptr, addend);
 }
 
 int tb200_gemm_bf16_nt_pull(const tb200_world_t* world, int bucket, size_t b_off,

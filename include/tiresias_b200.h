@@ -200,6 +200,12 @@ int tb200_conv3x3_fprop(const void* x, const void* w, void* y, int n, int h, int
                         size_t stats_floats, int* nparts, cudaStream_t stream);
 int tb200_conv3x3_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout,
                         cudaStream_t stream);
+/* Weight gradient of the same convolution on a halo-tile kernel: dw [cout][3][3][cin] bf16 from x [n,h,w,cin] and
+ * dy [n,h,w,cout]; cin a multiple of 64, cout 64 or a multiple of 128, w <= 255. `workspace`: fp32 scratch of
+ * tb200_conv3x3_wgrad_workspace(...) bytes (0 = shape not served). No reference counterpart.                */
+size_t tb200_conv3x3_wgrad_workspace(int n, int h, int wd, int cin, int cout);
+int tb200_conv3x3_wgrad(const void* x, const void* dy, void* dw, int n, int h, int wd, int cin, int cout,
+                        float* workspace, size_t workspace_bytes, cudaStream_t stream);
 /* Per-channel statistics partials [nparts][C][2] over `count` values per channel -> batch mean / invstd,
  * scale_shift = [gamma*invstd | beta - mean*gamma*invstd] for tb200_bn_apply, running statistics (may be NULL).
  * Compensated sums in a fixed order: bitwise reproducible.                                                */
@@ -259,6 +265,12 @@ int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void
  * current device (1 = no scratch; 0 = empty problem). Scratch bytes = splits * M * N * 4.
  * No counterpart in the reference.                                                           */
 int tb200_gemm_plan_splits(int M, int N, int K);
+
+/* D = A . B^T + addend with the operand layouts of tb200_gemm_bf16 (bf16 in and out, N a multiple of 8; D may
+ * alias addend). Used for the first convolution's dgrad of a residual block: the skip branch's gradient is added
+ * in the epilogue instead of by a separate element-wise kernel. No reference counterpart.                   */
+int tb200_gemm_bf16_add(const void* A, const void* B, void* D, const void* addend, int M, int N, int K, int a_mn_major,
+                        int b_mn_major, cudaStream_t stream);
 
 /* Plain GEMMs (not the convolutions, the pull variant or the allocation-free entry point) of at least
  * 256 x 256 x 256 run on the 2-CTA kernel (cta_group::2, 256 x 256 pair tiles; csrc/gemm_2cta.cuh).

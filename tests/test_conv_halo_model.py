@@ -79,3 +79,61 @@ def test_dgrad_is_a_forward_convolution_with_the_flipped_filter(k, pad):
     y.backward(dy)
     dx = torch.nn.functional.conv2d(dy, dgrad_weight(w), padding=k - 1 - pad)
     assert torch.allclose(dx, x.grad, rtol=1e-4, atol=1e-4)
+
+
+def wgrad_flat_model(x_nhwc: torch.Tensor, dy_nhwc: torch.Tensor, splits: int = 3) -> torch.Tensor:
+    """csrc/conv3x3.cu conv3x3_wgrad_kernel, step for step: super blocks of 128 flat padded positions (pitch
+    W+1 / H+1), a stage = the padded rows of x covering the block plus its halo and the padded rows of dy covering
+    the block (rows outside the tensor arrive as zeros, anything else in the stage is poison), a tap = the x
+    window shifted by (r-1)*Wp + (s-1) rows, splits over the positions summed in order."""
+    n, h, w, cin = x_nhwc.shape
+    cout = dy_nhwc.shape[3]
+    wp, hp = w + 1, h + 1
+    total = n * hp * wp
+    nrx = (3 * wp + 129 + wp - 1) // wp
+    nry = (wp + 127 + wp - 1) // wp
+    num_sb = (total + 127) // 128
+
+    def padded_row(t, rho):                       # one TMA box {C, Wp, 1, 1} at (0, 0, hp, img)
+        out = torch.zeros(wp, t.shape[3])
+        if rho >= 0:
+            img, hrow = divmod(rho, hp)
+            if img < n and hrow < h:
+                out[:w] = t[img, hrow]
+        return out
+
+    planes = []
+    for ks in range(splits):
+        acc = torch.zeros(9, cout, cin)
+        for sb in range(ks * num_sb // splits, (ks + 1) * num_sb // splits):
+            q0 = sb * 128
+            rho0 = (q0 + wp - 1) // wp - 2
+            rhoy = q0 // wp
+            xs = torch.full((nrx * wp + 8, cin), 1e30)
+            ys = torch.full((nry * wp + 8, cout), 1e30)
+            for i in range(nrx):
+                xs[i * wp:(i + 1) * wp] = padded_row(x_nhwc, rho0 + i)
+            for i in range(nry):
+                ys[i * wp:(i + 1) * wp] = padded_row(dy_nhwc, rhoy + i)
+            a0 = q0 - rhoy * wp
+            b_mid = q0 - rho0 * wp
+            assert 0 <= a0 and a0 + 128 <= nry * wp
+            for t in range(9):
+                r, s = divmod(t, 3)
+                b0 = b_mid + (r - 1) * wp + (s - 1)
+                assert 0 <= b0 and b0 + 128 <= nrx * wp
+                acc[t] += ys[a0:a0 + 128].t() @ xs[b0:b0 + 128]
+        planes.append(acc)
+    dw = sum(planes)                              # [9, cout, cin]
+    return dw.permute(1, 0, 2).reshape(cout, 3, 3, cin)
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 7, 7), (1, 14, 14), (3, 5, 9), (1, 28, 28), (2, 3, 56), (1, 1, 1), (1, 2, 130)])
+def test_wgrad_flat_space_geometry_equals_weight_gradient(n, h, w):
+    g = torch.Generator().manual_seed(3)
+    cin, cout = 4, 5
+    x = torch.randn(n, h, w, cin, generator=g)
+    dy = torch.randn(n, h, w, cout, generator=g)
+    got = wgrad_flat_model(x, dy)
+    ref = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2), (cout, cin, 3, 3), dy.permute(0, 3, 1, 2), stride=1, padding=1)
+    assert torch.allclose(got, ref.permute(0, 2, 3, 1), rtol=1e-4, atol=1e-4), (got - ref.permute(0, 2, 3, 1)).abs().max()

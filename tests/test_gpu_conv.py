@@ -209,3 +209,76 @@ def test_packed_stem_matches_fp32_conv(cuda_device, shape):
     assert weight.grad.shape == weight.shape
     assert torch.allclose(weight.grad.float(), wr.grad, rtol=2e-2, atol=2e-2 * scale), \
         float((weight.grad.float() - wr.grad).abs().max())
+
+
+@pytest.mark.parametrize("m,n,k", [(802, 256, 64), (3136, 512, 128), (1000, 2048, 512), (256, 264, 72)])
+def test_gemm_addend_epilogue(cuda_device, m, n, k):
+    """dx = dy . W + skip with the add in the GEMM's epilogue (one- and two-CTA kernels), also in place."""
+    from tiresias_b200.ops import native
+    torch.manual_seed(m)
+    dy = torch.randn(m, k, device=cuda_device).to(torch.bfloat16)
+    w = (torch.randn(k, n, device=cuda_device) / k ** 0.5).to(torch.bfloat16)        # [Cout, Cin] as stored
+    skip = torch.randn(m, n, device=cuda_device).to(torch.bfloat16)
+    ref = dy.float() @ w.float() + skip.float()
+    for mode in (0, 1):
+        native.lib().tb200_gemm_set_pair_mode(mode)
+        try:
+            got = native.gemm_add(dy, w, skip, b_mn_major=True)
+            assert torch.allclose(got.float(), ref, rtol=1e-2, atol=2e-2), (mode, (got.float() - ref).abs().max().item())
+            buf = skip.clone()
+            native.gemm_add(dy, w, buf, b_mn_major=True, out=buf)
+            assert torch.equal(buf, got)
+        finally:
+            native.lib().tb200_gemm_set_pair_mode(-1)
+
+
+@pytest.mark.parametrize("cin,width,stride", [(256, 64, 1), (256, 128, 2), (64, 64, 1)])
+def test_bottleneck_skip_gradient_fused_into_conv1_dgrad(cuda_device, cin, width, stride, monkeypatch):
+    """The residual block's two input gradients are summed by conv1's dgrad epilogue (no autograd add kernel):
+    same gradients as the unfused block."""
+    from tiresias_b200.models.vision import Bottleneck
+    from tiresias_b200.ops import conv, native
+    torch.manual_seed(0)
+    blk = Bottleneck(cin, width, stride, fused=True).to(cuda_device).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    torch.nn.init.normal_(blk.bn3.weight, 1.0, 0.1)
+    x0 = torch.randn(8, cin, 28, 28, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    calls = []
+    real = native.gemm_add
+    monkeypatch.setattr(native, "gemm_add", lambda *a, **k: (calls.append(1), real(*a, **k))[1])
+    outs = []
+    for fuse in (True, False):
+        monkeypatch.setattr(conv, "FUSE_SKIP_GRAD", fuse)
+        blk.zero_grad(set_to_none=True)
+        # x is a non-leaf (as inside the network): its gradient is what flows to the previous block
+        leaf = x0.clone().requires_grad_(True)
+        x = leaf * 1.0
+        y = blk(x)
+        torch.manual_seed(1)
+        y.backward(torch.randn(y.shape, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
+        outs.append((y.detach().float(), leaf.grad.float(), [p.grad.float() for p in blk.parameters()]))
+    assert len(calls) == 1           # the fused pass used the addend epilogue once, the unfused pass never
+    (y1, g1, p1), (y0, g0, p0) = outs
+    assert torch.equal(y1, y0)
+    assert torch.allclose(g1, g0, rtol=2e-2, atol=2e-2 * g0.abs().max().item()), (g1 - g0).abs().max().item()
+    for a, b in zip(p1, p0):
+        assert torch.allclose(a, b, rtol=2e-2, atol=2e-2 * max(b.abs().max().item(), 1e-3))
+
+
+@pytest.mark.parametrize("n,hw,cin,cout", [(2, (56, 56), 64, 64), (4, (28, 28), 128, 128), (3, (14, 14), 256, 256),
+                                           (5, (7, 7), 512, 512), (2, (17, 13), 64, 128), (1, (9, 30), 128, 64),
+                                           (33, (7, 7), 64, 256)])
+def test_conv3x3_wgrad_halo_matches_fp32(cuda_device, n, hw, cin, cout):
+    """Halo-tile weight gradient (positions as the reduction dimension, taps as shifted MN-major windows)."""
+    from tiresias_b200.ops import native
+    h, w = hw
+    torch.manual_seed(n * 100 + cin)
+    x = torch.randn(n, cin, h, w, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    dy = (torch.randn(n, cout, h, w, device=cuda_device) / (n * h * w) ** 0.5).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last)
+    assert native.conv3x3_wgrad_eligible(x, cout)
+    got = native.conv3x3_wgrad(x, dy).float()
+    ref = torch.nn.grad.conv2d_weight(x.float(), (cout, cin, 3, 3), dy.float(), stride=1, padding=1)
+    assert got.shape == ref.shape
+    assert torch.allclose(got, ref, rtol=1e-2, atol=1e-2), (got - ref).abs().max().item()
+    again = native.conv3x3_wgrad(x, dy).float()
+    assert torch.equal(got, again)                       # fixed split order: bitwise repeatable

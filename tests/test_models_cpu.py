@@ -145,3 +145,42 @@ def test_seq2seq_lstm_forward_backward_on_cpu():
     bert = BertEncoder(vocab=101, d_model=32, n_layers=2, n_heads=4, d_ff=64, max_len=16, fused=False)
     assert bert.head.weight is bert.tok.weight                                   # tied LM head
     assert bert(torch.randint(0, 101, (2, 7))).shape == (2, 7, 101)
+
+
+def test_skip_gradient_is_parked_before_the_main_branch_consumes_it():
+    """ops/conv.py GradBox: the skip branch, built last in the forward, runs first in the backward, so the main
+    branch's first op finds the skip gradient parked and autograd receives one (already summed) gradient."""
+    from tiresias_b200.ops.conv import GradBox, park_skip_grad
+    seen = []
+
+    class Main(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, x, box):
+            ctx.box = box
+            return x * 2.0
+
+        @staticmethod
+        def backward(ctx, g):
+            box = ctx.box
+            skip, box.grad, box.main_done = box.grad, None, True
+            seen.append(skip is not None)
+            return g * 2.0 + (skip if skip is not None else 0.0), None
+
+    leaf = torch.arange(6.0).reshape(2, 3).requires_grad_(True)
+    x = leaf * 1.0
+    box = GradBox()
+    main = torch.tanh(Main.apply(x, box)) * 5.0            # a few more nodes on the main branch
+    y = main + 3.0 * park_skip_grad(x, box)
+    y.sum().backward()
+    want = 5.0 * (1 - torch.tanh(2.0 * leaf.detach()) ** 2) * 2.0 + 3.0
+    assert seen == [True]
+    assert torch.allclose(leaf.grad, want)
+    # and when the main branch runs first (skip built first), nothing is lost: autograd adds as usual
+    seen.clear()
+    leaf.grad = None
+    x = leaf * 1.0
+    box = GradBox()
+    skip = 3.0 * park_skip_grad(x, box)
+    y = torch.tanh(Main.apply(x, box)) * 5.0 + skip
+    y.sum().backward()
+    assert torch.allclose(leaf.grad, want)

@@ -83,6 +83,17 @@ class Bottleneck(nn.Module):
             self.down_conv, self.down_bn = _conv(cin, cout, 1, stride, fused=fused), _bn(cout, False, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if isinstance(self.conv1, TcConv1x1) and self.conv1.fuses_skip_grad(x):
+            # Training on the tcgen05 path: the skip branch is built last, so its backward runs first and parks
+            # its gradient w.r.t. x; conv1's dgrad GEMM adds it in the epilogue (ops/conv.py GradBox) instead of
+            # autograd summing the two branches with an element-wise kernel.
+            box = GradBox()
+            out = self.bn1(self.conv1(x, grad_box=box))
+            out = self.conv3(self.bn2(self.conv2(out)))
+            idt = park_skip_grad(x, box)
+            if self.down_conv is not None:
+                idt = self.down_bn(self.down_conv(idt))
+            return self.bn3(out, idt)
         idt = x if self.down_conv is None else self.down_bn(self.down_conv(x))
         out = self.bn1(self.conv1(x))
         out = self.bn2(self.conv2(out))

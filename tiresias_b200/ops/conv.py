@@ -23,13 +23,56 @@ import math
 import torch
 from torch import nn
 
+import os
+
 from . import native
+
+HALO_WGRAD = os.environ.get("TB200_HALO_WGRAD", "1") != "0"             # A/B switch (bench only)
+FUSE_SKIP_GRAD = os.environ.get("TB200_FUSE_SKIP_GRAD", "1") != "0"     # A/B switch (bench only)
+
+
+class GradBox:
+    """Mailbox between the two consumers of a residual block's input: the skip path parks its gradient here
+    (:class:`_ParkSkipGrad`) and the first convolution's dgrad GEMM adds it in its epilogue, so autograd has
+    nothing left to sum (one element-wise add over the block input saved per block)."""
+
+    __slots__ = ("grad", "main_done")
+
+    def __init__(self):
+        self.grad = None
+        self.main_done = False
+
+
+class _ParkSkipGrad(torch.autograd.Function):
+    """Identity on the skip branch. Created AFTER the block's main branch in the forward, so its backward runs
+    before the main branch's (autograd runs ready nodes latest-created first): the skip gradient is parked in the
+    box and this node reports none. If the main branch's dgrad did run first, the gradient flows on as usual
+    and autograd adds — the order only decides whether the add is fused."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, box: GradBox):
+        ctx.box = box
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        box = ctx.box
+        if g is None or box.main_done:
+            return g, None
+        box.grad = g
+        return None, None
+
+
+def park_skip_grad(x: torch.Tensor, box: GradBox) -> torch.Tensor:
+    return _ParkSkipGrad.apply(x, box)
 
 
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, ops: frozenset = frozenset("fdw"), want_stats: bool = False):
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, ops: frozenset = frozenset("fdw"), want_stats: bool = False,
+                box: GradBox = None):
         ctx.set_materialize_grads(False)      # no zeros kernel for the statistics output's (absent) gradient
+        ctx.box = box
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         n, cin, h, w = x.shape
@@ -56,8 +99,12 @@ class _Conv1x1Fn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor, _dstats=None):
+        box = ctx.box
+        skip = None
+        if box is not None:                   # the skip branch's gradient, if its backward already ran
+            skip, box.grad, box.main_done = box.grad, None, True
         if dy is None:
-            return None, None, None, None
+            return skip, None, None, None, None
         x2d, w2d = ctx.saved_tensors
         n, cin, h, w, cout = ctx.shape
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -68,7 +115,14 @@ class _Conv1x1Fn(torch.autograd.Function):
         own_dx, own_dw = want_dx and "d" in ops, want_dw and "w" in ops
         dx = dw = None
         if own_dx:
-            dx = native.gemm(dy2d, w2d, b_mn_major=True).view(n, h, w, cin).permute(0, 3, 1, 2)
+            if skip is not None and skip.dtype == torch.bfloat16 and skip.shape == (n, cin, h, w):
+                if not skip.is_contiguous(memory_format=torch.channels_last):
+                    skip = skip.contiguous(memory_format=torch.channels_last)
+                s2d = skip.permute(0, 2, 3, 1).reshape(n * h * w, cin)
+                dx = native.gemm_add(dy2d, w2d, s2d, b_mn_major=True).view(n, h, w, cin).permute(0, 3, 1, 2)
+                skip = None
+            else:
+                dx = native.gemm(dy2d, w2d, b_mn_major=True).view(n, h, w, cin).permute(0, 3, 1, 2)
         if own_dw:
             dw = native.gemm(dy2d, x2d, a_mn_major=True, b_mn_major=True).view(cout, 1, 1, cin).permute(0, 3, 1, 2)
         if (want_dx and not own_dx) or (want_dw and not own_dw):
@@ -79,7 +133,9 @@ class _Conv1x1Fn(torch.autograd.Function):
                 [want_dx and not own_dx, want_dw and not own_dw, False])
             dx = dx if own_dx else lib_dx
             dw = dw if own_dw else lib_dw
-        return dx, dw, None, None
+        if skip is not None:                  # parked but not fused (library dgrad, or no input gradient wanted)
+            dx = skip if dx is None else dx + skip
+        return dx, dw, None, None, None
 
 
 def _attach_stats(y: torch.Tensor, partials: torch.Tensor) -> torch.Tensor:
@@ -106,11 +162,17 @@ class TcConv1x1(nn.Module):
         self.weight = nn.Parameter(torch.empty(out_channels, in_channels, 1, 1))
         nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, grad_box: GradBox = None) -> torch.Tensor:
+        """``grad_box``: see :class:`GradBox` (only honoured on the tcgen05 path; the caller checks
+        :meth:`fuses_skip_grad` before parking anything)."""
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16:
             want = self.emit_stats and self.training and torch.is_grad_enabled()
-            return _attach_stats(*_Conv1x1Fn.apply(x, self.weight, self.ops, want))
+            return _attach_stats(*_Conv1x1Fn.apply(x, self.weight, self.ops, want, grad_box))
         return torch.nn.functional.conv2d(x, self.weight)
+
+    def fuses_skip_grad(self, x: torch.Tensor) -> bool:
+        return (x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16 and x.requires_grad
+                and torch.is_grad_enabled() and FUSE_SKIP_GRAD)
 
     def extra_repr(self) -> str:
         return f"{self.in_channels}, {self.out_channels}, kernel_size=(1, 1), tcgen05"
@@ -194,7 +256,10 @@ class _Conv2dFn(torch.autograd.Function):
         if own_dx:
             dx = native.conv3x3_dgrad(dy, weight) if ctx.halo else native.conv2d_dgrad(dy, weight, x.shape, stride, pad)
         if own_dw:
-            dw = native.conv2d_wgrad(x, dy, weight.shape[2:], stride, pad)
+            if ctx.halo and HALO_WGRAD and native.conv3x3_wgrad_eligible(x, weight.shape[0]):
+                dw = native.conv3x3_wgrad(x, dy)
+            else:
+                dw = native.conv2d_wgrad(x, dy, weight.shape[2:], stride, pad)
         if (want_dx and not own_dx) or (want_dw and not own_dw):
             lib_dx, lib_dw, _ = _aten_backward(dy, x, weight, stride, pad, want_dx and not own_dx,
                                                want_dw and not own_dw)

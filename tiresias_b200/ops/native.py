@@ -129,6 +129,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_conv3x3_fprop.restype = ci
     lib.tb200_conv3x3_dgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, st]
     lib.tb200_conv3x3_dgrad.restype = ci
+    lib.tb200_conv3x3_wgrad_workspace.argtypes = [ci, ci, ci, ci, ci]
+    lib.tb200_conv3x3_wgrad_workspace.restype = sz
+    lib.tb200_conv3x3_wgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp, sz, st]
+    lib.tb200_conv3x3_wgrad.restype = ci
     lib.tb200_bn_fwd_train_stats.argtypes = [vp, vp, vp, vp, vp, ci, vp, vp, C.c_float, C.c_float, vp, vp, vp, vp, ci,
                                              sz, ci, ci, st]
     lib.tb200_bn_fwd_train_stats.restype = ci
@@ -145,6 +149,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_nvls_supported.restype = ci
     lib.tb200_nvls_selftest.argtypes = [ci, sz, ci, C.c_char_p, sz]
     lib.tb200_nvls_selftest.restype = ci
+    lib.tb200_gemm_bf16_add.argtypes = [vp, vp, vp, vp, ci, ci, ci, ci, ci, st]
+    lib.tb200_gemm_bf16_add.restype = ci
     lib.tb200_gemm_set_pair_mode.argtypes = [ci]
     lib.tb200_gemm_set_pair_mode.restype = None
     lib.tb200_gemm_reserve.argtypes = [sz]
@@ -289,6 +295,22 @@ def gemm(a: torch.Tensor, b: torch.Tensor, a_mn_major: bool = False, b_mn_major:
     return out
 
 
+def gemm_add(a: torch.Tensor, b: torch.Tensor, addend: torch.Tensor, a_mn_major: bool = False,
+             b_mn_major: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``A @ B^T + addend`` (bf16 [M, N]) with the addend folded into the GEMM's epilogue; ``out`` may be the
+    addend itself."""
+    assert a.dtype == b.dtype == addend.dtype == torch.bfloat16
+    assert a.is_contiguous() and b.is_contiguous() and addend.is_contiguous()
+    k, m = (a.shape if a_mn_major else a.shape[::-1])
+    kb, n = (b.shape if b_mn_major else b.shape[::-1])
+    assert k == kb and tuple(addend.shape) == (m, n), (a.shape, b.shape, addend.shape)
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.bfloat16, device=a.device)
+    check(lib().tb200_gemm_bf16_add(a.data_ptr(), b.data_ptr(), out.data_ptr(), addend.data_ptr(), m, n, k,
+                                    int(a_mn_major), int(b_mn_major), stream_ptr()))
+    return out
+
+
 def nvls_supported(device: int = 0) -> bool:
     """Can this GPU join an NVLS multicast object (NVSwitch fabric)?"""
     return lib().tb200_nvls_supported(device) == 1
@@ -423,6 +445,38 @@ def conv3x3_dgrad(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
     dx = torch.empty((n, h, w, cin), dtype=torch.bfloat16, device=dy.device)
     check(lib().tb200_conv3x3_dgrad(dyv.data_ptr(), wv.data_ptr(), dx.data_ptr(), n, h, w, cin, cout, stream_ptr()))
     return dx.permute(0, 3, 1, 2)
+
+
+_wgrad_ws: dict = {}
+
+
+def conv3x3_wgrad_eligible(x: torch.Tensor, cout: int) -> bool:
+    """Does the halo-tile weight-gradient kernel (tb200_conv3x3_wgrad) serve this 3x3 / stride 1 / pad 1 problem?"""
+    n, cin, h, w = x.shape
+    return lib().tb200_conv3x3_wgrad_workspace(n, h, w, cin, cout) > 0
+
+
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
+    """Weight gradient of a 3x3 / stride 1 / pad 1 convolution on the halo-tile kernel (tb200_conv3x3_wgrad):
+    x and dy are read once per half of the taps instead of once per tap / per output tile. Returns
+    [Cout,Cin,3,3] channels_last. The fp32 split planes live in a scratch cached per (device, stream)."""
+    assert x.dtype == torch.bfloat16 and dy.dtype == torch.bfloat16
+    xv, dyv = _nhwc(x), _nhwc(dy)
+    n, h, w, cin = xv.shape
+    cout = dyv.shape[3]
+    need = lib().tb200_conv3x3_wgrad_workspace(n, h, w, cin, cout)
+    if need == 0:
+        raise NativeError(f"conv3x3_wgrad: shape not served ({tuple(x.shape)} -> {cout}): " +
+                          lib().tb200_last_error().decode(errors="replace"))
+    key = (x.device.index, torch.cuda.current_stream(x.device).cuda_stream)
+    ws = _wgrad_ws.get(key)
+    if ws is None or ws.numel() * 4 < need:
+        ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=x.device)
+        _wgrad_ws[key] = ws
+    dw = torch.empty((cout, 3, 3, cin), dtype=torch.bfloat16, device=x.device)
+    check(lib().tb200_conv3x3_wgrad(xv.data_ptr(), dyv.data_ptr(), dw.data_ptr(), n, h, w, cin, cout, ws.data_ptr(),
+                                    ws.numel() * 4, stream_ptr()))
+    return dw.permute(0, 3, 1, 2)
 
 
 def conv2d_dgrad(dy: torch.Tensor, weight: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:
