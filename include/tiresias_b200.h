@@ -383,6 +383,25 @@ int tb200_maxpool3x3s2_fwd(const void* x, void* out, void* argmax, int N, int H,
                            cudaStream_t stream);
 int tb200_maxpool3x3s2_bwd(const void* argmax, const void* dout, void* dx, int N, int H, int W, int C,
                            cudaStream_t stream);
+/* The same pair for the other pooling geometries of the model zoo: (k, stride, pad) = (3,2,1), (2,2,0) (VGG),
+ * (3,2,0) (AlexNet / GoogLeNet / Inception); floor mode. argmax: one byte per output element.              */
+int tb200_maxpool_supported(int k, int stride, int pad);
+int tb200_maxpool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, int C, int k, int stride, int pad,
+                      cudaStream_t stream);
+int tb200_maxpool_bwd(const void* argmax, const void* dout, void* dx, int N, int H, int W, int C, int k, int stride,
+                      int pad, cudaStream_t stream);
+
+/* ---- LayerNorm over the last dimension of bf16 rows [rows, D], D in {256, 512, 768, 1024} (csrc/norm_kernels.cu):
+ * one warp per row, the row in registers; mean / rstd (fp32, [rows]) are saved by the forward for the backward;
+ * dgamma / dbeta are reduced in a fixed order (scratch: tb200_layernorm_scratch_floats(D) floats).
+ * gamma / beta / dgamma / dbeta in `param_dtype` (TB200_F32 or TB200_BF16). No reference counterpart.     */
+int tb200_layernorm_supported(int D);
+size_t tb200_layernorm_scratch_floats(int D);
+int tb200_layernorm_fwd(const void* x, void* y, const void* gamma, const void* beta, int param_dtype, float* mean,
+                        float* rstd, size_t rows, int D, float eps, cudaStream_t stream);
+int tb200_layernorm_bwd(const void* dy, const void* x, const void* gamma, int param_dtype, const float* mean,
+                        const float* rstd, void* dx, void* dgamma, void* dbeta, float* scratch, size_t scratch_floats,
+                        size_t rows, int D, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

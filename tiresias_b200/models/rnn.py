@@ -17,7 +17,7 @@ from torch.nn import functional as F
 
 from ..ops import native
 from ..ops.linear import TcLinear
-from .transformer import Block, _lin
+from .transformer import Block, _lin, _ln
 
 
 class Seq2SeqLSTM(nn.Module):
@@ -81,9 +81,9 @@ class BertEncoder(nn.Module):
         self.tok = nn.Embedding(vocab, d_model)
         self.pos = nn.Embedding(max_len, d_model)
         self.seg = nn.Embedding(2, d_model)
-        self.ln_e = nn.LayerNorm(d_model)
+        self.ln_e = _ln(d_model, fused)
         self.blocks = nn.ModuleList(Block(d_model, n_heads, d_ff, fused, causal=False) for _ in range(n_layers))
-        self.ln_f = nn.LayerNorm(d_model)
+        self.ln_f = _ln(d_model, fused)
         self.head = _lin(d_model, vocab, fused, bias=False)
         self.head.weight = self.tok.weight                   # tied, as in BERT's masked-LM head
         for e in (self.tok, self.pos, self.seg):

@@ -1,7 +1,7 @@
 """Transformer-base job model ("transformer" in model/model_factory.py:21-23; QKV/FFN shapes
 512x{512,2048} per SURVEY.md §2.6 K5). Pre-LN stack, d_model 512, 8 heads, FFN 2048 with ReLU
 (as in the original base model), tied token embedding, next-token loss on synthetic tokens.
-All projections run on the tcgen05 GEMM; attention uses torch SDPA.
+All projections run on the tcgen05 GEMM and the LayerNorms on csrc/norm_kernels.cu; attention uses torch SDPA.
 """
 from __future__ import annotations
 
@@ -10,6 +10,7 @@ from torch import nn
 from torch.nn import functional as F
 
 from ..ops import native
+from ..ops.layernorm import FusedLayerNorm
 from ..ops.linear import TcLinear
 
 
@@ -25,6 +26,10 @@ class _TorchLinear(nn.Linear):
         return torch.relu_(y) if self.relu else y
 
 
+def _ln(d: int, fused: bool) -> nn.Module:
+    return FusedLayerNorm(d) if fused else nn.LayerNorm(d)
+
+
 def _lin(cin: int, cout: int, fused: bool, relu: bool = False, bias: bool = True) -> nn.Module:
     if fused:
         return TcLinear(cin, cout, bias=bias, act=native.ACT_RELU if relu else native.ACT_NONE)
@@ -35,10 +40,10 @@ class Block(nn.Module):
     def __init__(self, d_model: int, n_heads: int, d_ff: int, fused: bool = True, causal: bool = True):
         super().__init__()
         self.n_heads, self.causal = n_heads, causal
-        self.ln1 = nn.LayerNorm(d_model)
+        self.ln1 = _ln(d_model, fused)
         self.qkv = _lin(d_model, 3 * d_model, fused)
         self.proj = _lin(d_model, d_model, fused)
-        self.ln2 = nn.LayerNorm(d_model)
+        self.ln2 = _ln(d_model, fused)
         self.ff1 = _lin(d_model, d_ff, fused, relu=True)
         self.ff2 = _lin(d_ff, d_model, fused)
 
@@ -59,7 +64,7 @@ class TransformerLM(nn.Module):
         self.tok = nn.Embedding(vocab, d_model)
         self.pos = nn.Embedding(max_len, d_model)
         self.blocks = nn.ModuleList(Block(d_model, n_heads, d_ff, fused) for _ in range(n_layers))
-        self.ln_f = nn.LayerNorm(d_model)
+        self.ln_f = _ln(d_model, fused)
         self.head = _lin(d_model, vocab, fused, bias=False)
         nn.init.normal_(self.tok.weight, std=0.02)
         nn.init.normal_(self.pos.weight, std=0.02)

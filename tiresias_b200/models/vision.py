@@ -16,7 +16,7 @@ from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
 from ..ops.conv import TcConv1x1, TcConv2d, _parse_ops, packed_stem_conv
 from ..ops.linear import TcLinear
-from ..ops.pooling import MaxPool3x3S2
+from ..ops.pooling import MaxPool, MaxPool3x3S2
 
 import os
 
@@ -198,7 +198,7 @@ class VGG(nn.Module):
         cin = 3
         for v in _VGG_CFG[depth]:
             if v == "M":
-                layers.append(nn.MaxPool2d(2, 2))
+                layers.append(MaxPool(2, 2) if fused else nn.MaxPool2d(2, 2))
             else:
                 layers += [nn.Conv2d(cin, v, 3, 1, 1), nn.ReLU(inplace=True)]
                 cin = v
@@ -229,12 +229,13 @@ class AlexNet(nn.Module):
 
     def __init__(self, num_classes: int = 1000, fused: bool = True):
         super().__init__()
+        pool = (lambda: MaxPool(3, 2)) if fused else (lambda: nn.MaxPool2d(3, 2))
         self.features = nn.Sequential(
-            nn.Conv2d(3, 64, 11, 4, 2), nn.ReLU(inplace=True), nn.MaxPool2d(3, 2),
-            nn.Conv2d(64, 192, 5, 1, 2), nn.ReLU(inplace=True), nn.MaxPool2d(3, 2),
+            nn.Conv2d(3, 64, 11, 4, 2), nn.ReLU(inplace=True), pool(),
+            nn.Conv2d(64, 192, 5, 1, 2), nn.ReLU(inplace=True), pool(),
             nn.Conv2d(192, 384, 3, 1, 1), nn.ReLU(inplace=True),
             nn.Conv2d(384, 256, 3, 1, 1), nn.ReLU(inplace=True),
-            nn.Conv2d(256, 256, 3, 1, 1), nn.ReLU(inplace=True), nn.MaxPool2d(3, 2))
+            nn.Conv2d(256, 256, 3, 1, 1), nn.ReLU(inplace=True), pool())
         self.fc6, self.fc7, self.fc8 = _classifier(256 * 6 * 6, num_classes, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

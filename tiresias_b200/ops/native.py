@@ -149,6 +149,16 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_nvls_supported.restype = ci
     lib.tb200_nvls_selftest.argtypes = [ci, sz, ci, C.c_char_p, sz]
     lib.tb200_nvls_selftest.restype = ci
+    lib.tb200_maxpool_fwd.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, st]
+    lib.tb200_maxpool_fwd.restype = ci
+    lib.tb200_maxpool_bwd.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, st]
+    lib.tb200_maxpool_bwd.restype = ci
+    lib.tb200_layernorm_scratch_floats.argtypes = [ci]
+    lib.tb200_layernorm_scratch_floats.restype = sz
+    lib.tb200_layernorm_fwd.argtypes = [vp, vp, vp, vp, ci, vp, vp, sz, ci, C.c_float, st]
+    lib.tb200_layernorm_fwd.restype = ci
+    lib.tb200_layernorm_bwd.argtypes = [vp, vp, vp, ci, vp, vp, vp, vp, vp, vp, sz, sz, ci, st]
+    lib.tb200_layernorm_bwd.restype = ci
     lib.tb200_gemm_bf16_add.argtypes = [vp, vp, vp, vp, ci, ci, ci, ci, ci, st]
     lib.tb200_gemm_bf16_add.restype = ci
     lib.tb200_gemm_set_pair_mode.argtypes = [ci]

@@ -41,6 +41,9 @@ DEFAULT_CASES = [
      "cluster": (4, 32, 8)},
     {"name": "horus+_q3_4x32x8", "scheme": "horus+", "schedule": "horus+", "num_queue": 3, "num_jobs": 64, "seed": 1,
      "cluster": (4, 32, 8)},
+    # long enough for the engines, not interpreter start-up, to dominate (reference ~20 s)
+    {"name": "horus_300_4x32x8", "scheme": "horus", "schedule": "horus", "num_queue": 1, "num_jobs": 300, "seed": 2,
+     "cluster": (4, 32, 8)},
 ]
 
 
