@@ -391,6 +391,15 @@ int tb200_maxpool_fwd(const void* x, void* out, void* argmax, int N, int H, int 
 int tb200_maxpool_bwd(const void* argmax, const void* dout, void* dx, int N, int H, int W, int C, int k, int stride,
                       int pad, cudaStream_t stream);
 
+/* ---- Multi-head attention, head dimension 64 (csrc/attention.cu): flash-style tcgen05 kernels reading Q, K, V in
+ * place from the fused projection output qkv [B*S, 3*H*64] (columns Q | K | V, each H heads of 64) and writing
+ * out [B*S, H*64]; softmax scale 1/8, optional causal mask. lse2 [B, H, S] fp32 is saved by the forward; the
+ * backward (deterministic: one kernel per key block for dK / dV, one per query block for dQ) writes dqkv in the
+ * layout of qkv; delta is a [B, H, S] fp32 scratch. No reference counterpart.                                */
+int tb200_attention_fwd(const void* qkv, void* out, float* lse2, int B, int S, int H, int causal, cudaStream_t stream);
+int tb200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse2, float* delta, void* dqkv,
+                        int B, int S, int H, int causal, cudaStream_t stream);
+
 /* ---- LayerNorm over the last dimension of bf16 rows [rows, D], D in {256, 512, 768, 1024} (csrc/norm_kernels.cu):
  * one warp per row, the row in registers; mean / rstd (fp32, [rows]) are saved by the forward for the backward;
  * dgamma / dbeta are reduced in a fixed order (scratch: tb200_layernorm_scratch_floats(D) floats).

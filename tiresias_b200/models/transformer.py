@@ -1,7 +1,8 @@
 """Transformer-base job model ("transformer" in model/model_factory.py:21-23; QKV/FFN shapes
 512x{512,2048} per SURVEY.md §2.6 K5). Pre-LN stack, d_model 512, 8 heads, FFN 2048 with ReLU
 (as in the original base model), tied token embedding, next-token loss on synthetic tokens.
-All projections run on the tcgen05 GEMM and the LayerNorms on csrc/norm_kernels.cu; attention uses torch SDPA.
+All projections run on the tcgen05 GEMM, the LayerNorms on csrc/norm_kernels.cu and (head dimension 64) the
+attention on the tcgen05 kernels of csrc/attention.cu; the stock arm (``fused=False``) uses torch throughout.
 """
 from __future__ import annotations
 
@@ -10,6 +11,7 @@ from torch import nn
 from torch.nn import functional as F
 
 from ..ops import native
+from ..ops.attention import attention_reference, fused_attention
 from ..ops.layernorm import FusedLayerNorm
 from ..ops.linear import TcLinear
 
@@ -39,7 +41,7 @@ def _lin(cin: int, cout: int, fused: bool, relu: bool = False, bias: bool = True
 class Block(nn.Module):
     def __init__(self, d_model: int, n_heads: int, d_ff: int, fused: bool = True, causal: bool = True):
         super().__init__()
-        self.n_heads, self.causal = n_heads, causal
+        self.n_heads, self.causal, self.fused = n_heads, causal, fused
         self.ln1 = _ln(d_model, fused)
         self.qkv = _lin(d_model, 3 * d_model, fused)
         self.proj = _lin(d_model, d_model, fused)
@@ -49,10 +51,10 @@ class Block(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         b, s, d = x.shape
-        qkv = self.qkv(self.ln1(x)).view(b, s, 3, self.n_heads, d // self.n_heads)
-        q, k, v = (t.transpose(1, 2) for t in qkv.unbind(dim=2))
-        a = F.scaled_dot_product_attention(q, k, v, is_causal=self.causal)
-        x = x + self.proj(a.transpose(1, 2).reshape(b, s, d))
+        qkv = self.qkv(self.ln1(x)).view(b * s, 3 * d)
+        attn = fused_attention if self.fused else attention_reference
+        a = attn(qkv, b, s, self.n_heads, self.causal)
+        x = x + self.proj(a.view(b, s, d))
         return x + self.ff2(self.ff1(self.ln2(x)))
 
 

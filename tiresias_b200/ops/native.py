@@ -153,6 +153,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_maxpool_fwd.restype = ci
     lib.tb200_maxpool_bwd.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, st]
     lib.tb200_maxpool_bwd.restype = ci
+    lib.tb200_attention_fwd.argtypes = [vp, vp, vp, ci, ci, ci, ci, st]
+    lib.tb200_attention_fwd.restype = ci
+    lib.tb200_attention_bwd.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, st]
+    lib.tb200_attention_bwd.restype = ci
     lib.tb200_layernorm_scratch_floats.argtypes = [ci]
     lib.tb200_layernorm_scratch_floats.restype = sz
     lib.tb200_layernorm_fwd.argtypes = [vp, vp, vp, vp, ci, vp, vp, sz, ci, C.c_float, st]
