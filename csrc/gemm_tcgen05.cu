@@ -1293,7 +1293,15 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
     const int sp = plan_pair_splits(M, N, K, sms / 2);
     const bool f32 = sp > 1 || d_dtype == TB200_F32;
     const bool storable = (N % (f32 ? 4 : 8)) == 0;
-    const bool big = M >= 256 && N >= 256 && K >= 256;
+    // measured (profiles/gemm_pair_r2.md): the pair tiles win on long reductions (8192^3 1.17x cuBLAS, one-CTA
+    // 0.97x) and lose on short ones, which are bound by the epilogue's stores (the one-CTA kernel has the deeper
+    // store pipeline); and they must not split K where the one-CTA plan would not (partial planes cost more
+    // than the idle pairs)
+    bool big = M >= 256 && N >= 256 && K >= 1024;
+    if (big && sp > 1) {
+      int bn1 = 0, sp1 = 1;
+      if (plan_tiles(M, N, K, false, 0, sms, &bn1, &sp1) || sp1 == 1) big = false;
+    }
     if (storable && (pair_mode() == 1 || big)) {
       use_pair = true;
       block_n = 256;

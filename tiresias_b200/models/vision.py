@@ -14,7 +14,7 @@ from torch import nn
 
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
-from ..ops.conv import TcConv1x1, TcConv2d, _parse_ops, packed_stem_conv
+from ..ops.conv import GradBox, TcConv1x1, TcConv2d, _parse_ops, packed_stem_conv, park_skip_grad
 from ..ops.linear import TcLinear
 from ..ops.pooling import MaxPool, MaxPool3x3S2
 
