@@ -30,6 +30,7 @@ job runs for real:
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Tuple
 
@@ -40,6 +41,10 @@ from ..models.zoo import ModelSpec, build as zoo_build
 from ..ops import native
 from ..ops.linear import TcLinear
 from .symm import SymmetricWorld
+
+# largest per-GPU activation (rows) for which a row-sharded weight is pulled inside its GEMM instead of being
+# broadcast by the push kernel (see Trainer.__init__); measured cut-off, profiles/comm_pull_r2.md
+PULL_MAX_ROWS = 128
 
 IMAGENET_MEAN = (0.485, 0.456, 0.406)
 IMAGENET_STD = (0.229, 0.224, 0.225)
@@ -152,15 +157,15 @@ class Trainer:
             self.model = (model if model is not None else
                           zoo_build(spec, fused=(mode != "nccl" or self.nccl_same_compute))).to(self.device)
         self.model.train()
-        # Pull layers (K2) fetch every B tile straight from its owner once per 128-row block of the activation, and
-        # peer memory is not cached in the local L2: with more than one row block the weight crosses NVLink that
-        # many times (measured, profiles/comm_pull_r2.md: 0.49x NCCL all_gather + cuBLAS at 256 rows, 0.07x at
-        # 4096). So a layer is pulled only when the whole per-GPU batch is one row block; otherwise the push
-        # kernel broadcasts the updated shard to every rank as for any other bucket.
+        # Pull layers (K2): the GEMM's copy-engine warps fetch every remote B tile once over NVLink while the tensor
+        # cores start on the local shard (csrc/gemm_tcgen05.cu). The first version re-fetched a remote tile per
+        # 128-row block of the activation and was only worth it for one row block; TB200_PULL_MAX_ROWS keeps that
+        # cut-off adjustable (profiles/comm_pull_r2.md has both generations' numbers).
         rows_per_step = batch_size * (spec.sample_shape[0] if spec.kind == "tokens" else 1)
+        max_rows = int(os.environ.get("TB200_PULL_MAX_ROWS", str(PULL_MAX_ROWS)))
         self.buckets, self.total = plan_buckets(
             self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
-            allow_pull=(pull_gemm and mode == "ps" and rows_per_step <= 128))
+            allow_pull=(pull_gemm and mode == "ps" and rows_per_step <= max_rows))
 
         self.pack_grads = mode != "nccl" or self.nccl_same_compute
         self._grad_view: Dict[int, torch.Tensor] = {}
