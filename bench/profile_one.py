@@ -16,7 +16,7 @@ from tiresias_b200.ops import native  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv", "halo1", "halo2", "halo3", "c3_1", "c3_2", "c3_3", "c3_4", "wgrad1", "wgrad3", "thin_stats", "stem"])
+    ap.add_argument("--kernel", required=True, choices=["gemm", "gemm_splitk", "gemm_smallk", "sgd", "push", "step", "bn", "conv", "halo1", "halo2", "halo3", "c3_1", "c3_2", "c3_3", "c3_4", "wgrad1", "wgrad3", "thin_stats", "stem", "pair8k", "pair_fc6", "wgrad_halo1", "wgrad_halo2", "wgrad_halo3", "attn", "bn_bits", "layernorm"])
     args = ap.parse_args()
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
@@ -28,6 +28,32 @@ def main():
         bias = torch.randn(n, device=dev)
         o = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
         run = lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o)  # noqa: E731
+    elif args.kernel in ("pair8k", "pair_fc6"):
+        # the 2-CTA (cta_group::2) kernel, pinned
+        m, n, k = {"pair8k": (8192, 8192, 8192), "pair_fc6": (256, 4096, 25088)}[args.kernel]
+        native.lib().tb200_gemm_set_pair_mode(1)
+        a = torch.randn(m, k, device=dev).to(torch.bfloat16)
+        b = (torch.randn(n, k, device=dev) / k ** 0.5).to(torch.bfloat16)
+        bias = torch.randn(n, device=dev)
+        o = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
+        run = lambda: native.gemm_nt(a, b, bias, native.ACT_RELU, out=o)  # noqa: E731
+    elif args.kernel.startswith("wgrad_halo"):
+        c, hw = {"wgrad_halo1": (64, 56), "wgrad_halo2": (128, 28), "wgrad_halo3": (256, 14)}[args.kernel]
+        x = torch.randn(256, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        dy = torch.randn(256, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        run = lambda: native.conv3x3_wgrad(x, dy)  # noqa: E731
+    elif args.kernel == "attn":
+        # Transformer-base attention at the bench shape: batch 64 x 128 tokens, 8 heads of 64, causal
+        from tiresias_b200.ops.attention import _AttentionFn
+        qkv = torch.randn(64 * 128, 1536, device=dev).to(torch.bfloat16).requires_grad_(True)
+        dout = torch.randn(64 * 128, 512, device=dev).to(torch.bfloat16)
+        run = lambda: _AttentionFn.apply(qkv, 64, 128, 8, True).backward(dout)  # noqa: E731
+    elif args.kernel == "layernorm":
+        from tiresias_b200.ops.layernorm import FusedLayerNorm
+        ln = FusedLayerNorm(512).to(dev).to(torch.bfloat16)
+        x = torch.randn(64 * 128 * 16, 512, device=dev).to(torch.bfloat16).requires_grad_(True)
+        dy = torch.randn_like(x)
+        run = lambda: ln(x).backward(dy)  # noqa: E731
     elif args.kernel == "conv":
         # ResNet-50 layer2 3x3 at batch 256 as an implicit GEMM (im2col-mode TMA loads)
         x = torch.randn(256, 128, 28, 28, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
@@ -65,7 +91,7 @@ def main():
         yp = native.stem7x7_pack(img, (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)).permute(0, 3, 1, 2)
         wp = native.stem7x7_weight_pack(w)
         run = lambda: native.conv2d_fprop_stats(yp, wp, 1, 0)  # noqa: E731
-    elif args.kernel == "bn":
+    elif args.kernel in ("bn", "bn_bits"):
         from tiresias_b200.ops.batchnorm import fused_bn_act
         x = torch.randn(64, 256, 56, 56, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
         res = torch.randn_like(x).requires_grad_(True)

@@ -303,15 +303,17 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
           if (p.stats) {
             // lane l sums channels k0 + 2l, +1 over the valid rows: word l of every staged row
             const uint32_t col = (uint32_t)(lane >> 2), wsel = (uint32_t)(lane & 3) * 4u;
+            // packed fp32x2 arithmetic (FADD2 / FFMA2); junk rows are zeroed by a select, not branched around
+            float2 sum2 = make_float2(st[c][0], st[c][2]), sq2 = make_float2(st[c][1], st[c][3]);
 #pragma unroll
             for (int rr = 0; rr < 32; ++rr) {
-              const uint32_t w = ld_shared_4(buf + (uint32_t)rr * 128u + ((col ^ (uint32_t)(rr & 7)) << 4) + wsel);
-              if ((vmask >> rr) & 1u) {
-                const float a = bf16_lo(w), b = bf16_hi(w);
-                st[c][0] += a; st[c][1] = fmaf(a, a, st[c][1]);
-                st[c][2] += b; st[c][3] = fmaf(b, b, st[c][3]);
-              }
+              uint32_t w = ld_shared_4(buf + (uint32_t)rr * 128u + ((col ^ (uint32_t)(rr & 7)) << 4) + wsel);
+              w = ((vmask >> rr) & 1u) ? w : 0u;
+              const float2 v = make_float2(bf16_lo(w), bf16_hi(w));
+              sum2 = __fadd2_rn(sum2, v);
+              sq2 = __ffma2_rn(v, v, sq2);
             }
+            st[c][0] = sum2.x; st[c][2] = sum2.y; st[c][1] = sq2.x; st[c][3] = sq2.y;
           }
           // stores: lane -> (row (lane/8) + 4i, 16-byte unit lane%8)
           const bool unit_ok = k0 + (int)swz * 8 < p.K;

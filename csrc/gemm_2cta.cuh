@@ -25,7 +25,7 @@ constexpr int kEpiTileBytes = 32 * 128;
 constexpr int kEpiBufs = 2;
 constexpr int kEpiBytes = 4 * kEpiBufs * kEpiTileBytes;   // 32 KB
 constexpr int kEpiBiasBytes = kAccumStages * 256 * 4;
-constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages) * 8 + 16;
+constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages) * 8 + 16 + 8 * 8;   // + 2 addend barriers per epilogue warp
 constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kEpiBiasBytes + kBarrierBytes;
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 
@@ -96,7 +96,7 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int tile, int* 
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-             const __grid_constant__ CUtensorMap map_d, const GemmParams p) {
+             const __grid_constant__ CUtensorMap map_d, const __grid_constant__ PullMaps extra, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = smem_u32(smem_raw);
   const uint32_t a_smem = smem_base;
@@ -109,6 +109,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };      // per CTA
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + kAccumStages + a); };   // leader's
   const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 2 * kAccumStages);
+  const uint32_t add_bar_base = tmem_slot + 16u;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_base));
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
@@ -124,6 +125,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
       mbar_init(tfull_bar(a), 1);      // one multicast commit
       mbar_init(tempty_bar(a), 8);     // four epilogue warps in each CTA
     }
+    for (int i = 0; i < 8; ++i) mbar_init(add_bar_base + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -212,6 +214,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
     int as = 0;
     uint32_t aphase = 0;
     int epi_buf = 0;
+    uint32_t add_count = 0;
     for (int it = pair_id; it < items; it += num_pairs) {
       const int ks = it % p.splits;
       const int tile = it / p.splits;
@@ -235,7 +238,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
       switch (variant) {
         case 14:
           epilogue_tile<kTileN, kEpiBufs, 0, false, false, false, true>(p, &map_d, tcol, bufs, kEpiTileBytes, epi_buf,
-                                                                        bias_s, row0, col_base, ks, lane);
+                                                                        bias_s, row0, col_base, ks, lane, nullptr,
+                                                                        &extra.addend, add_bar_base + 16u * ew, &add_count);
           break;
 #define TB_EPI2(ID, ACT, BIAS, F32)                                                                               \
   case ID:                                                                                                        \

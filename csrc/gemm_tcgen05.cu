@@ -53,7 +53,8 @@ struct Cfg {
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = kAccumStages * BLOCK_N;  // 512 or 256 (power of two)
-  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages + 2) * 8 + 16;
+  // pipeline barriers, 2 copy-engine barriers, the TMEM slot (16 bytes), 8 addend-tile barriers (2 per epilogue warp)
+  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages + 2) * 8 + 16 + 8 * 8;
   // Epilogue staging: per epilogue warp two 32-row x 128-byte tiles (swizzle-128B), TMA-stored.
   static constexpr int kEpiTileBytes = 32 * 128;
   // kEpiBufs staging tiles per epilogue warp: a TMA store occupies its tile for ~1 us, so with two tiles a
@@ -299,6 +300,7 @@ struct GemmParams {
 
 struct PullMaps {
   CUtensorMap b_local;             // this rank's full B: gathered by the copy engine, read by the producers
+  CUtensorMap addend;              // addend epilogue: [M, N] bf16 with the output map's box (64 columns x 32 rows)
 };
 
 __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -323,11 +325,16 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
 // (64 bf16 or 32 fp32 columns) TMEM -> registers, + bias (the tile's bias row sits in shared memory, loaded
 // by the epilogue warps while the tile's MMAs were still running; every lane reads it with broadcast
 // 16-byte loads), activation, pack, swizzled st.shared, TMA store.
+// ADD: the addend tile of a chunk (32 rows x 128 bytes, the output tile's own box) is fetched by TMA straight into
+// the staging tile that will hold the chunk's output, one chunk ahead (two barriers per warp, alternating); the lane
+// then adds its row in place. A first version read the addend with per-lane global loads (32 different 128-byte
+// lines per instruction) and cost as much as the element-wise add it replaced (profiles/conv_r2.md section 5).
 template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32, bool STATS = false, bool ADD = false>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* map_d, uint32_t tcol,
                                               uint32_t bufs, uint32_t tile_bytes, int& epi_buf, float* bias_s,
                                               int row0, int col_base, int ks, int lane,
-                                              float (*st)[4] = nullptr) {
+                                              float (*st)[4] = nullptr, const CUtensorMap* map_add = nullptr,
+                                              uint32_t add_bars = 0, uint32_t* add_count = nullptr) {
   constexpr int kCols = F32 ? 32 : 64;
   if (row0 >= p.M) return;
   const uint32_t swz = (uint32_t)(lane & 7);
@@ -336,29 +343,43 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
     const int col0 = col_base + c * kCols;
     if (col0 >= p.N) break;
     uint32_t r[kCols];
-    // ADD (bf16 output only): this lane's 128 bytes of the addend row, requested before the accumulator is read
-    uint4 ad[ADD ? 8 : 1];
     if constexpr (ADD) {
-      const bool row_in = row0 + lane < p.M;
-      const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.addend) +
-                                                       (size_t)(row_in ? row0 + lane : 0) * p.N + col0);
-#pragma unroll
-      for (int q = 0; q < 8; ++q)
-        ad[q] = (row_in && col0 + 8 * q < p.N) ? __ldg(ap + q) : make_uint4(0u, 0u, 0u, 0u);
+      // addend tile of chunk c: issued here for the first chunk of the tile, else one chunk ago; then the next one
+      if (lane == 0) {
+        if (c == 0) {
+          tma_store_wait_read_n<EPI_BUFS - 1>();                    // staging tile epi_buf is free
+          const uint32_t bar = add_bars + 8u * (*add_count & 1u);
+          mbar_expect_tx(bar, tile_bytes);
+          tma_load_2d(bufs + (uint32_t)epi_buf * tile_bytes, map_add, bar, col0, row0);
+        }
+        if (c + 1 < BLOCK_N / kCols && col0 + kCols < p.N) {
+          tma_store_wait_read_n<EPI_BUFS - 2>();                    // so is the next one
+          const uint32_t bar = add_bars + 8u * ((*add_count + 1u) & 1u);
+          mbar_expect_tx(bar, tile_bytes);
+          tma_load_2d(bufs + (uint32_t)((epi_buf + 1) % EPI_BUFS) * tile_bytes, map_add, bar, col0 + kCols, row0);
+        }
+      }
+      __syncwarp();
     }
     tc_ld_32x32(tcol + c * kCols, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
     if constexpr (!F32) tc_ld_32x32(tcol + c * kCols + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
     tc_ld_wait();
     if constexpr (ADD) {
+      // two loads alternate on two barriers: load k completes phase (k / 2) of barrier (k % 2)
+      mbar_wait(add_bars + 8u * (*add_count & 1u), (*add_count >> 1) & 1u);
+      const uint32_t arow = bufs + (uint32_t)epi_buf * tile_bytes + (uint32_t)lane * 128u;
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
-        const uint32_t w[4] = {ad[q].x, ad[q].y, ad[q].z, ad[q].w};
+        uint32_t w[4];
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
+                     : "r"(arow + (((uint32_t)q ^ swz) << 4)) : "memory");
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           r[8 * q + 2 * e] = __float_as_uint(__uint_as_float(r[8 * q + 2 * e]) + bf16_lo(w[e]));
           r[8 * q + 2 * e + 1] = __float_as_uint(__uint_as_float(r[8 * q + 2 * e + 1]) + bf16_hi(w[e]));
         }
       }
+      ++*add_count;
     }
 #pragma unroll
     for (int q = 0; q < kCols / 4; ++q) {
@@ -375,7 +396,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
       r[4 * q + 2] = __float_as_uint(x2); r[4 * q + 3] = __float_as_uint(x3);
     }
     const uint32_t buf = bufs + (uint32_t)epi_buf * tile_bytes;
-    if (lane == 0) tma_store_wait_read_n<EPI_BUFS - 1>();   // the store that last used this tile is done
+    if constexpr (!ADD) {
+      if (lane == 0) tma_store_wait_read_n<EPI_BUFS - 1>();   // the store that last used this tile is done
+    }
     __syncwarp();
     const uint32_t row_addr = buf + (uint32_t)lane * 128u;
 #pragma unroll
@@ -403,17 +426,18 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
       // channels col0 + 2l, +1 over the tile's 32 rows = word l of every staged row (rows past M were
       // zero-filled by the loads and add nothing). The staging tile is reused only EPI_BUFS chunks later.
       const uint32_t ucol = (uint32_t)(lane >> 2), wsel = (uint32_t)(lane & 3) * 4u;
-      float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+      // packed fp32x2 arithmetic (FADD2 / FFMA2): one add and one fma per pair of channels
+      float2 sum2 = make_float2(0.f, 0.f), sq2 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int rr = 0; rr < 32; ++rr) {
         uint32_t w;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w)
                      : "r"(buf + (uint32_t)rr * 128u + ((ucol ^ (uint32_t)(rr & 7)) << 4) + wsel) : "memory");
-        const float a = bf16_lo(w), b = bf16_hi(w);
-        s0 += a; q0 = fmaf(a, a, q0);
-        s1 += b; q1 = fmaf(b, b, q1);
+        const float2 v = make_float2(bf16_lo(w), bf16_hi(w));
+        sum2 = __fadd2_rn(sum2, v);
+        sq2 = __ffma2_rn(v, v, sq2);
       }
-      st[c][0] += s0; st[c][1] += q0; st[c][2] += s1; st[c][3] += q1;
+      st[c][0] += sum2.x; st[c][1] += sq2.x; st[c][2] += sum2.y; st[c][3] += sq2.y;
     }
     epi_buf = (epi_buf + 1) % EPI_BUFS;
   }
@@ -451,6 +475,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + kAccumStages + s); };
   auto copy_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + s); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + 2);
+  const uint32_t add_bar_base = tmem_slot + 16u;          // 2 per epilogue warp (addend epilogue)
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -473,6 +498,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     }
     mbar_init(copy_bar(0), 1);
     mbar_init(copy_bar(1), 1);
+    for (int i = 0; i < 8; ++i) mbar_init(add_bar_base + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -720,6 +746,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     int epi_buf = 0;
+    uint32_t add_count = 0;          // addend tiles fetched so far by this warp (addend epilogue)
     // BatchNorm-statistics epilogue: per-lane (sum, sum of squares) of two channels per 64-column chunk, carried
     // across this CTA's tiles of one n block and written as one partial row per (CTA, warp) when it changes
     float st[BLOCK_N / 64][4];
@@ -780,7 +807,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         switch (variant) {
           case 14:
             epilogue_tile<BLOCK_N, C::kEpiBufs, 0, false, false, false, true>(p, &map_d, tcol, bufs, C::kEpiTileBytes,
-                                                                              epi_buf, bias_s, row0, col_base, ks, lane);
+                                                                              epi_buf, bias_s, row0, col_base, ks, lane,
+                                                                              nullptr, &pull.addend,
+                                                                              add_bar_base + 16u * ew, &add_count);
             break;
           case 13:
             epilogue_tile<BLOCK_N, C::kEpiBufs, 0, false, false, true>(p, &map_d, tcol, bufs, C::kEpiTileBytes, epi_buf,
@@ -1203,11 +1232,11 @@ int plan_pair_splits(int M, int N, int K, int pairs) {
   return splits;
 }
 
-int launch_gemm_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const GemmParams& p, int pairs,
-                     cudaStream_t stream) {
+int launch_gemm_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const PullMaps& extra,
+                     const GemmParams& p, int pairs, cudaStream_t stream) {
   static DeviceOnce configured;
   if (int rc = ensure_dynamic_smem(configured, pair::gemm2_kernel, pair::kSmemBytes)) return rc;
-  pair::gemm2_kernel<<<2 * pairs, kGemmThreads, pair::kSmemBytes, stream>>>(ma, mb, md, p);
+  pair::gemm2_kernel<<<2 * pairs, kGemmThreads, pair::kSmemBytes, stream>>>(ma, mb, md, extra, p);
   return launched();
 }
 
@@ -1348,6 +1377,8 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   }
   PullMaps pm;
   memset(&pm, 0, sizeof(pm));
+  if (addend)
+    if (int rc = make_out_map(&pm.addend, addend, M, N, false, 1)) return rc;
   if (conv && conv->g.mode == 1) {
     if (int rc = make_im2col_map(&ma, conv->act, conv->n, conv->h, conv->w, conv->c, conv->g.R, conv->g.S,
                                  conv->g.stride, conv->pad, BLOCK_M, conv->has_corners ? conv->corners : nullptr))
@@ -1404,7 +1435,7 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   int rc;
   const bool thin = !pull && p.num_kb <= 4 && splits == 1;   // store-bound: deeper epilogue pipeline
   if (use_pair) {
-    rc = launch_gemm_pair(ma, mb, md, p, items < sms / 2 ? items : sms / 2, stream);
+    rc = launch_gemm_pair(ma, mb, md, pm, p, items < sms / 2 ? items : sms / 2, stream);
   } else if (block_n == 256) {
     rc = pull ? launch_gemm<256, true, false>(ma, mb, md, pm, p, grid, stream)
               : (thin ? launch_gemm<256, false, true>(ma, mb, md, pm, p, grid, stream)
