@@ -45,9 +45,14 @@ constexpr int kAccumStages = 2;
 // trades one mainloop stage for a deeper store pipeline in the epilogue.
 constexpr int kCopyPiece = 16 * 1024;   // pull variant: bytes per bulk copy of the copy engine (two in flight)
 
-template <int BLOCK_N, bool THIN, bool PULL = false>
+// EPI8 = eight epilogue warps instead of four (two per TMEM lane quarter, alternating 64-column chunks): the
+// BatchNorm-statistics epilogue triples the instructions per chunk and made the 1x1 forward convolutions
+// epilogue-issue bound (119 us against 88 us for the same GEMM without statistics, profiles/conv_r2.md section 5).
+template <int BLOCK_N, bool THIN, bool PULL = false, bool EPI8 = false>
 struct Cfg {
-  static constexpr int kStages = (BLOCK_N == 256 ? 4 : 6) - (THIN ? 1 : 0) - (PULL ? 1 : 0);
+  static constexpr int kStages = (BLOCK_N == 256 ? 4 : 6) - (THIN ? 1 : 0) - (PULL ? 1 : 0) - ((EPI8 && !THIN) ? 1 : 0);
+  static constexpr int kEpiWarps = EPI8 ? 8 : 4;
+  static constexpr int kThreads = 128 + 32 * kEpiWarps;
   static constexpr int kCopyBytes = PULL ? 2 * kCopyPiece : 0;
   static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
@@ -59,8 +64,8 @@ struct Cfg {
   static constexpr int kEpiTileBytes = 32 * 128;
   // kEpiBufs staging tiles per epilogue warp: a TMA store occupies its tile for ~1 us, so with two tiles a
   // warp could not retire more than ~8 GB/s and thin-K (store-bound) shapes topped out near 2.4 TB/s.
-  static constexpr int kEpiBufs = THIN ? 4 : 2;
-  static constexpr int kEpiBytes = 4 * kEpiBufs * kEpiTileBytes;
+  static constexpr int kEpiBufs = (THIN && !EPI8) ? 4 : 2;
+  static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiTileBytes;
   static constexpr int kEpiBiasBytes = kAccumStages * 256 * 4;   // the tile's bias row, per accumulator stage
   static constexpr int kSmemBytes =
       kStages * kStageBytes + kEpiBytes + kEpiBiasBytes + kCopyBytes + kBarrierBytes;
@@ -329,17 +334,18 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
 // the staging tile that will hold the chunk's output, one chunk ahead (two barriers per warp, alternating); the lane
 // then adds its row in place. A first version read the addend with per-lane global loads (32 different 128-byte
 // lines per instruction) and cost as much as the element-wise add it replaced (profiles/conv_r2.md section 5).
-template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32, bool STATS = false, bool ADD = false>
+template <int BLOCK_N, int EPI_BUFS, int ACT, bool BIAS, bool F32, bool STATS = false, bool ADD = false, int CSTEP = 1>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* map_d, uint32_t tcol,
                                               uint32_t bufs, uint32_t tile_bytes, int& epi_buf, float* bias_s,
                                               int row0, int col_base, int ks, int lane,
                                               float (*st)[4] = nullptr, const CUtensorMap* map_add = nullptr,
-                                              uint32_t add_bars = 0, uint32_t* add_count = nullptr) {
+                                              uint32_t add_bars = 0, uint32_t* add_count = nullptr, int c_first = 0) {
+  static_assert(CSTEP == 1 || !ADD, "the addend prefetch assumes consecutive chunks");
   constexpr int kCols = F32 ? 32 : 64;
   if (row0 >= p.M) return;
   const uint32_t swz = (uint32_t)(lane & 7);
 #pragma unroll 1
-  for (int c = 0; c < BLOCK_N / kCols; ++c) {
+  for (int c = c_first; c < BLOCK_N / kCols; c += CSTEP) {
     const int col0 = col_base + c * kCols;
     if (col0 >= p.N) break;
     uint32_t r[kCols];
@@ -452,13 +458,13 @@ __device__ __forceinline__ int pull_n_order(const GemmParams& p, int t) {
   return n >= p.num_n ? n - p.num_n : n;
 }
 
-template <int BLOCK_N, bool kPull, bool THIN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+template <int BLOCK_N, bool kPull, bool THIN, bool EPI8 = false>
+__global__ void __launch_bounds__(EPI8 ? 384 : kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                     const __grid_constant__ CUtensorMap map_b,
                     const __grid_constant__ CUtensorMap map_d,
                     const __grid_constant__ PullMaps pull, const GemmParams p) {
-  using C = Cfg<BLOCK_N, THIN, kPull>;
+  using C = Cfg<BLOCK_N, THIN, kPull, EPI8>;
   // SWIZZLE_128B tiles need 1024-byte alignment (the kernel has no static shared memory, so the
   // dynamic segment starts at the CTA's 1024-byte aligned shared-memory base).
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -494,7 +500,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     }
     for (int s = 0; s < kAccumStages; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 4);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(s), C::kEpiWarps);  // one arrive per epilogue warp
     }
     mbar_init(copy_bar(0), 1);
     mbar_init(copy_bar(1), 1);
@@ -742,7 +748,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     }
   } else if (warp >= 4) {
     // ================= epilogue =================
-    const int ew = warp - 4;  // == warp % 4: the TMEM lane quarter this warp may touch
+    const int ew = (warp - 4) & 3;   // == warp % 4: the TMEM lane quarter this warp may touch
+    const int half = (warp - 4) >> 2;   // EPI8: this warp takes the 64-column chunks c with c % 2 == half
     int as = 0;
     uint32_t aphase = 0;
     int epi_buf = 0;
@@ -754,11 +761,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     for (int c = 0; c < BLOCK_N / 64; ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
     int st_n = -1;
     auto flush_stats = [&](int n_blk) {
-      const size_t part = (size_t)blockIdx.x * 4 + ew;
+      const size_t part = (size_t)blockIdx.x * 4 + ew;         // (EPI8: the two warps of a quarter share the row)
 #pragma unroll
       for (int c = 0; c < BLOCK_N / 64; ++c) {
         const int col = n_blk * BLOCK_N + c * 64 + 2 * lane;
-        if (col < p.N)
+        if (col < p.N && (!EPI8 || (c & 1) == half))
           *reinterpret_cast<float4*>(p.stats + (part * p.N + col) * 2) = make_float4(st[c][0], st[c][1], st[c][2], st[c][3]);
         st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
       }
@@ -771,7 +778,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         if (st_n >= 0) flush_stats(st_n);
         st_n = n_blk;
       }
-      if (p.bias && p.splits == 1 && !p.direct_store) {
+      if (!EPI8 && p.bias && p.splits == 1 && !p.direct_store) {
         // Stage this tile's bias row (fp32) before waiting for the accumulator: the loads overlap the
         // MMAs. Buffer `as` was last read two tiles ago; the barrier of the tile in between orders it.
         float* bt = reinterpret_cast<float*>(smem_raw + (epi_bias_smem - smem_u32(smem_raw))) + as * 256;
@@ -797,10 +804,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         // ---- TMEM -> registers -> swizzled smem tile -> TMA store (coalesced, clipped at M / N) ----
         const int row0 = m_blk * BLOCK_M + ew * 32;
         const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-        const uint32_t bufs = epi_smem + (uint32_t)(ew * C::kEpiBufs) * C::kEpiTileBytes;
+        const uint32_t bufs = epi_smem + (uint32_t)((warp - 4) * C::kEpiBufs) * C::kEpiTileBytes;
 
         float* bias_s = reinterpret_cast<float*>(smem_raw + (epi_bias_smem - smem_u32(smem_raw))) + as * 256;
         const int col_base = n_blk * BLOCK_N;
+        if constexpr (EPI8) {
+          // statistics epilogue only (the host launches this instantiation for nothing else)
+          epilogue_tile<BLOCK_N, C::kEpiBufs, 0, false, false, true, false, 2>(p, &map_d, tcol, bufs, C::kEpiTileBytes,
+                                                                               epi_buf, bias_s, row0, col_base, ks, lane,
+                                                                               st, nullptr, 0, nullptr, half);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(as));
+          if (++as == kAccumStages) { as = 0; aphase ^= 1; }
+          continue;
+        }
         // One compact instruction stream per (activation, bias, output type): the element loop must not
         // carry per-element branches (a first version did and was instruction-fetch bound).
         const int variant = (p.splits > 1) ? 12 : (p.stats ? 13 : (p.addend ? 14 : (p.act * 4 + (p.bias ? 2 : 0) + (p.d_dtype == kF32 ? 1 : 0))));
@@ -1240,15 +1258,25 @@ int launch_gemm_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtenso
   return launched();
 }
 
-template <int BLOCK_N, bool kPull, bool THIN>
+template <int BLOCK_N, bool kPull, bool THIN, bool EPI8 = false>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const PullMaps& pull,
                 const GemmParams& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BLOCK_N, THIN, kPull>;
-  auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull, THIN>;
+  using C = Cfg<BLOCK_N, THIN, kPull, EPI8>;
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, kPull, THIN, EPI8>;
   static DeviceOnce configured;      // one per template instantiation
   if (int rc = ensure_dynamic_smem(configured, kern, C::kSmemBytes)) return rc;
-  kern<<<grid, kGemmThreads, C::kSmemBytes, stream>>>(ma, mb, md, pull, p);
+  kern<<<grid, C::kThreads, C::kSmemBytes, stream>>>(ma, mb, md, pull, p);
   return launched();
+}
+
+// TB200_STATS_EPI8=0 keeps the statistics epilogue on four warps (A/B runs)
+bool stats_epi8() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TB200_STATS_EPI8");
+    v = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return v == 1;
 }
 
 // Host-side description of the im2col operand of an implicit-GEMM convolution (see ConvGeom).
@@ -1436,6 +1464,12 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   const bool thin = !pull && p.num_kb <= 4 && splits == 1;   // store-bound: deeper epilogue pipeline
   if (use_pair) {
     rc = launch_gemm_pair(ma, mb, md, pm, p, items < sms / 2 ? items : sms / 2, stream);
+  } else if (p.stats && stats_epi8()) {
+    // eight epilogue warps (conv mode 1 included: the producer and MMA warps are the same code)
+    if (block_n == 256) rc = thin ? launch_gemm<256, false, true, true>(ma, mb, md, pm, p, grid, stream)
+                                  : launch_gemm<256, false, false, true>(ma, mb, md, pm, p, grid, stream);
+    else rc = thin ? launch_gemm<128, false, true, true>(ma, mb, md, pm, p, grid, stream)
+                   : launch_gemm<128, false, false, true>(ma, mb, md, pm, p, grid, stream);
   } else if (block_n == 256) {
     rc = pull ? launch_gemm<256, true, false>(ma, mb, md, pm, p, grid, stream)
               : (thin ? launch_gemm<256, false, true>(ma, mb, md, pm, p, grid, stream)

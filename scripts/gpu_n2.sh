@@ -23,7 +23,7 @@ for r in d.get('communication_bound_jobs', []): print(r)
 print('clocks', d.get('clocks'), d.get('nccl_error'))
 " || tail -5 gpurun_out/bench_n$N.log | cut -c1-300;;
     benchpull) # the headline with the fc layer pulled inside its GEMM whatever the batch (A/B against `bench`)
-           TB200_PULL_MAX_ROWS=1000000 timeout 600 $TR --master-port $(port) bench.py --gpus $N --steps 20 --warmup 5 --skip-sim --skip-nccl > gpurun_out/bench_pull_n$N.log 2>&1
+           TB200_PULL_MAX_ROWS=1000000 TB200_PULL_MIN_MB=2 timeout 600 $TR --master-port $(port) bench.py --gpus $N --steps 20 --warmup 5 --skip-sim --skip-nccl > gpurun_out/bench_pull_n$N.log 2>&1
            echo "== bench (pull at any batch) N=$N exit $?"; grep '^{' gpurun_out/bench_pull_n$N.log | tail -1 | python -c "
 import sys, json
 d = json.loads(sys.stdin.read())

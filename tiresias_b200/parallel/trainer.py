@@ -163,6 +163,7 @@ class Trainer:
         # cut-off adjustable (profiles/comm_pull_r2.md has both generations' numbers).
         rows_per_step = batch_size * (spec.sample_shape[0] if spec.kind == "tokens" else 1)
         max_rows = int(os.environ.get("TB200_PULL_MAX_ROWS", str(PULL_MAX_ROWS)))
+        pull_min_mb = float(os.environ.get("TB200_PULL_MIN_MB", str(pull_min_mb)))
         self.buckets, self.total = plan_buckets(
             self.model, self.world, int(bucket_mb * (1 << 20) / 2), int(pull_min_mb * (1 << 20) / 2),
             allow_pull=(pull_gemm and mode == "ps" and rows_per_step <= max_rows))
