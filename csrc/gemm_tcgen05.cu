@@ -1464,12 +1464,12 @@ int gemm_common(const tb200_world_t* world, int bucket, size_t b_off, int rows_p
   const bool thin = !pull && p.num_kb <= 4 && splits == 1;   // store-bound: deeper epilogue pipeline
   if (use_pair) {
     rc = launch_gemm_pair(ma, mb, md, pm, p, items < sms / 2 ? items : sms / 2, stream);
-  } else if (p.stats && stats_epi8()) {
-    // eight epilogue warps (conv mode 1 included: the producer and MMA warps are the same code)
-    if (block_n == 256) rc = thin ? launch_gemm<256, false, true, true>(ma, mb, md, pm, p, grid, stream)
-                                  : launch_gemm<256, false, false, true>(ma, mb, md, pm, p, grid, stream);
-    else rc = thin ? launch_gemm<128, false, true, true>(ma, mb, md, pm, p, grid, stream)
-                   : launch_gemm<128, false, false, true>(ma, mb, md, pm, p, grid, stream);
+  } else if (p.stats && stats_epi8() && block_n == 256) {
+    // eight epilogue warps, two per lane quarter on alternating 64-column chunks: measured on the ResNet-50 forward
+    // convolutions (profiles/conv_r2.md section 5) 119 -> 90 us on layer1's 64 -> 256 and 67 -> 55 us on layer2's
+    // 128 -> 512; 128-wide tiles have too few chunks per quarter to share and lose the deeper store pipeline
+    rc = thin ? launch_gemm<256, false, true, true>(ma, mb, md, pm, p, grid, stream)
+              : launch_gemm<256, false, false, true>(ma, mb, md, pm, p, grid, stream);
   } else if (block_n == 256) {
     rc = pull ? launch_gemm<256, true, false>(ma, mb, md, pm, p, grid, stream)
               : (thin ? launch_gemm<256, false, true>(ma, mb, md, pm, p, grid, stream)
