@@ -43,7 +43,8 @@ constexpr int kAccumStages = 2;
 
 // THIN = short reduction (K <= 256): the kernel is bound by its output stores, not by the mainloop, so it
 // trades one mainloop stage for a deeper store pipeline in the epilogue.
-constexpr int kCopyPiece = 16 * 1024;   // pull variant: bytes per bulk copy of the copy engine (two in flight)
+constexpr int kCopyPiece = 8 * 1024;    // pull variant: bytes per bulk copy of the copy engine
+constexpr int kCopyBufs = 4;            // staging buffers (three loads in flight)
 
 // EPI8 = eight epilogue warps instead of four (two per TMEM lane quarter, alternating 64-column chunks): the
 // BatchNorm-statistics epilogue triples the instructions per chunk and made the 1x1 forward convolutions
@@ -53,13 +54,13 @@ struct Cfg {
   static constexpr int kStages = (BLOCK_N == 256 ? 4 : 6) - (THIN ? 1 : 0) - (PULL ? 1 : 0) - ((EPI8 && !THIN) ? 1 : 0);
   static constexpr int kEpiWarps = EPI8 ? 8 : 4;
   static constexpr int kThreads = 128 + 32 * kEpiWarps;
-  static constexpr int kCopyBytes = PULL ? 2 * kCopyPiece : 0;
+  static constexpr int kCopyBytes = PULL ? kCopyBufs * kCopyPiece : 0;
   static constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
   static constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = kAccumStages * BLOCK_N;  // 512 or 256 (power of two)
-  // pipeline barriers, 2 copy-engine barriers, the TMEM slot (16 bytes), 8 addend-tile barriers (2 per epilogue warp)
-  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages + 2) * 8 + 16 + 8 * 8;
+  // pipeline barriers, 4 copy-engine barriers, the TMEM slot (16 bytes), 8 addend-tile barriers (2 per epilogue warp)
+  static constexpr int kBarrierBytes = (2 * kStages + 2 * kAccumStages + 4) * 8 + 16 + 8 * 8;
   // Epilogue staging: per epilogue warp two 32-row x 128-byte tiles (swizzle-128B), TMA-stored.
   static constexpr int kEpiTileBytes = 32 * 128;
   // kEpiBufs staging tiles per epilogue warp: a TMA store occupies its tile for ~1 us, so with two tiles a
@@ -473,14 +474,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t b_smem = smem_base + C::kStages * C::kABytes;
   const uint32_t epi_smem = smem_base + C::kStages * C::kStageBytes;   // 1024-byte aligned
   const uint32_t epi_bias_smem = epi_smem + C::kEpiBytes;
-  const uint32_t copy_smem = epi_bias_smem + C::kEpiBiasBytes;          // pull variant: 2 x kCopyPiece
+  const uint32_t copy_smem = epi_bias_smem + C::kEpiBiasBytes;          // pull variant: kCopyBufs x kCopyPiece
   const uint32_t bar_base = copy_smem + C::kCopyBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + s); };
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + kAccumStages + s); };
   auto copy_bar = [&](int s) { return bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + 2);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * C::kStages + 2 * kAccumStages + 4);
   const uint32_t add_bar_base = tmem_slot + 16u;          // 2 per epilogue warp (addend epilogue)
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
@@ -502,8 +503,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), C::kEpiWarps);  // one arrive per epilogue warp
     }
-    mbar_init(copy_bar(0), 1);
-    mbar_init(copy_bar(1), 1);
+    for (int i = 0; i < kCopyBufs; ++i) mbar_init(copy_bar(i), 1);
     for (int i = 0; i < 8; ++i) mbar_init(add_bar_base + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -673,11 +673,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   } else if (kPull && warp == 3 && lane == 0) {
     // ================= copy engine (pull variant) =================
     // The remote n tiles (BLOCK_N rows x K, contiguous in the owner's and in the local buffer) in the order the GEMM
-    // consumes them, cut into 16 KB pieces numbered across tiles; this CTA moves pieces blockIdx.x,
-    // blockIdx.x + gridDim.x, ... through a two-deep staging ring: the load of piece i+1 is in flight while piece i
-    // is stored, and a piece is counted into its tile once its store has completed (one group later).
+    // consumes them, cut into 8 KB pieces numbered across tiles; this CTA moves pieces blockIdx.x,
+    // blockIdx.x + gridDim.x, ... through a four-deep staging ring (1-D bulk copies peer -> shared -> local).
     uint32_t owner_ready = 0;                     // owners whose PARAM_DONE flag has been observed
-    uint32_t ph[2] = {0, 0};
     const size_t tile_bytes = (size_t)BLOCK_N * p.K * 2;
     const int ppt = (int)((tile_bytes + kCopyPiece - 1) / kCopyPiece);      // pieces per tile
     const int own_blks = p.rows_per_rank / BLOCK_N, own_first = p.rank * own_blks;
@@ -706,45 +704,50 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       mbar_expect_tx(copy_bar(buf), sz);
       bulk_load_1d(copy_smem + buf * kCopyPiece, p.owner_base[owner] + (size_t)n_blk * tile_bytes + off, sz, copy_bar(buf));
     };
-    auto count_in = [&](long long g) {
-      int n_blk; size_t off; uint32_t sz;
-      locate(g, &n_blk, &off, &sz);
+    // My pieces are g_k = blockIdx.x + k * gridDim.x. Ring of kCopyBufs staging buffers: loads run kCopyBufs - 1
+    // pieces ahead of the stores; completed pieces are counted in batches of four behind ONE pair of fences
+    // (a fence + counter update per piece made each piece cost ~5 us and held the engine at 400 GB/s of NVLink).
+    const long long n_my = total > blockIdx.x ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    auto piece = [&](long long k) { return (long long)blockIdx.x + k * gridDim.x; };
+    auto count_batch = [&](long long k0, long long k1) {      // pieces [k0, k1) of mine are complete in local memory
+      if (k0 >= k1) return;
       asm volatile("fence.proxy.async.global;" ::: "memory");
       __threadfence();
-      const unsigned prev = atomicAdd(p.pull_cnt + n_blk, 1u);
-      if (prev == (unsigned)ppt - 1) {
-        p.pull_cnt[n_blk] = 0;                     // self-resetting: ready for the next launch
-        __threadfence();
-        st_release_gpu(p.pull_ready + n_blk, epoch);
+      for (long long k = k0; k < k1; ++k) {
+        int n_blk; size_t off; uint32_t sz;
+        locate(piece(k), &n_blk, &off, &sz);
+        const unsigned prev = atomicAdd(p.pull_cnt + n_blk, 1u);
+        if (prev == (unsigned)ppt - 1) {
+          p.pull_cnt[n_blk] = 0;                     // self-resetting: ready for the next launch
+          __threadfence();
+          st_release_gpu(p.pull_ready + n_blk, epoch);
+        }
       }
     };
-    long long g = blockIdx.x;
-    int buf = 0;
-    long long prev_g = -1;                         // piece whose store is the latest committed group
-    if (g < total) issue_load(g, 0);
-    for (; g < total; g += gridDim.x) {
-      const long long gn = g + gridDim.x;
-      if (gn < total) {
-        if (prev_g >= 0) tma_store_wait_read_n<0>();   // the other buffer's store (piece prev_g) has read it
-        issue_load(gn, buf ^ 1);
-      }
+    for (long long k = 0; k < kCopyBufs - 1 && k < n_my; ++k) issue_load(piece(k), (int)k);
+    long long counted = 0;
+    for (long long k = 0; k < n_my; ++k) {
+      const int buf = (int)(k % kCopyBufs);
       int n_blk; size_t off; uint32_t sz;
-      locate(g, &n_blk, &off, &sz);
-      mbar_wait(copy_bar(buf), ph[buf]);
-      ph[buf] ^= 1;
+      locate(piece(k), &n_blk, &off, &sz);
+      mbar_wait(copy_bar(buf), (uint32_t)(k / kCopyBufs) & 1u);
       fence_proxy_async_smem();
       bulk_store_1d(p.local_base + (size_t)n_blk * tile_bytes + off, copy_smem + buf * kCopyPiece, sz);
       tma_store_commit();
-      if (prev_g >= 0) {
-        tma_store_wait_n<1>();                     // every group but the one just committed is complete
-        count_in(prev_g);
+      const long long kn = k + kCopyBufs - 1;        // next load: into the buffer piece k - 1 was stored from
+      if (kn < n_my) {
+        if (k >= 1) tma_store_wait_read_n<1>();      // every store but the one just committed has read its buffer
+        issue_load(piece(kn), (int)(kn % kCopyBufs));
       }
-      prev_g = g;
-      buf ^= 1;
+      if ((k & 3) == 3) {
+        tma_store_wait_n<1>();                       // every store but the one just committed is complete
+        count_batch(counted, k);
+        counted = k;
+      }
     }
-    if (prev_g >= 0) {
+    if (n_my > 0) {
       tma_store_wait_all();
-      count_in(prev_g);
+      count_batch(counted, n_my);
     }
   } else if (warp >= 4) {
     // ================= epilogue =================
