@@ -14,7 +14,7 @@ for entry in $SCHEDS; do
   sched=${entry%%:*}; extra=""
   if [ "$entry" != "$sched" ]; then extra=$(echo "${entry#*:}" | tr ':' ' '); fi
   tag=$(echo "$entry" | tr -c 'A-Za-z0-9\n' '_')
-  timeout 600 python -m tiresias_b200.exec.replay --trace $OUT/trace.csv --gpus $N --schedule $sched --comm $COMM \
+  timeout ${REPLAY_TIMEOUT:-300} python -m tiresias_b200.exec.replay --trace $OUT/trace.csv --gpus $N --schedule $sched --comm $COMM \
     --batch ${BATCH:-32} --calibration $OUT/calibration_${COMM}_${N}gpu.json --out $OUT/run_$tag \
     --queue-limit ${QLIMIT:-20} --check-every ${CHECK_EVERY:-10} $extra > $OUT/replay_$tag.log 2>&1
   echo "== replay $entry exit $?"; tail -n 4 $OUT/replay_$tag.log | cut -c1-500
