@@ -40,8 +40,12 @@ constexpr int kEpiBytes = 4 * 2 * 4096;   // 4 epilogue warps x 2 staging tiles 
 
 struct C3Params {
   int N, H, W, C, K;               // batch, image, reduction channels, output channels
-  int Wp, Hp;                      // pitches of the flat padded space: W+1, H+1
+  int Wp, Hp;                      // pitches of the flat padded space: W+1, H+1 (segment mode: Wp = 130)
   int NR;                          // padded rows fetched per A stage
+  int seg;                         // segment mode (wide images): a tile = 128 consecutive columns of ONE image row, its
+                                   // stage = three boxes {64 ch, 130 columns} of the rows above / at / below it
+  int nseg;                        // segments per image row
+  unsigned long long mSeg, mH;     // fastdiv multipliers for nseg and H
   int cblocks;                     // C / 64
   int num_m, num_n;
   int total_pos;                   // N * Hp * Wp
@@ -52,6 +56,10 @@ struct C3Params {
   int resident;                    // all weight tiles of the (single) n block stay in shared memory
   __nv_bfloat16* y;
   float* stats;                    // [gridDim.x * 4][K][2] per-channel (sum, sum of squares) partials, or null
+  const void* bias;                // optional per-output-channel bias (fprop; VGG / AlexNet style layers)
+  int bias_dtype;
+  int relu;                        // clamp the (biased) output at zero
+  int bias_off;                    // shared-memory offset of the epilogue warps' bias rows (4 x 256 floats)
 };
 
 template <int BLOCK_N, int TPG, bool DGRAD>
@@ -131,19 +139,30 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
       const uint32_t q0 = (uint32_t)m_tile * 128u;
       // first padded row the tile's windows touch: floor((q0 - Wp - 1) / Wp), can be -1 or -2 for the first tile
       const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
+      // segment mode: tile -> (image, row, segment)
+      const uint32_t srow = fastdiv((uint32_t)m_tile, p.mSeg), sseg = (uint32_t)m_tile - srow * (uint32_t)p.nseg;
+      const uint32_t sn = fastdiv(srow, p.mH), sh = srow - sn * (uint32_t)p.H;
       for (int cb = 0; cb < p.cblocks; ++cb) {
         mbar_wait(a_empty(as), aph ^ 1);
         if (elect_one()) {
           mbar_expect_tx(a_full(as), (uint32_t)p.NR * row_bytes);
-          int n, hp;
-          if (rho0 < 0) { n = -1; hp = rho0 + p.Hp; }
-          else { n = (int)fastdiv((uint32_t)rho0, p.mHp); hp = rho0 - n * p.Hp; }
           uint32_t dst = a_smem + (uint32_t)as * p.a_stage_bytes;
-          for (int i = 0; i < p.NR; ++i) {
-            // whole padded row: columns 0..W (column W, row H and images outside [0, N) arrive as zeros)
-            tma_load_4d(dst, &map_x, a_full(as), cb * 64, 0, hp, n);
-            dst += row_bytes;
-            if (++hp == p.Hp) { hp = 0; ++n; }
+          if (p.seg) {
+            // rows h-1, h, h+1, columns w0-1 .. w0+128 (whatever lies outside the image arrives as zeros)
+            for (int i = 0; i < 3; ++i) {
+              tma_load_4d(dst, &map_x, a_full(as), cb * 64, (int)sseg * 128 - 1, (int)sh - 1 + i, (int)sn);
+              dst += row_bytes;
+            }
+          } else {
+            int n, hp;
+            if (rho0 < 0) { n = -1; hp = rho0 + p.Hp; }
+            else { n = (int)fastdiv((uint32_t)rho0, p.mHp); hp = rho0 - n * p.Hp; }
+            for (int i = 0; i < p.NR; ++i) {
+              // whole padded row: columns 0..W (column W, row H and images outside [0, N) arrive as zeros)
+              tma_load_4d(dst, &map_x, a_full(as), cb * 64, 0, hp, n);
+              dst += row_bytes;
+              if (++hp == p.Hp) { hp = 0; ++n; }
+            }
           }
         }
         __syncwarp();
@@ -181,7 +200,8 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
       const uint32_t q0 = (uint32_t)m_tile * 128u;
       const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
       // rows between the stage's first position and the tile's first position: in [Wp+1, 2*Wp]
-      const uint32_t woff8 = (uint32_t)((int)q0 - rho0 * p.Wp) * 8u;
+      // (segment mode: always one stage row + one column)
+      const uint32_t woff8 = p.seg ? (uint32_t)(p.Wp + 1) * 8u : (uint32_t)((int)q0 - rho0 * p.Wp) * 8u;
       mbar_wait(t_empty(acc), accph ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BLOCK_N);
@@ -245,6 +265,9 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
 #pragma unroll
     for (int c = 0; c < kChunks; ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
     int cur_n = -1;
+    // this warp's copy of the n block's bias row (fp32), refilled when the n block changes
+    float* bias_row = reinterpret_cast<float*>(smem_raw + p.bias_off) + ew * 256;
+    int bias_n = -1;
     auto flush_stats = [&](int n_blk) {
       const size_t part = (size_t)blockIdx.x * 4 + ew;
 #pragma unroll
@@ -261,12 +284,34 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
         if (cur_n >= 0) flush_stats(cur_n);
         cur_n = n_blk;
       }
+      if (p.bias && n_blk != bias_n) {
+        __syncwarp();
+        for (int j = lane; j < BLOCK_N; j += 32) {
+          const int k = n_blk * BLOCK_N + j;
+          float b = 0.f;
+          if (k < p.K)
+            b = p.bias_dtype == TB200_F32 ? reinterpret_cast<const float*>(p.bias)[k]
+                                          : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[k]);
+          bias_row[j] = b;
+        }
+        __syncwarp();
+        bias_n = n_blk;
+      }
       // this lane's row: flat padded position -> (image, row, column); junk positions get pix = -1
       const uint32_t q = (uint32_t)m_tile * 128u + (uint32_t)(ew * 32 + lane);
-      const uint32_t rho = fastdiv(q, p.mWp), j = q - rho * (uint32_t)p.Wp;
-      const uint32_t n = fastdiv(rho, p.mHp), h = rho - n * (uint32_t)p.Hp;
-      const bool valid = q < (uint32_t)p.total_pos && j < (uint32_t)p.W && h < (uint32_t)p.H;
-      const int pix = valid ? (int)((n * (uint32_t)p.H + h) * (uint32_t)p.W + j) : -1;
+      bool valid;
+      int pix;
+      if (p.seg) {
+        const uint32_t srow = fastdiv((uint32_t)m_tile, p.mSeg), sseg = (uint32_t)m_tile - srow * (uint32_t)p.nseg;
+        const uint32_t wcol = sseg * 128u + (uint32_t)(ew * 32 + lane);
+        valid = wcol < (uint32_t)p.W;
+        pix = valid ? (int)(srow * (uint32_t)p.W + wcol) : -1;        // srow = image * H + row
+      } else {
+        const uint32_t rho = fastdiv(q, p.mWp), j = q - rho * (uint32_t)p.Wp;
+        const uint32_t n = fastdiv(rho, p.mHp), h = rho - n * (uint32_t)p.Hp;
+        valid = q < (uint32_t)p.total_pos && j < (uint32_t)p.W && h < (uint32_t)p.H;
+        pix = valid ? (int)((n * (uint32_t)p.H + h) * (uint32_t)p.W + j) : -1;
+      }
       const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
       mbar_wait(t_full(acc), accph);
       tc_fence_after();
@@ -286,6 +331,20 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(t_empty(acc));
+          }
+          if (p.bias) {
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+              const float4 b4 = *reinterpret_cast<const float4*>(bias_row + c * 64 + 4 * u);
+              v[4 * u] = __float_as_uint(__uint_as_float(v[4 * u]) + b4.x);
+              v[4 * u + 1] = __float_as_uint(__uint_as_float(v[4 * u + 1]) + b4.y);
+              v[4 * u + 2] = __float_as_uint(__uint_as_float(v[4 * u + 2]) + b4.z);
+              v[4 * u + 3] = __float_as_uint(__uint_as_float(v[4 * u + 3]) + b4.w);
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) v[j] = __float_as_uint(fmaxf(__uint_as_float(v[j]), 0.f));
           }
           const uint32_t buf = bufs + (uint32_t)(c & 1) * 4096u;
           __syncwarp();                                    // readers of this staging tile (chunk c-2) are done
@@ -615,12 +674,13 @@ int c3_map_2d(CUtensorMap* out, const void* base, int rows, int cols, int box_ro
 }
 
 template <int BLOCK_N, int TPG, bool DGRAD>
-int launch_c3(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* nparts_out, cudaStream_t stream) {
+int launch_c3(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* nparts_out, cudaStream_t stream,
+              bool dry_run = false) {
   constexpr int kSmemMax = 227 * 1024;
   constexpr int kTile = BLOCK_N * 128;
   const int row_bytes = p.Wp * 128;
   p.a_stage_bytes = (p.NR * row_bytes + 1023) / 1024 * 1024;
-  const int fixed = kEpiBytes + 1024;
+  const int fixed = kEpiBytes + 1024 + 4096;          // staging tiles, barriers, the epilogue warps' bias rows
   const int resident_bytes = 9 * p.cblocks * kTile;
   p.resident = (p.num_n == 1 && resident_bytes + 2 * p.a_stage_bytes + fixed <= kSmemMax) ? 1 : 0;
   int b_bytes;
@@ -642,7 +702,9 @@ int launch_c3(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* npa
   if (p.a_stages < 2) return fail("tb200_conv3x3: tile does not fit shared memory (W %s%ld)", "", p.W);
   p.epi_off = p.a_stages * p.a_stage_bytes + b_bytes;
   p.bar_off = p.epi_off + kEpiBytes;
-  const int total = p.bar_off + 1024;
+  p.bias_off = p.bar_off + 1024;
+  const int total = p.bias_off + 4096;
+  if (dry_run) return 0;
   auto kern = conv3x3_kernel<BLOCK_N, TPG, DGRAD>;
   static DeviceOnce configured;
   if (int rc = ensure_dynamic_smem(configured, kern, kSmemMax)) return rc;
@@ -659,14 +721,14 @@ int launch_c3(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* npa
 }
 
 int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, int c_red, int k_out, bool dgrad,
-                   float* stats, size_t stats_floats, int* nparts_out, cudaStream_t stream) {
+                   float* stats, size_t stats_floats, int* nparts_out, cudaStream_t stream, const void* bias = nullptr,
+                   int bias_dtype = 0, int relu = 0, bool dry_run = false) {
   const char* who = dgrad ? "tb200_conv3x3_dgrad" : "tb200_conv3x3_fprop";
   if (n <= 0 || h <= 0 || wd <= 0 || c_red <= 0 || k_out <= 0) return fail("%s: empty problem", who);
   if (c_red % 64) return fail("%s: the reduction channel count (%ld) must be a multiple of 64", who, c_red);
   if (k_out % 8) return fail("%s: the output channel count (%ld) must be a multiple of 8", who, k_out);
-  if (wd + 1 > 256) return fail("%s: image width %ld exceeds one TMA box (255)", who, wd);
   static thread_local bool ctx_bound = false;
-  if (!ctx_bound) {
+  if (!ctx_bound && !dry_run) {
     TB_CUDA_OK(cudaFree(nullptr));       // binds the primary context to this thread for the driver-API encode
     ctx_bound = true;
   }
@@ -682,8 +744,27 @@ int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, 
   p.NR = (3 * p.Wp + 129 + p.Wp - 1) / p.Wp;
   p.cblocks = c_red / 64;
   p.num_m = (int)((total + 127) / 128);
+  p.nseg = 1; p.mSeg = fastdiv_magic(1u); p.mH = fastdiv_magic((unsigned)h);
+  // Wide images: whole padded rows no longer fit two stages (W = 112: 72 KB per stage next to the weight ring), so
+  // a tile becomes a 128-column segment of one row with a three-row, 130-column stage (50 KB); costs the unused
+  // columns of the last segment (12.5 % at W = 112 and 224) instead of the flat layout's 1-3 %.
+  if (wd >= 100) {
+    p.seg = 1;
+    p.nseg = (wd + 127) / 128;
+    p.mSeg = fastdiv_magic((unsigned)p.nseg);
+    p.Wp = 130;
+    p.NR = 3;
+    p.mWp = fastdiv_magic(130u);
+    const long long tiles = (long long)n * h * p.nseg;
+    if (tiles >= (1ll << 24)) return fail("%s: problem too large (%ld tiles)", who, (long)tiles);
+    p.num_m = (int)tiles;
+  } else if (wd + 1 > 256) {
+    return fail("%s: image width %ld exceeds one TMA box (255)", who, wd);
+  }
   p.y = reinterpret_cast<__nv_bfloat16*>(y);
   p.stats = stats;
+  p.bias = bias; p.bias_dtype = bias_dtype; p.relu = relu;
+  if ((bias || relu) && (dgrad || stats)) return fail("%s: bias / ReLU belong to the plain forward pass", who);
   const int block_n = k_out <= 64 ? 64 : (k_out <= 128 ? 128 : 256);
   p.num_n = (k_out + block_n - 1) / block_n;
   if (stats) {
@@ -694,19 +775,33 @@ int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, 
       return fail("%s: statistics buffer too small (%ld floats needed)", who, (long)need);
   }
   CUtensorMap mx, mw;
-  if (int rc = c3_map_nhwc(&mx, x, n, h, wd, c_red, p.Wp)) return rc;
+  memset(&mx, 0, sizeof(mx));
+  memset(&mw, 0, sizeof(mw));
+  if (!dry_run)
+    if (int rc = c3_map_nhwc(&mx, x, n, h, wd, c_red, p.Wp)) return rc;      // box: one stage row
   if (!dgrad) {
     // wt [k_out][9][c_red] as [k_out rows, 9*c_red cols]
-    if (int rc = c3_map_2d(&mw, w, k_out, 9 * c_red, block_n)) return rc;
-    if (block_n == 64) return launch_c3<64, 3, false>(mx, mw, p, nparts_out, stream);
-    if (block_n == 128) return launch_c3<128, 3, false>(mx, mw, p, nparts_out, stream);
-    return launch_c3<256, 1, false>(mx, mw, p, nparts_out, stream);
+    if (!dry_run)
+      if (int rc = c3_map_2d(&mw, w, k_out, 9 * c_red, block_n)) return rc;
+    if (block_n == 64) return launch_c3<64, 3, false>(mx, mw, p, nparts_out, stream, dry_run);
+    if (block_n == 128) {
+      // three taps per weight group (48 KB) when two groups fit next to the input stages, else one tap per group
+      if (launch_c3<128, 3, false>(mx, mw, p, nparts_out, stream, true) == 0)
+        return launch_c3<128, 3, false>(mx, mw, p, nparts_out, stream, dry_run);
+      return launch_c3<128, 1, false>(mx, mw, p, nparts_out, stream, dry_run);
+    }
+    return launch_c3<256, 1, false>(mx, mw, p, nparts_out, stream, dry_run);
   }
   // forward weight wf [c_red][9][k_out] as [c_red rows, 9*k_out cols]; boxes of 64 x 64
-  if (int rc = c3_map_2d(&mw, w, c_red, 9 * k_out, 64)) return rc;
-  if (block_n == 64) return launch_c3<64, 3, true>(mx, mw, p, nparts_out, stream);
-  if (block_n == 128) return launch_c3<128, 3, true>(mx, mw, p, nparts_out, stream);
-  return launch_c3<256, 1, true>(mx, mw, p, nparts_out, stream);
+  if (!dry_run)
+    if (int rc = c3_map_2d(&mw, w, c_red, 9 * k_out, 64)) return rc;
+  if (block_n == 64) return launch_c3<64, 3, true>(mx, mw, p, nparts_out, stream, dry_run);
+  if (block_n == 128) {
+    if (launch_c3<128, 3, true>(mx, mw, p, nparts_out, stream, true) == 0)
+      return launch_c3<128, 3, true>(mx, mw, p, nparts_out, stream, dry_run);
+    return launch_c3<128, 1, true>(mx, mw, p, nparts_out, stream, dry_run);
+  }
+  return launch_c3<256, 1, true>(mx, mw, p, nparts_out, stream, dry_run);
 }
 
 
@@ -797,6 +892,20 @@ size_t tb200_conv_stats_floats(int cout) { return (size_t)device_sm_count() * 4 
 int tb200_conv3x3_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, float* stats,
                         size_t stats_floats, int* nparts, cudaStream_t stream) {
   return conv3x3_common(x, w, y, n, h, wd, cin, cout, false, stats, stats_floats, nparts, stream);
+}
+
+// The same forward pass with a per-output-channel bias (bias_dtype TB200_F32 / TB200_BF16, may be NULL) and an
+// optional ReLU in the epilogue: the convolution layers of VGG / AlexNet.
+int tb200_conv3x3_fprop_bias(const void* x, const void* w, const void* bias, int bias_dtype, int relu, void* y, int n,
+                             int h, int wd, int cin, int cout, cudaStream_t stream) {
+  return conv3x3_common(x, w, y, n, h, wd, cin, cout, false, nullptr, 0, nullptr, stream, bias, bias_dtype, relu ? 1 : 0);
+}
+
+// 1 when tb200_conv3x3_fprop / _dgrad serve this geometry (channel multiples, one padded row per TMA box, two
+// input stages next to the weight ring in shared memory), without touching the GPU.
+int tb200_conv3x3_supported(int n, int h, int wd, int c_red, int k_out, int dgrad) {
+  return conv3x3_common(nullptr, nullptr, nullptr, n, h, wd, c_red, k_out, dgrad != 0, nullptr, 0, nullptr, nullptr,
+                        nullptr, 0, 0, true) == 0 ? 1 : 0;
 }
 
 int tb200_conv3x3_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout,

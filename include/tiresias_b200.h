@@ -198,6 +198,11 @@ int tb200_conv2d_fprop_stats(const void* x, const void* w, void* y, int n, int h
                              cudaStream_t stream);
 int tb200_conv3x3_fprop(const void* x, const void* w, void* y, int n, int h, int wd, int cin, int cout, float* stats,
                         size_t stats_floats, int* nparts, cudaStream_t stream);
+/* tb200_conv3x3_fprop with a per-output-channel bias (TB200_F32 / TB200_BF16; may be NULL) and an optional ReLU in
+ * the epilogue (VGG / AlexNet style layers), and a geometry query that runs no GPU work.                      */
+int tb200_conv3x3_fprop_bias(const void* x, const void* w, const void* bias, int bias_dtype, int relu, void* y, int n,
+                             int h, int wd, int cin, int cout, cudaStream_t stream);
+int tb200_conv3x3_supported(int n, int h, int wd, int c_red, int k_out, int dgrad);
 int tb200_conv3x3_dgrad(const void* dy, const void* w, void* dx, int n, int h, int wd, int cin, int cout,
                         cudaStream_t stream);
 /* Weight gradient of the same convolution on a halo-tile kernel: dw [cout][3][3][cin] bf16 from x [n,h,w,cin] and

@@ -14,7 +14,7 @@ from torch import nn
 
 from ..ops import native
 from ..ops.batchnorm import FusedBatchNormAct
-from ..ops.conv import GradBox, TcConv1x1, TcConv2d, _parse_ops, packed_stem_conv, park_skip_grad
+from ..ops.conv import GradBox, TcConv1x1, TcConv2d, TcConv3x3Bias, _parse_ops, packed_stem_conv, park_skip_grad
 from ..ops.linear import TcLinear
 from ..ops.pooling import MaxPool, MaxPool3x3S2
 
@@ -199,6 +199,9 @@ class VGG(nn.Module):
         for v in _VGG_CFG[depth]:
             if v == "M":
                 layers.append(MaxPool(2, 2) if fused else nn.MaxPool2d(2, 2))
+            elif fused and cin % 64 == 0 and v % 64 == 0:
+                layers.append(TcConv3x3Bias(cin, v, relu=True))      # bias + ReLU in the convolution's epilogue
+                cin = v
             else:
                 layers += [nn.Conv2d(cin, v, 3, 1, 1), nn.ReLU(inplace=True)]
                 cin = v
@@ -230,12 +233,16 @@ class AlexNet(nn.Module):
     def __init__(self, num_classes: int = 1000, fused: bool = True):
         super().__init__()
         pool = (lambda: MaxPool(3, 2)) if fused else (lambda: nn.MaxPool2d(3, 2))
+
+        def c3(cin, cout):
+            if fused:
+                return (TcConv3x3Bias(cin, cout, relu=True),)
+            return (nn.Conv2d(cin, cout, 3, 1, 1), nn.ReLU(inplace=True))
+
         self.features = nn.Sequential(
             nn.Conv2d(3, 64, 11, 4, 2), nn.ReLU(inplace=True), pool(),
             nn.Conv2d(64, 192, 5, 1, 2), nn.ReLU(inplace=True), pool(),
-            nn.Conv2d(192, 384, 3, 1, 1), nn.ReLU(inplace=True),
-            nn.Conv2d(384, 256, 3, 1, 1), nn.ReLU(inplace=True),
-            nn.Conv2d(256, 256, 3, 1, 1), nn.ReLU(inplace=True), pool())
+            *c3(192, 384), *c3(384, 256), *c3(256, 256), pool())
         self.fc6, self.fc7, self.fc8 = _classifier(256 * 6 * 6, num_classes, fused)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

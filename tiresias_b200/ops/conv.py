@@ -27,6 +27,7 @@ import os
 
 from . import native
 
+OWN_BIAS_CONV = os.environ.get("TB200_OWN_BIAS_CONV", "1") != "0"       # VGG / AlexNet 3x3 layers on our kernels
 HALO_WGRAD = os.environ.get("TB200_HALO_WGRAD", "1") != "0"             # A/B switch (bench only)
 FUSE_SKIP_GRAD = os.environ.get("TB200_FUSE_SKIP_GRAD", "1") != "0"     # A/B switch (bench only)
 
@@ -295,6 +296,70 @@ class TcConv2d(nn.Module):
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
                 f"stride={self.stride}, padding={self.padding}, tcgen05 implicit GEMM passes={sorted(self.ops)}")
+
+
+class _Conv3x3BiasActFn(torch.autograd.Function):
+    """``relu?(conv3x3(x, w) + b)`` for the VGG / AlexNet style layers: bias and ReLU in the halo-tile kernel's epilogue;
+    backward = ReLU mask on dy (element-wise), halo-tile dgrad and wgrad (im2col wgrad where the halo one does not
+    serve the geometry), bias gradient as a channel sum."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, relu: bool):
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        if not weight.is_contiguous(memory_format=torch.channels_last):
+            weight = weight.contiguous(memory_format=torch.channels_last)
+        y = native.conv3x3_fprop_bias(x, weight, bias, relu)
+        ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.relu = relu
+        return y
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        x, weight, y = ctx.saved_tensors
+        if ctx.relu:
+            dy = dy * (y > 0)
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = native.conv3x3_dgrad(dy, weight)
+        if ctx.needs_input_grad[1]:
+            if HALO_WGRAD and native.conv3x3_wgrad_eligible(x, weight.shape[0]):
+                dw = native.conv3x3_wgrad(x, dy)
+            else:
+                dw = native.conv2d_wgrad(x, dy, (3, 3), 1, 1)
+        if ctx.needs_input_grad[2]:
+            db = dy.sum(dim=(0, 2, 3), dtype=torch.float32).to(dy.dtype)
+        return dx, dw, db, None
+
+
+class TcConv3x3Bias(nn.Module):
+    """``nn.Conv2d(cin, cout, 3, 1, 1)`` (with bias) + optional ReLU on the halo-tile kernels. ``cin`` and ``cout``
+    multiples of 64. Same parameter names and shapes as Conv2d, so checkpoints and the flat parameter layout match the
+    stock network's; anything the kernels do not serve goes to ``F.conv2d`` (+ ``relu``)."""
+
+    def __init__(self, in_channels: int, out_channels: int, relu: bool = True):
+        super().__init__()
+        if in_channels % 64 or out_channels % 64:
+            raise ValueError("TcConv3x3Bias needs channel counts that are multiples of 64")
+        self.in_channels, self.out_channels, self.relu = in_channels, out_channels, relu
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, 3, 3))
+        self.bias = nn.Parameter(torch.zeros(out_channels))
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        bound = 1.0 / math.sqrt(in_channels * 9)
+        nn.init.uniform_(self.bias, -bound, bound)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if (x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16 and OWN_BIAS_CONV
+                and native.conv3x3_supported(x.shape[0], x.shape[2], x.shape[3], self.in_channels, self.out_channels)
+                and native.conv3x3_supported(x.shape[0], x.shape[2], x.shape[3], self.out_channels, self.in_channels, True)):
+            return _Conv3x3BiasActFn.apply(x, self.weight, self.bias, self.relu)
+        y = torch.nn.functional.conv2d(x, self.weight, self.bias, stride=1, padding=1)
+        return torch.relu(y) if self.relu else y
+
+    def extra_repr(self) -> str:
+        return f"{self.in_channels}, {self.out_channels}, kernel_size=(3, 3), bias, relu={self.relu}, tcgen05 halo tile"
 
 
 class _PackedStemFn(torch.autograd.Function):

@@ -129,6 +129,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_conv3x3_fprop.restype = ci
     lib.tb200_conv3x3_dgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, st]
     lib.tb200_conv3x3_dgrad.restype = ci
+    lib.tb200_conv3x3_fprop_bias.argtypes = [vp, vp, vp, ci, ci, vp, ci, ci, ci, ci, ci, st]
+    lib.tb200_conv3x3_fprop_bias.restype = ci
+    lib.tb200_conv3x3_supported.argtypes = [ci, ci, ci, ci, ci, ci]
+    lib.tb200_conv3x3_supported.restype = ci
     lib.tb200_conv3x3_wgrad_workspace.argtypes = [ci, ci, ci, ci, ci]
     lib.tb200_conv3x3_wgrad_workspace.restype = sz
     lib.tb200_conv3x3_wgrad.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp, sz, st]
@@ -446,6 +450,25 @@ def conv3x3_fprop(x: torch.Tensor, weight: torch.Tensor, stats: bool = False):
                                     C.byref(nparts), stream_ptr()))
     y = y.permute(0, 3, 1, 2)
     return (y, ConvStats(buf[: nparts.value], nparts.value, n * h * w)) if stats else y
+
+
+def conv3x3_supported(n: int, h: int, w: int, c_red: int, k_out: int, dgrad: bool = False) -> bool:
+    """Do the halo-tile kernels serve this 3x3 / stride 1 / pad 1 geometry (no GPU work)?"""
+    return lib().tb200_conv3x3_supported(n, h, w, c_red, k_out, int(dgrad)) == 1
+
+
+def conv3x3_fprop_bias(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], relu: bool) -> torch.Tensor:
+    """``relu?(conv3x3(x, weight) + bias)`` with bias and ReLU in the halo-tile kernel's epilogue."""
+    assert x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    xv, wv = _nhwc(x), _nhwc(weight)
+    n, h, w, cin = xv.shape
+    cout = wv.shape[0]
+    assert wv.shape[1:] == (3, 3, cin)
+    y = torch.empty((n, h, w, cout), dtype=torch.bfloat16, device=x.device)
+    bptr, bdt = (bias.data_ptr(), dtype_code(bias.dtype)) if bias is not None else (0, 0)
+    check(lib().tb200_conv3x3_fprop_bias(xv.data_ptr(), wv.data_ptr(), bptr, bdt, int(relu), y.data_ptr(), n, h, w, cin,
+                                         cout, stream_ptr()))
+    return y.permute(0, 3, 1, 2)
 
 
 def conv3x3_dgrad(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
