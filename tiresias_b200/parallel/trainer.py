@@ -179,6 +179,7 @@ class Trainer:
         self.comm_stream = torch.cuda.Stream(self.device)
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_failed = False
+        self._eager_steps = 0                    # eager steps run by THIS object (warm-up before capture)
         self._steps = 0
         self.native_per_step = 0
         self.native_launches = 0
@@ -513,7 +514,10 @@ class Trainer:
     def _advance(self) -> None:
         """Run one device-side step on ``self.stream`` (eager, or capture-then-replay)."""
         graphable = self.use_graph and (self.mode != "nccl" or self.nccl_same_compute) and not self._graph_failed
-        if graphable and self._graph is None and self._steps >= 3:
+        # three eager steps IN THIS PROCESS first (a resumed job restores `_steps` but has run nothing here yet:
+        # first calls bind contexts, set function attributes and size workspaces, none of which may happen
+        # inside a capture - profiles/replay_r2/README.md)
+        if graphable and self._graph is None and self._eager_steps >= 3:
             torch.cuda.synchronize(self.device)
             self.symm.barrier()
             before = native.launch_count()
@@ -531,6 +535,7 @@ class Trainer:
         else:
             before = native.launch_count()
             self._device_step()
+            self._eager_steps += 1
             self.native_per_step = native.launch_count() - before
             self.native_launches += self.native_per_step
         self._steps += 1
@@ -670,6 +675,7 @@ class Trainer:
                         dist.all_gather_into_tensor(self.param_flat[b.offset: b.offset + b.length], shard,
                                                     group=self.comm_group)
         self._graph = None                       # captured before the restore: re-capture on the new state
+        self._eager_steps = 0
         torch.cuda.synchronize(self.device)
         self.symm.barrier()
         self.stream.wait_stream(torch.cuda.current_stream(self.device))
