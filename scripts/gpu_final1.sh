@@ -1,0 +1,19 @@
+#!/bin/bash
+# Final 1-GPU call of the round: the whole GPU suite, smoke(), the bench line, co-location through streams, ncu captures.
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -q -x --timeout 300 --timeout-method thread > gpurun_out/final_tests.log 2>&1
+echo "== pytest -m gpu exit $?"; tail -n 8 gpurun_out/final_tests.log | cut -c1-300
+timeout 200 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/final_smoke.log 2>&1; echo "== smoke exit $?"; tail -n 2 gpurun_out/final_smoke.log | cut -c1-300
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/final_bench.log 2>&1
+echo "== bench exit $?"; tail -n 1 gpurun_out/final_bench.log | python -c "
+import sys, json
+d = json.loads(sys.stdin.read())
+print('ours', d['ms_per_step'], d['value'], 'e2e', d['e2e'], 'launches', d['gpu_launches'])
+for k in ('nccl_same_compute', 'nccl_baseline'):
+    if k in d: print(k, {a: b for a, b in d[k].items() if a != 'what'})
+print('sim', [(c['config'], c.get('speedup_wall'), c.get('cluster_csv_identical')) for c in d.get('sim', {}).get('cases', [])])
+print('clocks', d.get('clocks'))
+" || tail -3 gpurun_out/final_bench.log | cut -c1-300
+timeout 300 python -m tiresias_b200.calib.interference --models vgg16,transformer --share streams --out gpurun_out/interference_streams.json > gpurun_out/final_interference.log 2>&1
+echo "== interference (streams) exit $?"; tail -n 4 gpurun_out/final_interference.log | cut -c1-400
+KERNELS="${KERNELS:-pair8k wgrad_halo2 attn bn_bits}" bash scripts/gpu_ncu.sh | tail -12
