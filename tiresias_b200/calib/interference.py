@@ -69,18 +69,20 @@ def run_group_streams(models: Sequence[str], gpu: int, batch: int, iters: int, m
     dev = torch.device("cuda", gpu)
     n = len(models)
     ready, go = threading.Barrier(n), threading.Barrier(n)
+    setup = threading.Lock()                    # model build, allocator growth and graph capture one tenant at a time
     out: List[Optional[Dict]] = [None] * n
     errs: List[str] = []
 
     def body(i: int, name: str) -> None:
         try:
             torch.cuda.set_device(gpu)
-            spec = zoo.resolve(name)
-            tr = Trainer(spec, batch, mode=mode, use_graph=True, device=dev)
-            x, y = zoo.synthetic_batch(spec, batch, seed=i)
-            for _ in range(6):                  # allocator growth, graph capture (eager steps serialise on the
-                tr.step(x, y)                   # autograd thread; the timed replays below do not)
-            tr.loss()
+            with setup:
+                spec = zoo.resolve(name)
+                tr = Trainer(spec, batch, mode=mode, use_graph=True, device=dev)
+                x, y = zoo.synthetic_batch(spec, batch, seed=i)
+                for _ in range(6):              # allocator growth, graph capture (eager steps serialise on the
+                    tr.step(x, y)               # autograd thread; the timed replays below do not)
+                tr.loss()
             ready.wait()
             start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             go.wait()

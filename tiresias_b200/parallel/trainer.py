@@ -31,6 +31,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Tuple
 
@@ -41,6 +42,8 @@ from ..models.zoo import ModelSpec, build as zoo_build
 from ..ops import native
 from ..ops.linear import TcLinear
 from .symm import SymmetricWorld
+
+_CAPTURE_LOCK = threading.Lock()
 
 # largest per-GPU activation (rows) for which a row-sharded weight is pulled inside its GEMM instead of being
 # broadcast by the push kernel (see Trainer.__init__); measured cut-off, profiles/comm_pull_r2.md
@@ -507,9 +510,12 @@ class Trainer:
         return out
 
     def _capture(self) -> None:
-        self._graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self._graph, stream=self.stream):
-            self._device_step()
+        # Jobs that share a GPU live in threads of one process (exec/worker.py, calib/interference.py): captures are
+        # serialised, and thread-local capture mode keeps the other tenants' CUDA calls legal while one captures.
+        with _CAPTURE_LOCK:
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph, stream=self.stream, capture_error_mode="thread_local"):
+                self._device_step()
 
     def _advance(self) -> None:
         """Run one device-side step on ``self.stream`` (eager, or capture-then-replay)."""
