@@ -28,6 +28,9 @@ import os
 from . import native
 
 OWN_BIAS_CONV = os.environ.get("TB200_OWN_BIAS_CONV", "1") != "0"       # VGG / AlexNet 3x3 layers on our kernels
+# widest image those layers take on our kernels (wider: segment-mode tiles and the im2col wgrad, measured slower than
+# cuDNN on VGG-16's 224- and 112-pixel layers - profiles/bench_vgg16_r2f.md)
+BIAS_CONV_MAX_W = int(os.environ.get("TB200_BIAS_CONV_MAX_W", "56"))
 HALO_WGRAD = os.environ.get("TB200_HALO_WGRAD", "1") != "0"             # A/B switch (bench only)
 FUSE_SKIP_GRAD = os.environ.get("TB200_FUSE_SKIP_GRAD", "1") != "0"     # A/B switch (bench only)
 
@@ -352,6 +355,7 @@ class TcConv3x3Bias(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if (x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16 and OWN_BIAS_CONV
+                and x.shape[3] <= BIAS_CONV_MAX_W
                 and native.conv3x3_supported(x.shape[0], x.shape[2], x.shape[3], self.in_channels, self.out_channels)
                 and native.conv3x3_supported(x.shape[0], x.shape[2], x.shape[3], self.out_channels, self.in_channels, True)):
             return _Conv3x3BiasActFn.apply(x, self.weight, self.bias, self.relu)
