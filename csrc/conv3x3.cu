@@ -401,6 +401,318 @@ conv3x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant_
 
 
 // =========================================================================================================
+// The same convolution on CTA pairs (cta_group::2) for 256 output channels per tile: a pair computes TWO consecutive
+// position tiles (UMMA M = 256, each CTA its own 128 positions and its own halo stage) against ONE weight tile of
+// which each CTA stages half (128 of the 256 output channels per tap and 64-channel block): the weight traffic
+// per SM - the bound of the 256- and 512-channel layers, which re-fetch 2.3 MB of weights per 128-position tile
+// (profiles/conv_r2.md) - halves. Plain per-CTA TMA loads; the MMA, its commit and the accumulator hand-back are the
+// only cluster-wide operations. Both CTAs place their tile's first position at the SAME stage offset (2 * Wp rows:
+// the rows are loaded shifted by up to Wp - 1 rows), because one MMA instruction carries one A descriptor.
+template <bool DGRAD>
+__global__ void __launch_bounds__(kC3Threads, 1)
+conv3x3_pair_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w, const C3Params p) {
+  constexpr int BLOCK_N = 256;
+  constexpr int kTileBytes = 128 * 128;                   // this CTA's half of one (tap, 64-channel block) weight tile
+  constexpr int kTmemCols = kC3Acc * BLOCK_N;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  const uint32_t a_smem = base;
+  const uint32_t b_smem = base + (uint32_t)(p.a_stages * p.a_stage_bytes);
+  const uint32_t epi_smem = base + (uint32_t)p.epi_off;
+  const uint32_t bar = base + (uint32_t)p.bar_off;
+  auto a_full = [&](int s) { return bar + 8u * s; };                         // leader's are the live ones
+  auto a_empty = [&](int s) { return bar + 8u * (p.a_stages + s); };         // per CTA
+  auto b_full = [&](int s) { return bar + 8u * (2 * p.a_stages + s); };      // leader's
+  auto b_empty = [&](int s) { return bar + 8u * (2 * p.a_stages + p.b_groups + s); };
+  const uint32_t t_base = bar + 8u * (2 * p.a_stages + 2 * p.b_groups);
+  auto t_full = [&](int s) { return t_base + 8u * s; };                      // per CTA
+  auto t_empty = [&](int s) { return t_base + 8u * (kC3Acc + s); };          // leader's
+  const uint32_t tmem_slot = t_base + 8u * 2 * kC3Acc;
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const uint32_t rank = cluster_ctarank();
+  const int pair_id = blockIdx.x / 2, num_pairs = gridDim.x / 2;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_x);
+    prefetch_tensormap(&map_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.a_stages; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
+    for (int s = 0; s < p.b_groups; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
+    for (int s = 0; s < kC3Acc; ++s) { mbar_init(t_full(s), 1); mbar_init(t_empty(s), 8); }
+    mbar_init_fence();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - base));
+
+  const int pm = (p.num_m + 1) / 2;                       // pairs of position tiles
+  const int items = pm * p.num_n;
+  const uint32_t row_bytes = (uint32_t)p.Wp * 128u;
+  const uint32_t fixed_rows = p.seg ? (uint32_t)(p.Wp + 1) : (uint32_t)(2 * p.Wp);   // stage row of the tile's first position
+
+  if (warp == 0) {
+    // ================= producer (both CTAs) =================
+    int as = 0, bg = 0;
+    uint32_t aph = 0, bph = 0;
+    for (int it = pair_id; it < items; it += num_pairs) {
+      const int m_tile = 2 * (it % pm) + (int)rank, n_blk = it / pm;
+      const uint32_t q0 = (uint32_t)m_tile * 128u;
+      const int rho0 = (int)fastdiv(q0 + (uint32_t)p.Wp - 1u, p.mWp) - 2;
+      const uint32_t woff = (uint32_t)((int)q0 - rho0 * p.Wp);               // in [Wp + 1, 2 * Wp]
+      const uint32_t srow = fastdiv((uint32_t)m_tile, p.mSeg), sseg = (uint32_t)m_tile - srow * (uint32_t)p.nseg;
+      const uint32_t sn = fastdiv(srow, p.mH), sh = srow - sn * (uint32_t)p.H;
+      for (int cb = 0; cb < p.cblocks; ++cb) {
+        mbar_wait(a_empty(as), aph ^ 1);
+        if (elect_one()) {
+          const uint32_t fb = mapa(a_full(as), 0);
+          if (rank == 0) mbar_expect_tx(a_full(as), 2u * (uint32_t)p.NR * row_bytes);
+          if (p.seg) {
+            uint32_t dst = a_smem + (uint32_t)as * p.a_stage_bytes;
+            for (int i = 0; i < 3; ++i) {
+              tma_load_4d_pair(dst, &map_x, fb, cb * 64, (int)sseg * 128 - 1, (int)sh - 1 + i, (int)sn);
+              dst += row_bytes;
+            }
+          } else {
+            int n, hp;
+            if (rho0 < 0) { n = -1; hp = rho0 + p.Hp; }
+            else { n = (int)fastdiv((uint32_t)rho0, p.mHp); hp = rho0 - n * p.Hp; }
+            // shifted so that the tile's first position sits 2 * Wp rows into the stage in BOTH CTAs
+            uint32_t dst = a_smem + (uint32_t)as * p.a_stage_bytes + ((uint32_t)(2 * p.Wp) - woff) * 128u;
+            for (int i = 0; i < p.NR; ++i) {
+              tma_load_4d_pair(dst, &map_x, fb, cb * 64, 0, hp, n);
+              dst += row_bytes;
+              if (++hp == p.Hp) { hp = 0; ++n; }
+            }
+          }
+        }
+        __syncwarp();
+        if (++as == p.a_stages) { as = 0; aph ^= 1; }
+#pragma unroll 1
+        for (int t = 0; t < 9; ++t) {
+          mbar_wait(b_empty(bg), bph ^ 1);
+          if (elect_one()) {
+            const uint32_t fb = mapa(b_full(bg), 0);
+            if (rank == 0) mbar_expect_tx(b_full(bg), 2u * kTileBytes);
+            const uint32_t dst = b_smem + (uint32_t)bg * kTileBytes;
+            if constexpr (!DGRAD) {
+              // wt [k_out][9][c_red]: this CTA's 128 of the tile's 256 output channels (box {64 c, 128 k})
+              tma_load_2d_pair(dst, &map_w, fb, t * p.C + cb * 64, n_blk * BLOCK_N + (int)rank * 128);
+            } else {
+              // forward weight wf [c_red][9][k_out]: two MN-major slabs {64 k_out, 64 c_red}
+#pragma unroll
+              for (int sl = 0; sl < 2; ++sl)
+                tma_load_2d_pair(dst + sl * 8192, &map_w, fb, (8 - t) * p.K + n_blk * BLOCK_N + (int)rank * 128 + sl * 64,
+                                 cb * 64);
+            }
+          }
+          __syncwarp();
+          if (++bg == p.b_groups) { bg = 0; bph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (leader CTA) =================
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(256, BLOCK_N, 0, DGRAD ? 1 : 0);
+      constexpr uint64_t kBDesc = DGRAD ? kDescMNMajor : kDescKMajor;
+      constexpr uint32_t kBStep = DGRAD ? 128u : 2u;
+      const int wp8 = p.Wp * 8;
+      int as = 0, bg = 0, acc = 0;
+      uint32_t aph = 0, bph = 0, accph = 0;
+      for (int it = pair_id; it < items; it += num_pairs) {
+        mbar_wait(t_empty(acc), accph ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BLOCK_N);
+        uint32_t accumulate = 0;
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          mbar_wait(a_full(as), aph);
+          tc_fence_after();
+          const uint32_t a_mid = desc_units(a_smem + (uint32_t)as * p.a_stage_bytes) + fixed_rows * 8u;
+#pragma unroll
+          for (int t = 0; t < 9; ++t) {
+            mbar_wait(b_full(bg), bph);
+            tc_fence_after();
+            const int r = t / 3, s2 = t % 3;
+            const uint64_t adesc = kDescKMajor | (uint64_t)(a_mid + (uint32_t)((r - 1) * wp8 + (s2 - 1) * 8));
+            const uint64_t bdesc = kBDesc | (uint64_t)desc_units(b_smem + (uint32_t)bg * kTileBytes);
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tc_mma2_bf16(tmem_d, adesc + 2u * k, bdesc + kBStep * k, idesc, (k == 0) ? accumulate : 1u);
+              tc_commit2(b_empty(bg));
+            }
+            __syncwarp();
+            accumulate = 1;
+            if (++bg == p.b_groups) { bg = 0; bph ^= 1; }
+          }
+          if (elect_one()) tc_commit2(a_empty(as));
+          __syncwarp();
+          if (++as == p.a_stages) { as = 0; aph ^= 1; }
+        }
+        if (elect_one()) tc_commit2(t_full(acc));
+        __syncwarp();
+        if (++acc == kC3Acc) { acc = 0; accph ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue =================
+    // Warp ew owns tile rows [32*ew, +32); lane = row for the TMEM loads. Per 64 output channels:
+    // TMEM -> registers -> bf16 -> swizzled staging tile (32 rows x 128 B) -> (statistics from the staged
+    // bf16 values) -> coalesced 16-byte global stores of the valid rows (4 rows x 128 B per instruction).
+    const int ew = warp - 4;
+    int acc = 0;
+    uint32_t accph = 0;
+    const uint32_t bufs = epi_smem + (uint32_t)(ew * 2) * 4096u;
+    const uint32_t swz = (uint32_t)(lane & 7);
+    constexpr int kChunks = BLOCK_N / 64;
+    float st[kChunks][4];
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
+    int cur_n = -1;
+    // this warp's copy of the n block's bias row (fp32), refilled when the n block changes
+    float* bias_row = reinterpret_cast<float*>(smem_raw + p.bias_off) + ew * 256;
+    int bias_n = -1;
+    auto flush_stats = [&](int n_blk) {
+      const size_t part = (size_t)blockIdx.x * 4 + ew;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        const int k = n_blk * BLOCK_N + c * 64 + 2 * lane;
+        if (k < p.K)
+          *reinterpret_cast<float4*>(p.stats + (part * p.K + k) * 2) = make_float4(st[c][0], st[c][1], st[c][2], st[c][3]);
+        st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
+      }
+    };
+    for (int it = pair_id; it < items; it += num_pairs) {
+      const int m_tile = 2 * (it % pm) + (int)rank, n_blk = it / pm;
+      if (p.stats && n_blk != cur_n) {
+        if (cur_n >= 0) flush_stats(cur_n);
+        cur_n = n_blk;
+      }
+      if (p.bias && n_blk != bias_n) {
+        __syncwarp();
+        for (int j = lane; j < BLOCK_N; j += 32) {
+          const int k = n_blk * BLOCK_N + j;
+          float b = 0.f;
+          if (k < p.K)
+            b = p.bias_dtype == TB200_F32 ? reinterpret_cast<const float*>(p.bias)[k]
+                                          : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[k]);
+          bias_row[j] = b;
+        }
+        __syncwarp();
+        bias_n = n_blk;
+      }
+      // this lane's row: flat padded position -> (image, row, column); junk positions get pix = -1
+      const uint32_t q = (uint32_t)m_tile * 128u + (uint32_t)(ew * 32 + lane);
+      bool valid;
+      int pix;
+      if (p.seg) {
+        const uint32_t srow = fastdiv((uint32_t)m_tile, p.mSeg), sseg = (uint32_t)m_tile - srow * (uint32_t)p.nseg;
+        const uint32_t wcol = sseg * 128u + (uint32_t)(ew * 32 + lane);
+        valid = wcol < (uint32_t)p.W && m_tile < p.num_m;     // (an odd tile count leaves the last pair's second tile empty)
+        pix = valid ? (int)(srow * (uint32_t)p.W + wcol) : -1;        // srow = image * H + row
+      } else {
+        const uint32_t rho = fastdiv(q, p.mWp), j = q - rho * (uint32_t)p.Wp;
+        const uint32_t n = fastdiv(rho, p.mHp), h = rho - n * (uint32_t)p.Hp;
+        valid = q < (uint32_t)p.total_pos && j < (uint32_t)p.W && h < (uint32_t)p.H;
+        pix = valid ? (int)((n * (uint32_t)p.H + h) * (uint32_t)p.W + j) : -1;
+      }
+      const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+      mbar_wait(t_full(acc), accph);
+      tc_fence_after();
+      const uint32_t tcol = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BLOCK_N);
+      int nchunks = (p.K - n_blk * BLOCK_N + 63) / 64;
+      if (nchunks > kChunks) nchunks = kChunks;
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c) {
+        if (c < nchunks) {
+          const int k0 = n_blk * BLOCK_N + c * 64;
+          uint32_t v[64];
+          tc_ld_32x32(tcol + c * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          tc_ld_32x32(tcol + c * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          tc_ld_wait();
+          if (c == nchunks - 1) {
+            // the accumulator has been read: hand the TMEM stage back before the stores
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa(t_empty(acc), 0));
+          }
+          if (p.bias) {
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+              const float4 b4 = *reinterpret_cast<const float4*>(bias_row + c * 64 + 4 * u);
+              v[4 * u] = __float_as_uint(__uint_as_float(v[4 * u]) + b4.x);
+              v[4 * u + 1] = __float_as_uint(__uint_as_float(v[4 * u + 1]) + b4.y);
+              v[4 * u + 2] = __float_as_uint(__uint_as_float(v[4 * u + 2]) + b4.z);
+              v[4 * u + 3] = __float_as_uint(__uint_as_float(v[4 * u + 3]) + b4.w);
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) v[j] = __float_as_uint(fmaxf(__uint_as_float(v[j]), 0.f));
+          }
+          const uint32_t buf = bufs + (uint32_t)(c & 1) * 4096u;
+          __syncwarp();                                    // readers of this staging tile (chunk c-2) are done
+          const uint32_t row_addr = buf + (uint32_t)lane * 128u;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(v[8 * u]), __uint_as_float(v[8 * u + 1]));
+            o.y = pack_bf16(__uint_as_float(v[8 * u + 2]), __uint_as_float(v[8 * u + 3]));
+            o.z = pack_bf16(__uint_as_float(v[8 * u + 4]), __uint_as_float(v[8 * u + 5]));
+            o.w = pack_bf16(__uint_as_float(v[8 * u + 6]), __uint_as_float(v[8 * u + 7]));
+            st_shared_16(row_addr + (((uint32_t)u ^ swz) << 4), o);
+          }
+          __syncwarp();
+          if (p.stats) {
+            // lane l sums channels k0 + 2l, +1 over the valid rows: word l of every staged row
+            const uint32_t col = (uint32_t)(lane >> 2), wsel = (uint32_t)(lane & 3) * 4u;
+            // packed fp32x2 arithmetic (FADD2 / FFMA2); junk rows are zeroed by a select, not branched around
+            float2 sum2 = make_float2(st[c][0], st[c][2]), sq2 = make_float2(st[c][1], st[c][3]);
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) {
+              uint32_t w = ld_shared_4(buf + (uint32_t)rr * 128u + ((col ^ (uint32_t)(rr & 7)) << 4) + wsel);
+              w = ((vmask >> rr) & 1u) ? w : 0u;
+              const float2 v = make_float2(bf16_lo(w), bf16_hi(w));
+              sum2 = __fadd2_rn(sum2, v);
+              sq2 = __ffma2_rn(v, v, sq2);
+            }
+            st[c][0] = sum2.x; st[c][2] = sum2.y; st[c][1] = sq2.x; st[c][3] = sq2.y;
+          }
+          // stores: lane -> (row (lane/8) + 4i, 16-byte unit lane%8)
+          const bool unit_ok = k0 + (int)swz * 8 < p.K;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = (lane >> 3) + 4 * i;
+            const int pr = __shfl_sync(0xffffffffu, pix, rr);
+            const uint4 o = ld_shared_16(buf + (uint32_t)rr * 128u + ((swz ^ (uint32_t)(rr & 7)) << 4));
+            if (pr >= 0 && unit_ok)
+              *reinterpret_cast<uint4*>(p.y + (size_t)pr * p.K + k0 + swz * 8) = o;
+          }
+        }
+      }
+      if (++acc == kC3Acc) { acc = 0; accph ^= 1; }
+    }
+    if (p.stats && cur_n >= 0) flush_stats(cur_n);
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+  }
+}
+
+// =========================================================================================================
 // Weight gradient of the same convolution, also as a halo-tile implicit GEMM:
 //   dW[co, r, s, ci] = sum over positions q of dy[q, co] * x[q + (r-1)*(W+1) + (s-1), ci]
 // in the flat padded space used above (dy is zero at the shared pad column / row because its loads are
@@ -720,6 +1032,69 @@ int launch_c3(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* npa
   return launched();
 }
 
+// SM count, or `dflt` where no device is present (geometry queries on a CPU-only host)
+int device_sm_count_or(int dflt) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return dflt; }
+  return device_sm_count();
+}
+
+// TB200_CONV_PAIR=0 keeps the 256-wide tiles on the one-CTA kernel (A/B runs)
+bool conv_pair_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TB200_CONV_PAIR");
+    v = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return v == 1;
+}
+
+template <bool DGRAD>
+int launch_c3_pair(const CUtensorMap& mx, const CUtensorMap& mw, C3Params p, int* nparts_out, cudaStream_t stream,
+                   bool dry_run) {
+  constexpr int kSmemMax = 227 * 1024;
+  constexpr int kTile = 128 * 128;
+  const int row_bytes = p.Wp * 128;
+  const int rows = p.seg ? 3 : p.NR + 1;                 // flat mode: the rows land shifted by up to Wp - 1 rows
+  p.a_stage_bytes = (rows * row_bytes + 1023) / 1024 * 1024;
+  const int fixed = kEpiBytes + 1024 + 4096;
+  p.resident = 0;
+  p.a_stages = 2;
+  p.b_groups = (kSmemMax - fixed - 2 * p.a_stage_bytes) / kTile;
+  if (p.b_groups > 8) p.b_groups = 8;
+  if (p.b_groups < 3) return fail("tb200_conv3x3 (pair): tile does not fit shared memory (W %s%ld)", "", p.W);
+  const int b_bytes = p.b_groups * kTile;
+  p.a_stages = (kSmemMax - fixed - b_bytes) / p.a_stage_bytes;
+  if (p.a_stages > 3) p.a_stages = 3;
+  p.epi_off = p.a_stages * p.a_stage_bytes + b_bytes;
+  p.bar_off = p.epi_off + kEpiBytes;
+  p.bias_off = p.bar_off + 1024;
+  const int total = p.bias_off + 4096;
+  if (dry_run) return 0;
+  auto kern = conv3x3_pair_kernel<DGRAD>;
+  static DeviceOnce configured;
+  if (int rc = ensure_dynamic_smem(configured, kern, kSmemMax)) return rc;
+  const int sms = device_sm_count();
+  const int items = ((p.num_m + 1) / 2) * p.num_n;
+  const int pairs = items < sms / 2 ? items : sms / 2;
+  if (p.stats) {
+    TB_CUDA_OK(cudaMemsetAsync(p.stats, 0, (size_t)(2 * pairs) * 4 * p.K * 2 * sizeof(float), stream));
+    if (nparts_out) *nparts_out = 2 * pairs * 4;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kC3Threads);
+  cfg.dynamicSmemBytes = (size_t)total;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  TB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, mx, mw, p));
+  return launched();
+}
+
 int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, int c_red, int k_out, bool dgrad,
                    float* stats, size_t stats_floats, int* nparts_out, cudaStream_t stream, const void* bias = nullptr,
                    int bias_dtype = 0, int relu = 0, bool dry_run = false) {
@@ -781,8 +1156,11 @@ int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, 
     if (int rc = c3_map_nhwc(&mx, x, n, h, wd, c_red, p.Wp)) return rc;      // box: one stage row
   if (!dgrad) {
     // wt [k_out][9][c_red] as [k_out rows, 9*c_red cols]
+    const bool pair = block_n == 256 && conv_pair_enabled() && device_sm_count_or(148) >= 2 &&
+                      launch_c3_pair<false>(mx, mw, p, nparts_out, stream, true) == 0;
     if (!dry_run)
-      if (int rc = c3_map_2d(&mw, w, k_out, 9 * c_red, block_n)) return rc;
+      if (int rc = c3_map_2d(&mw, w, k_out, 9 * c_red, pair ? 128 : block_n)) return rc;
+    if (pair) return launch_c3_pair<false>(mx, mw, p, nparts_out, stream, dry_run);
     if (block_n == 64) return launch_c3<64, 3, false>(mx, mw, p, nparts_out, stream, dry_run);
     if (block_n == 128) {
       // three taps per weight group (48 KB) when two groups fit next to the input stages, else one tap per group
@@ -795,6 +1173,9 @@ int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, 
   // forward weight wf [c_red][9][k_out] as [c_red rows, 9*k_out cols]; boxes of 64 x 64
   if (!dry_run)
     if (int rc = c3_map_2d(&mw, w, c_red, 9 * k_out, 64)) return rc;
+  if (block_n == 256 && conv_pair_enabled() && device_sm_count_or(148) >= 2 &&
+      launch_c3_pair<true>(mx, mw, p, nparts_out, stream, true) == 0)
+    return launch_c3_pair<true>(mx, mw, p, nparts_out, stream, dry_run);
   if (block_n == 64) return launch_c3<64, 3, true>(mx, mw, p, nparts_out, stream, dry_run);
   if (block_n == 128) {
     if (launch_c3<128, 3, true>(mx, mw, p, nparts_out, stream, true) == 0)

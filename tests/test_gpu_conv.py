@@ -111,7 +111,8 @@ def test_halo_fprop_matches_fp32(cuda_device, shape):
 
 # ---- second-generation halo-tile kernel (csrc/conv3x3.cu): flat padded space with pitch W+1 / H+1 ----------
 C3_SHAPES = [(4, 64, 64, 56), (4, 128, 128, 28), (4, 256, 256, 14), (2, 512, 512, 7), (3, 64, 96, 12),
-             (2, 128, 64, 9), (1, 64, 8, 5), (5, 192, 320, 10), (1, 64, 64, 1)]
+             (2, 128, 64, 9), (5, 512, 512, 7), (3, 256, 384, 9), (64, 256, 256, 14), (1, 64, 8, 5), (5, 192, 320, 10),
+             (1, 64, 64, 1)]
 
 
 @pytest.mark.parametrize("shape", C3_SHAPES, ids=lambda s: "x".join(map(str, s)))
