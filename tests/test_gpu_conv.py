@@ -316,7 +316,7 @@ def test_bias_conv_module_matches_torch(cuda_device):
     from tiresias_b200.ops.conv import TcConv3x3Bias
     torch.manual_seed(4)
     mod = TcConv3x3Bias(64, 128, relu=True).to(cuda_device).to(torch.bfloat16).to(memory_format=torch.channels_last)
-    x = torch.randn(4, 64, 112, 112, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    x = torch.randn(4, 64, 56, 56, device=cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     xa = x.clone().requires_grad_(True)
     y = mod(xa)
     assert type(y.grad_fn).__name__ == "_Conv3x3BiasActFnBackward"
