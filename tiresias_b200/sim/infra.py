@@ -207,6 +207,9 @@ class Node:
         self.placed_jobs: Dict[str, object] = {}
         self.finished_tasks: List[str] = []
         self.interference_factor = FACTOR
+        # tasks resident on this node's devices, summed over devices (every device mutation goes through the three
+        # Node methods below): `devices_empty()` lets the placement memoise the scoring of untouched nodes
+        self._dev_tasks = 0
 
     # -- counters ---------------------------------------------------------------------------------
     def get_network_usage(self):
@@ -233,6 +236,9 @@ class Node:
     def is_idle(self) -> bool:
         return not (self.running_tasks or self.placed_tasks or self.placed_jobs)
 
+    def devices_empty(self) -> bool:
+        return self._dev_tasks == 0
+
     def get_free_devices(self, pack: bool) -> int:
         if pack:
             return len(self.device_cache)
@@ -245,6 +251,7 @@ class Node:
         self.cpu_used, self.mem_used = num * cpu, num * mem
         for d in self.device_cache.values():
             d.reset()
+        self._dev_tasks = 0
 
     # -- capacity questions -------------------------------------------------------------------------
     def can_fit_num_task(self, tasks, pack: bool = False) -> int:
@@ -307,8 +314,11 @@ class Node:
         for d in self.device_cache.values():
             if missing <= 0:
                 break
+            new = task.task_id not in d.running_tasks
             if d.add_task(task, pack=pack):
                 missing -= 1
+                if new:
+                    self._dev_tasks += 1
         if missing == 0:
             self.placed_tasks[task.task_id] = task
         return missing == 0
@@ -365,6 +375,7 @@ class Node:
         for d in self.device_cache.values():
             if task.task_id in d.running_tasks:
                 d.pop_task(task.task_id)
+                self._dev_tasks -= 1
             if len(d.running_tasks) <= 1:
                 for t in d.running_tasks.values():
                     if t.interfered:
