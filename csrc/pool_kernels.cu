@@ -31,88 +31,111 @@ struct PoolShape {
   int N, H, W, C, OH, OW, vecC;
 };
 
-// One thread per (n, oh, ow, 8 channels). Also records, per channel, which of the K*K window positions
+// Forward: a CTA walks output rows (n, oh); its threads cover the row's (ow, 8-channel vector) pairs, so all index
+// arithmetic is 32-bit and per row (the first version decoded a 64-bit linear index per element: the divisions, not
+// the memory system, bounded it at 43 % of the DRAM roofline). Records, per channel, which of the K*K window positions
 // (kh*K + kw) held the first maximum: one byte per output element, the backward's only bookkeeping.
 template <int K, int S, int P>
 __global__ void __launch_bounds__(kPoolThreads) maxpool_fwd_kernel(const uint4* __restrict__ x,
                                                                    uint4* __restrict__ out,
                                                                    uint2* __restrict__ argmax, PoolShape s) {
-  const size_t total = (size_t)s.N * s.OH * s.OW * s.vecC;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const int v = (int)(i % s.vecC);
-    size_t t = i / s.vecC;
-    const int ow = (int)(t % s.OW); t /= s.OW;
-    const int oh = (int)(t % s.OH);
-    const int n = (int)(t / s.OH);
-    float m[8];
-    uint32_t pos[8];
+  const int rows = s.N * s.OH, per_row = s.OW * s.vecC;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int n = row / s.OH, oh = row - n * s.OH;
+    const uint4* xin = x + (size_t)n * s.H * s.W * s.vecC;
+    for (int e = threadIdx.x; e < per_row; e += kPoolThreads) {
+      const int ow = e / s.vecC, v = e - ow * s.vecC;
+      float m[8];
+      uint32_t pos[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { m[k] = -INFINITY; pos[k] = 0; }
+      for (int k = 0; k < 8; ++k) { m[k] = -INFINITY; pos[k] = 0; }
+      // all window loads first (independent), then the comparisons
+      uint4 win[K * K];
+      bool ok[K * K];
 #pragma unroll
-    for (int kh = 0; kh < K; ++kh) {
-      const int h = oh * S - P + kh;
-      if (h < 0 || h >= s.H) continue;
+      for (int kh = 0; kh < K; ++kh) {
+        const int h = oh * S - P + kh;
 #pragma unroll
-      for (int kw = 0; kw < K; ++kw) {
-        const int w = ow * S - P + kw;
-        if (w < 0 || w >= s.W) continue;
+        for (int kw = 0; kw < K; ++kw) {
+          const int w = ow * S - P + kw;
+          ok[kh * K + kw] = h >= 0 && h < s.H && w >= 0 && w < s.W;
+          if (ok[kh * K + kw]) win[kh * K + kw] = ld_stream_16(xin + ((size_t)h * s.W + w) * s.vecC + v);
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < K * K; ++t) {
+        if (!ok[t]) continue;
         float f[8];
-        unpack8(ld_stream_16(x + (((size_t)n * s.H + h) * s.W + w) * s.vecC + v), f);
+        unpack8(win[t], f);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          if (f[k] > m[k]) { m[k] = f[k]; pos[k] = kh * K + kw; }     // strict: the first maximum wins
+          if (f[k] > m[k]) { m[k] = f[k]; pos[k] = t; }              // strict: the first maximum wins
       }
+      const size_t o = (size_t)row * per_row + e;
+      out[o] = pack8(m);
+      if (argmax)
+        argmax[o] = make_uint2(pos[0] | (pos[1] << 8) | (pos[2] << 16) | (pos[3] << 24),
+                               pos[4] | (pos[5] << 8) | (pos[6] << 16) | (pos[7] << 24));
     }
-    out[i] = pack8(m);
-    if (argmax)
-      argmax[i] = make_uint2(pos[0] | (pos[1] << 8) | (pos[2] << 16) | (pos[3] << 24),
-                             pos[4] | (pos[5] << 8) | (pos[6] << 16) | (pos[7] << 24));
   }
 }
 
-// One thread per (n, h, w, 8 channels) of the INPUT: gathers from the (at most ceil(K/S)^2) windows that
-// contain the element. No atomics, deterministic; DRAM traffic = dout + argmax read once, dx written once.
+// Backward: a CTA walks INPUT rows (n, h); every input element gathers from the (at most ceil(K/S)^2) windows that
+// contain it and takes a window's gradient iff the window's argmax byte names its position. No atomics,
+// deterministic; the argmax words and gradient vectors of all candidate windows are requested before any is used.
 template <int K, int S, int P>
 __global__ void __launch_bounds__(kPoolThreads) maxpool_bwd_kernel(const uint2* __restrict__ argmax,
                                                                    const uint4* __restrict__ dout,
                                                                    uint4* __restrict__ dx, PoolShape s) {
-  const size_t total = (size_t)s.N * s.H * s.W * s.vecC;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const int v = (int)(i % s.vecC);
-    size_t t = i / s.vecC;
-    const int w = (int)(t % s.W); t /= s.W;
-    const int h = (int)(t % s.H);
-    const int n = (int)(t / s.H);
-    float g[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = 0.f;
-    // windows (oh, ow) with oh*S-P <= h <= oh*S-P+K-1: oh from ceil((h+P-K+1)/S) to floor((h+P)/S)
-    const int oh1 = (h + P) / S, ow1 = (w + P) / S;
+  constexpr int kMaxWin = (K + S - 1) / S;                  // windows per axis that can contain one element
+  const int rows = s.N * s.H, per_row = s.W * s.vecC;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int n = row / s.H, h = row - n * s.H;
+    // windows (oh, .) with oh*S-P <= h <= oh*S-P+K-1: oh from ceil((h+P-K+1)/S) to floor((h+P)/S)
+    const int oh1 = (h + P) / S;
     const int oh0 = h + P - K + 1 <= 0 ? 0 : (h + P - K + S) / S;
-    const int ow0 = w + P - K + 1 <= 0 ? 0 : (w + P - K + S) / S;
-    for (int oh = oh0; oh <= oh1; ++oh) {
-      if (oh >= s.OH) continue;
-      const uint32_t kh = (uint32_t)(h - (oh * S - P));
-      for (int ow = ow0; ow <= ow1; ++ow) {
-        if (ow >= s.OW) continue;
-        const uint32_t me = kh * K + (uint32_t)(w - (ow * S - P));
-        const size_t o = (((size_t)n * s.OH + oh) * s.OW + ow) * s.vecC + v;
-        const uint2 am = __ldg(argmax + o);
-        const uint32_t hit_lo = am.x ^ (me * 0x01010101u), hit_hi = am.y ^ (me * 0x01010101u);
-        if ((((hit_lo - 0x01010101u) & ~hit_lo) | ((hit_hi - 0x01010101u) & ~hit_hi)) & 0x80808080u) {
-          float go[8];                      // at least one channel's argmax byte equals my position
-          unpack8(__ldg(dout + o), go);
+    const size_t obase = (size_t)n * s.OH * s.OW * s.vecC;
+    for (int e = threadIdx.x; e < per_row; e += kPoolThreads) {
+      const int w = e / s.vecC, v = e - w * s.vecC;
+      const int ow1 = (w + P) / S;
+      const int ow0 = w + P - K + 1 <= 0 ? 0 : (w + P - K + S) / S;
+      uint2 am[kMaxWin * kMaxWin];
+      uint4 go[kMaxWin * kMaxWin];
+      uint32_t me[kMaxWin * kMaxWin];
+      bool ok[kMaxWin * kMaxWin];
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (((hit_lo >> (8 * k)) & 0xffu) == 0) g[k] += go[k];
-            if (((hit_hi >> (8 * k)) & 0xffu) == 0) g[4 + k] += go[4 + k];
+      for (int a = 0; a < kMaxWin; ++a) {
+        const int oh = oh0 + a;
+#pragma unroll
+        for (int b = 0; b < kMaxWin; ++b) {
+          const int ow = ow0 + b;
+          const int t = a * kMaxWin + b;
+          ok[t] = oh <= oh1 && oh < s.OH && ow <= ow1 && ow < s.OW;
+          if (ok[t]) {
+            const size_t o = obase + ((size_t)oh * s.OW + ow) * s.vecC + v;
+            am[t] = __ldg(argmax + o);
+            go[t] = __ldg(dout + o);
+            me[t] = (uint32_t)(h - (oh * S - P)) * K + (uint32_t)(w - (ow * S - P));
           }
         }
       }
+      float g[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = 0.f;
+#pragma unroll
+      for (int t = 0; t < kMaxWin * kMaxWin; ++t) {
+        if (!ok[t]) continue;
+        const uint32_t hit_lo = am[t].x ^ (me[t] * 0x01010101u), hit_hi = am[t].y ^ (me[t] * 0x01010101u);
+        float f[8];
+        unpack8(go[t], f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (((hit_lo >> (8 * k)) & 0xffu) == 0) g[k] += f[k];
+          if (((hit_hi >> (8 * k)) & 0xffu) == 0) g[4 + k] += f[4 + k];
+        }
+      }
+      dx[(size_t)row * per_row + e] = pack8(g);
     }
-    dx[i] = pack8(g);
   }
 }
 
@@ -122,9 +145,9 @@ int check(const char* who, int N, int H, int W, int C) {
   return 0;
 }
 
-int grid_for_elems(size_t n) {
-  size_t want = (n + kPoolThreads - 1) / kPoolThreads;
-  const size_t cap = 148 * 16;
+int grid_for_rows(size_t rows) {
+  size_t want = rows;
+  const size_t cap = (size_t)device_sm_count() * 16;
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   return (int)want;
@@ -134,8 +157,7 @@ template <int K, int S, int P>
 int pool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, int C, cudaStream_t stream) {
   if (H + 2 * P < K || W + 2 * P < K) return fail("tb200_maxpool_fwd: input smaller than the window%s");
   PoolShape s{N, H, W, C, (H + 2 * P - K) / S + 1, (W + 2 * P - K) / S + 1, C / 8};
-  const size_t total = (size_t)N * s.OH * s.OW * s.vecC;
-  maxpool_fwd_kernel<K, S, P><<<grid_for_elems(total), kPoolThreads, 0, stream>>>(
+  maxpool_fwd_kernel<K, S, P><<<grid_for_rows((size_t)N * s.OH), kPoolThreads, 0, stream>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(out), reinterpret_cast<uint2*>(argmax), s);
   return launched();
 }
@@ -144,8 +166,7 @@ template <int K, int S, int P>
 int pool_bwd(const void* argmax, const void* dout, void* dx, int N, int H, int W, int C, cudaStream_t stream) {
   if (H + 2 * P < K || W + 2 * P < K) return fail("tb200_maxpool_bwd: input smaller than the window%s");
   PoolShape s{N, H, W, C, (H + 2 * P - K) / S + 1, (W + 2 * P - K) / S + 1, C / 8};
-  const size_t total = (size_t)N * H * W * s.vecC;
-  maxpool_bwd_kernel<K, S, P><<<grid_for_elems(total), kPoolThreads, 0, stream>>>(
+  maxpool_bwd_kernel<K, S, P><<<grid_for_rows((size_t)N * H), kPoolThreads, 0, stream>>>(
       reinterpret_cast<const uint2*>(argmax), reinterpret_cast<const uint4*>(dout), reinterpret_cast<uint4*>(dx), s);
   return launched();
 }
