@@ -59,7 +59,8 @@ __global__ void __launch_bounds__(kPoolThreads) maxpool_fwd_kernel(const uint4* 
         for (int kw = 0; kw < K; ++kw) {
           const int w = ow * S - P + kw;
           ok[kh * K + kw] = h >= 0 && h < s.H && w >= 0 && w < s.W;
-          if (ok[kh * K + kw]) win[kh * K + kw] = ld_stream_16(xin + ((size_t)h * s.W + w) * s.vecC + v);
+          // (L1-allocating loads: the next output of this row re-reads the overlapping column)
+          if (ok[kh * K + kw]) win[kh * K + kw] = __ldg(xin + ((size_t)h * s.W + w) * s.vecC + v);
         }
       }
 #pragma unroll
@@ -139,6 +140,67 @@ __global__ void __launch_bounds__(kPoolThreads) maxpool_bwd_kernel(const uint2* 
   }
 }
 
+// 3x3 / stride 2 / pad 1 backward, one thread per 2 x 2 INPUT patch (rows 2a, 2a+1; columns 2b, 2b+1) and channel
+// vector: the four inputs lie in windows (a, a+1) x (b, b+1) only - even rows / columns in one of them, odd ones in
+// two - so four (argmax, gradient) pairs serve four outputs (the generic kernel fetches up to four pairs per output).
+__global__ void __launch_bounds__(kPoolThreads) maxpool321_bwd_patch_kernel(const uint2* __restrict__ argmax,
+                                                                            const uint4* __restrict__ dout,
+                                                                            uint4* __restrict__ dx, PoolShape s) {
+  const int prow = (s.H + 1) / 2, pcol = (s.W + 1) / 2;
+  const int rows = s.N * prow, per_row = pcol * s.vecC;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int n = row / prow, a = row - n * prow;
+    const size_t obase = (size_t)n * s.OH * s.OW * s.vecC;
+    const size_t ibase = (size_t)n * s.H * s.W * s.vecC;
+    for (int e = threadIdx.x; e < per_row; e += kPoolThreads) {
+      const int b = e / s.vecC, v = e - b * s.vecC;
+      uint2 am[4];
+      uint4 go[4];
+      bool ok[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int oh = a + (t >> 1), ow = b + (t & 1);
+        ok[t] = oh < s.OH && ow < s.OW;
+        if (ok[t]) {
+          const size_t o = obase + ((size_t)oh * s.OW + ow) * s.vecC + v;
+          am[t] = __ldg(argmax + o);
+          go[t] = __ldg(dout + o);
+        }
+      }
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy) {
+        const int h = 2 * a + dy;
+        if (h >= s.H) continue;
+#pragma unroll
+        for (int dxx = 0; dxx < 2; ++dxx) {
+          const int w = 2 * b + dxx;
+          if (w >= s.W) continue;
+          float g[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) g[k] = 0.f;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            // window (a + t/2, b + t%2) covers rows 2*oh-1 .. 2*oh+1: row 2a+dy lies in window row a always and in
+            // a+1 only when dy == 1 (likewise for columns)
+            if ((t >> 1) > dy || (t & 1) > dxx || !ok[t]) continue;
+            const int oh = a + (t >> 1), ow = b + (t & 1);
+            const uint32_t me = (uint32_t)(h - (2 * oh - 1)) * 3u + (uint32_t)(w - (2 * ow - 1));
+            const uint32_t hit_lo = am[t].x ^ (me * 0x01010101u), hit_hi = am[t].y ^ (me * 0x01010101u);
+            float f[8];
+            unpack8(go[t], f);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (((hit_lo >> (8 * k)) & 0xffu) == 0) g[k] += f[k];
+              if (((hit_hi >> (8 * k)) & 0xffu) == 0) g[4 + k] += f[4 + k];
+            }
+          }
+          dx[ibase + ((size_t)h * s.W + w) * s.vecC + v] = pack8(g);
+        }
+      }
+    }
+  }
+}
+
 int check(const char* who, int N, int H, int W, int C) {
   if (N <= 0 || H <= 0 || W <= 0 || C <= 0) return fail("%s: empty input", who);
   if (C % 8) return fail("%s: channels (%ld) must be a multiple of 8", who, C);
@@ -193,7 +255,13 @@ int tb200_maxpool_bwd(const void* argmax, const void* dout, void* dx, int N, int
                       int pad, cudaStream_t stream) {
   if (int rc = check("tb200_maxpool_bwd", N, H, W, C)) return rc;
   if (!argmax) return fail("tb200_maxpool_bwd: needs the forward's argmax map%s");
-  if (k == 3 && stride == 2 && pad == 1) return pool_bwd<3, 2, 1>(argmax, dout, dx, N, H, W, C, stream);
+  if (k == 3 && stride == 2 && pad == 1) {
+    if (H < 3 || W < 3) return pool_bwd<3, 2, 1>(argmax, dout, dx, N, H, W, C, stream);
+    PoolShape s{N, H, W, C, (H + 2 - 3) / 2 + 1, (W + 2 - 3) / 2 + 1, C / 8};
+    maxpool321_bwd_patch_kernel<<<grid_for_rows((size_t)N * ((H + 1) / 2)), kPoolThreads, 0, stream>>>(
+        reinterpret_cast<const uint2*>(argmax), reinterpret_cast<const uint4*>(dout), reinterpret_cast<uint4*>(dx), s);
+    return launched();
+  }
   if (k == 3 && stride == 2 && pad == 0) return pool_bwd<3, 2, 0>(argmax, dout, dx, N, H, W, C, stream);
   if (k == 2 && stride == 2 && pad == 0) return pool_bwd<2, 2, 0>(argmax, dout, dx, N, H, W, C, stream);
   return fail("tb200_maxpool_bwd: geometry not served%s");
