@@ -154,8 +154,10 @@ class Trainer:
         self.stem_pad8 = stem_pad8
         self._lib = native.lib()
 
-        torch.manual_seed(seed)           # identical initial weights on every rank
-        with torch.device(self.device):
+        # (seeding and model initialisation use the device's default generator, which a capturing tenant of this process
+        # has registered with its graph: hold the capture lock - profiles/replay_r2b/README.md)
+        with _CAPTURE_LOCK, torch.device(self.device):
+            torch.manual_seed(seed)       # identical initial weights on every rank
             # the NCCL arm is the stock-PyTorch network (nn.BatchNorm2d / nn.Linear, cuDNN + cuBLAS)
             self.model = (model if model is not None else
                           zoo_build(spec, fused=(mode != "nccl" or self.nccl_same_compute))).to(self.device)
