@@ -1707,6 +1707,20 @@ int tb200_gemm_reserve_stream(size_t bytes, cudaStream_t stream) {
   return get_workspace(bytes, stream, &unused);
 }
 
+// Frees the split-K workspace kept for (current device, stream): a long-lived worker process creates new streams
+// for every job it runs, and the workspaces of finished jobs would otherwise stay allocated. The caller guarantees
+// that nothing is in flight on the stream.
+int tb200_gemm_release_stream(cudaStream_t stream) {
+  int dev = 0;
+  TB_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_ws_mutex);
+  auto it = g_ws.find(((unsigned long long)(uintptr_t)stream << 6) ^ (unsigned long long)dev);
+  if (it == g_ws.end()) return 0;
+  if (it->second.ptr) TB_CUDA_OK(cudaFree(it->second.ptr));
+  g_ws.erase(it);
+  return 0;
+}
+
 }  // extern "C"
 
 // =================================================================================================

@@ -233,6 +233,8 @@ int tb200_probe_shifted_mn_operand(const void* A, const void* B, float* D, int s
  * the one of the current device's NULL stream, tb200_gemm_reserve_stream the one of `stream`.               */
 int tb200_gemm_reserve(size_t bytes);
 int tb200_gemm_reserve_stream(size_t bytes, cudaStream_t stream);
+/* Frees the workspace kept for (current device, stream); nothing may be in flight on the stream.            */
+int tb200_gemm_release_stream(cudaStream_t stream);
 
 /* ---- tb200_gemm_bf16_nt without any allocation (no counterpart in the reference, which has
  *      no native code). Same arguments, same kernels and same results as tb200_gemm_bf16_nt.

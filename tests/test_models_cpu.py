@@ -184,3 +184,46 @@ def test_skip_gradient_is_parked_before_the_main_branch_consumes_it():
     y = torch.tanh(Main.apply(x, box)) * 5.0 + skip
     y.sum().backward()
     assert torch.allclose(leaf.grad, want)
+
+
+def test_new_op_modules_fall_back_to_torch_on_cpu():
+    """FusedLayerNorm, MaxPool, TcConv3x3Bias and fused_attention on CPU tensors are their torch counterparts (the
+    native kernels serve bf16 CUDA tensors only), so model wiring can be tested without a GPU."""
+    from tiresias_b200.ops.attention import attention_reference, fused_attention
+    from tiresias_b200.ops.conv import TcConv3x3Bias
+    from tiresias_b200.ops.layernorm import FusedLayerNorm
+    from tiresias_b200.ops.pooling import MaxPool
+    torch.manual_seed(0)
+    x = torch.randn(3, 10, 512)
+    ln, ref = FusedLayerNorm(512), torch.nn.LayerNorm(512)
+    ref.load_state_dict(ln.state_dict())
+    assert torch.equal(ln(x), ref(x))
+    img = torch.randn(2, 8, 13, 17)
+    for k, s, p in ((3, 2, 1), (2, 2, 0), (3, 2, 0)):
+        assert torch.equal(MaxPool(k, s, p)(img), torch.nn.functional.max_pool2d(img, k, s, p))
+    conv = TcConv3x3Bias(64, 128, relu=True)
+    xin = torch.randn(1, 64, 6, 6)
+    want = torch.relu(torch.nn.functional.conv2d(xin, conv.weight, conv.bias, padding=1))
+    assert torch.allclose(conv(xin), want)
+    assert sorted(n for n, _ in conv.named_parameters()) == ["bias", "weight"]
+    qkv = torch.randn(2 * 16, 3 * 2 * 64)
+    assert torch.equal(fused_attention(qkv, 2, 16, 2, True), attention_reference(qkv, 2, 16, 2, True))
+
+
+def test_release_stream_caches_is_keyed_by_device_and_stream():
+    """Trainer.close() drops the scratch of ITS streams only (ops/native.py::release_stream_caches)."""
+    from tiresias_b200.ops import batchnorm, layernorm, native
+    saved = [dict(c) for c in (batchnorm._scratch, layernorm._scratch, native._wgrad_ws)]
+    try:
+        batchnorm._scratch[(0, 111)] = torch.zeros(1)
+        batchnorm._scratch[(0, 222)] = torch.zeros(1)
+        layernorm._scratch[(0, 111, 512)] = torch.zeros(1)
+        native._wgrad_ws[(1, 111)] = torch.zeros(1)
+
+        assert native.drop_python_stream_caches(0, 111) == 2
+        assert (0, 111) not in batchnorm._scratch and (0, 222) in batchnorm._scratch
+        assert (0, 111, 512) not in layernorm._scratch and (1, 111) in native._wgrad_ws
+    finally:
+        for c, s in zip((batchnorm._scratch, layernorm._scratch, native._wgrad_ws), saved):
+            c.clear()
+            c.update(s)

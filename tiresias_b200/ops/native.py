@@ -171,6 +171,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.tb200_gemm_bf16_add.restype = ci
     lib.tb200_gemm_set_pair_mode.argtypes = [ci]
     lib.tb200_gemm_set_pair_mode.restype = None
+    lib.tb200_gemm_release_stream.argtypes = [st]
+    lib.tb200_gemm_release_stream.restype = ci
     lib.tb200_gemm_reserve.argtypes = [sz]
     lib.tb200_gemm_bf16_nt_pull.argtypes = [C.POINTER(World), C.c_int, sz, C.c_int, vp, vp, vp,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -485,6 +487,29 @@ def conv3x3_dgrad(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
 
 
 _wgrad_ws: dict = {}
+
+
+def release_stream_caches(device, stream: torch.cuda.Stream) -> None:
+    """Drop every per-(device, stream) scratch this package keeps (BatchNorm / LayerNorm scratch, the 3x3 wgrad
+    split planes, the native split-K workspace). Called by ``Trainer.close()``: a worker process runs many jobs, each
+    on streams of its own, and the scratch of finished jobs must not accumulate. Nothing may be in flight."""
+    dev = device.index if getattr(device, "index", None) is not None else torch.cuda.current_device()
+    sp = stream.cuda_stream
+    drop_python_stream_caches(dev, sp)
+    with torch.cuda.device(dev):
+        check(lib().tb200_gemm_release_stream(sp))
+
+
+def drop_python_stream_caches(dev: int, stream_ptr_: int) -> int:
+    """The Python half of :func:`release_stream_caches`: every cache is keyed ``(device index, stream handle, ...)``.
+    Returns the number of entries dropped."""
+    from . import batchnorm, layernorm
+    dropped = 0
+    for cache in (batchnorm._scratch, layernorm._scratch, _wgrad_ws):
+        for key in [k for k in cache if k[0] == dev and k[1] == stream_ptr_]:
+            del cache[key]
+            dropped += 1
+    return dropped
 
 
 def conv3x3_wgrad_eligible(x: torch.Tensor, cout: int) -> bool:

@@ -691,5 +691,9 @@ class Trainer:
     def close(self) -> None:
         self.synchronize()
         self._graph = None
+        if self.device.type == "cuda":
+            # per-stream kernel scratch of this job (a worker process outlives its jobs)
+            for s in (self.stream, self.comm_stream, self.copy_stream):
+                native.release_stream_caches(self.device, s)
         if self.mode != "nccl":
             self.symm.close()
