@@ -11,7 +11,9 @@
 //   warp 2        : TMEM allocator (tcgen05.alloc / dealloc, 2 accumulator stages)
 //   warp 3        : (pull variant) copy engine: bulk-copies the remote shards of B into the local weight buffer, n tile
 //                   by n tile, and publishes a per-tile "ready" flag the producers wait on
-//   warps 4-7     : epilogue      - tcgen05.ld TMEM -> registers, bias/activation, cast, store
+//   warps 4-7     : epilogue      - tcgen05.ld TMEM -> registers, bias / activation / addend / BatchNorm statistics,
+//                   cast, swizzled staging tile, TMA store (EPI8 instantiations: warps 4-11, two per lane quarter)
+// Large plain GEMMs run on the 2-CTA kernel of gemm_2cta.cuh (included below; same parameters and epilogue).
 //
 // The pull variant (K2) is the load side of the parameter pull that the reference only prices
 // as "model_size / bandwidth" (core/network/network_service.py:34-37): B is sharded by rows
@@ -19,7 +21,7 @@
 // memory; measured at 4 and 8 GPUs that loses to NCCL all_gather + cuBLAS by 2-17x, because peer memory is
 // not cached in the local L2 and every 128-row block of A re-fetched the tile over NVLink
 // (profiles/comm_pull_r2.md). Now every remote byte crosses NVLink ONCE: warp 3 of every CTA is a copy engine
-// (cp.async.bulk owner -> shared -> local weight buffer, 16 KB pieces, double buffered) that walks the n tiles in
+// (cp.async.bulk owner -> shared -> local weight buffer, 8 KB pieces through four staging buffers) that walks the n tiles in
 // the order the GEMM consumes them and publishes one flag per tile; the producers wait for a tile's flag and
 // then load it from LOCAL memory like any other GEMM, so the transfer of tile n+1.. overlaps the MMAs of tile
 // n. After the kernel the full gathered matrix is resident locally (backward and the other layers use it).
