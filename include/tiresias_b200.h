@@ -268,7 +268,8 @@ int tb200_gemm_bf16_nt_noalloc(const void* A, const void* B, void* D, const void
                                int bias_dtype, int M, int N, int K, int d_dtype, int act,
                                cudaStream_t stream);
 
-/* Split-K partial planes tb200_gemm_bf16_nt / _noalloc use for an [M,K] x [N,K]^T problem on the
+/* Split-K partial planes the one-CTA kernel (always the one behind _noalloc; tb200_gemm_bf16_nt may pick the 2-CTA
+ * kernel and its own plan for large problems, whose workspace is internal) uses for an [M,K] x [N,K]^T problem on the
  * current device (1 = no scratch; 0 = empty problem). Scratch bytes = splits * M * N * 4.
  * No counterpart in the reference.                                                           */
 int tb200_gemm_plan_splits(int M, int N, int K);
