@@ -614,7 +614,7 @@ int attn_map(CUtensorMap* out, const void* base, size_t rows, int cols) {
 int attn_check(const char* who, int B, int S, int H) {
   if (B <= 0 || S <= 0 || H <= 0) return fail("%s: empty problem", who);
   if ((long long)B * S >= (1ll << 31) / 4 || S > 65536 || H > 65535 || B > 65535)
-    return fail("%s: problem too large%s", who);
+    return fail("%s: problem too large", who);
   static thread_local bool ctx_bound = false;
   if (!ctx_bound) {
     if (cudaFree(nullptr) != cudaSuccess) return fail("%s: no CUDA context", who);

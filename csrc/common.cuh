@@ -21,8 +21,14 @@ namespace tb200 {
 extern thread_local char g_last_error[512];
 extern std::atomic<unsigned long long> g_launch_count;
 
+// `fmt` may hold one %s (it must come first) followed by up to two %ld. A second %s would make snprintf read a
+// long as a pointer (it did, in two messages of round 2, and crashed the caller instead of reporting): refuse it.
 inline int fail(const char* fmt, const char* a = "", long b = 0, long c = 0) {
-  snprintf(g_last_error, sizeof(g_last_error), fmt, a, b, c);
+  int strings = 0;
+  for (const char* p = fmt; *p; ++p)
+    if (p[0] == '%' && p[1] == 's') ++strings;
+  if (strings > 1) snprintf(g_last_error, sizeof(g_last_error), "(malformed error format) %.400s", fmt);
+  else snprintf(g_last_error, sizeof(g_last_error), fmt, a, b, c);
   return 1;
 }
 

@@ -1190,7 +1190,7 @@ int conv3x3_common(const void* x, const void* w, void* y, int n, int h, int wd, 
 int w3_plan(W3Params& p, int n, int h, int wd, int cin, int cout) {
   const char* who = "tb200_conv3x3_wgrad";
   if (n <= 0 || h <= 0 || wd <= 0 || cin <= 0 || cout <= 0) return fail("%s: empty problem", who);
-  if (cin % 64 || cout % 64) return fail("%s: channel counts must be multiples of 64%s", who);
+  if (cin % 64 || cout % 64) return fail("%s: channel counts must be multiples of 64", who);
   if (wd + 1 > 256) return fail("%s: image width %ld exceeds one TMA box (255)", who, wd);
   p.N = n; p.H = h; p.W = wd; p.Cin = cin; p.Cout = cout;
   p.Wp = wd + 1; p.Hp = h + 1;
@@ -1206,7 +1206,7 @@ int w3_plan(W3Params& p, int n, int h, int wd, int cin, int cout) {
   p.x_bytes = (p.NRx * row_bytes + 1023) / 1024 * 1024;
   p.y_slab_bytes = (p.NRy * row_bytes + 1023) / 1024 * 1024;
   p.m_slabs = cout == 64 ? 1 : 2;
-  if (cout % 128 && cout != 64) return fail("%s: Cout %s(%ld) must be 64 or a multiple of 128", who, cout);
+  if (cout % 128 && cout != 64) return fail("%s: Cout (%ld) must be 64 or a multiple of 128", who, cout);
   // Cout == 64: the MMA still spans 128 rows; its second slab aliases the first one 8 rows further (rows 64-127
   // of the accumulator are never read), so the stage reserves those 1024 bytes
   p.stage_bytes = p.x_bytes + p.m_slabs * p.y_slab_bytes + (p.m_slabs == 1 ? 1024 : 0);

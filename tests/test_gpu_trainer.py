@@ -119,6 +119,22 @@ def test_resnet50_step(cuda_device):
     tr.close()
 
 
+@pytest.mark.parametrize("name", ["googlenet", "mobilenet_v1_025", "vgg11", "transformer"])
+def test_other_model_families_step(cuda_device, name):
+    """Channel counts that are not multiples of 64 / 128 (GoogLeNet's 96- and 208-wide 3x3 layers, MobileNet's
+    depthwise stack) must route to the kernels that serve them, not crash in an eligibility query."""
+    from tiresias_b200.parallel.trainer import Trainer
+    spec = resolve(name)
+    tr = Trainer(spec, batch_size=4, mode="ps", use_graph=False, device=cuda_device)
+    x, y = synthetic_batch(spec, 4)
+    for _ in range(2):
+        tr.step(x, y)
+    loss = tr.loss()
+    assert loss == loss and 0 < loss < 30
+    assert tr.check_status() == 0
+    tr.close()
+
+
 def test_profile_phases_reports_every_phase(cuda_device):
     from tiresias_b200.parallel.trainer import Trainer
     tr = Trainer(TINY, batch_size=32, mode="ps", use_graph=False, device=cuda_device, bucket_mb=0.05)
