@@ -55,3 +55,26 @@ def test_small_kernel_eligibility_queries(lib):
     assert lib.tb200_bn_mask_supported(802816, 72) == 0
     assert lib.tb200_bn_mask_supported(16, 64) == 0
     assert lib.tb200_layernorm_scratch_floats(512) == 148 * 4 * 2 * 512
+
+
+def test_argument_errors_are_reported_not_crashed(lib):
+    """Validation that runs before any device work: every refusal returns non-zero and leaves a readable message
+    (two of these messages had a malformed format in round 2 and crashed the caller instead)."""
+    cases = [
+        (lambda: lib.tb200_conv3x3_fprop(0, 0, 0, 2, 8, 8, 96, 64, 0, 0, None, 0), b"multiple of 64"),
+        (lambda: lib.tb200_conv3x3_dgrad(0, 0, 0, 2, 8, 8, 64, 60, 0), b"multiple of 64"),
+        (lambda: lib.tb200_conv3x3_wgrad(0, 0, 0, 2, 8, 8, 64, 64, 0, 0, 0), b"workspace too small"),
+        (lambda: lib.tb200_conv3x3_wgrad(0, 0, 0, 2, 8, 8, 96, 64, 0, 0, 0), b"multiples of 64"),
+        (lambda: lib.tb200_conv3x3_wgrad(0, 0, 0, 2, 8, 8, 64, 192, 0, 0, 0), b"Cout (192)"),
+        (lambda: lib.tb200_attention_fwd(0, 0, 0, 0, 128, 8, 1, 0), b"empty problem"),
+        (lambda: lib.tb200_attention_fwd(0, 0, 0, 70000, 128, 8, 1, 0), b"too large"),
+        (lambda: lib.tb200_layernorm_fwd(0, 0, 0, 0, 0, 0, 0, 16, 500, 1e-5, 0), b"D (500)"),
+        (lambda: lib.tb200_layernorm_bwd(0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 16, 512, 0), b"scratch too small"),
+        (lambda: lib.tb200_maxpool_fwd(0, 0, 0, 2, 8, 8, 8, 5, 2, 2, 0), b"geometry not served"),
+        (lambda: lib.tb200_maxpool_fwd(0, 0, 0, 2, 8, 8, 7, 3, 2, 1, 0), b"channels (7)"),
+        (lambda: lib.tb200_gemm_bf16_add(0, 0, 0, 0, 16, 16, 16, 0, 0, 0), b"null addend"),
+        (lambda: lib.tb200_conv2d_fprop(0, 0, 0, 2, 8, 8, 3, 64, 3, 3, 1, 1, 0), b"channel count (3)"),
+    ]
+    for call, needle in cases:
+        assert call() != 0
+        assert needle in lib.tb200_last_error(), (needle, lib.tb200_last_error())
